@@ -1,0 +1,136 @@
+/* openbnsl_b200.h -- C ABI of the B200 (sm_100a) contingency-counting engine.
+ *
+ * This is the drop-in boundary for OpenBNSL's data-parallel hot path.  The
+ * reference has no FFI layer of its own: its only accelerator slot is
+ * src/template_cuda.cu (an unbound matmul demo, include/template.h:6-11), and
+ * its hot path is the per-tuple pair
+ *     ContingencyTable<true>(var_ids, df)          include/base/contingency_table.h:34-56
+ *  -> calculate_local_score<double,true>(...)      include/score/local_score.h:22-62
+ *  |  citest<true>(...)                            include/citest/citest.h:41-148
+ * called from exhaustive_search.cpp:55-72 and pc.cpp:38-39 one tuple at a
+ * time.  The functions below are what those call sites bind to instead: the
+ * same computations over BATCHES of tuples.  Plain pointers and sizes only;
+ * no C++ or torch types.  See INTEGRATION.md for the reference-side stubs.
+ *
+ * Conventions
+ *  - Every function returns an int status (OBN_OK == 0).  obn_last_error()
+ *    returns a thread-local message for the last failing call.
+ *  - All pointer arguments are HOST pointers unless the name ends in `_dev`.
+ *    The library copies; it never keeps a host pointer after returning.
+ *  - Calls are synchronous: outputs are valid on return.
+ *  - A ctx is bound to ONE CUDA device (one process per GPU is the intended
+ *    deployment; multi-GPU sharding happens above this boundary) and must be
+ *    used by one host thread at a time.
+ *  - There is no CPU fallback.  Without a usable CUDA device obn_ctx_create
+ *    fails with OBN_ERR_CUDA and nothing else can be called.
+ */
+#ifndef OPENBNSL_B200_H
+#define OPENBNSL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define OBN_API __attribute__((visibility("default")))
+#else
+#define OBN_API
+#endif
+
+enum {
+  OBN_OK = 0,
+  OBN_ERR_INVALID = 1,     /* bad argument (maps to std::invalid_argument) */
+  OBN_ERR_CUDA = 2,        /* CUDA runtime error / no device               */
+  OBN_ERR_OOM = 3,         /* device or host allocation failed             */
+  OBN_ERR_UNSUPPORTED = 4, /* e.g. a dense table with more than 2^31 cells */
+  OBN_ERR_RANGE = 5        /* index out of range (maps to std::out_of_range) */
+};
+
+enum { OBN_CI_CHI2 = 0, OBN_CI_G2 = 1 };
+
+typedef struct obn_ctx obn_ctx;
+typedef struct obn_dataset obn_dataset;
+
+OBN_API const char* obn_last_error(void);
+OBN_API const char* obn_version(void);
+
+/* ---- context ------------------------------------------------------------ */
+OBN_API int obn_ctx_create(int device, obn_ctx** out);
+OBN_API void obn_ctx_destroy(obn_ctx* ctx);
+/* The CUDA stream (cudaStream_t) all work of this ctx is issued on. */
+OBN_API void* obn_ctx_stream(obn_ctx* ctx);
+
+/* ---- dataset: replaces DataframeWrapper's two vector<vector<uint8_t>>
+ * (include/base/dataframe_wrapper.h:42-45) by ONE padded column-major uint8
+ * matrix in HBM: column v, row r lives at v * stride + r, stride a multiple of
+ * 128 bytes.  `cards[v]` is DataframeWrapper::num_of_values[v] (<= 256). */
+OBN_API int obn_dataset_upload(obn_ctx* ctx, const uint8_t* col_major,
+                               size_t n_vars, size_t n_rows, size_t row_stride,
+                               const uint32_t* cards, obn_dataset** out);
+OBN_API void obn_dataset_destroy(obn_dataset* ds);
+OBN_API size_t obn_dataset_n_vars(const obn_dataset* ds);
+OBN_API size_t obn_dataset_n_rows(const obn_dataset* ds);
+
+/* ---- batched hot path ---------------------------------------------------
+ * A batch is a CSR list of tuples: tuple t covers the variables
+ * var_ids[offsets[t] .. offsets[t+1]), ASCENDING (contingency_table.h:37-38:
+ * unsorted -> OBN_ERR_INVALID "var_ids must be sorted"). */
+
+/* Replaces the ContingencyTable ctor (contingency_table.h:34-56).  Dense int32
+ * counts per tuple in REFERENCE KEY ORDER (first variable most significant,
+ * :76-85), tuple t written at counts_out + out_offsets[t]; zero cells are the
+ * keys the reference's std::map would not contain. */
+OBN_API int obn_count_tables(obn_ctx* ctx, const obn_dataset* ds,
+                             const uint32_t* var_ids, const uint64_t* offsets,
+                             size_t n_tuples, int32_t* counts_out,
+                             const uint64_t* out_offsets);
+
+/* Replaces ContingencyTable + calculate_local_score (local_score.h:22-62) for
+ * BDeu: score of child[t] given the other variables of tuple t.
+ * exact_order != 0 reproduces the reference's floating-point term order with
+ * host-libm lgamma tables (bit-identical scores; slower).  */
+OBN_API int obn_bdeu_scores(obn_ctx* ctx, const obn_dataset* ds,
+                            const uint32_t* var_ids, const uint64_t* offsets,
+                            size_t n_tuples, const uint32_t* child, double ess,
+                            int exact_order, double* scores_out);
+
+/* The reference's own sharing in exhaustive_search.cpp:55-72: ONE table per
+ * subset W serves |W| scores.  scores_out[offsets[t] + i] is the score of
+ * child var_ids[offsets[t]+i] given W \ child. */
+OBN_API int obn_bdeu_subset_scores(obn_ctx* ctx, const obn_dataset* ds,
+                                   const uint32_t* var_ids,
+                                   const uint64_t* offsets, size_t n_tuples,
+                                   double ess, int exact_order,
+                                   double* scores_out);
+
+/* Replaces ContingencyTable + citest (citest.h:41-148) for chi-square / G2:
+ * tuple t must contain x[t] and y[t]; all its other variables condition.
+ * Outputs the statistic, the degrees of freedom and p = pchisq(stat, dof)
+ * (citest.h:17-21); the decision p >= level stays with the caller.  Any of
+ * the three output pointers may be NULL. */
+OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
+                         const uint32_t* var_ids, const uint64_t* offsets,
+                         size_t n_tuples, const uint32_t* x, const uint32_t* y,
+                         int kind, double* stat_out, uint64_t* dof_out,
+                         double* p_out);
+
+/* ---- instrumentation -----------------------------------------------------
+ * Device time (CUDA events on the ctx stream) and launch count of the
+ * counting kernels since the last reset; used by bench.py for the roofline. */
+typedef struct obn_profile {
+  double count_kernel_ms;    /* sum of counting-kernel durations            */
+  uint64_t count_launches;   /* number of counting-kernel launches          */
+  uint64_t total_launches;   /* all kernels launched by this ctx            */
+  double algorithmic_bytes;  /* sum over tuples of k * n_rows               */
+  uint64_t tuples;           /* tuples evaluated                            */
+} obn_profile;
+OBN_API int obn_profile_enable(obn_ctx* ctx, int on);
+OBN_API int obn_profile_read(obn_ctx* ctx, obn_profile* out, int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OPENBNSL_B200_H */

@@ -1,0 +1,404 @@
+// obn_batch.inl -- host-side batch dispatcher: validates a CSR tuple batch,
+// sorts the tuples into kernel tiers by table size, uploads ONE packed input
+// buffer, launches one counting kernel per tier, downloads ONE packed output.
+// Included at the end of obn_capi.cu.
+
+namespace obn {
+
+struct BatchSpec {
+  obn_ctx* c;
+  const obn_dataset* ds;
+  const uint32_t* var_ids;
+  const uint64_t* offsets;
+  size_t n;
+  int mode;
+  const uint32_t* role_a = nullptr;
+  const uint32_t* role_b = nullptr;
+  int kind = 0;
+  double ess = 1.0;
+  int exact = 0;
+  // host outputs
+  double* stat = nullptr;
+  uint64_t* dof = nullptr;
+  double* p = nullptr;
+  double* scores = nullptr;
+  int32_t* counts = nullptr;
+  const uint64_t* counts_off = nullptr;
+};
+
+struct GroupCfg { int tier, kw, nthr; };
+static const GroupCfg kGroups[5] = {
+    {TIER_PRIVATE, 8, 256}, {TIER_PRIVATE, 16, 256}, {TIER_PRIVATE, 16, 128},
+    {TIER_SHARED, 16, 256}, {TIER_GLOBAL, 32, 256}};
+
+static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+template <int KW, int TIER>
+static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, size_t smem, cudaStream_t s) {
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  count_kernel<KW, TIER><<<grid, nthr, smem, s>>>(a);
+  return cudaGetLastError();
+}
+
+static const size_t kScratchMaxBytes = (size_t)8 << 30;
+
+static int run_batch(BatchSpec& S) {
+  obn_ctx* c = S.c;
+  const obn_dataset* ds = S.ds;
+  if (!c || !ds) return fail(OBN_ERR_INVALID, "ctx or dataset is NULL");
+  if (ds->ctx != c) return fail(OBN_ERR_INVALID, "dataset belongs to another ctx");
+  const size_t n = S.n;
+  if (n == 0) return OBN_OK;
+  if (!S.offsets) return fail(OBN_ERR_INVALID, "offsets is NULL");
+  if (n >= 0xffffffffull) return fail(OBN_ERR_UNSUPPORTED, "more than 2^32-2 tuples in one batch");
+  const size_t total_vars = S.offsets[n];
+  if (total_vars && !S.var_ids) return fail(OBN_ERR_INVALID, "var_ids is NULL");
+  if ((S.mode == MODE_CI) && (!S.role_a || !S.role_b)) return fail(OBN_ERR_INVALID, "x or y is NULL");
+  if ((S.mode == MODE_BDEU_ONE) && !S.role_a) return fail(OBN_ERR_INVALID, "child is NULL");
+  OBN_CUDA(cudaSetDevice(c->device));
+
+  // ---- validate + classify --------------------------------------------------
+  const size_t budget = c->smem_optin > 4096 ? c->smem_optin - 2048 : 46 * 1024;
+  std::vector<uint32_t> cells(n);
+  std::vector<uint8_t> group(n);
+  std::vector<uint32_t> rxy(n, 0);
+  size_t group_count[5] = {0, 0, 0, 0, 0};
+  double alg_bytes = 0;
+  for (size_t t = 0; t < n; ++t) {
+    const uint64_t o0 = S.offsets[t], o1 = S.offsets[t + 1];
+    if (o1 < o0) return fail(OBN_ERR_INVALID, "offsets must be non-decreasing");
+    const size_t k = o1 - o0;
+    if (k > (size_t)kMaxTupleVars)
+      return fail(OBN_ERR_UNSUPPORTED, "tuple %zu has %zu variables (max %d)", t, k, kMaxTupleVars);
+    uint64_t cl = 1;
+    bool has_a = false, has_b = false;
+    for (size_t i = 0; i < k; ++i) {
+      const uint32_t v = S.var_ids[o0 + i];
+      if (v >= ds->n_vars) return fail(OBN_ERR_RANGE, "variable id %u out of range", v);
+      if (i && S.var_ids[o0 + i - 1] > v) return fail(OBN_ERR_INVALID, "var_ids must be sorted");
+      cl *= ds->cards[v];
+      if (cl >= (1ull << 31))
+        return fail(OBN_ERR_UNSUPPORTED, "tuple %zu: dense table has >= 2^31 cells", t);
+      if (S.role_a && v == S.role_a[t]) has_a = true;
+      if (S.role_b && v == S.role_b[t]) has_b = true;
+    }
+    if (S.mode == MODE_CI) {
+      if (S.role_a[t] == S.role_b[t]) return fail(OBN_ERR_INVALID, "x and y must differ");
+      if (!has_a || !has_b) return fail(OBN_ERR_INVALID, "x or y not contained in contingency table");
+      rxy[t] = ds->cards[S.role_a[t]] + ds->cards[S.role_b[t]];
+    } else if (S.mode == MODE_BDEU_ONE && !has_a) {
+      return fail(OBN_ERR_INVALID, "child_var not present in contingency table");
+    }
+    cells[t] = (uint32_t)cl;
+    int g;
+    if (cl <= 256) g = 0;
+    else if (cl * (4 + 512) + 16 <= budget) g = 1;
+    else if (cl * (4 + 256) + 16 <= budget) g = 2;
+    else if (cl * 4 + 16 + 8 * 512 * 4 <= budget && cl <= 65536) g = 3;
+    else g = 4;
+    group[t] = (uint8_t)g;
+    ++group_count[g];
+    alg_bytes += (double)k * (double)ds->n_rows;
+  }
+
+  // ---- exact-order BDeu: host-libm lgamma tables ----------------------------
+  const bool bdeu = (S.mode == MODE_BDEU_ONE || S.mode == MODE_BDEU_ALL);
+  const bool exact = bdeu && S.exact;
+  std::vector<uint32_t> lut_ijk, lut_ij;
+  size_t lut_stride = 0, n_luts = 0;
+  if (exact) {
+    std::map<uint64_t, uint32_t> ids;
+    std::vector<double> avals;
+    auto id_of = [&](double a) {
+      uint64_t bits;
+      memcpy(&bits, &a, 8);
+      auto it = ids.find(bits);
+      if (it != ids.end()) return it->second;
+      const uint32_t id = (uint32_t)avals.size();
+      ids[bits] = id;
+      avals.push_back(a);
+      return id;
+    };
+    lut_ijk.resize(n);
+    lut_ij.assign(total_vars, 0);
+    for (size_t t = 0; t < n; ++t) {
+      const double a_ijk = S.ess / (double)(size_t)cells[t];      // local_score.h:41
+      lut_ijk[t] = id_of(a_ijk);
+      for (uint64_t i = S.offsets[t]; i < S.offsets[t + 1]; ++i)
+        lut_ij[i] = id_of(a_ijk * (double)(size_t)ds->cards[S.var_ids[i]]);   // :45
+    }
+    n_luts = avals.size();
+    lut_stride = ds->n_rows + 1;
+    const size_t bytes = n_luts * lut_stride * sizeof(double);
+    if (bytes > ((size_t)4 << 30))
+      return fail(OBN_ERR_UNSUPPORTED, "exact_order needs %zu lgamma tables of %zu entries", n_luts, lut_stride);
+    std::vector<double> lut(n_luts * lut_stride);
+    for (size_t j = 0; j < n_luts; ++j) {
+      const double a = avals[j];
+      const double lg_a = std::lgamma(a);
+      double* row = lut.data() + j * lut_stride;
+      for (size_t m = 0; m < lut_stride; ++m) row[m] = std::lgamma((double)m + a) - lg_a;   // :53,:59
+    }
+    if (int rc = c->d_lut.reserve(bytes)) return rc;
+    OBN_CUDA(cudaMemcpyAsync(c->d_lut.p, lut.data(), bytes, cudaMemcpyHostToDevice, c->stream));
+    OBN_CUDA(cudaStreamSynchronize(c->stream));
+  }
+
+  // ---- packed input buffer ---------------------------------------------------
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align16(off + bytes); return o; };
+  const size_t o_var = take(total_vars * 4), o_off = take((n + 1) * 8), o_perm = take(n * 4);
+  const size_t o_ra = take(S.role_a ? n * 4 : 0), o_rb = take(S.role_b ? n * 4 : 0);
+  const size_t o_soff = take(n * 8);
+  const size_t o_coff = take(S.mode == MODE_COUNTS ? n * 8 : 0);
+  const size_t o_lijk = take(exact ? n * 4 : 0), o_lij = take(exact ? total_vars * 4 : 0);
+  const size_t in_bytes = off;
+  if (int rc = c->h_in.reserve(in_bytes)) return rc;
+  if (int rc = c->d_in.reserve(in_bytes)) return rc;
+  unsigned char* hin = c->h_in.as<unsigned char>();
+  if (total_vars) memcpy(hin + o_var, S.var_ids, total_vars * 4);
+  memcpy(hin + o_off, S.offsets, (n + 1) * 8);
+  if (S.role_a) memcpy(hin + o_ra, S.role_a, n * 4);
+  if (S.role_b) memcpy(hin + o_rb, S.role_b, n * 4);
+  if (exact) {
+    memcpy(hin + o_lijk, lut_ijk.data(), n * 4);
+    if (total_vars) memcpy(hin + o_lij, lut_ij.data(), total_vars * 4);
+  }
+  uint32_t* perm = reinterpret_cast<uint32_t*>(hin + o_perm);
+  uint64_t* soff = reinterpret_cast<uint64_t*>(hin + o_soff);
+  size_t gstart[6];
+  gstart[0] = 0;
+  for (int g = 0; g < 5; ++g) gstart[g + 1] = gstart[g] + group_count[g];
+  {
+    size_t fill[5];
+    for (int g = 0; g < 5; ++g) fill[g] = gstart[g];
+    for (size_t t = 0; t < n; ++t) perm[fill[group[t]]++] = (uint32_t)t;
+  }
+
+  // ---- output buffer ----------------------------------------------------------
+  size_t out_bytes = 0, counts_total = 0;
+  if (S.mode == MODE_CI) out_bytes = n * 24;
+  else if (S.mode == MODE_BDEU_ONE) out_bytes = n * 8;
+  else if (S.mode == MODE_BDEU_ALL) out_bytes = total_vars * 8;
+  else {
+    uint64_t* coff = reinterpret_cast<uint64_t*>(hin + o_coff);
+    for (size_t t = 0; t < n; ++t) { coff[t] = counts_total; counts_total += cells[t]; }
+    out_bytes = counts_total * 4;
+  }
+  if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
+
+  // ---- plan launches (chunks of one group whose scratch fits) -----------------
+  struct Launch { int g; size_t begin, end; int splits; uint32_t vps; size_t smem; size_t scratch_ints; };
+  std::vector<Launch> launches;
+  const uint32_t n_full = (uint32_t)(ds->n_rows >> 4);
+  size_t max_scratch_ints = 0, max_launch_tuples = 0;
+  for (int g = 0; g < 5; ++g) {
+    if (!group_count[g]) continue;
+    const GroupCfg cfg = kGroups[g];
+    size_t i = gstart[g];
+    while (i < gstart[g + 1]) {
+      // smem + occupancy estimate from the largest table in the remaining chunk
+      size_t j = i, scratch_ints = 0;
+      uint32_t max_cells = 0, max_rxy = 0;
+      // first pass: decide whether this chunk needs scratch (splits > 1 or global tier)
+      const size_t remaining = gstart[g + 1] - i;
+      for (size_t q = i; q < gstart[g + 1]; ++q) {
+        max_cells = std::max(max_cells, cells[perm[q]]);
+        max_rxy = std::max(max_rxy, rxy[perm[q]]);
+      }
+      size_t smem;
+      const int nw = cfg.nthr / 32;
+      if (cfg.tier == TIER_PRIVATE) smem = align16((size_t)max_cells * 4) + (size_t)max_cells * cfg.nthr * 2;
+      else if (cfg.tier == TIER_SHARED) smem = align16((size_t)max_cells * 4) + (size_t)nw * max_rxy * 4;
+      else smem = (size_t)nw * max_rxy * 4;
+      smem = std::max<size_t>(align16(smem), 16);
+      int occ = (int)std::min<size_t>(2048 / cfg.nthr, (228 * 1024) / (smem + 2048));
+      occ = std::max(1, std::min(occ, 32));
+      const size_t target = (size_t)c->sm_count * occ;
+      int min_splits = 1;
+      if (cfg.tier == TIER_PRIVATE) {
+        const uint64_t max_vps = (uint64_t)4094 * cfg.nthr;   // 16-bit private counters
+        min_splits = (int)((n_full + max_vps - 1) / max_vps);
+        if (min_splits < 1) min_splits = 1;
+      }
+      int max_splits = std::max<int>(1, (int)(n_full / (uint32_t)(cfg.nthr * 2)));
+      int splits = (int)((target + remaining - 1) / remaining);
+      splits = std::max(min_splits, std::min(splits, std::max(max_splits, min_splits)));
+      const bool need_scratch = splits > 1 || cfg.tier == TIER_GLOBAL;
+      if (need_scratch) {
+        for (j = i; j < gstart[g + 1]; ++j) {
+          const size_t add = (cells[perm[j]] + 3u) & ~3u;
+          if (scratch_ints && (scratch_ints + add) * 4 > kScratchMaxBytes) break;
+          soff[j] = scratch_ints;
+          scratch_ints += add;
+        }
+        if (scratch_ints * 4 > kScratchMaxBytes && j == i + 1 && scratch_ints * 4 > ((size_t)16 << 30))
+          return fail(OBN_ERR_UNSUPPORTED, "table too large for scratch");
+      } else {
+        for (j = i; j < gstart[g + 1]; ++j) soff[j] = 0;
+      }
+      uint32_t vps = (n_full + splits - 1) / splits;
+      if (vps == 0) vps = 1;
+      launches.push_back({g, i, j, splits, vps, smem, scratch_ints});
+      max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
+      max_launch_tuples = std::max(max_launch_tuples, j - i);
+      i = j;
+    }
+  }
+  if (max_scratch_ints)
+    if (int rc = c->d_scratch.reserve(max_scratch_ints * 4, true)) return rc;
+  if (int rc = c->d_tickets.reserve(max_launch_tuples * 4, true)) return rc;
+
+  OBN_CUDA(cudaMemcpyAsync(c->d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
+
+  // ---- launch ------------------------------------------------------------------
+  unsigned char* din = c->d_in.as<unsigned char>();
+  unsigned char* dout = c->d_out.as<unsigned char>();
+  BatchArgs a{};
+  a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows; a.cards = ds->cards_dev;
+  a.var_ids = reinterpret_cast<const uint32_t*>(din + o_var);
+  a.offsets = reinterpret_cast<const uint64_t*>(din + o_off);
+  a.role_a = S.role_a ? reinterpret_cast<const uint32_t*>(din + o_ra) : nullptr;
+  a.role_b = S.role_b ? reinterpret_cast<const uint32_t*>(din + o_rb) : nullptr;
+  a.mode = S.mode; a.kind = S.kind; a.ess = S.ess;
+  if (exact) {
+    a.lut = c->d_lut.as<double>(); a.lut_stride = lut_stride;
+    a.lut_ijk = reinterpret_cast<const uint32_t*>(din + o_lijk);
+    a.lut_ij = reinterpret_cast<const uint32_t*>(din + o_lij);
+  }
+  double* d_stat = reinterpret_cast<double*>(dout);
+  unsigned long long* d_dof = reinterpret_cast<unsigned long long*>(dout + n * 8);
+  double* d_p = reinterpret_cast<double*>(dout + n * 16);
+  if (S.mode == MODE_CI) { a.stat = d_stat; a.dof = d_dof; }
+  else if (bdeu) a.scores = reinterpret_cast<double*>(dout);
+  else { a.counts_out = reinterpret_cast<int32_t*>(dout); a.counts_off = reinterpret_cast<const uint64_t*>(din + o_coff); }
+  a.scratch = c->d_scratch.as<int32_t>();
+  a.tickets = c->d_tickets.as<unsigned int>();
+
+  size_t ev_first = c->ev_used;
+  for (const Launch& L : launches) {
+    const GroupCfg cfg = kGroups[L.g];
+    a.perm = reinterpret_cast<const uint32_t*>(din + o_perm) + L.begin;
+    a.scratch_off = reinterpret_cast<const uint64_t*>(din + o_soff) + L.begin;
+    a.splits = L.splits;
+    a.vec_per_split = L.vps;
+    const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c->profile_on) {
+      if (c->ev_used == c->ev_pool.size()) {
+        cudaEvent_t x, y;
+        OBN_CUDA(cudaEventCreate(&x));
+        OBN_CUDA(cudaEventCreate(&y));
+        c->ev_pool.push_back({x, y});
+      }
+      e0 = c->ev_pool[c->ev_used].first;
+      e1 = c->ev_pool[c->ev_used].second;
+      ++c->ev_used;
+      OBN_CUDA(cudaEventRecord(e0, c->stream));
+    }
+    cudaError_t e;
+    if (L.g == 0) e = launch_count<8, TIER_PRIVATE>(a, grid, cfg.nthr, L.smem, c->stream);
+    else if (L.g <= 2) e = launch_count<16, TIER_PRIVATE>(a, grid, cfg.nthr, L.smem, c->stream);
+    else if (L.g == 3) e = launch_count<16, TIER_SHARED>(a, grid, cfg.nthr, L.smem, c->stream);
+    else e = launch_count<32, TIER_GLOBAL>(a, grid, cfg.nthr, L.smem, c->stream);
+    if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "count_kernel launch failed: %s", cudaGetErrorString(e));
+    if (c->profile_on) OBN_CUDA(cudaEventRecord(e1, c->stream));
+    ++c->prof.count_launches;
+    ++c->prof.total_launches;
+  }
+  if (S.mode == MODE_CI && S.p) {
+    pvalue_kernel<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(d_stat, d_dof, d_p, (uint32_t)n);
+    OBN_CUDA(cudaGetLastError());
+    ++c->prof.total_launches;
+  }
+
+  // ---- download ------------------------------------------------------------------
+  if (int rc = c->h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
+  if (out_bytes) OBN_CUDA(cudaMemcpyAsync(c->h_out.p, dout, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  const unsigned char* hout = c->h_out.as<unsigned char>();
+  if (S.mode == MODE_CI) {
+    if (S.stat) memcpy(S.stat, hout, n * 8);
+    if (S.dof) memcpy(S.dof, hout + n * 8, n * 8);
+    if (S.p) memcpy(S.p, hout + n * 16, n * 8);
+  } else if (S.mode == MODE_BDEU_ONE) {
+    memcpy(S.scores, hout, n * 8);
+  } else if (S.mode == MODE_BDEU_ALL) {
+    if (total_vars) memcpy(S.scores, hout, total_vars * 8);
+  } else {
+    const int32_t* src = reinterpret_cast<const int32_t*>(hout);
+    size_t o = 0;
+    for (size_t t = 0; t < n; ++t) {
+      memcpy(S.counts + S.counts_off[t], src + o, (size_t)cells[t] * 4);
+      o += cells[t];
+    }
+  }
+  if (c->profile_on) {
+    for (size_t i = ev_first; i < c->ev_used; ++i) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, c->ev_pool[i].first, c->ev_pool[i].second);
+      c->prof.count_kernel_ms += ms;
+    }
+    c->ev_used = ev_first;
+  }
+  c->prof.algorithmic_bytes += alg_bytes;
+  c->prof.tuples += n;
+  return OBN_OK;
+}
+
+}  // namespace obn
+
+extern "C" {
+
+int obn_count_tables(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
+                     size_t n_tuples, int32_t* counts_out, const uint64_t* out_offsets) {
+  if (n_tuples && (!counts_out || !out_offsets)) return fail(OBN_ERR_INVALID, "counts_out/out_offsets is NULL");
+  BatchSpec S{c, ds, var_ids, offsets, n_tuples, MODE_COUNTS};
+  S.counts = counts_out;
+  S.counts_off = out_offsets;
+  return run_batch(S);
+}
+
+int obn_bdeu_scores(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
+                    size_t n_tuples, const uint32_t* child, double ess, int exact_order, double* scores_out) {
+  if (n_tuples && !scores_out) return fail(OBN_ERR_INVALID, "scores_out is NULL");
+  BatchSpec S{c, ds, var_ids, offsets, n_tuples, MODE_BDEU_ONE};
+  S.role_a = child;
+  S.ess = ess;
+  S.exact = exact_order;
+  S.scores = scores_out;
+  return run_batch(S);
+}
+
+int obn_bdeu_subset_scores(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids,
+                           const uint64_t* offsets, size_t n_tuples, double ess, int exact_order,
+                           double* scores_out) {
+  if (n_tuples && !scores_out) return fail(OBN_ERR_INVALID, "scores_out is NULL");
+  BatchSpec S{c, ds, var_ids, offsets, n_tuples, MODE_BDEU_ALL};
+  S.ess = ess;
+  S.exact = exact_order;
+  S.scores = scores_out;
+  return run_batch(S);
+}
+
+int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
+                 size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
+                 uint64_t* dof_out, double* p_out) {
+  if (kind != OBN_CI_CHI2 && kind != OBN_CI_G2) return fail(OBN_ERR_INVALID, "Unsupported CI test type");
+  BatchSpec S{c, ds, var_ids, offsets, n_tuples, MODE_CI};
+  S.role_a = x;
+  S.role_b = y;
+  S.kind = kind;
+  S.stat = stat_out;
+  S.dof = dof_out;
+  S.p = p_out;
+  return run_batch(S);
+}
+
+}  // extern "C"

@@ -1,0 +1,133 @@
+// obn_capi.cu -- the extern "C" layer (include/openbnsl_b200.h).  This is the
+// translation unit that takes the place of the reference's src/template_cuda.cu.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+
+#include "obn_count_kernel.cuh"
+#include "obn_host.hpp"
+
+namespace obn {
+thread_local std::string g_last_error;
+}
+using namespace obn;
+
+extern "C" {
+
+const char* obn_last_error(void) { return g_last_error.c_str(); }
+const char* obn_version(void) { return "openbnsl_b200 0.1 (sm_100a)"; }
+
+int obn_ctx_create(int device, obn_ctx** out) {
+  if (!out) return fail(OBN_ERR_INVALID, "obn_ctx_create: out is NULL");
+  *out = nullptr;
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    return fail(OBN_ERR_CUDA, "no usable CUDA device (%s); this library has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (device < 0 || device >= n_dev)
+    return fail(OBN_ERR_INVALID, "device %d out of range [0,%d)", device, n_dev);
+  OBN_CUDA(cudaSetDevice(device));
+  obn_ctx* c = new obn_ctx();
+  c->device = device;
+  int v = 0;
+  OBN_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device));
+  c->sm_count = v;
+  OBN_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+  c->smem_optin = (size_t)v;
+  OBN_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  OBN_CUDA(cudaEventCreate(&c->ev0));
+  OBN_CUDA(cudaEventCreate(&c->ev1));
+  *out = c;
+  return OBN_OK;
+}
+
+void obn_ctx_destroy(obn_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_lut, &c->d_scratch, &c->d_tickets}) b->release();
+  c->h_in.release();
+  c->h_out.release();
+  for (auto& pr : c->ev_pool) {
+    cudaEventDestroy(pr.first);
+    cudaEventDestroy(pr.second);
+  }
+  cudaEventDestroy(c->ev0);
+  cudaEventDestroy(c->ev1);
+  cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+void* obn_ctx_stream(obn_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int obn_dataset_upload(obn_ctx* c, const uint8_t* col_major, size_t n_vars, size_t n_rows,
+                       size_t row_stride, const uint32_t* cards, obn_dataset** out) {
+  if (!c || !out || !cards || (!col_major && n_vars * n_rows))
+    return fail(OBN_ERR_INVALID, "obn_dataset_upload: NULL argument");
+  *out = nullptr;
+  if (row_stride < n_rows) return fail(OBN_ERR_INVALID, "row_stride < n_rows");
+  if (n_rows >= (1ull << 31)) return fail(OBN_ERR_UNSUPPORTED, "n_rows must be < 2^31 (int32 counts)");
+  if (n_vars >= (1ull << 31)) return fail(OBN_ERR_UNSUPPORTED, "too many variables");
+  for (size_t v = 0; v < n_vars; ++v)
+    if (cards[v] == 0 || cards[v] > 256)
+      return fail(OBN_ERR_INVALID, "cardinality of variable %zu is %u, must be in [1,256]", v, cards[v]);
+  OBN_CUDA(cudaSetDevice(c->device));
+  obn_dataset* d = new obn_dataset();
+  d->ctx = c;
+  d->n_vars = n_vars;
+  d->n_rows = n_rows;
+  d->stride = ((n_rows + 127) / 128) * 128;
+  if (d->stride == 0) d->stride = 128;
+  d->cards.assign(cards, cards + n_vars);
+  const size_t bytes = std::max<size_t>(d->stride * n_vars, 128);
+  cudaError_t e = cudaMalloc((void**)&d->data, bytes);
+  if (e != cudaSuccess) {
+    delete d;
+    return fail(OBN_ERR_OOM, "cudaMalloc(%zu) for the dataset failed: %s", bytes, cudaGetErrorString(e));
+  }
+  e = cudaMalloc((void**)&d->cards_dev, std::max<size_t>(n_vars, 1) * sizeof(uint32_t));
+  if (e != cudaSuccess) {
+    cudaFree(d->data);
+    delete d;
+    return fail(OBN_ERR_OOM, "cudaMalloc for cards failed: %s", cudaGetErrorString(e));
+  }
+  // padding bytes are zero so that speculative vector reads stay in range
+  OBN_CUDA(cudaMemsetAsync(d->data, 0, bytes, c->stream));
+  if (n_vars && n_rows)
+    OBN_CUDA(cudaMemcpy2DAsync(d->data, d->stride, col_major, row_stride, n_rows, n_vars,
+                               cudaMemcpyHostToDevice, c->stream));
+  if (n_vars)
+    OBN_CUDA(cudaMemcpyAsync(d->cards_dev, cards, n_vars * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                             c->stream));
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  *out = d;
+  return OBN_OK;
+}
+
+void obn_dataset_destroy(obn_dataset* d) {
+  if (!d) return;
+  cudaSetDevice(d->ctx->device);
+  cudaFree(d->data);
+  cudaFree(d->cards_dev);
+  delete d;
+}
+size_t obn_dataset_n_vars(const obn_dataset* d) { return d ? d->n_vars : 0; }
+size_t obn_dataset_n_rows(const obn_dataset* d) { return d ? d->n_rows : 0; }
+
+int obn_profile_enable(obn_ctx* c, int on) {
+  if (!c) return fail(OBN_ERR_INVALID, "ctx is NULL");
+  c->profile_on = on != 0;
+  return OBN_OK;
+}
+int obn_profile_read(obn_ctx* c, obn_profile* out, int reset) {
+  if (!c || !out) return fail(OBN_ERR_INVALID, "NULL argument");
+  *out = c->prof;
+  if (reset) c->prof = obn_profile{};
+  return OBN_OK;
+}
+
+}  // extern "C"
+
+#include "obn_batch.inl"

@@ -1,0 +1,109 @@
+// obn_host.hpp -- host-side plumbing of the C-ABI library (ctx, buffers, errors).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/openbnsl_b200.h"
+
+namespace obn {
+
+extern thread_local std::string g_last_error;
+
+inline int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+
+#define OBN_CUDA(call)                                                              \
+  do {                                                                              \
+    cudaError_t e_ = (call);                                                        \
+    if (e_ != cudaSuccess)                                                          \
+      return obn::fail(e_ == cudaErrorMemoryAllocation ? OBN_ERR_OOM : OBN_ERR_CUDA, \
+                       "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),      \
+                       __FILE__, __LINE__);                                         \
+  } while (0)
+
+// grow-only device buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes, bool zero_new = false) {
+    if (bytes <= cap) return OBN_OK;
+    size_t want = bytes + bytes / 4 + 256;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    OBN_CUDA(cudaMalloc(&p, want));
+    cap = want;
+    if (zero_new) OBN_CUDA(cudaMemset(p, 0, want));
+    return OBN_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// grow-only pinned host buffer (staging for async H2D / D2H)
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return OBN_OK;
+    size_t want = bytes + bytes / 4 + 256;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    OBN_CUDA(cudaMallocHost(&p, want));
+    cap = want;
+    return OBN_OK;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace obn
+
+struct obn_dataset {
+  obn_ctx* ctx = nullptr;
+  uint8_t* data = nullptr;      // device, column-major, padded
+  uint32_t* cards_dev = nullptr;
+  std::vector<uint32_t> cards;  // host copy
+  size_t n_vars = 0, n_rows = 0, stride = 0;
+};
+
+struct obn_ctx {
+  int device = 0;
+  int sm_count = 148;
+  size_t smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // batch staging: one packed upload and one packed download per batch
+  obn::DevBuf d_in, d_out, d_lut;
+  obn::DevBuf d_scratch;   // int32, kept all-zero between launches
+  obn::DevBuf d_tickets;   // uint32, kept all-zero between launches
+  obn::PinBuf h_in, h_out;
+  // profiling
+  bool profile_on = false;
+  obn_profile prof = {};
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool;
+  size_t ev_used = 0;
+};

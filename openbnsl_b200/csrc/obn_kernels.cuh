@@ -1,0 +1,191 @@
+// obn_kernels.cuh -- the batched contingency-counting kernels (sm_100a) and
+// their fused epilogues.  One CTA owns one (tuple, row-split); see DESIGN.md.
+//
+// Replaces, per tuple, the reference's
+//   ContingencyTable<true> ctor      include/base/contingency_table.h:34-56
+//   calculate_local_score (BDeu)     include/score/local_score.h:22-62
+//   citest (chi-square / G-square)   include/citest/citest.h:73-137
+#pragma once
+#include "obn_device.cuh"
+
+namespace obn {
+
+enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3 };
+enum Tier : int { TIER_PRIVATE = 0, TIER_SHARED = 1, TIER_GLOBAL = 2 };
+
+struct BatchArgs {
+  // dataset
+  const uint8_t* data;      // column-major codes, column v at data + v*stride
+  size_t stride;            // bytes between columns (multiple of 128)
+  uint32_t n_rows;
+  const uint32_t* cards;    // [n_vars]
+  // batch (device copies of the CSR arrays)
+  const uint32_t* var_ids;
+  const uint64_t* offsets;
+  const uint32_t* perm;     // tuple ids evaluated by this launch
+  const uint32_t* role_a;   // CI: x      BDEU_ONE: child
+  const uint32_t* role_b;   // CI: y
+  int mode;
+  int kind;                 // CI: 0 chi2, 1 G2
+  double ess;
+  // exact-order BDeu (host-libm lgamma tables); null => fast mode
+  const double* lut;        // [n_luts][lut_stride]
+  size_t lut_stride;
+  const uint32_t* lut_ijk;  // [n_tuples]
+  const uint32_t* lut_ij;   // CSR-shaped like var_ids
+  // outputs (device)
+  double* stat;
+  unsigned long long* dof;
+  double* scores;           // BDEU_ONE: [tuple]   BDEU_ALL: [offsets[t] + i]
+  int32_t* counts_out;      // MODE_COUNTS
+  const uint64_t* counts_off;
+  // row splitting / global tier
+  int splits;               // CTAs per tuple
+  uint32_t vec_per_split;   // 16-row vectors per split
+  int32_t* scratch;         // zero on entry, zero on exit
+  const uint64_t* scratch_off;  // [launch tuples]
+  unsigned int* tickets;        // [launch tuples], zero on entry and exit
+};
+
+// ---------------------------------------------------------------------------
+// epilogues.  `tab` is the dense int32 table in KERNEL digit order (generic
+// pointer: shared or global).  All threads of the CTA participate.
+// ---------------------------------------------------------------------------
+
+// chi-square / G-square with per-slice observed-margin dof and Yates
+// (citest.h:86-137).  Kernel digit order puts x then y as the two fastest
+// digits, so slice s is the contiguous block tab[s*rx*ry ...) laid out
+// x_state * ry + y_state exactly like the reference's slice (citest.h:83).
+__device__ __forceinline__ void epilogue_ci(const int32_t* tab, uint32_t cells, uint32_t rx,
+                                            uint32_t ry, int kind, int32_t* wscratch,
+                                            double* red_d, unsigned long long* red_u,
+                                            double* stat_out, unsigned long long* dof_out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const uint32_t sl = rx * ry;
+  const uint32_t n_slices = cells / sl;
+  int32_t* rs = wscratch;        // [rx]
+  int32_t* cs = wscratch + rx;   // [ry]
+  double stat = 0.0;
+  unsigned long long dof = 0;
+  for (uint32_t s = warp; s < n_slices; s += nw) {
+    const int32_t* t = tab + (size_t)s * sl;
+    int tot = 0, robs = 0, cobs = 0;
+    for (uint32_t i = lane; i < rx; i += 32) {
+      int a = 0;
+      for (uint32_t j = 0; j < ry; ++j) a += t[i * ry + j];
+      rs[i] = a;
+      tot += a;
+      robs += (a > 0);
+    }
+    for (uint32_t j = lane; j < ry; j += 32) {
+      int a = 0;
+      for (uint32_t i = 0; i < rx; ++i) a += t[i * ry + j];
+      cs[j] = a;
+      cobs += (a > 0);
+    }
+    tot = warp_sum(tot);
+    robs = warp_sum(robs);
+    cobs = warp_sum(cobs);
+    __syncwarp();
+    if (tot != 0) {                                        // citest.h:100
+      const unsigned d = (unsigned)(robs - 1) * (unsigned)(cobs - 1);   // :109
+      const bool yates = (d == 1);                         // :110
+      if (lane == 0) dof += d;
+      const double n_total = (double)tot;
+      for (uint32_t c = lane; c < sl; c += 32) {
+        const uint32_t i = c / ry, j = c - i * ry;
+        const int ri = rs[i], cj = cs[j];
+        if (ri > 0 && cj > 0) {
+          double obs = (double)t[c];
+          const double ex = (double)ri * (double)cj / n_total;          // :116
+          if (yates) {                                                  // :120-125
+            const double diff = ex - obs;
+            const double dir = (diff > 0) ? 1.0 : (diff < 0) ? -1.0 : 0.0;
+            obs += fmin(0.5, fabs(diff)) * dir;
+          }
+          if (kind == 0) {
+            const double df = obs - ex;
+            stat += df * df / ex;                                       // :127-129
+          } else if (obs > 0) {
+            stat += 2.0 * obs * log(obs / ex);                          // :130-131
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+  stat = block_sum(stat, red_d);
+  dof = block_sum(dof, red_u);
+  if (threadIdx.x == 0) {
+    *stat_out = stat;
+    *dof_out = dof;
+  }
+}
+
+__device__ __forceinline__ double bdeu_term(int n, double a, double lg_a) {
+  return n ? (lgamma((double)n + a) - lg_a) : 0.0;   // local_score.h:52-53
+}
+
+// BDeu, fast mode: parallel sums (warp-shuffle reductions).  Scores of the
+// children ci in [c_begin, c_end) of the table are written to out[ci - c_begin].
+__device__ __forceinline__ void epilogue_bdeu_fast(const int32_t* tab, uint32_t cells, int k,
+                                                   const uint32_t* card, double ess, int c_begin,
+                                                   int c_end, double* red_d, double* out) {
+  const double a_ijk = ess / (double)cells;             // local_score.h:41
+  const double lg_ijk = lgamma(a_ijk);
+  double t1 = 0.0;
+  for (uint32_t c = threadIdx.x; c < cells; c += blockDim.x) t1 += bdeu_term(tab[c], a_ijk, lg_ijk);
+  t1 = block_sum(t1, red_d);
+  for (int ci = c_begin; ci < c_end; ++ci) {
+    const uint32_t rc = card[ci];
+    uint32_t w = 1;
+    for (int i = k - 1; i > ci; --i) w *= card[i];
+    const double a_ij = a_ijk * (double)rc;             // :45
+    const double lg_ij = lgamma(a_ij);
+    const uint32_t n_cfg = cells / rc;
+    double t2 = 0.0;
+    for (uint32_t j = threadIdx.x; j < n_cfg; j += blockDim.x) {
+      const uint32_t hi = j / w, lo = j - hi * w;
+      const int32_t* p = tab + (size_t)hi * rc * w + lo;
+      int n_ij = 0;
+      for (uint32_t c = 0; c < rc; ++c) n_ij += p[(size_t)c * w];
+      t2 += bdeu_term(n_ij, a_ij, lg_ij);
+    }
+    t2 = block_sum(t2, red_d);
+    if (threadIdx.x == 0) out[ci - c_begin] = t1 - t2;
+  }
+}
+
+// BDeu, exact-order mode: ONE thread per child performs the reference's
+// sequence of fp64 additions (all N_ijk terms in ascending key order, then
+// all N_ij terms in ascending parent-key order, local_score.h:51-60) on terms
+// taken from host-libm tables lut[m] = lgamma(m + a) - lgamma(a), so the sum
+// is bit-identical to the reference's.
+__device__ __forceinline__ void epilogue_bdeu_exact(const int32_t* tab, uint32_t cells, int k,
+                                                    const uint32_t* card, const double* lut_ijk,
+                                                    const double* lut_base, size_t lut_stride,
+                                                    const uint32_t* lut_ij_ids, int c_begin,
+                                                    int c_end, double* out) {
+  const int ci = c_begin + (int)threadIdx.x;
+  if (ci >= c_end) return;
+  double ls = 0.0;
+  for (uint32_t c = 0; c < cells; ++c) {
+    const int n = tab[c];
+    if (n) ls += lut_ijk[n];
+  }
+  const uint32_t rc = card[ci];
+  uint32_t w = 1;
+  for (int i = k - 1; i > ci; --i) w *= card[i];
+  const double* lut_ij = lut_base + (size_t)lut_ij_ids[ci] * lut_stride;
+  const uint32_t n_hi = cells / (rc * w);
+  for (uint32_t hi = 0; hi < n_hi; ++hi)
+    for (uint32_t lo = 0; lo < w; ++lo) {
+      const int32_t* p = tab + (size_t)hi * rc * w + lo;
+      int n_ij = 0;
+      for (uint32_t c = 0; c < rc; ++c) n_ij += p[(size_t)c * w];
+      if (n_ij) ls -= lut_ij[n_ij];
+    }
+  out[ci - c_begin] = ls;
+}
+
+}  // namespace obn
