@@ -126,6 +126,8 @@ typedef struct obn_profile {
   uint64_t total_launches;   /* all kernels launched by this ctx            */
   double algorithmic_bytes;  /* sum over tuples of k * n_rows               */
   uint64_t tuples;           /* tuples evaluated                            */
+  double h2d_bytes;          /* bytes copied host -> device (batches + datasets) */
+  double d2h_bytes;          /* bytes copied device -> host (results)       */
 } obn_profile;
 OBN_API int obn_profile_enable(obn_ctx* ctx, int on);
 OBN_API int obn_profile_read(obn_ctx* ctx, obn_profile* out, int reset);

@@ -1,0 +1,53 @@
+#include "engine.hpp"
+
+#include <algorithm>
+#include <cstdlib>
+
+namespace obn {
+
+Engine::Engine() {
+  const char* d = std::getenv("OBN_DEVICE");
+  if (!d) d = std::getenv("LOCAL_RANK");
+  device_ = d ? std::atoi(d) : 0;
+  check(obn_ctx_create(device_, &ctx_));
+}
+Engine::~Engine() {
+  // Deliberately no obn_ctx_destroy at process exit: the CUDA runtime may
+  // already be torn down when static destructors run.
+}
+Engine& Engine::instance() {
+  static Engine e;
+  return e;
+}
+
+DeviceDataset::DeviceDataset(const uint8_t* col_major, size_t n_vars, size_t n_rows, size_t stride,
+                             const uint32_t* cards) {
+  check(obn_dataset_upload(Engine::instance().ctx(), col_major, n_vars, n_rows, stride, cards, &ds_));
+}
+DeviceDataset::~DeviceDataset() { obn_dataset_destroy(ds_); }
+
+// rebased offsets for a sub-range of a batch
+static const uint64_t* rebase(const TupleBatch& b, size_t begin, size_t end, std::vector<uint64_t>& tmp) {
+  if (begin == 0) return b.offsets.data();
+  tmp.resize(end - begin + 1);
+  const uint64_t o = b.offsets[begin];
+  for (size_t i = begin; i <= end; ++i) tmp[i - begin] = b.offsets[i] - o;
+  return tmp.data();
+}
+
+void GpuEvaluator::ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) {
+  if (end <= begin) return;
+  const uint64_t* off = rebase(b, begin, end, tmp_off_);
+  check(obn_ci_tests(Engine::instance().ctx(), ds_, b.var_ids.data() + b.offsets[begin], off, end - begin,
+                     b.x.data() + begin, b.y.data() + begin, kind, nullptr, nullptr, p));
+}
+
+void GpuEvaluator::subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
+                                 double* out) {
+  if (end <= begin) return;
+  const uint64_t* off = rebase(b, begin, end, tmp_off_);
+  check(obn_bdeu_subset_scores(Engine::instance().ctx(), ds_, b.var_ids.data() + b.offsets[begin], off,
+                               end - begin, ess, exact_order, out));
+}
+
+}  // namespace obn

@@ -1,0 +1,111 @@
+// engine.hpp -- C++ face of the C ABI for the host drivers: RAII handles,
+// status -> exception mapping, the tuple-batch evaluator interface and the
+// communicator interface used for multi-GPU sharding.
+#pragma once
+#include <cstdint>
+#include <functional>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "openbnsl_b200.h"
+
+namespace obn {
+
+// status -> the exception classes the reference throws for the same condition
+inline void check(int rc) {
+  if (rc == OBN_OK) return;
+  const std::string msg = obn_last_error();
+  switch (rc) {
+    case OBN_ERR_INVALID: throw std::invalid_argument(msg);
+    case OBN_ERR_RANGE: throw std::out_of_range(msg);
+    case OBN_ERR_OOM: throw std::bad_alloc();
+    default: throw std::runtime_error(msg);
+  }
+}
+
+// One ctx per process (one process per GPU).  Device = $OBN_DEVICE, else
+// $LOCAL_RANK, else 0.  Creation fails loudly when no GPU is usable.
+class Engine {
+ public:
+  static Engine& instance();
+  obn_ctx* ctx() const { return ctx_; }
+  int device() const { return device_; }
+  ~Engine();
+
+ private:
+  Engine();
+  obn_ctx* ctx_ = nullptr;
+  int device_ = 0;
+};
+
+class DeviceDataset {
+ public:
+  DeviceDataset(const uint8_t* col_major, size_t n_vars, size_t n_rows, size_t stride,
+                const uint32_t* cards);
+  ~DeviceDataset();
+  DeviceDataset(const DeviceDataset&) = delete;
+  DeviceDataset& operator=(const DeviceDataset&) = delete;
+  obn_dataset* handle() const { return ds_; }
+
+ private:
+  obn_dataset* ds_ = nullptr;
+};
+
+// A CSR batch of tuples (ascending var ids inside each tuple).
+struct TupleBatch {
+  std::vector<uint32_t> var_ids;
+  std::vector<uint64_t> offsets{0};
+  std::vector<uint32_t> x, y;        // CI roles
+  size_t size() const { return offsets.size() - 1; }
+  void clear() {
+    var_ids.clear();
+    offsets.assign(1, 0);
+    x.clear();
+    y.clear();
+  }
+};
+
+// What the drivers need from the hot path.  The product implementation is
+// GpuEvaluator (the C ABI); tests inject a checker-backed one to exercise the
+// driver/sharding logic on machines without a GPU.
+struct Evaluator {
+  virtual ~Evaluator() = default;
+  // p-values of tuples [begin, end) of the batch -> p[0 .. end-begin)
+  virtual void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) = 0;
+  // scores of every child of tuples [begin, end) -> out[offsets[t]-offsets[begin] + i]
+  virtual void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
+                             double* out) = 0;
+};
+
+class GpuEvaluator : public Evaluator {
+ public:
+  explicit GpuEvaluator(obn_dataset* ds) : ds_(ds) {}
+  void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) override;
+  void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
+                     double* out) override;
+
+ private:
+  obn_dataset* ds_;
+  std::vector<uint64_t> tmp_off_;
+};
+
+// Collectives between the per-GPU processes.  Default = single rank.
+struct Comm {
+  int rank = 0;
+  int world = 1;
+  // in-place elementwise MIN over ranks
+  std::function<void(int32_t*, size_t)> allreduce_min_i32;
+  // gather `bytes` bytes from every rank into recv (world * bytes), rank order
+  std::function<void(const void*, void*, size_t)> allgather;
+};
+
+// contiguous shard [begin, end) of n items for rank r of w
+inline void shard_range(size_t n, int r, int w, size_t* begin, size_t* end) {
+  const size_t base = n / (size_t)w, rem = n % (size_t)w;
+  *begin = (size_t)r * base + std::min<size_t>((size_t)r, rem);
+  *end = *begin + base + ((size_t)r < rem ? 1 : 0);
+}
+
+}  // namespace obn

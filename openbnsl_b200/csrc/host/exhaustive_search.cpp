@@ -1,0 +1,131 @@
+// exhaustive_search.cpp -- Silander-Myllymaki DP over the subset lattice with
+// the reference's tie-breaking (src/structure_learning/exhaustive_search.cpp:14-165),
+// restructured level-synchronously: all subsets of one size form ONE batch of
+// tuples whose |W| local scores each come from one table (the reference's own
+// sharing, :55-72).  Multi-GPU: a level's subsets are sharded over ranks in
+// Gosper order and the scores are all-gathered once per level.
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+#include "structure_learning.hpp"
+
+namespace obn {
+
+namespace {
+
+// include/utils/next_combmask.h:41-46
+inline bool next_combmask(uint64_t& comb, int n) {
+  if (comb == 0) return false;
+  const uint64_t x = comb & (~comb + 1);
+  const uint64_t y = comb + x;
+  comb = (((comb & ~y) / x) >> 1) | y;
+  return comb < ((uint64_t)1 << n);
+}
+
+}  // namespace
+
+PDAG exhaustive_search_driver(size_t n_vars, Evaluator& ev, const Comm& comm, const EsOptions& opt,
+                              EsStats* stats) {
+  const size_t n = n_vars;
+  if (n == 0) return PDAG(0);
+  if (opt.max_parents > n - 1) throw std::invalid_argument("max_parents must be in [0, num_of_vars-1]");
+  if (n > 64) throw std::invalid_argument("num_of_vars must be in [0, 64]");
+  if (n > 30) throw std::runtime_error("exhaustive_search: 2^n DP tables for n > 30 do not fit memory");
+  const size_t max_varset = opt.max_parents + 1;
+  const size_t n_combs = (size_t)1 << n;
+
+  std::vector<double> best_gs(n_combs, 0.0);
+  std::vector<uint8_t> best_ch(n_combs, 0xff);
+  std::vector<double> bl_score(n_combs * n);        // [W_without_child * n + child]
+  std::vector<uint32_t> bl_ps(n_combs * n);
+  const double ninf = -std::numeric_limits<double>::infinity();
+
+  TupleBatch batch;
+  std::vector<double> scores, gathered;
+  for (size_t size = 0; size <= n; ++size) {                       // :47
+    const bool calc_ls = size <= max_varset;                       // :48
+    // ---- the level's tuples, in Gosper order (:51,:129) --------------------
+    if (calc_ls && size > 0) {
+      batch.clear();
+      uint64_t W = ((uint64_t)1 << size) - 1;
+      do {
+        for (uint64_t m = W; m; m &= m - 1) batch.var_ids.push_back((uint32_t)__builtin_ctzll(m));
+        batch.offsets.push_back(batch.var_ids.size());
+      } while (next_combmask(W, (int)n));
+      const size_t T = batch.size();
+      scores.assign(T * size, 0.0);
+      if (comm.world > 1) {
+        size_t b, e;
+        shard_range(T, comm.rank, comm.world, &b, &e);
+        const size_t chunk = (T + comm.world - 1) / comm.world;   // equal-size slots for all-gather
+        std::vector<double> mine(chunk * size, 0.0);
+        ev.subset_scores(batch, b, e, opt.ess, opt.exact_order, mine.data());
+        gathered.assign(chunk * size * comm.world, 0.0);
+        comm.allgather(mine.data(), gathered.data(), chunk * size * sizeof(double));
+        for (int r = 0; r < comm.world; ++r) {
+          size_t rb, re;
+          shard_range(T, r, comm.world, &rb, &re);
+          std::memcpy(scores.data() + rb * size, gathered.data() + (size_t)r * chunk * size,
+                      (re - rb) * size * sizeof(double));
+        }
+      } else {
+        ev.subset_scores(batch, 0, T, opt.ess, opt.exact_order, scores.data());
+      }
+      if (stats) {
+        stats->tables += T;
+        stats->scores += T * size;
+      }
+    } else if (calc_ls && stats) {
+      stats->tables += 1;   // the empty subset's table (N rows in one cell); no child, no score
+    }
+    // ---- DP for this level (:59-116) -----------------------------------------
+    uint64_t W = ((uint64_t)1 << size) - 1;
+    size_t t = 0;
+    do {
+      double bgs = 0;
+      int bch = -1;
+      size_t ci = 0;
+      for (uint64_t m = W; m; m &= m - 1, ++ci) {
+        const uint32_t child = (uint32_t)__builtin_ctzll(m);
+        const uint64_t pa = W - ((uint64_t)1 << child);
+        const double ls = calc_ls ? scores[t * size + ci] : ninf;        // :65-73
+        double bls = ls;
+        uint32_t bps = (uint32_t)pa;
+        for (uint64_t q = pa; q; q &= q - 1) {                           // :75-87
+          const uint64_t sub = pa - (q & (~q + 1));
+          const double s = bl_score[sub * n + child];
+          if (s >= bls) {
+            bls = s;
+            bps = bl_ps[sub * n + child];
+          }
+        }
+        bl_score[pa * n + child] = bls;
+        bl_ps[pa * n + child] = bps;
+        const double gs = best_gs[pa] + bls;                             // :89-94
+        if (bgs >= 0 || gs > bgs) {
+          bgs = gs;
+          bch = (int)child;
+        }
+      }
+      best_gs[W] = bgs;
+      best_ch[W] = (uint8_t)bch;
+      ++t;
+    } while (next_combmask(W, (int)n));
+  }
+
+  PDAG g(n);                                                            // :133-148
+  uint64_t W = n_combs - 1;
+  for (size_t i = 0; i < n; ++i) {
+    const uint8_t ch = best_ch[W];
+    const uint64_t pa = W - ((uint64_t)1 << ch);
+    const uint32_t ps = bl_ps[pa * n + ch];
+    for (size_t j = 0; j < n; ++j)
+      if ((ps >> j) & 1u) g.add_edge(j, ch);
+    W = pa;
+  }
+  if (stats) stats->best_score = best_gs[n_combs - 1];
+  return g;
+}
+
+}  // namespace obn

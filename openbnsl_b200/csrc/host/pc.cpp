@@ -1,0 +1,302 @@
+// pc.cpp -- PC / PC-stable skeleton + collider orientation with the reference's
+// semantics (src/structure_learning/pc.cpp:16-86), restructured for batching:
+//
+//  * stable mode: all CI questions of one depth depend only on the snapshot
+//    graph, so they are independent.  The driver evaluates them in ROUNDS: each
+//    round takes the next `quota` candidate sets of every still-undecided
+//    edge (in the reference's enumeration order: (x,y) combinations first,
+//    then (y,x); pc.cpp:31-45), ships them as ONE batch to the evaluator, and
+//    resolves every edge at its FIRST passing candidate -- exactly the set the
+//    serial reference would have stopped at.  The quota grows geometrically,
+//    which keeps batches large without evaluating the whole frontier of edges
+//    that separate early.
+//  * non-stable mode mutates the graph between pairs (pc.cpp:25,40), so pairs
+//    are sequential; each pair's candidates form one batch.
+//  * (v,u|Z) is the same test as (u,v|Z) (citest.h:48 swaps), so candidates of
+//    the second direction that were already asked in the first are skipped.
+//  * multi-GPU: each round's batch is sharded over ranks; one all-reduce(min)
+//    of "first passing candidate index per edge" per round.
+#include <algorithm>
+#include <climits>
+
+#include "structure_learning.hpp"
+
+namespace obn {
+
+namespace {
+
+// lexicographic k-combinations of m items (include/utils/gen_comb.h:5-38)
+struct CombIter {
+  int m = 0, k = 0;
+  std::vector<int> idx;
+  bool valid = false;
+  void start(int m_, int k_) {
+    m = m_;
+    k = k_;
+    idx.resize(k);
+    for (int i = 0; i < k; ++i) idx[i] = i;
+    valid = k <= m;
+  }
+  void next() {
+    int i = k - 1;
+    while (i >= 0 && idx[i] == m - k + i) --i;
+    if (i < 0) {
+      valid = false;
+      return;
+    }
+    ++idx[i];
+    for (int j = i + 1; j < k; ++j) idx[j] = idx[j - 1] + 1;
+  }
+};
+
+struct PairCursor {
+  uint32_t x = 0, y = 0;
+  std::vector<uint32_t> neigh[2];   // adj(x)\y, adj(y)\x  (ascending)
+  std::vector<char> in_first;       // membership of adj(x)\y, for de-duplication
+  CombIter it;
+  int dir = 0;
+  bool done = false;                // no candidates left
+  bool removed = false;
+
+  void begin(size_t k, size_t n_vars) {
+    in_first.assign(n_vars, 0);
+    for (auto v : neigh[0]) in_first[v] = 1;
+    dir = 0;
+    it.start((int)neigh[0].size(), (int)k);
+    settle(k);
+  }
+  // move to a valid, non-duplicate candidate (or mark done)
+  void settle(size_t k) {
+    for (;;) {
+      if (!it.valid) {
+        if (dir == 1) {
+          done = true;
+          return;
+        }
+        dir = 1;
+        it.start((int)neigh[1].size(), (int)k);
+        continue;
+      }
+      if (dir == 1) {
+        bool dup = true;               // Z subset of adj(x)\y  => asked already in direction 0
+        for (int i = 0; i < it.k; ++i)
+          if (!in_first[neigh[1][it.idx[i]]]) {
+            dup = false;
+            break;
+          }
+        if (it.k == 0) dup = true;     // Z = {} is always shared
+        if (dup && (int)neigh[0].size() >= it.k) {
+          it.next();
+          continue;
+        }
+      }
+      return;
+    }
+  }
+  void current(std::vector<uint32_t>& z) const {
+    z.clear();
+    for (int i = 0; i < it.k; ++i) z.push_back(neigh[dir][it.idx[i]]);
+  }
+  void advance(size_t k) {
+    it.next();
+    settle(k);
+  }
+};
+
+using Sepsets = std::vector<std::vector<uint32_t>>;   // index x*n+y, valid iff has[x*n+y]
+
+void orient_colliders(AdjMatGraph& g, const Sepsets& sep) {   // pc.cpp:54-74
+  const size_t n = g.num_vars();
+  std::vector<uint32_t> neigh;
+  for (size_t y = 0; y < n; ++y) {
+    bool changed = true;
+    while (changed) {
+      changed = false;
+      g.undirected_neighbors_without(y, (size_t)-1, neigh);
+      for (size_t i = 0; i + 1 < neigh.size(); ++i)
+        for (size_t j = i + 1; j < neigh.size(); ++j) {
+          const size_t x = neigh[i], z = neigh[j];
+          if (g.is_adjacent(x, z)) continue;
+          const auto& s = sep[x * n + z];
+          if (std::find(s.begin(), s.end(), (uint32_t)y) == s.end()) {
+            g.orient_edge(x, y);
+            g.orient_edge(z, y);
+            changed = true;
+          }
+        }
+    }
+  }
+}
+
+// decide(batch, zs_flat/off are inside batch) -> first[pair_slot] = index of the
+// first independent candidate of that pair within the batch, INT_MAX if none.
+using DecideFn = std::function<void(const TupleBatch&, const std::vector<uint32_t>& pair_of_test,
+                                    size_t n_slots, std::vector<int32_t>& first)>;
+
+void append_test(TupleBatch& b, uint32_t u, uint32_t v, const std::vector<uint32_t>& z,
+                 std::vector<uint32_t>& tmp) {
+  tmp.assign(z.begin(), z.end());
+  tmp.push_back(u);
+  tmp.push_back(v);
+  std::sort(tmp.begin(), tmp.end());                 // pc.cpp:34-37
+  b.var_ids.insert(b.var_ids.end(), tmp.begin(), tmp.end());
+  b.offsets.push_back(b.var_ids.size());
+  b.x.push_back(u);
+  b.y.push_back(v);
+}
+
+PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, const DecideFn& decide,
+            PcStats* stats) {
+  AdjMatGraph g(n);
+  Sepsets sep(n * n);
+  if (stats) {
+    stats->recorded.clear();
+    stats->tests_per_depth.assign(max_cond_vars + 1, 0);
+    stats->batches_per_depth.assign(max_cond_vars + 1, 0);
+  }
+  TupleBatch batch;
+  std::vector<uint32_t> pair_of_test, z, tmp;
+  std::vector<std::vector<uint32_t>> z_of_test;
+  std::vector<int32_t> first;
+
+  for (size_t k = 0; k <= max_cond_vars; ++k) {              // pc.cpp:22 (no early exit)
+    if (stable) {
+      // all pairs see the graph as it was when the depth started (pc.cpp:24-25)
+      std::vector<PairCursor> pairs;
+      for (size_t x = 0; x < n; ++x)
+        for (size_t y = x + 1; y < n; ++y) {
+          if (!g.has_undirected_edge(x, y)) continue;
+          PairCursor pc;
+          pc.x = (uint32_t)x;
+          pc.y = (uint32_t)y;
+          g.undirected_neighbors_without(x, y, pc.neigh[0]);
+          g.undirected_neighbors_without(y, x, pc.neigh[1]);
+          if (pc.neigh[0].size() < k && pc.neigh[1].size() < k) continue;
+          pc.begin(k, n);
+          if (!pc.done) pairs.push_back(std::move(pc));
+        }
+      size_t quota = 1;
+      for (;;) {
+        size_t live = 0;
+        for (auto& p : pairs) live += (!p.done && !p.removed);
+        if (!live) break;
+        quota = std::max<size_t>(quota, target_batch / live);
+        batch.clear();
+        pair_of_test.clear();
+        z_of_test.clear();
+        for (size_t pi = 0; pi < pairs.size(); ++pi) {
+          PairCursor& p = pairs[pi];
+          if (p.done || p.removed) continue;
+          for (size_t q = 0; q < quota && !p.done; ++q) {
+            p.current(z);
+            const uint32_t u = p.dir ? p.y : p.x, v = p.dir ? p.x : p.y;
+            append_test(batch, u, v, z, tmp);
+            pair_of_test.push_back((uint32_t)pi);
+            z_of_test.push_back(z);
+            p.advance(k);
+          }
+        }
+        decide(batch, pair_of_test, pairs.size(), first);
+        if (stats) {
+          stats->tests_per_depth[k] += batch.size();
+          stats->batches_per_depth[k] += 1;
+          if (stats->record) {
+            TupleBatch& r = stats->recorded;
+            const uint64_t base = r.var_ids.size();
+            r.var_ids.insert(r.var_ids.end(), batch.var_ids.begin(), batch.var_ids.end());
+            for (size_t q = 1; q < batch.offsets.size(); ++q) r.offsets.push_back(base + batch.offsets[q]);
+            r.x.insert(r.x.end(), batch.x.begin(), batch.x.end());
+            r.y.insert(r.y.end(), batch.y.begin(), batch.y.end());
+          }
+        }
+        for (size_t pi = 0; pi < pairs.size(); ++pi) {
+          if (first[pi] == INT_MAX) continue;
+          PairCursor& p = pairs[pi];
+          p.removed = true;
+          g.remove_undirected_edge(p.x, p.y);                 // pc.cpp:40-42
+          sep[p.x * n + p.y] = z_of_test[(size_t)first[pi]];
+          sep[p.y * n + p.x] = sep[p.x * n + p.y];
+        }
+        quota *= 2;
+      }
+    } else {
+      for (size_t x = 0; x < n; ++x)
+        for (size_t y = x + 1; y < n; ++y) {
+          if (!g.has_undirected_edge(x, y)) continue;
+          PairCursor p;
+          p.x = (uint32_t)x;
+          p.y = (uint32_t)y;
+          g.undirected_neighbors_without(x, y, p.neigh[0]);   // live graph
+          g.undirected_neighbors_without(y, x, p.neigh[1]);
+          p.begin(k, n);
+          if (p.done) continue;
+          batch.clear();
+          pair_of_test.clear();
+          z_of_test.clear();
+          while (!p.done) {
+            p.current(z);
+            const uint32_t u = p.dir ? p.y : p.x, v = p.dir ? p.x : p.y;
+            append_test(batch, u, v, z, tmp);
+            pair_of_test.push_back(0);
+            z_of_test.push_back(z);
+            p.advance(k);
+          }
+          decide(batch, pair_of_test, 1, first);
+          if (stats) {
+            stats->tests_per_depth[k] += batch.size();
+            stats->batches_per_depth[k] += 1;
+          }
+          if (first[0] != INT_MAX) {
+            g.remove_undirected_edge(x, y);
+            sep[x * n + y] = z_of_test[(size_t)first[0]];
+            sep[y * n + x] = sep[x * n + y];
+          }
+        }
+    }
+  }
+  orient_colliders(g, sep);
+  // g.apply_meeks_rules(false) is disabled in the reference (pc.cpp:84)
+  return g.to_pdag();
+}
+
+}  // namespace
+
+PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, const PcOptions& opt,
+                               PcStats* stats) {
+  std::vector<double> p;
+  DecideFn decide = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
+                        std::vector<int32_t>& first) {
+    first.assign(n_slots, INT_MAX);
+    size_t begin = 0, end = b.size();
+    if (comm.world > 1) shard_range(b.size(), comm.rank, comm.world, &begin, &end);
+    p.resize(end - begin);
+    ev.ci_pvalues(b, begin, end, opt.kind, p.data());
+    for (size_t t = begin; t < end; ++t)
+      if (p[t - begin] >= opt.level) {                      // citest.h:147
+        int32_t& f = first[pair_of_test[t]];
+        if ((int32_t)t < f) f = (int32_t)t;
+      }
+    if (comm.world > 1) comm.allreduce_min_i32(first.data(), first.size());
+  };
+  return run_pc(n_vars, opt.max_cond_vars, opt.stable, opt.target_batch, decide, stats);
+}
+
+PDAG pc_oracle(size_t n_vars, const PDAG& truth, size_t max_cond_vars, bool stable) {
+  DecideFn decide = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
+                        std::vector<int32_t>& first) {
+    first.assign(n_slots, INT_MAX);
+    std::vector<size_t> z;
+    for (size_t t = 0; t < b.size(); ++t) {
+      if (first[pair_of_test[t]] != INT_MAX) continue;
+      z.clear();
+      for (uint64_t i = b.offsets[t]; i < b.offsets[t + 1]; ++i)
+        if (b.var_ids[i] != b.x[t] && b.var_ids[i] != b.y[t]) z.push_back(b.var_ids[i]);
+      size_t xx = b.x[t], yy = b.y[t];
+      if (xx >= yy) std::swap(xx, yy);                       // citest.h:48
+      if (is_d_separated(truth, xx, yy, z)) first[pair_of_test[t]] = (int32_t)t;
+    }
+  };
+  return run_pc(n_vars, max_cond_vars, stable, 1 << 14, decide, nullptr);
+}
+
+}  // namespace obn

@@ -1,0 +1,60 @@
+// structure_learning.hpp -- the two drivers that consume the hot path.
+//   pc                 src/structure_learning/pc.cpp:16-86
+//   exhaustive_search  src/structure_learning/exhaustive_search.cpp:14-165
+// The drivers are written against Evaluator / Comm (engine.hpp) so that the
+// same code runs on one GPU, on N GPUs (tuples sharded over ranks) and, in the
+// CPU test-suite only, against a checker-backed evaluator.
+#pragma once
+#include <cstdint>
+#include <functional>
+#include <vector>
+
+#include "engine.hpp"
+#include "graph.hpp"
+#include "types.hpp"
+
+namespace obn {
+
+struct PcStats {
+  std::vector<uint64_t> tests_per_depth;   // CI tests evaluated (after de-duplication)
+  std::vector<uint64_t> batches_per_depth;
+  bool record = false;                     // keep every evaluated test in `recorded`
+  TupleBatch recorded;
+  uint64_t total_tests() const {
+    uint64_t s = 0;
+    for (auto v : tests_per_depth) s += v;
+    return s;
+  }
+};
+
+// `decide` answers a batch of CI questions: p-values for statistical tests
+// (independent iff p >= level).  cards are only needed to size nothing here;
+// the driver is purely combinatorial.
+struct PcOptions {
+  size_t max_cond_vars = 0;
+  bool stable = true;
+  int kind = OBN_CI_G2;
+  double level = 0.05;
+  size_t target_batch = 8192;     // tests per round the driver aims for
+};
+
+PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, const PcOptions& opt,
+                               PcStats* stats);
+
+// OracleGraph variant (d-separation on a known graph; host only, no data)
+PDAG pc_oracle(size_t n_vars, const PDAG& truth, size_t max_cond_vars, bool stable);
+
+struct EsOptions {
+  double ess = 1.0;
+  size_t max_parents = 0;
+  int exact_order = 2;            // 0 fast, 1 exact (error if tables do not fit), 2 auto
+};
+struct EsStats {
+  uint64_t tables = 0, scores = 0;
+  double best_score = 0.0;
+};
+
+PDAG exhaustive_search_driver(size_t n_vars, Evaluator& ev, const Comm& comm, const EsOptions& opt,
+                              EsStats* stats);
+
+}  // namespace obn

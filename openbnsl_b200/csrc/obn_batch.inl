@@ -109,12 +109,12 @@ static int run_batch(BatchSpec& S) {
 
   // ---- exact-order BDeu: host-libm lgamma tables ----------------------------
   const bool bdeu = (S.mode == MODE_BDEU_ONE || S.mode == MODE_BDEU_ALL);
-  const bool exact = bdeu && S.exact;
+  bool exact = bdeu && S.exact;   // 1 = required, 2 = if the tables fit
   std::vector<uint32_t> lut_ijk, lut_ij;
   size_t lut_stride = 0, n_luts = 0;
+  std::vector<double> avals;
   if (exact) {
     std::map<uint64_t, uint32_t> ids;
-    std::vector<double> avals;
     auto id_of = [&](double a) {
       uint64_t bits;
       memcpy(&bits, &a, 8);
@@ -136,8 +136,14 @@ static int run_batch(BatchSpec& S) {
     n_luts = avals.size();
     lut_stride = ds->n_rows + 1;
     const size_t bytes = n_luts * lut_stride * sizeof(double);
-    if (bytes > ((size_t)4 << 30))
-      return fail(OBN_ERR_UNSUPPORTED, "exact_order needs %zu lgamma tables of %zu entries", n_luts, lut_stride);
+    if (bytes > ((size_t)2 << 30)) {
+      if (S.exact != 2)
+        return fail(OBN_ERR_UNSUPPORTED, "exact_order needs %zu lgamma tables of %zu entries", n_luts, lut_stride);
+      exact = false;
+    }
+  }
+  if (exact) {
+    const size_t bytes = n_luts * lut_stride * sizeof(double);
     std::vector<double> lut(n_luts * lut_stride);
     for (size_t j = 0; j < n_luts; ++j) {
       const double a = avals[j];
@@ -347,6 +353,8 @@ static int run_batch(BatchSpec& S) {
     }
     c->ev_used = ev_first;
   }
+  c->prof.h2d_bytes += (double)in_bytes;
+  c->prof.d2h_bytes += (double)out_bytes;
   c->prof.algorithmic_bytes += alg_bytes;
   c->prof.tuples += n;
   return OBN_OK;

@@ -102,6 +102,7 @@ int obn_dataset_upload(obn_ctx* c, const uint8_t* col_major, size_t n_vars, size
     OBN_CUDA(cudaMemcpyAsync(d->cards_dev, cards, n_vars * sizeof(uint32_t), cudaMemcpyHostToDevice,
                              c->stream));
   OBN_CUDA(cudaStreamSynchronize(c->stream));
+  c->prof.h2d_bytes += (double)(n_vars * n_rows + n_vars * 4);
   *out = d;
   return OBN_OK;
 }
