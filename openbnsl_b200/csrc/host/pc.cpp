@@ -158,6 +158,18 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
   std::vector<uint32_t> pair_of_test, z, tmp;
   std::vector<std::vector<uint32_t>> z_of_test;
   std::vector<int32_t> first;
+  auto note_batch = [&](size_t k) {
+    if (!stats) return;
+    stats->tests_per_depth[k] += batch.size();
+    stats->batches_per_depth[k] += 1;
+    if (!stats->record) return;
+    TupleBatch& r = stats->recorded;
+    const uint64_t base = r.var_ids.size();
+    r.var_ids.insert(r.var_ids.end(), batch.var_ids.begin(), batch.var_ids.end());
+    for (size_t q = 1; q < batch.offsets.size(); ++q) r.offsets.push_back(base + batch.offsets[q]);
+    r.x.insert(r.x.end(), batch.x.begin(), batch.x.end());
+    r.y.insert(r.y.end(), batch.y.begin(), batch.y.end());
+  };
 
   for (size_t k = 0; k <= max_cond_vars; ++k) {              // pc.cpp:22 (no early exit)
     if (stable) {
@@ -197,18 +209,7 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
           }
         }
         decide(batch, pair_of_test, pairs.size(), first);
-        if (stats) {
-          stats->tests_per_depth[k] += batch.size();
-          stats->batches_per_depth[k] += 1;
-          if (stats->record) {
-            TupleBatch& r = stats->recorded;
-            const uint64_t base = r.var_ids.size();
-            r.var_ids.insert(r.var_ids.end(), batch.var_ids.begin(), batch.var_ids.end());
-            for (size_t q = 1; q < batch.offsets.size(); ++q) r.offsets.push_back(base + batch.offsets[q]);
-            r.x.insert(r.x.end(), batch.x.begin(), batch.x.end());
-            r.y.insert(r.y.end(), batch.y.begin(), batch.y.end());
-          }
-        }
+        note_batch(k);
         for (size_t pi = 0; pi < pairs.size(); ++pi) {
           if (first[pi] == INT_MAX) continue;
           PairCursor& p = pairs[pi];
@@ -242,10 +243,7 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
             p.advance(k);
           }
           decide(batch, pair_of_test, 1, first);
-          if (stats) {
-            stats->tests_per_depth[k] += batch.size();
-            stats->batches_per_depth[k] += 1;
-          }
+          note_batch(k);
           if (first[0] != INT_MAX) {
             g.remove_undirected_edge(x, y);
             sep[x * n + y] = z_of_test[(size_t)first[0]];

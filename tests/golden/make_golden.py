@@ -1,0 +1,126 @@
+"""Generates tests/golden/*.json from the UNMODIFIED reference compiled in
+oracle/_ref (oracle/build_ref.py).  Run in the build container, where
+/root/reference exists:   python tests/golden/make_golden.py
+
+The reference's own tests hold no stored vectors for this path (every
+expectation is computed live by pgmpy), so the fixtures
+are outputs of the reference itself on seeded synthetic data.  The statistic
+and dof of citest<>() are read through the Boost-shim recorder
+(oracle/ref_harness.cpp); everything else comes from the reference's Python
+module.  The enumeration KATs are the gtest known answers
+(gtest/utils/next_combination.cpp:19-58, gtest/utils/comb2vec.cpp:7-56).
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+import oracle  # noqa: E402
+from openbnsl_b200 import networks as nw  # noqa: E402
+
+
+def adj_of(g, n):
+    return [[int(g.has_edge(p, v)) for v in range(n)] for p in range(n)]
+
+
+def dataset_cases():
+    yield "asia_10k_s0", nw.asia(), 10000, 0
+    yield "alarm_3k_s1", nw.alarm(), 3000, 1
+    yield "munin_like_2k_s2", nw.munin1_like(), 2000, 2
+
+
+def main():
+    ref, har = oracle.reference_modules()
+    assert ref is not None, "build oracle/_ref first (python oracle/build_ref.py)"
+    for name, net, n_rows, seed in dataset_cases():
+        codes = net.sample(n_rows, seed)
+        # ranks of observed states, as DataframeWrapper would compute them
+        cols, cards = [], []
+        for v in range(net.n):
+            u, inv = np.unique(codes[:, v], return_inverse=True)
+            cols.append(inv.astype(np.uint8)); cards.append(len(u))
+        codes = np.stack(cols, axis=1)
+        df = ref.base.DataframeWrapper(nw.to_reference_frame(codes, net.names, cards))
+        assert list(df.num_of_values) == cards
+        rng = np.random.default_rng(1000 + seed)
+        n = net.n
+        out = {"name": name, "n_rows": n_rows, "seed": seed, "cards": cards, "network": name.split("_")[0],
+               "codes_sha": int(np.frombuffer(codes.tobytes(), dtype=np.uint8).astype(np.uint64).sum())}
+        # ---- contingency tables ------------------------------------------------
+        tables = []
+        for k in (0, 1, 2, 3, 4, 5):
+            for _ in range(3):
+                vs = sorted(rng.choice(n, size=k, replace=False).tolist())
+                ct = ref.base.ContingencyTable(vs, df)
+                tables.append({"var_ids": vs, "counts": {str(a): int(b) for a, b in ct.counts.items()}})
+        out["tables"] = tables
+        # ---- BDeu local scores ---------------------------------------------------
+        scores = []
+        for npar in (0, 1, 2, 3, 4, 5):
+            for ess in (1.0, 10.0):
+                vs = rng.choice(n, size=npar + 1, replace=False).tolist()
+                child, pa = vs[0], sorted(vs[1:])
+                ct = ref.base.ContingencyTable(sorted(vs), df)
+                s = ref.score.calculate_local_score(child, pa, ct, ref.score.BDeu(ess))
+                scores.append({"child": child, "parents": pa, "ess": ess, "score": s})
+        out["scores"] = scores
+        # ---- CI tests (stat / dof / p through the shim recorder) -----------------
+        xs, ys, zs = [], [], []
+        for nz in (0, 0, 1, 1, 2, 2, 3, 4):
+            for _ in range(4):
+                vs = rng.choice(n, size=nz + 2, replace=False).tolist()
+                xs.append(vs[0]); ys.append(vs[1]); zs.append(sorted(vs[2:]))
+        zf = [v for z in zs for v in z]
+        zo = np.cumsum([0] + [len(z) for z in zs])
+        ci = []
+        for kind in (0, 1):
+            r = har.ci_batch(df, np.asarray(xs, dtype=np.int64), np.asarray(ys, dtype=np.int64),
+                             np.asarray(zf, dtype=np.int64), zo.astype(np.int64), kind, 0.05, 1)
+            for i in range(len(xs)):
+                ct = ref.base.ContingencyTable(sorted(zs[i] + [xs[i], ys[i]]), df)
+                T = ref.citest.ChiSquare(0.05) if kind == 0 else ref.citest.GSquare(0.05)
+                dec = bool(ref.citest.citest(xs[i], ys[i], zs[i], ct, T))
+                assert dec == bool(r["decision"][i])
+                st = float(r["stat"][i])
+                ci.append({"x": xs[i], "y": ys[i], "z": zs[i], "kind": kind, "stat": None if st != st else st,
+                           "dof": int(r["dof"][i]), "p": float(r["p"][i]), "independent_at_0.05": dec})
+        out["ci"] = ci
+        # ---- drivers ----------------------------------------------------------------
+        if n <= 8:
+            out["exhaustive_search"] = [
+                {"max_parents": mp, "ess": 1.0,
+                 "adj": adj_of(ref.structure_learning.exhaustive_search(df, ref.score.BDeu(1.0), mp), n)}
+                for mp in (0, 1, 3, 7)]
+        if n <= 40:
+            pcs = []
+            for kind, level in ((0, 0.01), (1, 0.05)):
+                for stable in (True, False):
+                    T = ref.citest.ChiSquare(level) if kind == 0 else ref.citest.GSquare(level)
+                    mc = 4 if n <= 8 else 2
+                    g = ref.structure_learning.pc(df, T, mc, stable)
+                    pcs.append({"kind": kind, "level": level, "stable": stable, "max_cond_vars": mc, "adj": adj_of(g, n)})
+            out["pc"] = pcs
+        with open(os.path.join(HERE, name + ".json"), "w") as f:
+            json.dump(out, f)
+        print("wrote", name, os.path.getsize(os.path.join(HERE, name + ".json")), "bytes")
+
+    # gtest known answers for the enumeration utilities
+    kat = {"next_combmask_counts": [{"n": 5, "k": 3, "count": 10}, {"n": 10, "k": 3, "count": 120},
+                                    {"n": 31, "k": 3, "count": 4495}, {"n": 63, "k": 3, "count": 39711},
+                                    {"n": 0, "k": 0, "count": 1}, {"n": 31, "k": 0, "count": 1},
+                                    {"n": 63, "k": 0, "count": 1}, {"n": 31, "k": 31, "count": 1},
+                                    {"n": 63, "k": 63, "count": 1}],
+           "combmask2vec": [{"mask": 0, "vec": []}, {"mask": 1, "vec": [0]}, {"mask": 0b1010, "vec": [1, 3]},
+                            {"mask": 31, "vec": [0, 1, 2, 3, 4]}, {"mask": (1 << 50) | (1 << 30), "vec": [30, 50]},
+                            {"mask": (1 << 64) - 1, "vec": list(range(64))}]}
+    with open(os.path.join(HERE, "enumeration_kat.json"), "w") as f:
+        json.dump(kat, f)
+
+
+if __name__ == "__main__":
+    main()

@@ -32,3 +32,39 @@ class OracleEvaluator:
 
 def pdag_to_adj(g, n):
     return np.array([[1 if g.has_edge(p, v) else 0 for v in range(n)] for p in range(n)], dtype=np.uint8)
+
+
+# ---------------------------------------------------------------------------
+# golden fixtures (tests/golden/*.json, made by tests/golden/make_golden.py)
+# ---------------------------------------------------------------------------
+import json
+import os
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDEN_SETS = ["asia_10k_s0", "alarm_3k_s1", "munin_like_2k_s2"]
+
+
+def ranked(codes):
+    """Re-code every column as ranks of its OBSERVED states (dataframe_wrapper.cpp:36-58)."""
+    cols, cards = [], []
+    for v in range(codes.shape[1]):
+        u, inv = np.unique(codes[:, v], return_inverse=True)
+        cols.append(inv.astype(np.uint8))
+        cards.append(len(u))
+    return np.stack(cols, axis=1), cards
+
+
+def load_golden(name):
+    from openbnsl_b200 import networks as nw
+    with open(os.path.join(GOLDEN_DIR, name + ".json")) as f:
+        g = json.load(f)
+    net = {"asia": nw.asia, "alarm": nw.alarm, "munin": nw.munin1_like}[g["network"]]()
+    codes, cards = ranked(net.sample(g["n_rows"], g["seed"]))
+    assert cards == g["cards"]
+    assert int(np.frombuffer(codes.tobytes(), dtype=np.uint8).astype(np.uint64).sum()) == g["codes_sha"], \
+        "synthetic data generator drifted from the one the fixtures were made with"
+    return g, net, codes, cards
+
+
+def close(a, b, rel=1e-9, abs_=0.0):
+    return abs(a - b) <= max(rel * max(abs(a), abs(b)), abs_)

@@ -1,0 +1,137 @@
+"""GPU parity of the drop-in surface (pybind11 module -> C++ drivers -> C ABI ->
+sm_100a kernels) against the golden fixtures of the unmodified reference and
+against the oracle at the benchmark's full size.  Mirrors the reference's own
+tests: pytest/base/test_contingency_table.py, pytest/score/test_local_score.py,
+pytest/citest/test_citest.py, pytest/structure_learning/test_{exhaustive_search,pc}.py."""
+import numpy as np
+import pytest
+
+import oracle
+import openbnsl_b200
+from helpers import GOLDEN_SETS, close, load_golden, pdag_to_adj, ranked
+from openbnsl_b200 import networks as nw
+
+pytestmark = pytest.mark.gpu
+L = openbnsl_b200.openbnsllib
+
+
+@pytest.fixture(scope="module", params=GOLDEN_SETS)
+def gold(request):
+    g, net, codes, cards = load_golden(request.param)
+    import types
+    frame = nw.to_reference_frame(codes, net.names, cards)      # str cells, like the reference's input
+    df = L.base.DataframeWrapper(frame)
+    assert list(df.num_of_values) == cards
+    return g, net, df
+
+
+def test_golden_tables(gold):
+    g, net, df = gold
+    for t in g["tables"]:
+        ct = L.base.ContingencyTable(t["var_ids"], df)
+        assert {str(k): v for k, v in ct.counts.items()} == t["counts"]
+        assert sum(ct.counts.values()) == df.num_of_datapoints
+        assert list(ct.var_ids) == t["var_ids"]
+        assert list(ct.cardinalities) == [g["cards"][v] for v in t["var_ids"]]
+
+
+def test_golden_scores_bit_exact(gold):
+    g, net, df = gold
+    for s in g["scores"]:
+        ct = L.base.ContingencyTable(sorted(s["parents"] + [s["child"]]), df)
+        got = L.score.calculate_local_score(s["child"], s["parents"], ct, L.score.BDeu(s["ess"]))
+        assert got == s["score"], s          # exact-order mode: bit-identical to the reference
+
+
+def test_golden_ci(gold):
+    g, net, df = gold
+    for c in g["ci"]:
+        ct = L.base.ContingencyTable(sorted(c["z"] + [c["x"], c["y"]]), df)
+        T = L.citest.ChiSquare(0.05) if c["kind"] == 0 else L.citest.GSquare(0.05)
+        stat, dof, p = L.citest.citest_statistic(c["x"], c["y"], c["z"], ct, T)
+        assert dof == c["dof"]
+        if c["stat"] is not None:
+            assert close(stat, c["stat"], 1e-9, 1e-9), c
+        assert close(p, c["p"], 1e-9, 1e-12), c
+        if abs(c["p"] - 0.05) > 1e-9:
+            assert L.citest.citest(c["x"], c["y"], c["z"], ct, T) == c["independent_at_0.05"]
+        # argument order must not matter (citest.h:48)
+        assert L.citest.citest_statistic(c["y"], c["x"], c["z"], ct, T)[1] == c["dof"]
+
+
+def test_golden_drivers(gold):
+    g, net, df = gold
+    for e in g.get("exhaustive_search", []):
+        got = L.structure_learning.exhaustive_search(df, L.score.BDeu(e["ess"]), e["max_parents"])
+        assert pdag_to_adj(got, net.n).tolist() == e["adj"], e["max_parents"]      # identical DAG
+    for e in g.get("pc", []):
+        T = L.citest.ChiSquare(e["level"]) if e["kind"] == 0 else L.citest.GSquare(e["level"])
+        got = L.structure_learning.pc(df, T, e["max_cond_vars"], e["stable"])
+        assert pdag_to_adj(got, net.n).tolist() == e["adj"], (e["kind"], e["stable"])
+
+
+def test_errors_on_gpu(gold):
+    g, net, df = gold
+    ct = L.base.ContingencyTable([0, 1], df)
+    with pytest.raises(ValueError, match="differ"):
+        L.citest.citest(1, 1, [], ct, L.citest.GSquare())
+    with pytest.raises(ValueError, match="not contained"):
+        L.citest.citest(0, 2, [], ct, L.citest.GSquare())
+    with pytest.raises(ValueError, match="child_var"):
+        L.score.calculate_local_score(2, [0], ct, L.score.BDeu())
+    with pytest.raises(ValueError, match="Unsupported score type"):
+        L.score.calculate_local_score(0, [1], ct, L.score.K2())
+
+
+# ---------------------------------------------------------------------------
+# full-size configurations (BASELINE.json configs[0] and configs[1])
+# ---------------------------------------------------------------------------
+def test_config0_asia_es_full_lattice_fast_and_exact():
+    net = nw.asia()
+    codes, cards = ranked(net.sample(10000, 0))
+    ods = oracle.Dataset(codes, cards)
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+    want, gs, ch, ls = oracle.exhaustive_search(ods, 1.0, 7, want_tables=True)
+    for exact in (1, 0):
+        got = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 7, exact_order=exact)
+        st = L.structure_learning.last_es_stats()
+        assert st["tables"] == 256 and st["scores"] == 1024
+        if exact:
+            assert (pdag_to_adj(got, 8) == want).all()
+            assert st["best_score"] == gs[255]                     # bit-identical network score
+        else:
+            assert close(st["best_score"], gs[255], 1e-9)
+    # the learned structure is the true Asia CPDAG skeleton
+    und = {(min(a, b), max(a, b)) for a, b in net.edges()}
+    got_und = {(min(a, b), max(a, b)) for a in range(8) for b in range(8) if want[a, b]}
+    assert got_und == und - {(net.names.index("asia"), net.names.index("tub"))} or got_und == und
+
+
+def test_config1_alarm_pc_full_size():
+    net = nw.alarm()
+    codes, cards = ranked(net.sample(100_000, 0))
+    ods = oracle.Dataset(codes, cards)
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+    for stable in (True, False):
+        got = L.structure_learning.pc(df, L.citest.GSquare(0.05), 4, stable, record_tests=True)
+        want = oracle.pc(ods, 1, 0.05, 4, stable)
+        assert (pdag_to_adj(got, net.n) == want).all(), stable
+    # size-independent properties on the recorded frontier of the last run
+    var_ids, offsets, x, y = L.structure_learning.last_pc_tests()
+    assert len(x) == L.structure_learning.last_pc_stats()["total_tests"] > 1000
+    from openbnsl_b200 import capi
+    ctx = capi.Context(0)
+    ds = ctx.upload(codes, cards)
+    pick = np.random.default_rng(0).choice(len(x), size=200, replace=False)
+    tuples = [[int(v) for v in var_ids[int(offsets[t]):int(offsets[t + 1])]] for t in pick]
+    for t, c in zip(tuples, ds.count_tables(tuples)):
+        assert int(c.sum()) == 100_000
+        marg = oracle.count_table(ods, t[:1])                     # marginalising must give the 1-var table
+        assert np.array_equal(c.reshape(len(marg), -1).sum(axis=1), marg)
+    stat, dof, p = ds.ci_tests(x[pick], y[pick], [[v for v in t if v not in (int(a), int(b))]
+                                                  for t, a, b in zip(tuples, x[pick], y[pick])], 1)
+    for i, t in enumerate(tuples):
+        a, b = int(x[pick][i]), int(y[pick][i])
+        s, d, pv = oracle.citest(ods, a, b, [v for v in t if v not in (a, b)], 1)
+        assert d == int(dof[i]) and close(stat[i], s, 1e-9, 1e-9) and close(p[i], pv, 1e-9, 1e-12)
+    ctx.close()
