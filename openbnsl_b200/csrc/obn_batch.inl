@@ -26,27 +26,39 @@ struct BatchSpec {
   const uint64_t* counts_off = nullptr;
 };
 
-struct GroupCfg { int tier, kw, nthr; };
-static const GroupCfg kGroups[5] = {
-    {TIER_PRIVATE, 8, 256}, {TIER_PRIVATE, 16, 256}, {TIER_PRIVATE, 16, 128},
-    {TIER_SHARED, 16, 256}, {TIER_GLOBAL, 32, 256}};
+// Table-size classes.  One launch covers the tuples of one class, so that the
+// dynamic shared memory of the launch (sized by the class's largest table) is
+// within 4x of what each tuple needs and occupancy stays high.
+//   class  cells        kernel
+//   0      <= 64        <8,  SMEM, scale4>   four 8-bit keys per register, key = byte offset
+//   1      <= 256       <8,  SMEM, plain>
+//   2..4   <= 1Ki/4Ki/16Ki  <16, SMEM, scale4>
+//   5      <= smem      <32, SMEM, plain>
+//   6      larger       <32, GLOBAL, plain>  table in L2-resident global scratch
+static const int kNumClasses = 7;
+static const uint32_t kClassCells[kNumClasses - 2] = {64, 256, 1024, 4096, 16384};
 
 static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-template <int KW, int TIER>
+template <int KW, int TIER, bool SCALE4>
 static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, size_t smem, cudaStream_t s) {
   static size_t configured = 0;
   if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER>,
+    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;
   }
-  count_kernel<KW, TIER><<<grid, nthr, smem, s>>>(a);
+  count_kernel<KW, TIER, SCALE4><<<grid, nthr, smem, s>>>(a);
   return cudaGetLastError();
 }
 
 static const size_t kScratchMaxBytes = (size_t)8 << 30;
+
+static int env_int(const char* name, int dflt) {
+  const char* v = std::getenv(name);
+  return v && *v ? std::atoi(v) : dflt;
+}
 
 static int run_batch(BatchSpec& S) {
   obn_ctx* c = S.c;
@@ -68,8 +80,9 @@ static int run_batch(BatchSpec& S) {
   std::vector<uint32_t> cells(n);
   std::vector<uint8_t> group(n);
   std::vector<uint32_t> rxy(n, 0);
-  size_t group_count[5] = {0, 0, 0, 0, 0};
+  size_t group_count[kNumClasses] = {};
   double alg_bytes = 0;
+  if (ds->n_vars > (1u << 24)) return fail(OBN_ERR_UNSUPPORTED, "more than 2^24 variables");
   for (size_t t = 0; t < n; ++t) {
     const uint64_t o0 = S.offsets[t], o1 = S.offsets[t + 1];
     if (o1 < o0) return fail(OBN_ERR_INVALID, "offsets must be non-decreasing");
@@ -96,12 +109,9 @@ static int run_batch(BatchSpec& S) {
       return fail(OBN_ERR_INVALID, "child_var not present in contingency table");
     }
     cells[t] = (uint32_t)cl;
-    int g;
-    if (cl <= 256) g = 0;
-    else if (cl * (4 + 512) + 16 <= budget) g = 1;
-    else if (cl * (4 + 256) + 16 <= budget) g = 2;
-    else if (cl * 4 + 16 + 8 * 512 * 4 <= budget && cl <= 65536) g = 3;
-    else g = 4;
+    int g = 0;
+    while (g < kNumClasses - 2 && cl > kClassCells[g]) ++g;
+    if (g == kNumClasses - 2 && cl * 4 + 16 + 8 * 512 * 4 > budget) g = kNumClasses - 1;
     group[t] = (uint8_t)g;
     ++group_count[g];
     alg_bytes += (double)k * (double)ds->n_rows;
@@ -168,7 +178,10 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->h_in.reserve(in_bytes)) return rc;
   if (int rc = c->d_in.reserve(in_bytes)) return rc;
   unsigned char* hin = c->h_in.as<unsigned char>();
-  if (total_vars) memcpy(hin + o_var, S.var_ids, total_vars * 4);
+  {
+    uint32_t* desc = reinterpret_cast<uint32_t*>(hin + o_var);
+    for (size_t i = 0; i < total_vars; ++i) desc[i] = S.var_ids[i] | ((ds->cards[S.var_ids[i]] - 1u) << 24);
+  }
   memcpy(hin + o_off, S.offsets, (n + 1) * 8);
   if (S.role_a) memcpy(hin + o_ra, S.role_a, n * 4);
   if (S.role_b) memcpy(hin + o_rb, S.role_b, n * 4);
@@ -178,12 +191,12 @@ static int run_batch(BatchSpec& S) {
   }
   uint32_t* perm = reinterpret_cast<uint32_t*>(hin + o_perm);
   uint64_t* soff = reinterpret_cast<uint64_t*>(hin + o_soff);
-  size_t gstart[6];
+  size_t gstart[kNumClasses + 1];
   gstart[0] = 0;
-  for (int g = 0; g < 5; ++g) gstart[g + 1] = gstart[g] + group_count[g];
+  for (int g = 0; g < kNumClasses; ++g) gstart[g + 1] = gstart[g] + group_count[g];
   {
-    size_t fill[5];
-    for (int g = 0; g < 5; ++g) fill[g] = gstart[g];
+    size_t fill[kNumClasses];
+    for (int g = 0; g < kNumClasses; ++g) fill[g] = gstart[g];
     for (size_t t = 0; t < n; ++t) perm[fill[group[t]]++] = (uint32_t)t;
   }
 
@@ -199,44 +212,41 @@ static int run_batch(BatchSpec& S) {
   }
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
-  // ---- plan launches (chunks of one group whose scratch fits) -----------------
-  struct Launch { int g; size_t begin, end; int splits; uint32_t vps; size_t smem; size_t scratch_ints; };
+  // ---- plan launches: one per class (chunked only when the scratch would not fit)
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; };
   std::vector<Launch> launches;
-  const uint32_t n_full = (uint32_t)(ds->n_rows >> 4);
+  const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
   size_t max_scratch_ints = 0, max_launch_tuples = 0;
-  for (int g = 0; g < 5; ++g) {
+  const int force_t = env_int("OBN_FORCE_T", 0), force_splits = env_int("OBN_FORCE_SPLITS", 0);
+  const size_t target_threads = (size_t)c->sm_count * 2048 * (size_t)env_int("OBN_WAVES", 2);
+  for (int g = 0; g < kNumClasses; ++g) {
     if (!group_count[g]) continue;
-    const GroupCfg cfg = kGroups[g];
+    const bool global_tier = (g == kNumClasses - 1);
     size_t i = gstart[g];
     while (i < gstart[g + 1]) {
-      // smem + occupancy estimate from the largest table in the remaining chunk
-      size_t j = i, scratch_ints = 0;
-      uint32_t max_cells = 0, max_rxy = 0;
-      // first pass: decide whether this chunk needs scratch (splits > 1 or global tier)
       const size_t remaining = gstart[g + 1] - i;
+      uint32_t max_cells = 0, max_rxy = 0;
       for (size_t q = i; q < gstart[g + 1]; ++q) {
         max_cells = std::max(max_cells, cells[perm[q]]);
         max_rxy = std::max(max_rxy, rxy[perm[q]]);
       }
-      size_t smem;
-      const int nw = cfg.nthr / 32;
-      if (cfg.tier == TIER_PRIVATE) smem = align16((size_t)max_cells * 4) + (size_t)max_cells * cfg.nthr * 2;
-      else if (cfg.tier == TIER_SHARED) smem = align16((size_t)max_cells * 4) + (size_t)nw * max_rxy * 4;
-      else smem = (size_t)nw * max_rxy * 4;
+      // threads per tuple: fill the machine `OBN_WAVES` times over, but keep >= 4 vectors per thread
+      size_t tpt = (target_threads + remaining - 1) / remaining;
+      tpt = std::min<size_t>(tpt, std::max<size_t>(32, n_vec / 4));
+      size_t p2 = 32;
+      while (p2 < tpt) p2 <<= 1;
+      int nthr = (int)std::min<size_t>(p2, 256);
+      int splits = (int)std::max<size_t>(1, p2 / 256);
+      // a split must amortise its merge (cells atomics) and its prologue
+      const uint32_t min_vps = std::max<uint32_t>(256u, max_cells / 8u);
+      splits = std::min<int>(splits, (int)std::max<uint32_t>(1u, n_vec / min_vps));
+      if (force_t) nthr = force_t;
+      if (force_splits) splits = std::max(1, std::min<int>(force_splits, (int)std::max<uint32_t>(1u, n_vec)));
+      const int nw = nthr / 32;
+      size_t smem = (global_tier ? 0 : align16((size_t)max_cells * 4)) + (size_t)nw * max_rxy * 4;
       smem = std::max<size_t>(align16(smem), 16);
-      int occ = (int)std::min<size_t>(2048 / cfg.nthr, (228 * 1024) / (smem + 2048));
-      occ = std::max(1, std::min(occ, 32));
-      const size_t target = (size_t)c->sm_count * occ;
-      int min_splits = 1;
-      if (cfg.tier == TIER_PRIVATE) {
-        const uint64_t max_vps = (uint64_t)4094 * cfg.nthr;   // 16-bit private counters
-        min_splits = (int)((n_full + max_vps - 1) / max_vps);
-        if (min_splits < 1) min_splits = 1;
-      }
-      int max_splits = std::max<int>(1, (int)(n_full / (uint32_t)(cfg.nthr * 2)));
-      int splits = (int)((target + remaining - 1) / remaining);
-      splits = std::max(min_splits, std::min(splits, std::max(max_splits, min_splits)));
-      const bool need_scratch = splits > 1 || cfg.tier == TIER_GLOBAL;
+      const bool need_scratch = splits > 1 || global_tier;
+      size_t j = i, scratch_ints = 0;
       if (need_scratch) {
         for (j = i; j < gstart[g + 1]; ++j) {
           const size_t add = (cells[perm[j]] + 3u) & ~3u;
@@ -244,14 +254,12 @@ static int run_batch(BatchSpec& S) {
           soff[j] = scratch_ints;
           scratch_ints += add;
         }
-        if (scratch_ints * 4 > kScratchMaxBytes && j == i + 1 && scratch_ints * 4 > ((size_t)16 << 30))
-          return fail(OBN_ERR_UNSUPPORTED, "table too large for scratch");
       } else {
         for (j = i; j < gstart[g + 1]; ++j) soff[j] = 0;
       }
-      uint32_t vps = (n_full + splits - 1) / splits;
+      uint32_t vps = (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, splits, vps, smem, scratch_ints});
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints});
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
       max_launch_tuples = std::max(max_launch_tuples, j - i);
       i = j;
@@ -268,7 +276,7 @@ static int run_batch(BatchSpec& S) {
   unsigned char* dout = c->d_out.as<unsigned char>();
   BatchArgs a{};
   a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows; a.cards = ds->cards_dev;
-  a.var_ids = reinterpret_cast<const uint32_t*>(din + o_var);
+  a.desc = reinterpret_cast<const uint32_t*>(din + o_var);
   a.offsets = reinterpret_cast<const uint64_t*>(din + o_off);
   a.role_a = S.role_a ? reinterpret_cast<const uint32_t*>(din + o_ra) : nullptr;
   a.role_b = S.role_b ? reinterpret_cast<const uint32_t*>(din + o_rb) : nullptr;
@@ -281,7 +289,7 @@ static int run_batch(BatchSpec& S) {
   double* d_stat = reinterpret_cast<double*>(dout);
   unsigned long long* d_dof = reinterpret_cast<unsigned long long*>(dout + n * 8);
   double* d_p = reinterpret_cast<double*>(dout + n * 16);
-  if (S.mode == MODE_CI) { a.stat = d_stat; a.dof = d_dof; }
+  if (S.mode == MODE_CI) { a.stat = d_stat; a.dof = d_dof; a.pval = S.p ? d_p : nullptr; }
   else if (bdeu) a.scores = reinterpret_cast<double*>(dout);
   else { a.counts_out = reinterpret_cast<int32_t*>(dout); a.counts_off = reinterpret_cast<const uint64_t*>(din + o_coff); }
   a.scratch = c->d_scratch.as<int32_t>();
@@ -289,7 +297,6 @@ static int run_batch(BatchSpec& S) {
 
   size_t ev_first = c->ev_used;
   for (const Launch& L : launches) {
-    const GroupCfg cfg = kGroups[L.g];
     a.perm = reinterpret_cast<const uint32_t*>(din + o_perm) + L.begin;
     a.scratch_off = reinterpret_cast<const uint64_t*>(din + o_soff) + L.begin;
     a.splits = L.splits;
@@ -309,18 +316,14 @@ static int run_batch(BatchSpec& S) {
       OBN_CUDA(cudaEventRecord(e0, c->stream));
     }
     cudaError_t e;
-    if (L.g == 0) e = launch_count<8, TIER_PRIVATE>(a, grid, cfg.nthr, L.smem, c->stream);
-    else if (L.g <= 2) e = launch_count<16, TIER_PRIVATE>(a, grid, cfg.nthr, L.smem, c->stream);
-    else if (L.g == 3) e = launch_count<16, TIER_SHARED>(a, grid, cfg.nthr, L.smem, c->stream);
-    else e = launch_count<32, TIER_GLOBAL>(a, grid, cfg.nthr, L.smem, c->stream);
+    if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, c->stream);
+    else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, c->stream);
+    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, c->stream);
+    else if (L.g == 5) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, c->stream);
+    else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, c->stream);
     if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "count_kernel launch failed: %s", cudaGetErrorString(e));
     if (c->profile_on) OBN_CUDA(cudaEventRecord(e1, c->stream));
     ++c->prof.count_launches;
-    ++c->prof.total_launches;
-  }
-  if (S.mode == MODE_CI && S.p) {
-    pvalue_kernel<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(d_stat, d_dof, d_p, (uint32_t)n);
-    OBN_CUDA(cudaGetLastError());
     ++c->prof.total_launches;
   }
 

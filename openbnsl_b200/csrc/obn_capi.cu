@@ -2,6 +2,7 @@
 // translation unit that takes the place of the reference's src/template_cuda.cu.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 

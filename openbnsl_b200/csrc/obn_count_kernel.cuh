@@ -1,17 +1,28 @@
-// obn_count_kernel.cuh -- the counting kernel proper.
+// obn_count_kernel.cuh -- the counting kernel proper (sm_100a).
 //
-//   TIER_PRIVATE  every thread owns a private column of 16-bit counters in
-//                 shared memory (hist16[cell][thread]); increments are plain
-//                 LDS/IADD/STS with no atomics and no bank conflicts (thread t
-//                 always hits bank t/2).  Reduced over threads into an int32
-//                 table before the epilogue.
-//   TIER_SHARED   one int32 histogram per CTA, shared-memory atomics.
-//   TIER_GLOBAL   int32 table in global scratch (L2 atomics) for tables that
-//                 do not fit shared memory.
+// One CTA owns one (tuple, row-split).  Every row of the split is turned into a
+// mixed-radix cell index and counted into ONE int32 table per CTA:
 //
-// Keys are built from 16-byte vector loads (16 rows per column per load) with
-// packed arithmetic: KW=8 keeps four 8-bit keys per register (tables of <=256
-// cells), KW=16 two 16-bit keys, KW=32 one.
+//   TIER_SMEM    table in shared memory, incremented with `atomicAdd(p, 1)`,
+//                which ptxas lowers to ATOMS.POPC.INC.32 -- the hardware form of
+//                warp-aggregated increments (lanes that hit the same cell are
+//                popcounted and applied as one add).  Measured on B200
+//                (benchmarks/micro/smem_incr.cu, profiles/r1_micro_smem_incr.txt):
+//                16 increments/clk/SM, against 6-9 for lane-private LDS/IADD/STS
+//                counters and 0.5-3 for __match_any_sync aggregation in software.
+//   TIER_GLOBAL  table in global scratch (L2 atomics) for tables that do not
+//                fit shared memory.
+//
+// Category codes are read as 16-byte vectors (16 rows of one column per load,
+// coalesced: consecutive lanes read consecutive 16-byte chunks) and combined
+// with packed arithmetic: KW=8 keeps four 8-bit keys per register (tables of
+// <= 256 cells), KW=16 two 16-bit keys, KW=32 one.  With SCALE4 the packed key
+// is pre-multiplied by 4 so that an extracted field IS the byte offset of the
+// cell (one ALU op + one ATOMS per row).
+//
+// Rows beyond n_rows up to the next multiple of 16 are zero padding in every
+// column (obn_dataset_upload), i.e. they land in cell 0; the CTA that owns the
+// last vector subtracts them again.
 #pragma once
 #include "obn_kernels.cuh"
 
@@ -33,164 +44,220 @@ struct KeyVec;               // keys of 16 consecutive rows
 template <>
 struct KeyVec<8> {
   uint32_t w[4];
-  __device__ __forceinline__ void zero() { w[0] = w[1] = w[2] = w[3] = 0; }
+  __device__ __forceinline__ void init(const uint4& c) { w[0] = c.x; w[1] = c.y; w[2] = c.z; w[3] = c.w; }
   __device__ __forceinline__ void push(const uint4& c, uint32_t card) {
     w[0] = w[0] * card + c.x; w[1] = w[1] * card + c.y;
     w[2] = w[2] * card + c.z; w[3] = w[3] * card + c.w;
   }
-  __device__ __forceinline__ uint32_t get(int r) const { return (w[r >> 2] >> ((r & 3) * 8)) & 0xffu; }
+  __device__ __forceinline__ void scale4() {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) w[i] <<= 2;
+  }
+  __device__ __forceinline__ uint32_t get(int r) const { return __byte_perm(w[r >> 2], 0, 0x4440 + (r & 3)); }
 };
 template <>
 struct KeyVec<16> {
   uint32_t w[8];
-  __device__ __forceinline__ void zero() {
+  __device__ __forceinline__ void init(const uint4& c) {
+    const uint32_t s[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) w[i] = 0;
+    for (int i = 0; i < 4; ++i) {
+      w[2 * i] = __byte_perm(s[i], 0, 0x4140);        // bytes 0,1 -> halves
+      w[2 * i + 1] = __byte_perm(s[i], 0, 0x4342);    // bytes 2,3 -> halves
+    }
   }
   __device__ __forceinline__ void push(const uint4& c, uint32_t card) {
     const uint32_t s[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      w[2 * i] = w[2 * i] * card + __byte_perm(s[i], 0, 0x4140);       // bytes 0,1 -> halves
-      w[2 * i + 1] = w[2 * i + 1] * card + __byte_perm(s[i], 0, 0x4342);  // bytes 2,3 -> halves
+      w[2 * i] = w[2 * i] * card + __byte_perm(s[i], 0, 0x4140);
+      w[2 * i + 1] = w[2 * i + 1] * card + __byte_perm(s[i], 0, 0x4342);
     }
   }
-  __device__ __forceinline__ uint32_t get(int r) const { return (w[r >> 1] >> ((r & 1) * 16)) & 0xffffu; }
+  __device__ __forceinline__ void scale4() {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] <<= 2;
+  }
+  __device__ __forceinline__ uint32_t get(int r) const { return (r & 1) ? (w[r >> 1] >> 16) : (w[r >> 1] & 0xffffu); }
 };
 template <>
 struct KeyVec<32> {
   uint32_t w[16];
-  __device__ __forceinline__ void zero() {
+  __device__ __forceinline__ void init(const uint4& c) {
+    const uint32_t s[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-    for (int i = 0; i < 16; ++i) w[i] = 0;
+    for (int i = 0; i < 16; ++i) w[i] = __byte_perm(s[i >> 2], 0, 0x4440 + (i & 3));
   }
   __device__ __forceinline__ void push(const uint4& c, uint32_t card) {
     const uint32_t s[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-    for (int i = 0; i < 16; ++i) w[i] = w[i] * card + ((s[i >> 2] >> ((i & 3) * 8)) & 0xffu);
+    for (int i = 0; i < 16; ++i) w[i] = w[i] * card + __byte_perm(s[i >> 2], 0, 0x4440 + (i & 3));
+  }
+  __device__ __forceinline__ void scale4() {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] <<= 2;
   }
   __device__ __forceinline__ uint32_t get(int r) const { return w[r]; }
 };
 
-template <int KW, int TIER>
-__global__ void __launch_bounds__(256) count_kernel(const BatchArgs A) {
+// 16 increments for one key vector.  `base` is the table as a byte pointer.
+template <int KW, int TIER, bool SCALE4>
+__device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* base) {
+  if (SCALE4) key.scale4();
+#pragma unroll
+  for (int r = 0; r < 16; ++r) {
+    const uint32_t f = key.get(r);
+    unsigned int* p = reinterpret_cast<unsigned int*>(base + (SCALE4 ? (size_t)f : ((size_t)f << 2)));
+    atomicAdd(p, 1u);      // TIER_SMEM: ATOMS.POPC.INC.32   TIER_GLOBAL: RED.E.ADD
+  }
+}
+
+// Row scan with the column count known at compile time: column pointers and
+// cards live in registers, and the loads of the NEXT 16-row vector are issued
+// before the increments of the current one (register double buffering).
+template <int KW, int TIER, bool SCALE4, int K>
+__device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, uint32_t v_begin,
+                                            uint32_t v_end, uint32_t tid, uint32_t nthr) {
+  const uint8_t* col[K];
+  uint32_t card[K];
+#pragma unroll
+  for (int i = 0; i < K; ++i) { col[i] = T.col[i]; card[i] = T.card[i]; }
+  uint4 cur[K], nxt[K];
+  uint32_t v = v_begin + tid;
+  if (v < v_end) {
+#pragma unroll
+    for (int i = 0; i < K; ++i) cur[i] = ld_codes16(col[i] + ((size_t)v << 4));
+  }
+  for (; v < v_end; v += nthr) {
+    const uint32_t vn = v + nthr;
+    if (vn < v_end) {
+#pragma unroll
+      for (int i = 0; i < K; ++i) nxt[i] = ld_codes16(col[i] + ((size_t)vn << 4));
+    }
+    KeyVec<KW> key;
+    key.init(cur[0]);
+#pragma unroll
+    for (int i = 1; i < K; ++i) key.push(cur[i], card[i]);
+    count16<KW, TIER, SCALE4>(key, base);
+#pragma unroll
+    for (int i = 0; i < K; ++i) cur[i] = nxt[i];
+  }
+}
+
+// Any column count (descriptors stay in shared memory).
+template <int KW, int TIER, bool SCALE4>
+__device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
+                                              uint32_t v_end, uint32_t tid, uint32_t nthr) {
+  for (uint32_t v = v_begin + tid; v < v_end; v += nthr) {
+    const size_t off = (size_t)v << 4;
+    KeyVec<KW> key;
+    key.init(ld_codes16(T.col[0] + off));
+    for (int i = 1; i < k; ++i) key.push(ld_codes16(T.col[i] + off), T.card[i]);
+    count16<KW, TIER, SCALE4>(key, base);
+  }
+}
+
+template <int KW, int TIER, bool SCALE4>
+__global__ void __launch_bounds__(256, 4) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ CtaTuple T;
   __shared__ double red_d[32];
   __shared__ unsigned long long red_u[32];
 
-  const int tid = threadIdx.x, nthr = blockDim.x;
+  const uint32_t tid = threadIdx.x, nthr = blockDim.x;
   const uint32_t lt = blockIdx.x / A.splits;       // launch-local tuple
   const uint32_t split = blockIdx.x - lt * A.splits;
   const uint32_t t = A.perm[lt];
 
-  // ---- tuple prologue: digit order, column pointers, cells ----------------
-  if (tid == 0) {
+  // ---- tuple prologue (one warp, one lane per variable) ---------------------
+  // desc[i] = var_id | (card-1) << 24, ascending var ids.  Kernel digit order:
+  // conditioning variables first (most significant), then x, then y, so that
+  // every Z-slice is a contiguous rx*ry block laid out like citest.h:83.
+  if (tid < 32) {
     const uint64_t o0 = A.offsets[t], o1 = A.offsets[t + 1];
     const int k = (int)(o1 - o0);
-    T.k = k;
-    uint32_t xa = 0xffffffffu, ya = 0xffffffffu;
+    uint32_t xa = 0xffffffffu, ya = 0xffffffffu, child = 0xffffffffu;
     if (A.mode == MODE_CI) {
       xa = A.role_a[t]; ya = A.role_b[t];
       if (xa > ya) { const uint32_t s = xa; xa = ya; ya = s; }   // citest.h:48
+    } else if (A.mode == MODE_BDEU_ONE) {
+      child = A.role_a[t];
     }
-    int n = 0;
-    uint32_t cells = 1;
-    T.child_pos = -1;
-    for (int i = 0; i < k; ++i) {
-      const uint32_t v = A.var_ids[o0 + i];
-      const uint32_t c = A.cards[v];
-      T.ref_card[i] = c;
-      cells *= c;
-      if (A.mode == MODE_BDEU_ONE && v == A.role_a[t]) T.child_pos = i;
-      if (v == xa || v == ya) continue;
-      T.col[n] = A.data + (size_t)v * A.stride;
-      T.card[n] = c;
-      ++n;
+    const bool live = (int)tid < k;
+    const uint32_t d = live ? A.desc[o0 + tid] : 0u;
+    const uint32_t v = d & 0xffffffu, c = (d >> 24) + 1u;
+    const bool is_x = live && v == xa, is_y = live && v == ya;
+    const unsigned m_z = __ballot_sync(0xffffffffu, live && !is_x && !is_y);
+    const int n_z = __popc(m_z);
+    int pos;
+    if (is_x) pos = n_z;
+    else if (is_y) pos = n_z + 1;
+    else pos = __popc(m_z & ((1u << tid) - 1u));
+    if (live) {
+      T.col[pos] = A.data + (size_t)v * A.stride;
+      T.card[pos] = c;
+      T.ref_card[tid] = c;
+      if (is_x) T.rx = c;
+      if (is_y) T.ry = c;
     }
-    if (A.mode == MODE_CI) {
-      T.col[n] = A.data + (size_t)xa * A.stride; T.card[n] = A.cards[xa]; ++n;
-      T.col[n] = A.data + (size_t)ya * A.stride; T.card[n] = A.cards[ya]; ++n;
-      T.rx = A.cards[xa]; T.ry = A.cards[ya];
+    uint32_t prod = live ? c : 1u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) prod *= __shfl_xor_sync(0xffffffffu, prod, o);
+    const unsigned m_child = __ballot_sync(0xffffffffu, live && v == child);
+    if (tid == 0) {
+      T.k = k;
+      T.cells = prod;
+      T.child_pos = m_child ? (__ffs(m_child) - 1) : -1;
     }
-    T.cells = cells;
   }
   __syncthreads();
   const int k = T.k;
   const uint32_t cells = T.cells;
 
-  // ---- shared-memory carve-up ---------------------------------------------
-  int32_t* tab;                     // dense int32 table the epilogue reads
-  uint16_t* hist16 = nullptr;       // TIER_PRIVATE only
+  // ---- table + epilogue scratch ---------------------------------------------
+  int32_t* tab;
   int32_t* wscratch;                // per-warp epilogue scratch
-  if (TIER == TIER_PRIVATE) {
+  if (TIER == TIER_SMEM) {
     tab = reinterpret_cast<int32_t*>(smem_raw);
-    const uint32_t tab_bytes = (cells * 4u + 15u) & ~15u;
-    hist16 = reinterpret_cast<uint16_t*>(smem_raw + tab_bytes);
-    wscratch = reinterpret_cast<int32_t*>(hist16);       // aliased: hist16 is dead by then
-    const uint32_t n16 = (cells * (uint32_t)nthr * 2u) / 16u;
-    uint4* z = reinterpret_cast<uint4*>(hist16);
-    for (uint32_t i = tid; i < n16; i += nthr) z[i] = make_uint4(0, 0, 0, 0);
-  } else if (TIER == TIER_SHARED) {
-    tab = reinterpret_cast<int32_t*>(smem_raw);
-    const uint32_t tab_bytes = (cells * 4u + 15u) & ~15u;
-    wscratch = reinterpret_cast<int32_t*>(smem_raw + tab_bytes);
+    wscratch = reinterpret_cast<int32_t*>(smem_raw + (((size_t)cells * 4u + 15u) & ~(size_t)15u));
     for (uint32_t i = tid; i < cells; i += nthr) tab[i] = 0;
+    __syncthreads();
   } else {
     tab = A.scratch + A.scratch_off[lt];
     wscratch = reinterpret_cast<int32_t*>(smem_raw);
   }
-  __syncthreads();
 
-  // ---- main loop over this split's 16-row vectors -------------------------
-  const uint32_t n_full = A.n_rows >> 4;
+  // ---- main loop over this split's 16-row vectors -----------------------------
+  const uint32_t n_vec = (A.n_rows + 15u) >> 4;
   const uint32_t v_begin = split * A.vec_per_split;
   uint32_t v_end = v_begin + A.vec_per_split;
-  if (v_end > n_full) v_end = n_full;
-  uint16_t* my16 = hist16 + tid;
-  for (uint32_t v = v_begin + tid; v < v_end; v += nthr) {
-    KeyVec<KW> key;
-    key.zero();
-    const size_t off = (size_t)v << 4;
-    for (int i = 0; i < k; ++i) key.push(ld_codes16(T.col[i] + off), T.card[i]);
-#pragma unroll
-    for (int r = 0; r < 16; ++r) {
-      const uint32_t cell = key.get(r);
-      if (TIER == TIER_PRIVATE) my16[cell * nthr] += 1;
-      else if (TIER == TIER_SHARED) atomicAdd(&tab[cell], 1);
-      else atomicAdd(&tab[cell], 1);
-    }
+  if (v_end > n_vec) v_end = n_vec;
+  unsigned char* base = reinterpret_cast<unsigned char*>(tab);
+  switch (k) {
+    case 0: break;
+    case 1: scan_rows_k<KW, TIER, SCALE4, 1>(T, base, v_begin, v_end, tid, nthr); break;
+    case 2: scan_rows_k<KW, TIER, SCALE4, 2>(T, base, v_begin, v_end, tid, nthr); break;
+    case 3: scan_rows_k<KW, TIER, SCALE4, 3>(T, base, v_begin, v_end, tid, nthr); break;
+    case 4: scan_rows_k<KW, TIER, SCALE4, 4>(T, base, v_begin, v_end, tid, nthr); break;
+    case 5: scan_rows_k<KW, TIER, SCALE4, 5>(T, base, v_begin, v_end, tid, nthr); break;
+    case 6: scan_rows_k<KW, TIER, SCALE4, 6>(T, base, v_begin, v_end, tid, nthr); break;
+    default: scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr); break;
   }
-  // tail rows (n_rows % 16) belong to the last split; one thread, scalar.
-  // TIER_PRIVATE: thread 0 adds them to ITS private counters.
-  if (split == (uint32_t)A.splits - 1 && tid == 0) {
-    for (uint32_t r = n_full << 4; r < A.n_rows; ++r) {
-      uint32_t cell = 0;
-      for (int i = 0; i < k; ++i) cell = cell * T.card[i] + T.col[i][r];
-      if (TIER == TIER_PRIVATE) my16[cell * nthr] += 1;
-      else atomicAdd(&tab[cell], 1);
+  if (tid == 0) {
+    if (k == 0) {
+      // the empty tuple: one cell holding every row of the split (contingency_table.h:52-55)
+      const uint32_t r0 = v_begin << 4;
+      uint32_t r1 = v_end << 4;
+      if (r1 > A.n_rows) r1 = A.n_rows;
+      if (r1 > r0) atomicAdd(&tab[0], (int)(r1 - r0));
+    } else if (v_end == n_vec && v_end > v_begin) {
+      const int pad = (int)((n_vec << 4) - A.n_rows);     // zero-padding rows counted into cell 0
+      if (pad) atomicAdd(&tab[0], -pad);
     }
   }
   __syncthreads();
 
-  // ---- TIER_PRIVATE: reduce the per-thread counters into `tab` -------------
-  if (TIER == TIER_PRIVATE) {
-    const int lane = tid & 31, warp = tid >> 5, nw = nthr >> 5;
-    const uint32_t words = (uint32_t)nthr >> 1;          // u32 words per cell row
-    for (uint32_t c = warp; c < cells; c += nw) {
-      const uint32_t* row = reinterpret_cast<const uint32_t*>(hist16 + (size_t)c * nthr);
-      int s = 0;
-      for (uint32_t i = lane; i < words; i += 32) {
-        const uint32_t x = row[i];
-        s += (int)(x & 0xffffu) + (int)(x >> 16);
-      }
-      s = warp_sum(s);
-      if (lane == 0) tab[c] = s;
-    }
-    __syncthreads();
-  }
-
-  // ---- row splits: merge through global scratch, last CTA continues -------
+  // ---- row splits: merge through global scratch, last CTA continues ---------
   if (A.splits > 1 || TIER == TIER_GLOBAL) {
     int32_t* g = A.scratch + A.scratch_off[lt];
     if (TIER != TIER_GLOBAL) {
@@ -218,7 +285,7 @@ __global__ void __launch_bounds__(256) count_kernel(const BatchArgs A) {
   // ---- fused epilogue -------------------------------------------------------
   if (A.mode == MODE_CI) {
     epilogue_ci(tab, cells, T.rx, T.ry, A.kind, wscratch + (tid >> 5) * (T.rx + T.ry),
-                red_d, red_u, &A.stat[t], &A.dof[t]);
+                red_d, red_u, &A.stat[t], &A.dof[t], A.pval ? &A.pval[t] : nullptr);
   } else if (A.mode == MODE_BDEU_ONE || A.mode == MODE_BDEU_ALL) {
     const int c0 = (A.mode == MODE_BDEU_ONE) ? T.child_pos : 0;
     const int c1 = (A.mode == MODE_BDEU_ONE) ? T.child_pos + 1 : k;
@@ -239,12 +306,6 @@ __global__ void __launch_bounds__(256) count_kernel(const BatchArgs A) {
     for (uint32_t c = tid; c < cells; c += nthr) tab[c] = 0;
     if (tid == 0) A.tickets[lt] = 0;
   }
-}
-
-// p = pchisq(stat, dof) for a batch (citest.h:17-21,139)
-__global__ void pvalue_kernel(const double* stat, const unsigned long long* dof, double* p, uint32_t n) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) p[i] = pchisq(stat[i], dof[i]);
 }
 
 }  // namespace obn

@@ -11,7 +11,7 @@
 namespace obn {
 
 enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3 };
-enum Tier : int { TIER_PRIVATE = 0, TIER_SHARED = 1, TIER_GLOBAL = 2 };
+enum Tier : int { TIER_SMEM = 0, TIER_GLOBAL = 1 };
 
 struct BatchArgs {
   // dataset
@@ -20,7 +20,7 @@ struct BatchArgs {
   uint32_t n_rows;
   const uint32_t* cards;    // [n_vars]
   // batch (device copies of the CSR arrays)
-  const uint32_t* var_ids;
+  const uint32_t* desc;     // [offsets[n]]  var_id | (card-1) << 24, ascending var ids per tuple
   const uint64_t* offsets;
   const uint32_t* perm;     // tuple ids evaluated by this launch
   const uint32_t* role_a;   // CI: x      BDEU_ONE: child
@@ -36,6 +36,7 @@ struct BatchArgs {
   // outputs (device)
   double* stat;
   unsigned long long* dof;
+  double* pval;             // CI: p = pchisq(stat, dof) (citest.h:139); may be null
   double* scores;           // BDEU_ONE: [tuple]   BDEU_ALL: [offsets[t] + i]
   int32_t* counts_out;      // MODE_COUNTS
   const uint64_t* counts_off;
@@ -56,17 +57,65 @@ struct BatchArgs {
 // (citest.h:86-137).  Kernel digit order puts x then y as the two fastest
 // digits, so slice s is the contiguous block tab[s*rx*ry ...) laid out
 // x_state * ry + y_state exactly like the reference's slice (citest.h:83).
-__device__ __forceinline__ void epilogue_ci(const int32_t* tab, uint32_t cells, uint32_t rx,
-                                            uint32_t ry, int kind, int32_t* wscratch,
-                                            double* red_d, unsigned long long* red_u,
-                                            double* stat_out, unsigned long long* dof_out) {
+
+// one cell's contribution (citest.h:116-131)
+__device__ __forceinline__ double ci_cell(double obs, int ri, int cj, double n_total, bool yates, int kind) {
+  const double ex = (double)ri * (double)cj / n_total;              // :116
+  if (yates) {                                                      // :120-125
+    const double diff = ex - obs;
+    const double dir = (diff > 0) ? 1.0 : (diff < 0) ? -1.0 : 0.0;
+    obs += fmin(0.5, fabs(diff)) * dir;
+  }
+  if (kind == 0) {
+    const double df = obs - ex;
+    return df * df / ex;                                            // :127-129
+  }
+  return (obs > 0) ? 2.0 * obs * log(obs / ex) : 0.0;               // :130-131
+}
+
+// Small slices (rx, ry <= 4, the common case for the named networks): ONE LANE
+// per slice, the slice held in registers.
+__device__ __forceinline__ void ci_slices_small(const int32_t* tab, uint32_t n_slices, uint32_t rx, uint32_t ry,
+                                                int kind, double& stat, unsigned long long& dof) {
+  const uint32_t sl = rx * ry;
+  for (uint32_t s = threadIdx.x; s < n_slices; s += blockDim.x) {
+    const int32_t* t = tab + (size_t)s * sl;
+    int o[4][4], rs[4] = {0, 0, 0, 0}, cs[4] = {0, 0, 0, 0};
+    int tot = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int v = ((uint32_t)i < rx && (uint32_t)j < ry) ? t[i * ry + j] : 0;
+        o[i][j] = v;
+        rs[i] += v;
+        cs[j] += v;
+        tot += v;
+      }
+    if (tot == 0) continue;                                             // citest.h:100
+    int robs = 0, cobs = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { robs += (rs[i] > 0); cobs += (cs[i] > 0); }
+    const unsigned d = (unsigned)(robs - 1) * (unsigned)(cobs - 1);     // :109
+    const bool yates = (d == 1);                                        // :110
+    dof += d;
+    const double n_total = (double)tot;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (rs[i] > 0 && cs[j] > 0) stat += ci_cell((double)o[i][j], rs[i], cs[j], n_total, yates, kind);
+  }
+}
+
+// Any slice shape: one warp per slice, margins in per-warp scratch.
+__device__ __forceinline__ void ci_slices_any(const int32_t* tab, uint32_t n_slices, uint32_t rx, uint32_t ry,
+                                              int kind, int32_t* wscratch, double& stat,
+                                              unsigned long long& dof) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const uint32_t sl = rx * ry;
-  const uint32_t n_slices = cells / sl;
   int32_t* rs = wscratch;        // [rx]
   int32_t* cs = wscratch + rx;   // [ry]
-  double stat = 0.0;
-  unsigned long long dof = 0;
   for (uint32_t s = warp; s < n_slices; s += nw) {
     const int32_t* t = tab + (size_t)s * sl;
     int tot = 0, robs = 0, cobs = 0;
@@ -95,30 +144,28 @@ __device__ __forceinline__ void epilogue_ci(const int32_t* tab, uint32_t cells, 
       for (uint32_t c = lane; c < sl; c += 32) {
         const uint32_t i = c / ry, j = c - i * ry;
         const int ri = rs[i], cj = cs[j];
-        if (ri > 0 && cj > 0) {
-          double obs = (double)t[c];
-          const double ex = (double)ri * (double)cj / n_total;          // :116
-          if (yates) {                                                  // :120-125
-            const double diff = ex - obs;
-            const double dir = (diff > 0) ? 1.0 : (diff < 0) ? -1.0 : 0.0;
-            obs += fmin(0.5, fabs(diff)) * dir;
-          }
-          if (kind == 0) {
-            const double df = obs - ex;
-            stat += df * df / ex;                                       // :127-129
-          } else if (obs > 0) {
-            stat += 2.0 * obs * log(obs / ex);                          // :130-131
-          }
-        }
+        if (ri > 0 && cj > 0) stat += ci_cell((double)t[c], ri, cj, n_total, yates, kind);
       }
     }
     __syncwarp();
   }
+}
+
+__device__ __forceinline__ void epilogue_ci(const int32_t* tab, uint32_t cells, uint32_t rx,
+                                            uint32_t ry, int kind, int32_t* wscratch,
+                                            double* red_d, unsigned long long* red_u,
+                                            double* stat_out, unsigned long long* dof_out, double* p_out) {
+  const uint32_t n_slices = cells / (rx * ry);
+  double stat = 0.0;
+  unsigned long long dof = 0;
+  if (rx <= 4 && ry <= 4) ci_slices_small(tab, n_slices, rx, ry, kind, stat, dof);
+  else ci_slices_any(tab, n_slices, rx, ry, kind, wscratch, stat, dof);
   stat = block_sum(stat, red_d);
   dof = block_sum(dof, red_u);
   if (threadIdx.x == 0) {
     *stat_out = stat;
     *dof_out = dof;
+    if (p_out) *p_out = pchisq(stat, dof);               // citest.h:139
   }
 }
 
