@@ -169,8 +169,9 @@ static int run_batch(BatchSpec& S) {
   // ---- packed input buffer ---------------------------------------------------
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align16(off + bytes); return o; };
-  const size_t o_var = take(total_vars * 4), o_off = take((n + 1) * 8), o_perm = take(n * 4);
-  const size_t o_ra = take(S.role_a ? n * 4 : 0), o_rb = take(S.role_b ? n * 4 : 0);
+  if (total_vars >= 0xffffffffull) return fail(OBN_ERR_UNSUPPORTED, "more than 2^32-2 variable slots in one batch");
+  const size_t o_var = take(total_vars * 4), o_hdr = take(n * 16);
+  const size_t o_roles = take(S.role_a ? n * 8 : 0);
   const size_t o_soff = take(n * 8);
   const size_t o_coff = take(S.mode == MODE_COUNTS ? n * 8 : 0);
   const size_t o_lijk = take(exact ? n * 4 : 0), o_lij = take(exact ? total_vars * 4 : 0);
@@ -182,14 +183,11 @@ static int run_batch(BatchSpec& S) {
     uint32_t* desc = reinterpret_cast<uint32_t*>(hin + o_var);
     for (size_t i = 0; i < total_vars; ++i) desc[i] = S.var_ids[i] | ((ds->cards[S.var_ids[i]] - 1u) << 24);
   }
-  memcpy(hin + o_off, S.offsets, (n + 1) * 8);
-  if (S.role_a) memcpy(hin + o_ra, S.role_a, n * 4);
-  if (S.role_b) memcpy(hin + o_rb, S.role_b, n * 4);
   if (exact) {
     memcpy(hin + o_lijk, lut_ijk.data(), n * 4);
     if (total_vars) memcpy(hin + o_lij, lut_ij.data(), total_vars * 4);
   }
-  uint32_t* perm = reinterpret_cast<uint32_t*>(hin + o_perm);
+  std::vector<uint32_t> perm(n);
   uint64_t* soff = reinterpret_cast<uint64_t*>(hin + o_soff);
   size_t gstart[kNumClasses + 1];
   gstart[0] = 0;
@@ -198,6 +196,23 @@ static int run_batch(BatchSpec& S) {
     size_t fill[kNumClasses];
     for (int g = 0; g < kNumClasses; ++g) fill[g] = gstart[g];
     for (size_t t = 0; t < n; ++t) perm[fill[group[t]]++] = (uint32_t)t;
+  }
+  {
+    uint32_t* hdr = reinterpret_cast<uint32_t*>(hin + o_hdr);
+    uint32_t* roles = S.role_a ? reinterpret_cast<uint32_t*>(hin + o_roles) : nullptr;
+    for (size_t q = 0; q < n; ++q) {
+      const uint32_t t = perm[q];
+      hdr[4 * q + 0] = t;
+      hdr[4 * q + 1] = (uint32_t)S.offsets[t];
+      hdr[4 * q + 2] = (uint32_t)(S.offsets[t + 1] - S.offsets[t]);
+      hdr[4 * q + 3] = cells[t];
+      if (roles) {
+        uint32_t ra = S.role_a[t], rb = S.role_b ? S.role_b[t] : 0xffffffffu;
+        if (S.role_b && ra > rb) std::swap(ra, rb);                  // citest.h:48
+        roles[2 * q + 0] = ra;
+        roles[2 * q + 1] = rb;
+      }
+    }
   }
 
   // ---- output buffer ----------------------------------------------------------
@@ -213,12 +228,12 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
-  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; };
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; };
   std::vector<Launch> launches;
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
   size_t max_scratch_ints = 0, max_launch_tuples = 0;
   const int force_t = env_int("OBN_FORCE_T", 0), force_splits = env_int("OBN_FORCE_SPLITS", 0);
-  const size_t target_threads = (size_t)c->sm_count * 2048 * (size_t)env_int("OBN_WAVES", 2);
+  const size_t target_threads = (size_t)c->sm_count * (size_t)env_int("OBN_THREADS_PER_SM", 768);
   for (int g = 0; g < kNumClasses; ++g) {
     if (!group_count[g]) continue;
     const bool global_tier = (g == kNumClasses - 1);
@@ -230,16 +245,20 @@ static int run_batch(BatchSpec& S) {
         max_cells = std::max(max_cells, cells[perm[q]]);
         max_rxy = std::max(max_rxy, rxy[perm[q]]);
       }
-      // threads per tuple: fill the machine `OBN_WAVES` times over, but keep >= 4 vectors per thread
-      size_t tpt = (target_threads + remaining - 1) / remaining;
-      tpt = std::min<size_t>(tpt, std::max<size_t>(32, n_vec / 4));
+      // CTA width / row splits (benchmarks/kernel_sweep.py, profiles/r1_kernel_sweep.txt): the
+      // best geometry keeps about 768 threads per SM busy in total, with the widest CTA
+      // that allows; row splits only pay when a launch has too few tuples to do that
+      // (each split repeats the prologue and adds a merge through L2).
+      size_t tpt = target_threads / remaining;
       size_t p2 = 32;
-      while (p2 < tpt) p2 <<= 1;
-      int nthr = (int)std::min<size_t>(p2, 256);
-      int splits = (int)std::max<size_t>(1, p2 / 256);
-      // a split must amortise its merge (cells atomics) and its prologue
-      const uint32_t min_vps = std::max<uint32_t>(256u, max_cells / 8u);
-      splits = std::min<int>(splits, (int)std::max<uint32_t>(1u, n_vec / min_vps));
+      while (p2 * 2 <= tpt && p2 < 256) p2 <<= 1;
+      int nthr = (int)p2;
+      int splits = 1;
+      if (nthr == 256) {
+        const uint32_t min_vps = std::max<uint32_t>(1024u, max_cells / 4u);
+        splits = (int)std::min<size_t>(tpt / 256, std::max<uint32_t>(1u, n_vec / min_vps));
+        splits = std::max(1, splits);
+      }
       if (force_t) nthr = force_t;
       if (force_splits) splits = std::max(1, std::min<int>(force_splits, (int)std::max<uint32_t>(1u, n_vec)));
       const int nw = nthr / 32;
@@ -259,15 +278,31 @@ static int run_batch(BatchSpec& S) {
       }
       uint32_t vps = (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints});
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false});
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
       max_launch_tuples = std::max(max_launch_tuples, j - i);
       i = j;
     }
   }
+  // launches of one batch run concurrently on the ctx's streams, so each gets its own slice of
+  // the scratch; when the slices would not fit, a barrier serialises and the slices restart at 0
+  {
+    size_t base = 0, need = 0;
+    for (Launch& L : launches) {
+      if (base && (base + L.scratch_ints) * 4 > kScratchMaxBytes) {
+        L.barrier_before = true;
+        base = 0;
+      }
+      L.scratch_base = base;
+      base += L.scratch_ints;
+      need = std::max(need, base);
+    }
+    max_scratch_ints = need;
+  }
+  (void)max_launch_tuples;
   if (max_scratch_ints)
     if (int rc = c->d_scratch.reserve(max_scratch_ints * 4, true)) return rc;
-  if (int rc = c->d_tickets.reserve(max_launch_tuples * 4, true)) return rc;
+  if (int rc = c->d_tickets.reserve(n * 4, true)) return rc;
 
   OBN_CUDA(cudaMemcpyAsync(c->d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
 
@@ -277,9 +312,6 @@ static int run_batch(BatchSpec& S) {
   BatchArgs a{};
   a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows; a.cards = ds->cards_dev;
   a.desc = reinterpret_cast<const uint32_t*>(din + o_var);
-  a.offsets = reinterpret_cast<const uint64_t*>(din + o_off);
-  a.role_a = S.role_a ? reinterpret_cast<const uint32_t*>(din + o_ra) : nullptr;
-  a.role_b = S.role_b ? reinterpret_cast<const uint32_t*>(din + o_rb) : nullptr;
   a.mode = S.mode; a.kind = S.kind; a.ess = S.ess;
   if (exact) {
     a.lut = c->d_lut.as<double>(); a.lut_stride = lut_stride;
@@ -295,37 +327,73 @@ static int run_batch(BatchSpec& S) {
   a.scratch = c->d_scratch.as<int32_t>();
   a.tickets = c->d_tickets.as<unsigned int>();
 
-  size_t ev_first = c->ev_used;
+  // fork/join over the ctx's auxiliary streams: launch i of a segment goes to stream i % (1+kAuxStreams)
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (c->profile_on) {
+    if (c->ev_used == c->ev_pool.size()) {
+      cudaEvent_t x, y;
+      OBN_CUDA(cudaEventCreate(&x));
+      OBN_CUDA(cudaEventCreate(&y));
+      c->ev_pool.push_back({x, y});
+    }
+    e0 = c->ev_pool[c->ev_used].first;
+    e1 = c->ev_pool[c->ev_used].second;
+    ++c->ev_used;
+    OBN_CUDA(cudaEventRecord(e0, c->stream));
+  }
+  const int n_streams = std::max(1, std::min(1 + obn_ctx::kAuxStreams, env_int("OBN_STREAMS", 1 + obn_ctx::kAuxStreams)));
+  bool aux_used[obn_ctx::kAuxStreams] = {};
+  bool forked = false;
+  int slot = 0;
+  auto join = [&]() -> int {
+    for (int j = 0; j < obn_ctx::kAuxStreams; ++j)
+      if (aux_used[j]) {
+        OBN_CUDA(cudaEventRecord(c->ev_join[j], c->aux[j]));
+        OBN_CUDA(cudaStreamWaitEvent(c->stream, c->ev_join[j], 0));
+        aux_used[j] = false;
+      }
+    forked = false;
+    slot = 0;
+    return OBN_OK;
+  };
   for (const Launch& L : launches) {
-    a.perm = reinterpret_cast<const uint32_t*>(din + o_perm) + L.begin;
+    if (L.barrier_before)
+      if (int rc = join()) return rc;
+    cudaStream_t st = c->stream;
+    const int sidx = slot % n_streams;
+    ++slot;
+    if (sidx > 0) {
+      if (!forked) {
+        OBN_CUDA(cudaEventRecord(c->ev_fork, c->stream));
+        forked = true;
+      }
+      if (!aux_used[sidx - 1]) {
+        OBN_CUDA(cudaStreamWaitEvent(c->aux[sidx - 1], c->ev_fork, 0));
+        aux_used[sidx - 1] = true;
+      }
+      st = c->aux[sidx - 1];
+    }
+    a.hdr = reinterpret_cast<const uint4*>(din + o_hdr) + L.begin;
+    a.roles = S.role_a ? reinterpret_cast<const uint2*>(din + o_roles) + L.begin : nullptr;
     a.scratch_off = reinterpret_cast<const uint64_t*>(din + o_soff) + L.begin;
+    a.scratch = c->d_scratch.as<int32_t>() + L.scratch_base;
+    a.tickets = c->d_tickets.as<unsigned int>() + L.begin;
     a.splits = L.splits;
     a.vec_per_split = L.vps;
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (c->profile_on) {
-      if (c->ev_used == c->ev_pool.size()) {
-        cudaEvent_t x, y;
-        OBN_CUDA(cudaEventCreate(&x));
-        OBN_CUDA(cudaEventCreate(&y));
-        c->ev_pool.push_back({x, y});
-      }
-      e0 = c->ev_pool[c->ev_used].first;
-      e1 = c->ev_pool[c->ev_used].second;
-      ++c->ev_used;
-      OBN_CUDA(cudaEventRecord(e0, c->stream));
-    }
     cudaError_t e;
-    if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, c->stream);
-    else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, c->stream);
-    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, c->stream);
-    else if (L.g == 5) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, c->stream);
-    else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, c->stream);
+    if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
+    else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
+    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
+    else if (L.g == 5) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
+    else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, st);
     if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "count_kernel launch failed: %s", cudaGetErrorString(e));
-    if (c->profile_on) OBN_CUDA(cudaEventRecord(e1, c->stream));
     ++c->prof.count_launches;
     ++c->prof.total_launches;
   }
+  if (int rc = join()) return rc;
+  if (c->profile_on) OBN_CUDA(cudaEventRecord(e1, c->stream));
+  const size_t ev_first = c->ev_used - (c->profile_on ? 1 : 0);
 
   // ---- download ------------------------------------------------------------------
   if (int rc = c->h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;

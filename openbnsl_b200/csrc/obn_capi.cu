@@ -38,6 +38,11 @@ int obn_ctx_create(int device, obn_ctx** out) {
   OBN_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
   c->smem_optin = (size_t)v;
   OBN_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (int j = 0; j < obn_ctx::kAuxStreams; ++j) {
+    OBN_CUDA(cudaStreamCreateWithFlags(&c->aux[j], cudaStreamNonBlocking));
+    OBN_CUDA(cudaEventCreateWithFlags(&c->ev_join[j], cudaEventDisableTiming));
+  }
+  OBN_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   OBN_CUDA(cudaEventCreate(&c->ev0));
   OBN_CUDA(cudaEventCreate(&c->ev1));
   *out = c;
@@ -55,6 +60,11 @@ void obn_ctx_destroy(obn_ctx* c) {
     cudaEventDestroy(pr.first);
     cudaEventDestroy(pr.second);
   }
+  for (int j = 0; j < obn_ctx::kAuxStreams; ++j) {
+    cudaStreamDestroy(c->aux[j]);
+    cudaEventDestroy(c->ev_join[j]);
+  }
+  cudaEventDestroy(c->ev_fork);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
   cudaStreamDestroy(c->stream);

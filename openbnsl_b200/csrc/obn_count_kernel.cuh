@@ -32,8 +32,6 @@ struct CtaTuple {            // per-CTA tuple description in shared memory
   const uint8_t* col[kMaxTupleVars];   // column pointers in KERNEL digit order
   uint32_t card[kMaxTupleVars];        // cards in kernel digit order
   uint32_t ref_card[kMaxTupleVars];    // cards in ascending-var (reference) order
-  int k;
-  uint32_t cells;
   uint32_t rx, ry;
   int child_pos;             // BDEU_ONE: position of the child in reference order
   unsigned int ticket;
@@ -167,24 +165,27 @@ __global__ void __launch_bounds__(256, 4) count_kernel(const BatchArgs A) {
   const uint32_t tid = threadIdx.x, nthr = blockDim.x;
   const uint32_t lt = blockIdx.x / A.splits;       // launch-local tuple
   const uint32_t split = blockIdx.x - lt * A.splits;
-  const uint32_t t = A.perm[lt];
+  // per-launch-tuple header, written by the host in launch order:
+  //   x = tuple id in the batch, y = offset of its descriptors, z = #variables, w = #cells
+  const uint4 hdr = __ldg(&A.hdr[lt]);
+  const uint32_t t = hdr.x;
+  const int k = (int)hdr.z;
+  const uint32_t cells = hdr.w;
 
   // ---- tuple prologue (one warp, one lane per variable) ---------------------
   // desc[i] = var_id | (card-1) << 24, ascending var ids.  Kernel digit order:
   // conditioning variables first (most significant), then x, then y, so that
   // every Z-slice is a contiguous rx*ry block laid out like citest.h:83.
   if (tid < 32) {
-    const uint64_t o0 = A.offsets[t], o1 = A.offsets[t + 1];
-    const int k = (int)(o1 - o0);
     uint32_t xa = 0xffffffffu, ya = 0xffffffffu, child = 0xffffffffu;
     if (A.mode == MODE_CI) {
-      xa = A.role_a[t]; ya = A.role_b[t];
-      if (xa > ya) { const uint32_t s = xa; xa = ya; ya = s; }   // citest.h:48
+      const uint2 r = __ldg(&A.roles[lt]);
+      xa = r.x; ya = r.y;                                        // host stores x < y (citest.h:48)
     } else if (A.mode == MODE_BDEU_ONE) {
-      child = A.role_a[t];
+      child = __ldg(&A.roles[lt]).x;
     }
     const bool live = (int)tid < k;
-    const uint32_t d = live ? A.desc[o0 + tid] : 0u;
+    const uint32_t d = live ? __ldg(&A.desc[hdr.y + tid]) : 0u;
     const uint32_t v = d & 0xffffffu, c = (d >> 24) + 1u;
     const bool is_x = live && v == xa, is_y = live && v == ya;
     const unsigned m_z = __ballot_sync(0xffffffffu, live && !is_x && !is_y);
@@ -200,32 +201,22 @@ __global__ void __launch_bounds__(256, 4) count_kernel(const BatchArgs A) {
       if (is_x) T.rx = c;
       if (is_y) T.ry = c;
     }
-    uint32_t prod = live ? c : 1u;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) prod *= __shfl_xor_sync(0xffffffffu, prod, o);
     const unsigned m_child = __ballot_sync(0xffffffffu, live && v == child);
-    if (tid == 0) {
-      T.k = k;
-      T.cells = prod;
-      T.child_pos = m_child ? (__ffs(m_child) - 1) : -1;
-    }
+    if (tid == 0) T.child_pos = m_child ? (__ffs(m_child) - 1) : -1;
   }
-  __syncthreads();
-  const int k = T.k;
-  const uint32_t cells = T.cells;
 
-  // ---- table + epilogue scratch ---------------------------------------------
+  // ---- table + epilogue scratch (zeroed while the descriptor loads are in flight)
   int32_t* tab;
   int32_t* wscratch;                // per-warp epilogue scratch
   if (TIER == TIER_SMEM) {
     tab = reinterpret_cast<int32_t*>(smem_raw);
     wscratch = reinterpret_cast<int32_t*>(smem_raw + (((size_t)cells * 4u + 15u) & ~(size_t)15u));
     for (uint32_t i = tid; i < cells; i += nthr) tab[i] = 0;
-    __syncthreads();
   } else {
     tab = A.scratch + A.scratch_off[lt];
     wscratch = reinterpret_cast<int32_t*>(smem_raw);
   }
+  __syncthreads();
 
   // ---- main loop over this split's 16-row vectors -----------------------------
   const uint32_t n_vec = (A.n_rows + 15u) >> 4;
@@ -289,10 +280,10 @@ __global__ void __launch_bounds__(256, 4) count_kernel(const BatchArgs A) {
   } else if (A.mode == MODE_BDEU_ONE || A.mode == MODE_BDEU_ALL) {
     const int c0 = (A.mode == MODE_BDEU_ONE) ? T.child_pos : 0;
     const int c1 = (A.mode == MODE_BDEU_ONE) ? T.child_pos + 1 : k;
-    double* out = (A.mode == MODE_BDEU_ONE) ? &A.scores[t] : &A.scores[A.offsets[t]];
+    double* out = (A.mode == MODE_BDEU_ONE) ? &A.scores[t] : &A.scores[hdr.y];
     if (A.lut) {
       epilogue_bdeu_exact(tab, cells, k, T.ref_card, A.lut + (size_t)A.lut_ijk[t] * A.lut_stride,
-                          A.lut, A.lut_stride, A.lut_ij + A.offsets[t], c0, c1, out);
+                          A.lut, A.lut_stride, A.lut_ij + hdr.y, c0, c1, out);
     } else {
       epilogue_bdeu_fast(tab, cells, k, T.ref_card, A.ess, c0, c1, red_d, out);
     }

@@ -45,7 +45,10 @@ struct DevBuf {
     cap = 0;
     OBN_CUDA(cudaMalloc(&p, want));
     cap = want;
-    if (zero_new) OBN_CUDA(cudaMemset(p, 0, want));
+    if (zero_new) {      // rare (grow only); the ctx streams are non-blocking, so fence explicitly
+      OBN_CUDA(cudaMemset(p, 0, want));
+      OBN_CUDA(cudaDeviceSynchronize());
+    }
     return OBN_OK;
   }
   void release() {
@@ -95,6 +98,10 @@ struct obn_ctx {
   int sm_count = 148;
   size_t smem_optin = 0;
   cudaStream_t stream = nullptr;
+  // the launches of one batch (one per table-size class) overlap on these
+  static constexpr int kAuxStreams = 3;
+  cudaStream_t aux[kAuxStreams] = {};
+  cudaEvent_t ev_fork = nullptr, ev_join[kAuxStreams] = {};
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // batch staging: one packed upload and one packed download per batch
   obn::DevBuf d_in, d_out, d_lut;

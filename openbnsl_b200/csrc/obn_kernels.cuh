@@ -21,10 +21,8 @@ struct BatchArgs {
   const uint32_t* cards;    // [n_vars]
   // batch (device copies of the CSR arrays)
   const uint32_t* desc;     // [offsets[n]]  var_id | (card-1) << 24, ascending var ids per tuple
-  const uint64_t* offsets;
-  const uint32_t* perm;     // tuple ids evaluated by this launch
-  const uint32_t* role_a;   // CI: x      BDEU_ONE: child
-  const uint32_t* role_b;   // CI: y
+  const uint4* hdr;         // per launch tuple: {tuple id, desc offset, #vars, #cells}
+  const uint2* roles;       // per launch tuple: CI {x, y} with x < y; BDEU_ONE {child, -}
   int mode;
   int kind;                 // CI: 0 chi2, 1 G2
   double ess;
