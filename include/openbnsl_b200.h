@@ -128,6 +128,8 @@ typedef struct obn_profile {
   uint64_t tuples;           /* tuples evaluated                            */
   double h2d_bytes;          /* bytes copied host -> device (batches + datasets) */
   double d2h_bytes;          /* bytes copied device -> host (results)       */
+  double host_prep_ms;       /* host: validate + classify + pack the batch  */
+  double host_wait_ms;       /* host: enqueue copies/launches + wait for the stream */
 } obn_profile;
 OBN_API int obn_profile_enable(obn_ctx* ctx, int on);
 OBN_API int obn_profile_read(obn_ctx* ctx, obn_profile* out, int reset);

@@ -31,7 +31,8 @@ EXPORTS = [
 class Profile(C.Structure):
     _fields_ = [("count_kernel_ms", C.c_double), ("count_launches", C.c_uint64),
                 ("total_launches", C.c_uint64), ("algorithmic_bytes", C.c_double),
-                ("tuples", C.c_uint64), ("h2d_bytes", C.c_double), ("d2h_bytes", C.c_double)]
+                ("tuples", C.c_uint64), ("h2d_bytes", C.c_double), ("d2h_bytes", C.c_double),
+                ("host_prep_ms", C.c_double), ("host_wait_ms", C.c_double)]
 
 
 _lib = None

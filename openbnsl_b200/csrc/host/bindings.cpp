@@ -118,6 +118,8 @@ PYBIND11_MODULE(openbnsllib, m) {
     d["total_launches"] = p.total_launches;
     d["algorithmic_bytes"] = p.algorithmic_bytes;
     d["tuples"] = p.tuples;
+    d["host_prep_ms"] = p.host_prep_ms;
+    d["host_wait_ms"] = p.host_wait_ms;
     d["h2d_bytes"] = p.h2d_bytes;
     d["d2h_bytes"] = p.d2h_bytes;
     return d;
@@ -279,6 +281,9 @@ PYBIND11_MODULE(openbnsllib, m) {
     d["tests_per_depth"] = g_last_pc_stats.tests_per_depth;
     d["batches_per_depth"] = g_last_pc_stats.batches_per_depth;
     d["total_tests"] = g_last_pc_stats.total_tests();
+    d["enumerate_ms"] = g_last_pc_stats.enumerate_ms;
+    d["evaluate_ms"] = g_last_pc_stats.evaluate_ms;
+    d["resolve_ms"] = g_last_pc_stats.resolve_ms;
     return d;
   });
   sl.def("last_es_stats", []() {

@@ -17,6 +17,7 @@
 //  * multi-GPU: each round's batch is sharded over ranks; one all-reduce(min)
 //    of "first passing candidate index per edge" per round.
 #include <algorithm>
+#include <chrono>
 #include <climits>
 
 #include "structure_learning.hpp"
@@ -154,6 +155,22 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
     stats->tests_per_depth.assign(max_cond_vars + 1, 0);
     stats->batches_per_depth.assign(max_cond_vars + 1, 0);
   }
+  using clk = std::chrono::steady_clock;
+  auto ms_since = [](clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); };
+  if (stats) stats->enumerate_ms = stats->evaluate_ms = stats->resolve_ms = 0;
+  clk::time_point t_phase = clk::now();
+  auto lap = [&](double PcStats::*slot) {
+    if (stats) stats->*slot += ms_since(t_phase);
+    t_phase = clk::now();
+  };
+  struct FastCursor {
+    uint32_t x = 0, y = 0, m[2] = {0, 0}, skip[2] = {0, 0};
+    uint8_t dir = 0;
+    bool valid = false, done = false, removed = false;
+  };
+  std::vector<FastCursor> cursors;
+  std::vector<uint32_t> idx_arena;
+  std::vector<std::vector<uint32_t>> adj(n);
   TupleBatch batch;
   std::vector<uint32_t> pair_of_test, z, tmp;
   std::vector<std::vector<uint32_t>> z_of_test;
@@ -173,51 +190,113 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
 
   for (size_t k = 0; k <= max_cond_vars; ++k) {              // pc.cpp:22 (no early exit)
     if (stable) {
-      // all pairs see the graph as it was when the depth started (pc.cpp:24-25)
-      std::vector<PairCursor> pairs;
+      // All pairs see the graph as it was when the depth started (pc.cpp:24-25): snapshot the
+      // adjacency lists once.  Cursors are allocation-free: candidate j of direction d of pair
+      // (x,y) is the j-th lexicographic k-combination of adj(u)\{v} (gen_comb.h:5-38), kept as
+      // k indices into the snapshot list of u (skipping v's position).
+      const AdjMatGraph snap = g;
+      for (size_t v = 0; v < n; ++v) snap.undirected_neighbors_without(v, (size_t)-1, adj[v]);
+      cursors.clear();
       for (size_t x = 0; x < n; ++x)
         for (size_t y = x + 1; y < n; ++y) {
-          if (!g.has_undirected_edge(x, y)) continue;
-          PairCursor pc;
-          pc.x = (uint32_t)x;
-          pc.y = (uint32_t)y;
-          g.undirected_neighbors_without(x, y, pc.neigh[0]);
-          g.undirected_neighbors_without(y, x, pc.neigh[1]);
-          if (pc.neigh[0].size() < k && pc.neigh[1].size() < k) continue;
-          pc.begin(k, n);
-          if (!pc.done) pairs.push_back(std::move(pc));
+          if (!snap.has_undirected_edge(x, y)) continue;
+          FastCursor c;
+          c.x = (uint32_t)x;
+          c.y = (uint32_t)y;
+          c.m[0] = (uint32_t)adj[x].size() - 1;
+          c.m[1] = (uint32_t)adj[y].size() - 1;
+          c.skip[0] = (uint32_t)(std::lower_bound(adj[x].begin(), adj[x].end(), (uint32_t)y) - adj[x].begin());
+          c.skip[1] = (uint32_t)(std::lower_bound(adj[y].begin(), adj[y].end(), (uint32_t)x) - adj[y].begin());
+          if (c.m[0] < k && c.m[1] < k) continue;
+          cursors.push_back(c);
         }
+      idx_arena.assign(cursors.size() * std::max<size_t>(k, 1), 0);
+      auto item = [&](const FastCursor& c, int dir, uint32_t i) -> uint32_t {   // i-th element of adj(u)\{v}
+        const std::vector<uint32_t>& a = adj[dir ? c.y : c.x];
+        return a[i + (i >= c.skip[dir] ? 1u : 0u)];
+      };
+      auto start_dir = [&](FastCursor& c, uint32_t* idx, int dir) {
+        c.dir = (uint8_t)dir;
+        c.valid = k <= c.m[dir];
+        for (size_t i = 0; i < k; ++i) idx[i] = (uint32_t)i;
+      };
+      auto next_comb = [&](FastCursor& c, uint32_t* idx) {
+        const uint32_t m = c.m[c.dir];
+        int i = (int)k - 1;
+        while (i >= 0 && idx[i] == m - (uint32_t)k + (uint32_t)i) --i;
+        if (i < 0) { c.valid = false; return; }
+        ++idx[i];
+        for (size_t j = (size_t)i + 1; j < k; ++j) idx[j] = idx[j - 1] + 1;
+      };
+      // move to a valid candidate that was not already asked in direction 0 (citest.h:48 makes
+      // (y,x|Z) the same test as (x,y|Z) whenever Z is also a subset of adj(x)\{y})
+      auto settle = [&](FastCursor& c, uint32_t* idx) {
+        for (;;) {
+          if (!c.valid) {
+            if (c.dir == 1) { c.done = true; return; }
+            start_dir(c, idx, 1);
+            continue;
+          }
+          if (c.dir == 1 && c.m[0] >= k) {
+            bool dup = true;
+            for (size_t i = 0; i < k && dup; ++i) dup = snap.has_undirected_edge(c.x, item(c, 1, idx[i]));
+            if (dup) { next_comb(c, idx); continue; }
+          }
+          return;
+        }
+      };
+      for (size_t pi = 0; pi < cursors.size(); ++pi) {
+        uint32_t* idx = idx_arena.data() + pi * std::max<size_t>(k, 1);
+        start_dir(cursors[pi], idx, 0);
+        settle(cursors[pi], idx);
+      }
       size_t quota = 1;
       for (;;) {
         size_t live = 0;
-        for (auto& p : pairs) live += (!p.done && !p.removed);
+        for (const auto& c : cursors) live += (!c.done && !c.removed);
         if (!live) break;
         quota = std::max<size_t>(quota, target_batch / live);
         batch.clear();
         pair_of_test.clear();
-        z_of_test.clear();
-        for (size_t pi = 0; pi < pairs.size(); ++pi) {
-          PairCursor& p = pairs[pi];
-          if (p.done || p.removed) continue;
-          for (size_t q = 0; q < quota && !p.done; ++q) {
-            p.current(z);
-            const uint32_t u = p.dir ? p.y : p.x, v = p.dir ? p.x : p.y;
-            append_test(batch, u, v, z, tmp);
+        for (size_t pi = 0; pi < cursors.size(); ++pi) {
+          FastCursor& c = cursors[pi];
+          if (c.done || c.removed) continue;
+          uint32_t* idx = idx_arena.data() + pi * std::max<size_t>(k, 1);
+          for (size_t q = 0; q < quota && !c.done; ++q) {
+            // tuple = sort(Z + {x,y}) (pc.cpp:34-37): Z is ascending already, merge x < y into it
+            uint32_t pend[2] = {c.x, c.y};
+            int np = 0;
+            for (size_t i = 0; i < k; ++i) {
+              const uint32_t z = item(c, c.dir, idx[i]);
+              while (np < 2 && pend[np] < z) batch.var_ids.push_back(pend[np++]);
+              batch.var_ids.push_back(z);
+            }
+            while (np < 2) batch.var_ids.push_back(pend[np++]);
+            batch.offsets.push_back(batch.var_ids.size());
+            batch.x.push_back(c.dir ? c.y : c.x);
+            batch.y.push_back(c.dir ? c.x : c.y);
             pair_of_test.push_back((uint32_t)pi);
-            z_of_test.push_back(z);
-            p.advance(k);
+            next_comb(c, idx);
+            settle(c, idx);
           }
         }
-        decide(batch, pair_of_test, pairs.size(), first);
+        lap(&PcStats::enumerate_ms);
+        decide(batch, pair_of_test, cursors.size(), first);
+        lap(&PcStats::evaluate_ms);
         note_batch(k);
-        for (size_t pi = 0; pi < pairs.size(); ++pi) {
+        for (size_t pi = 0; pi < cursors.size(); ++pi) {
           if (first[pi] == INT_MAX) continue;
-          PairCursor& p = pairs[pi];
-          p.removed = true;
-          g.remove_undirected_edge(p.x, p.y);                 // pc.cpp:40-42
-          sep[p.x * n + p.y] = z_of_test[(size_t)first[pi]];
-          sep[p.y * n + p.x] = sep[p.x * n + p.y];
+          FastCursor& c = cursors[pi];
+          c.removed = true;
+          g.remove_undirected_edge(c.x, c.y);                 // pc.cpp:40-42
+          std::vector<uint32_t>& sz = sep[(size_t)c.x * n + c.y];
+          sz.clear();
+          const size_t t = (size_t)first[pi];
+          for (uint64_t i = batch.offsets[t]; i < batch.offsets[t + 1]; ++i)
+            if (batch.var_ids[i] != c.x && batch.var_ids[i] != c.y) sz.push_back(batch.var_ids[i]);
+          sep[(size_t)c.y * n + c.x] = sz;
         }
+        lap(&PcStats::resolve_ms);
         quota *= 2;
       }
     } else {
@@ -252,7 +331,9 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         }
     }
   }
+  lap(&PcStats::enumerate_ms);
   orient_colliders(g, sep);
+  lap(&PcStats::resolve_ms);
   // g.apply_meeks_rules(false) is disabled in the reference (pc.cpp:84)
   return g.to_pdag();
 }

@@ -18,6 +18,7 @@ namespace obn {
 struct PcStats {
   std::vector<uint64_t> tests_per_depth;   // CI tests evaluated (after de-duplication)
   std::vector<uint64_t> batches_per_depth;
+  double enumerate_ms = 0, evaluate_ms = 0, resolve_ms = 0;   // host wall time of the three driver phases
   bool record = false;                     // keep every evaluated test in `recorded`
   TupleBatch recorded;
   uint64_t total_tests() const {

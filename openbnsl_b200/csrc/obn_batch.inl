@@ -74,6 +74,7 @@ static int run_batch(BatchSpec& S) {
   if ((S.mode == MODE_CI) && (!S.role_a || !S.role_b)) return fail(OBN_ERR_INVALID, "x or y is NULL");
   if ((S.mode == MODE_BDEU_ONE) && !S.role_a) return fail(OBN_ERR_INVALID, "child is NULL");
   OBN_CUDA(cudaSetDevice(c->device));
+  const auto t_begin = std::chrono::steady_clock::now();
 
   // ---- validate + classify --------------------------------------------------
   const size_t budget = c->smem_optin > 4096 ? c->smem_optin - 2048 : 46 * 1024;
@@ -304,6 +305,7 @@ static int run_batch(BatchSpec& S) {
     if (int rc = c->d_scratch.reserve(max_scratch_ints * 4, true)) return rc;
   if (int rc = c->d_tickets.reserve(n * 4, true)) return rc;
 
+  const auto t_packed = std::chrono::steady_clock::now();
   OBN_CUDA(cudaMemcpyAsync(c->d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
 
   // ---- launch ------------------------------------------------------------------
@@ -399,6 +401,9 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
   if (out_bytes) OBN_CUDA(cudaMemcpyAsync(c->h_out.p, dout, out_bytes, cudaMemcpyDeviceToHost, c->stream));
   OBN_CUDA(cudaStreamSynchronize(c->stream));
+  const auto t_synced = std::chrono::steady_clock::now();
+  c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
+  c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(t_synced - t_packed).count();
   const unsigned char* hout = c->h_out.as<unsigned char>();
   if (S.mode == MODE_CI) {
     if (S.stat) memcpy(S.stat, hout, n * 8);

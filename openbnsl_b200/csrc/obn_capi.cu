@@ -1,6 +1,7 @@
 // obn_capi.cu -- the extern "C" layer (include/openbnsl_b200.h).  This is the
 // translation unit that takes the place of the reference's src/template_cuda.cu.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
