@@ -71,6 +71,11 @@ OBN_API int obn_dataset_upload(obn_ctx* ctx, const uint8_t* col_major,
                                size_t n_vars, size_t n_rows, size_t row_stride,
                                const uint32_t* cards, obn_dataset** out);
 OBN_API void obn_dataset_destroy(obn_dataset* ds);
+/* Page-lock / unlock a caller-owned host buffer (e.g. the column-major matrix a
+ * DataframeWrapper keeps, dataframe_wrapper.h:42) so that obn_dataset_upload
+ * runs at full PCIe rate.  Optional. */
+OBN_API int obn_host_pin(obn_ctx* ctx, const void* p, size_t bytes);
+OBN_API int obn_host_unpin(obn_ctx* ctx, const void* p);
 OBN_API size_t obn_dataset_n_vars(const obn_dataset* ds);
 OBN_API size_t obn_dataset_n_rows(const obn_dataset* ds);
 

@@ -22,7 +22,7 @@ CI_CHI2, CI_G2 = 0, 1
 
 EXPORTS = [
     "obn_last_error", "obn_version", "obn_ctx_create", "obn_ctx_destroy", "obn_ctx_stream",
-    "obn_dataset_upload", "obn_dataset_destroy", "obn_dataset_n_vars", "obn_dataset_n_rows",
+    "obn_dataset_upload", "obn_dataset_destroy", "obn_host_pin", "obn_host_unpin", "obn_dataset_n_vars", "obn_dataset_n_rows",
     "obn_count_tables", "obn_bdeu_scores", "obn_bdeu_subset_scores", "obn_ci_tests",
     "obn_profile_enable", "obn_profile_read",
 ]
@@ -57,6 +57,8 @@ def load():
     L.obn_ctx_stream.argtypes = [vp]
     L.obn_ctx_stream.restype = vp
     L.obn_dataset_upload.argtypes = [vp, u8p, C.c_size_t, C.c_size_t, C.c_size_t, u32p, C.POINTER(vp)]
+    L.obn_host_pin.argtypes = [vp, vp, C.c_size_t]
+    L.obn_host_unpin.argtypes = [vp, vp]
     L.obn_dataset_destroy.argtypes = [vp]
     L.obn_dataset_destroy.restype = None
     L.obn_dataset_n_vars.argtypes = [vp]

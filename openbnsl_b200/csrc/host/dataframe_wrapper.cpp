@@ -155,8 +155,15 @@ std::vector<std::vector<dtype>> DataframeWrapper::data_row_major() const {
   return out;
 }
 
+DataframeWrapper::~DataframeWrapper() {
+  dev_.reset();
+  if (pinned_) obn_host_unpin(Engine::instance().ctx(), colmajor.data());
+}
+
 obn_dataset* DataframeWrapper::device() const {
   if (!dev_) {
+    if (!pinned_ && !colmajor.empty())     // best effort: an unpinned upload is only slower
+      pinned_ = obn_host_pin(Engine::instance().ctx(), colmajor.data(), colmajor.size()) == OBN_OK;
     std::vector<uint32_t> cards(num_of_values.begin(), num_of_values.end());
     dev_.reset(new DeviceDataset(colmajor.data(), num_of_vars, num_of_datapoints, num_of_datapoints, cards.data()));
   }

@@ -44,9 +44,13 @@ struct DataframeWrapper {
   // device residency (lazy; throws if no GPU is usable -- no CPU fallback)
   obn_dataset* device() const;
   void release_device() const { dev_.reset(); }
+  ~DataframeWrapper();
+  DataframeWrapper(const DataframeWrapper&) = delete;
+  DataframeWrapper& operator=(const DataframeWrapper&) = delete;
 
  private:
   mutable std::unique_ptr<DeviceDataset> dev_;
+  mutable bool pinned_ = false;   // colmajor is page-locked (obn_host_pin) from the first upload on
 };
 
 struct ContingencyTable {

@@ -312,7 +312,7 @@ static int run_batch(BatchSpec& S) {
   unsigned char* din = c->d_in.as<unsigned char>();
   unsigned char* dout = c->d_out.as<unsigned char>();
   BatchArgs a{};
-  a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows; a.cards = ds->cards_dev;
+  a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows;
   a.desc = reinterpret_cast<const uint32_t*>(din + o_var);
   a.mode = S.mode; a.kind = S.kind; a.ess = S.ess;
   if (exact) {

@@ -55,6 +55,7 @@ void obn_ctx_destroy(obn_ctx* c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_lut, &c->d_scratch, &c->d_tickets}) b->release();
+  if (c->ds_cache) cudaFree(c->ds_cache);
   c->h_in.release();
   c->h_out.release();
   for (auto& pr : c->ev_pool) {
@@ -94,38 +95,69 @@ int obn_dataset_upload(obn_ctx* c, const uint8_t* col_major, size_t n_vars, size
   if (d->stride == 0) d->stride = 128;
   d->cards.assign(cards, cards + n_vars);
   const size_t bytes = std::max<size_t>(d->stride * n_vars, 128);
-  cudaError_t e = cudaMalloc((void**)&d->data, bytes);
-  if (e != cudaSuccess) {
-    delete d;
-    return fail(OBN_ERR_OOM, "cudaMalloc(%zu) for the dataset failed: %s", bytes, cudaGetErrorString(e));
+  if (c->ds_cache && c->ds_cache_bytes >= bytes) {       // reuse the buffer of the last destroyed dataset
+    d->data = c->ds_cache;
+    d->capacity = c->ds_cache_bytes;
+    c->ds_cache = nullptr;
+    c->ds_cache_bytes = 0;
+  } else {
+    cudaError_t e = cudaMalloc((void**)&d->data, bytes);
+    if (e != cudaSuccess) {
+      delete d;
+      return fail(OBN_ERR_OOM, "cudaMalloc(%zu) for the dataset failed: %s", bytes, cudaGetErrorString(e));
+    }
+    d->capacity = bytes;
   }
-  e = cudaMalloc((void**)&d->cards_dev, std::max<size_t>(n_vars, 1) * sizeof(uint32_t));
-  if (e != cudaSuccess) {
-    cudaFree(d->data);
-    delete d;
-    return fail(OBN_ERR_OOM, "cudaMalloc for cards failed: %s", cudaGetErrorString(e));
-  }
-  // padding bytes are zero so that speculative vector reads stay in range
-  OBN_CUDA(cudaMemsetAsync(d->data, 0, bytes, c->stream));
-  if (n_vars && n_rows)
+  // padding bytes are zero: rows n_rows .. stride of every column count into cell 0 and are
+  // subtracted again by the kernel; vector reads never leave the column
+  if (n_vars == 0 || n_rows == 0) {
+    OBN_CUDA(cudaMemsetAsync(d->data, 0, bytes, c->stream));
+  } else {
+    if (d->stride > n_rows)
+      OBN_CUDA(cudaMemset2DAsync(d->data + n_rows, d->stride, 0, d->stride - n_rows, n_vars, c->stream));
     OBN_CUDA(cudaMemcpy2DAsync(d->data, d->stride, col_major, row_stride, n_rows, n_vars,
                                cudaMemcpyHostToDevice, c->stream));
-  if (n_vars)
-    OBN_CUDA(cudaMemcpyAsync(d->cards_dev, cards, n_vars * sizeof(uint32_t), cudaMemcpyHostToDevice,
-                             c->stream));
+  }
   OBN_CUDA(cudaStreamSynchronize(c->stream));
-  c->prof.h2d_bytes += (double)(n_vars * n_rows + n_vars * 4);
+  c->prof.h2d_bytes += (double)(n_vars * n_rows);
   *out = d;
   return OBN_OK;
 }
 
 void obn_dataset_destroy(obn_dataset* d) {
   if (!d) return;
-  cudaSetDevice(d->ctx->device);
-  cudaFree(d->data);
-  cudaFree(d->cards_dev);
+  obn_ctx* c = d->ctx;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  if (c->ds_cache) cudaFree(c->ds_cache);              // keep exactly one buffer for the next upload
+  c->ds_cache = d->data;
+  c->ds_cache_bytes = d->capacity;
   delete d;
 }
+
+int obn_host_pin(obn_ctx* c, const void* p, size_t bytes) {
+  if (!c || !p || !bytes) return fail(OBN_ERR_INVALID, "obn_host_pin: NULL argument");
+  OBN_CUDA(cudaSetDevice(c->device));
+  cudaError_t e = cudaHostRegister(const_cast<void*>(p), bytes, cudaHostRegisterDefault);
+  if (e == cudaErrorHostMemoryAlreadyRegistered) {
+    cudaGetLastError();
+    return OBN_OK;
+  }
+  if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "cudaHostRegister failed: %s", cudaGetErrorString(e));
+  return OBN_OK;
+}
+
+int obn_host_unpin(obn_ctx* c, const void* p) {
+  if (!c || !p) return fail(OBN_ERR_INVALID, "obn_host_unpin: NULL argument");
+  cudaSetDevice(c->device);
+  cudaError_t e = cudaHostUnregister(const_cast<void*>(p));
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(OBN_ERR_CUDA, "cudaHostUnregister failed: %s", cudaGetErrorString(e));
+  }
+  return OBN_OK;
+}
+
 size_t obn_dataset_n_vars(const obn_dataset* d) { return d ? d->n_vars : 0; }
 size_t obn_dataset_n_rows(const obn_dataset* d) { return d ? d->n_rows : 0; }
 

@@ -88,7 +88,7 @@ struct PinBuf {
 struct obn_dataset {
   obn_ctx* ctx = nullptr;
   uint8_t* data = nullptr;      // device, column-major, padded
-  uint32_t* cards_dev = nullptr;
+  size_t capacity = 0;          // bytes allocated behind `data`
   std::vector<uint32_t> cards;  // host copy
   size_t n_vars = 0, n_rows = 0, stride = 0;
 };
@@ -108,6 +108,8 @@ struct obn_ctx {
   obn::DevBuf d_scratch;   // int32, kept all-zero between launches
   obn::DevBuf d_tickets;   // uint32, kept all-zero between launches
   obn::PinBuf h_in, h_out;
+  uint8_t* ds_cache = nullptr;  // device buffer of the last destroyed dataset, reused by the next upload
+  size_t ds_cache_bytes = 0;
   // profiling
   bool profile_on = false;
   obn_profile prof = {};

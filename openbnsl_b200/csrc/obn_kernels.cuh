@@ -18,7 +18,6 @@ struct BatchArgs {
   const uint8_t* data;      // column-major codes, column v at data + v*stride
   size_t stride;            // bytes between columns (multiple of 128)
   uint32_t n_rows;
-  const uint32_t* cards;    // [n_vars]
   // batch (device copies of the CSR arrays)
   const uint32_t* desc;     // [offsets[n]]  var_id | (card-1) << 24, ascending var ids per tuple
   const uint4* hdr;         // per launch tuple: {tuple id, desc offset, #vars, #cells}
