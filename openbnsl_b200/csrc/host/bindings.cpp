@@ -8,6 +8,7 @@
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "dataframe_wrapper.hpp"
@@ -70,7 +71,7 @@ struct PyEvaluator : Evaluator {
 };
 
 PDAG run_pc(size_t n_vars, Evaluator* ev, const CITestType& test, size_t max_cond_vars, bool stable,
-            const py::object& comm, size_t target_batch, bool record = false) {
+            const py::object& comm, size_t target_batch, bool record = false, size_t shard_min_slots = 0) {
   g_last_pc_stats.record = record;
   if (std::holds_alternative<OracleGraph>(test))
     return pc_oracle(n_vars, std::get<OracleGraph>(test).graph, max_cond_vars, stable);
@@ -85,6 +86,7 @@ PDAG run_pc(size_t n_vars, Evaluator* ev, const CITestType& test, size_t max_con
     o.level = std::get<GSquare>(test).level;
   }
   if (target_batch) o.target_batch = target_batch;
+  o.shard_min_slots = shard_min_slots;
   const Comm c = make_comm(comm);
   return pc_skeleton_and_colliders(n_vars, *ev, c, o, &g_last_pc_stats);
 }
@@ -259,7 +261,13 @@ PYBIND11_MODULE(openbnsllib, m) {
            if (std::holds_alternative<OracleGraph>(test))
              return run_pc(df.num_of_vars, nullptr, test, max_cond_vars, stable, comm, target_batch);
            GpuEvaluator ev(df.device());
-           return run_pc(df.num_of_vars, &ev, test, max_cond_vars, stable, comm, target_batch, record_tests);
+           // shard a round over the GPUs only when it is worth a collective: >= 4 GB of algorithmic
+           // bytes (about 0.6 ms of one B200) unless OBN_SHARD_MIN_BYTES says otherwise
+           const char* e = std::getenv("OBN_SHARD_MIN_BYTES");
+           const double min_bytes = e && *e ? std::atof(e) : 4e9;
+           const size_t min_slots = (size_t)(min_bytes / (double)std::max<size_t>(1, df.num_of_datapoints));
+           return run_pc(df.num_of_vars, &ev, test, max_cond_vars, stable, comm, target_batch, record_tests,
+                         min_slots);
          },
          "Run PC algorithm", py::arg("df"), py::arg("ci_test_type"), py::arg("max_cond_vars"),
          py::arg("stable") = true, py::kw_only(), py::arg("comm") = py::none(), py::arg("target_batch") = 0,

@@ -347,7 +347,8 @@ PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, c
                         std::vector<int32_t>& first) {
     first.assign(n_slots, INT_MAX);
     size_t begin = 0, end = b.size();
-    if (comm.world > 1) shard_range(b.size(), comm.rank, comm.world, &begin, &end);
+    const bool sharded = comm.world > 1 && b.var_ids.size() >= opt.shard_min_slots;
+    if (sharded) shard_range(b.size(), comm.rank, comm.world, &begin, &end);
     p.resize(end - begin);
     ev.ci_pvalues(b, begin, end, opt.kind, p.data());
     for (size_t t = begin; t < end; ++t)
@@ -355,7 +356,7 @@ PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, c
         int32_t& f = first[pair_of_test[t]];
         if ((int32_t)t < f) f = (int32_t)t;
       }
-    if (comm.world > 1) comm.allreduce_min_i32(first.data(), first.size());
+    if (sharded) comm.allreduce_min_i32(first.data(), first.size());
   };
   return run_pc(n_vars, opt.max_cond_vars, opt.stable, opt.target_batch, decide, stats);
 }

@@ -37,6 +37,10 @@ struct PcOptions {
   int kind = OBN_CI_G2;
   double level = 0.05;
   size_t target_batch = 8192;     // tests per round the driver aims for
+  // multi-GPU: a round is sharded over ranks (+ one all-reduce) only when it holds at least this
+  // many variable slots (sum of tuple widths); smaller rounds are evaluated redundantly by every
+  // rank, which costs less than the collective's latency and needs no exchange at all
+  size_t shard_min_slots = 0;
 };
 
 PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, const PcOptions& opt,

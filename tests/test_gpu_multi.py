@@ -1,0 +1,76 @@
+"""Two-GPU NCCL test of the sharded drivers (skipped on a one-GPU box).
+
+Each rank owns one GPU, the dataset is replicated, every PC round / lattice
+level is sharded over the ranks (OBN_SHARD_MIN_BYTES=0 forces sharding even for
+small rounds) and the learned graphs must equal the golden ones produced by the
+unmodified reference."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys, json
+sys.path.insert(0, %(root)r); sys.path.insert(0, os.path.join(%(root)r, "tests"))
+import torch, torch.distributed as dist
+rank = int(os.environ["RANK"]); local = int(os.environ["LOCAL_RANK"])
+os.environ["OBN_DEVICE"] = str(local)
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+import openbnsl_b200
+from openbnsl_b200.dist import TorchComm
+from helpers import load_golden, pdag_to_adj
+L = openbnsl_b200.openbnsllib
+comm = TorchComm()
+ok = True
+g, net, codes, cards = load_golden("alarm_3k_s1")
+df = L.base.DataframeWrapper.from_codes(codes, net.names, [int(c) for c in cards])
+for e in g["pc"]:
+    if not e["stable"]:
+        continue
+    T = L.citest.ChiSquare(e["level"]) if e["kind"] == 0 else L.citest.GSquare(e["level"])
+    got = L.structure_learning.pc(df, T, e["max_cond_vars"], True, comm=comm)
+    ok &= pdag_to_adj(got, net.n).tolist() == e["adj"]
+g, net, codes, cards = load_golden("asia_10k_s0")
+df = L.base.DataframeWrapper.from_codes(codes, net.names, [int(c) for c in cards])
+for e in g["exhaustive_search"]:
+    got = L.structure_learning.exhaustive_search(df, L.score.BDeu(e["ess"]), e["max_parents"], comm=comm)
+    ok &= pdag_to_adj(got, net.n).tolist() == e["adj"]
+t = torch.tensor([int(ok), comm.n_collectives], device="cuda")
+dist.all_reduce(t, op=dist.ReduceOp.MIN)
+if rank == 0:
+    print("MULTI_GPU_RESULT", json.dumps({"ok": bool(t[0].item()), "collectives": int(t[1].item())}))
+dist.destroy_process_group()
+'''
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.timeout(600)
+def test_two_gpu_pc_and_es_match_golden(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER % {"root": ROOT})
+    env = dict(os.environ, OBN_SHARD_MIN_BYTES="0")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)],
+                       capture_output=True, text=True, env=env, timeout=540)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("MULTI_GPU_RESULT")]
+    assert line, r.stdout[-2000:]
+    import json
+    res = json.loads(line[0].split(" ", 1)[1])
+    assert res["ok"] and res["collectives"] > 0
