@@ -1,0 +1,120 @@
+#!/usr/bin/env python
+"""run_configs.py -- the five BASELINE.json configurations on one B200.
+
+Prints one JSON line per configuration: learn time, CI tests/s or local
+scores/s, and the counting kernel's algorithmic GB/s (CUDA events inside the
+library) as a fraction of the measured HBM peak.  C3's full lattice (2^24
+tables x 1M rows) is not run to completion on one GPU; its first levels
+(max_parents = 3 and 5) are.
+
+usage: python benchmarks/run_configs.py [c1 c2 c3 c4 c5]
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import openbnsl_b200  # noqa: E402
+from openbnsl_b200 import networks as nw  # noqa: E402
+
+L = openbnsl_b200.openbnsllib
+
+
+def peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
+def frame(net, n_rows, seed):
+    t0 = time.perf_counter()
+    codes = net.sample(n_rows, seed)
+    cards = []
+    for v in range(net.n):                     # codes must be ranks of OBSERVED states
+        u = np.unique(codes[:, v])
+        if len(u) != int(u.max()) + 1:
+            lut = np.zeros(256, dtype=np.uint8)
+            lut[u] = np.arange(len(u), dtype=np.uint8)
+            codes[:, v] = lut[codes[:, v]]
+        cards.append(len(u))
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+    return df, cards, time.perf_counter() - t0
+
+
+def report(name, what, units, unit_name, secs, prof, extra=None):
+    k_s = prof["count_kernel_ms"] * 1e-3
+    gbs = prof["algorithmic_bytes"] / k_s / 1e9 if k_s > 0 else 0.0
+    line = {"config": name, "what": what, "learn_time_s": secs, unit_name: units, unit_name + "_per_s": units / secs,
+            "kernel_ms": prof["count_kernel_ms"], "algorithmic_GB": prof["algorithmic_bytes"] / 1e9,
+            "kernel_algorithmic_GBps": gbs, "hbm_peak_GBps": peak(), "roofline_frac": gbs / peak(),
+            "launches": int(prof["count_launches"]), "host_prep_ms": prof["host_prep_ms"],
+            "host_wait_ms": prof["host_wait_ms"]}
+    if extra:
+        line.update(extra)
+    print(json.dumps(line), flush=True)
+
+
+def run_pc(name, net, n_rows, test, depth, what, reps=1):
+    df, cards, t_gen = frame(net, n_rows, 0)
+    L.profile_enable(True)
+    df.to_device()
+    L.structure_learning.pc(df, test, min(depth, 1), True)          # warm-up (allocations, first launches)
+    L.profile_read(True)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        g = L.structure_learning.pc(df, test, depth, True)
+    secs = (time.perf_counter() - t0) / reps
+    prof = L.profile_read(True)
+    for key in ("count_kernel_ms", "algorithmic_bytes", "host_prep_ms", "host_wait_ms", "count_launches"):
+        prof[key] = prof[key] / reps
+    st = L.structure_learning.last_pc_stats()
+    n_edges = sum(1 for v in range(net.n) for p in range(net.n) if g.has_edge(p, v))
+    report(name, what, st["total_tests"], "ci_tests", secs, prof,
+           {"tests_per_depth": [int(x) for x in st["tests_per_depth"]], "n_vars": net.n, "n_rows": n_rows,
+            "max_card": int(max(cards)), "pdag_arcs": n_edges, "enumerate_ms": st["enumerate_ms"],
+            "evaluate_ms": st["evaluate_ms"], "data_gen_s": t_gen})
+
+
+def run_es(name, net, n_rows, max_parents, what, exact=2):
+    df, cards, t_gen = frame(net, n_rows, 0)
+    L.profile_enable(True)
+    df.to_device()
+    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 0, exact_order=exact)
+    L.profile_read(True)
+    t0 = time.perf_counter()
+    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=exact)
+    secs = time.perf_counter() - t0
+    prof = L.profile_read(True)
+    st = L.structure_learning.last_es_stats()
+    report(name, what, st["scores"], "local_scores", secs, prof,
+           {"tables": int(st["tables"]), "n_vars": net.n, "n_rows": n_rows, "max_parents": max_parents,
+            "exact_order": exact, "data_gen_s": t_gen})
+
+
+def main():
+    which = [a.lower() for a in sys.argv[1:]] or ["c1", "c2", "c3", "c4", "c5"]
+    if "c1" in which:
+        run_es("C1", nw.asia(), 10_000, 7, "exhaustive search BDeu, Asia, 8 vars, 10k rows, full lattice")
+        run_es("C1", nw.asia(), 10_000, 3, "exhaustive search BDeu, Asia, 8 vars, 10k rows, max_parents=3")
+    if "c2" in which:
+        run_pc("C2", nw.alarm(), 100_000, L.citest.GSquare(0.05), 4,
+               "PC-stable G2, Alarm structure, 37 vars, 100k rows, depth<=4", reps=20)
+    if "c3" in which:
+        net = nw.random_binary(24)
+        run_es("C3", net, 1_000_000, 3, "exhaustive search BDeu, 24 binary vars, 1M rows, max_parents=3 (12 951 tables)", exact=0)
+        run_es("C3", net, 1_000_000, 5, "exhaustive search BDeu, 24 binary vars, 1M rows, max_parents=5 (190 051 tables)", exact=0)
+    if "c4" in which:
+        run_pc("C4", nw.hepar2_like(), 1_000_000, L.citest.GSquare(0.05), 4,
+               "PC-stable G2, Hepar2-like, 70 vars, 1M rows, depth<=4")
+    if "c5" in which:
+        run_pc("C5", nw.munin1_like(), 1_000_000, L.citest.ChiSquare(0.05), 3,
+               "PC-stable chi2, Munin1-like, 186 vars, cards<=21, 1M rows, depth<=3")
+
+
+if __name__ == "__main__":
+    main()
