@@ -122,6 +122,31 @@ OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
                          int kind, double* stat_out, uint64_t* dof_out,
                          double* p_out);
 
+/* ---- exhaustive search on the device --------------------------------------
+ * Level-synchronous Silander-Myllymaki DP with the reference's tie-breaking
+ * (src/structure_learning/exhaustive_search.cpp:47-148).  The DP tables
+ * (best_ls_tbl: n * 2^n (score, parent set); best_gs_tbl / best_ch_tbl: 2^n,
+ * :33-40) live in HBM for the whole search.  Per lattice level the caller
+ *   1. obn_es_level_begin   hands over the level's subsets (bit masks, all of
+ *                           size k, in the reference's Gosper order, :51,:129),
+ *   2. obn_es_level_scores  has the |W| local scores of the subsets
+ *                           [begin, end) computed (one table per subset, :55-72)
+ *                           into the level buffer -- a multi-GPU caller gives
+ *                           each rank one range and all-gathers the buffer
+ *                           (obn_es_level_buffer) in place,
+ *   3. obn_es_level_dp      runs :59-116 for every subset of the level.
+ * obn_es_finish backtracks (:133-148): parent_masks[v] = bit mask of v's parents. */
+typedef struct obn_es obn_es;
+OBN_API int obn_es_begin(obn_ctx* ctx, const obn_dataset* ds, double ess, size_t max_parents,
+                         int exact_order, obn_es** out);
+OBN_API int obn_es_level_begin(obn_es* es, const uint64_t* masks, size_t n_subsets, int k,
+                               size_t buffer_subsets);
+OBN_API int obn_es_level_scores(obn_es* es, size_t begin, size_t end);
+OBN_API int obn_es_level_buffer(obn_es* es, void** scores_dev, size_t* n_doubles);
+OBN_API int obn_es_level_dp(obn_es* es);
+OBN_API int obn_es_finish(obn_es* es, uint64_t* parent_masks, double* best_score);
+OBN_API void obn_es_end(obn_es* es);
+
 /* ---- instrumentation -----------------------------------------------------
  * Device time (CUDA events on the ctx stream) and launch count of the
  * counting kernels since the last reset; used by bench.py for the roofline. */

@@ -36,6 +36,10 @@ Comm make_comm(const py::object& o) {
   if (c.world < 1 || c.rank < 0 || c.rank >= c.world) throw std::invalid_argument("bad comm rank/world");
   py::object red = o.attr("allreduce_min_i32"), gat = o.attr("allgather");
   c.allreduce_min_i32 = [red](int32_t* p, size_t n) { red(view<int32_t>(p, n)); };
+  if (py::hasattr(o, "allgather_dev")) {
+    py::object gd = o.attr("allgather_dev");
+    c.allgather_dev = [gd](uintptr_t p, size_t bytes) { gd((size_t)p, bytes); };
+  }
   c.allgather = [gat, w = c.world](const void* s, void* r, size_t bytes) {
     gat(view<uint8_t>(static_cast<const uint8_t*>(s), bytes), view<uint8_t>(static_cast<uint8_t*>(r), bytes * w));
   };
@@ -245,16 +249,28 @@ PYBIND11_MODULE(openbnsllib, m) {
   auto sl = m.def_submodule("structure_learning", "Structure learning submodule");
   sl.def("exhaustive_search",
          [](const DataframeWrapper& df, const ScoreType& st, size_t max_parents, bool /*is_deterministic*/,
-            int exact_order, const py::object& comm) {
+            int exact_order, const py::object& comm, bool host_dp) {
            if (!std::holds_alternative<BDeu>(st)) throw std::invalid_argument("Unsupported score type.");
            if (df.num_of_vars && max_parents > df.num_of_vars - 1)
              throw std::invalid_argument("max_parents must be in [0, num_of_vars-1]");
-           GpuEvaluator ev(df.device());
-           return run_es(df.num_of_vars, &ev, st, max_parents, exact_order, comm);
+           if (host_dp) {                 // scores on the GPU, DP tables on the host (A/B and debugging)
+             GpuEvaluator ev(df.device());
+             return run_es(df.num_of_vars, &ev, st, max_parents, exact_order, comm);
+           }
+           EsOptions o;
+           o.ess = std::get<BDeu>(st).ess;
+           o.max_parents = max_parents;
+           o.exact_order = exact_order;
+           const char* e = std::getenv("OBN_SHARD_MIN_BYTES");
+           o.shard_min_bytes = e && *e ? std::atof(e) : 4e9;
+           const Comm c = make_comm(comm);
+           if (c.world > 1 && !c.allgather_dev) throw std::invalid_argument("comm lacks allgather_dev");
+           g_last_es_stats = EsStats{};
+           return exhaustive_search_device(df.device(), c, o, &g_last_es_stats);
          },
          "Run exhaustive search algorithm", py::arg("df"), py::arg("score_type"), py::arg("max_parents"),
          py::arg("is_deterministic") = false, py::kw_only(), py::arg("exact_order") = 2,
-         py::arg("comm") = py::none());
+         py::arg("comm") = py::none(), py::arg("host_dp") = false);
   sl.def("pc",
          [](const DataframeWrapper& df, const CITestType& test, size_t max_cond_vars, bool stable,
             const py::object& comm, size_t target_batch, bool record_tests) {
@@ -299,6 +315,10 @@ PYBIND11_MODULE(openbnsllib, m) {
     d["tables"] = g_last_es_stats.tables;
     d["scores"] = g_last_es_stats.scores;
     d["best_score"] = g_last_es_stats.best_score;
+    d["enumerate_ms"] = g_last_es_stats.enumerate_ms;
+    d["score_ms"] = g_last_es_stats.score_ms;
+    d["gather_ms"] = g_last_es_stats.gather_ms;
+    d["dp_ms"] = g_last_es_stats.dp_ms;
     return d;
   });
 

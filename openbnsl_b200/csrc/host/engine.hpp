@@ -99,6 +99,9 @@ struct Comm {
   std::function<void(int32_t*, size_t)> allreduce_min_i32;
   // gather `bytes` bytes from every rank into recv (world * bytes), rank order
   std::function<void(const void*, void*, size_t)> allgather;
+  // in-place all-gather of a DEVICE buffer of world * bytes_per_rank bytes: rank r contributes
+  // the r-th slice (NCCL over NVLink; the data never visits the host)
+  std::function<void(uintptr_t, size_t)> allgather_dev;
 };
 
 // contiguous shard [begin, end) of n items for rank r of w

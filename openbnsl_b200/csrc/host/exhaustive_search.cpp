@@ -4,6 +4,7 @@
 // tuples whose |W| local scores each come from one table (the reference's own
 // sharing, :55-72).  Multi-GPU: a level's subsets are sharded over ranks in
 // Gosper order and the scores are all-gathered once per level.
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <limits>
@@ -125,6 +126,69 @@ PDAG exhaustive_search_driver(size_t n_vars, Evaluator& ev, const Comm& comm, co
     W = pa;
   }
   if (stats) stats->best_score = best_gs[n_combs - 1];
+  return g;
+}
+
+PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions& opt, EsStats* stats) {
+  const size_t n = obn_dataset_n_vars(ds);
+  if (n == 0) return PDAG(0);
+  obn_ctx* ctx = Engine::instance().ctx();
+  obn_es* es = nullptr;
+  check(obn_es_begin(ctx, ds, opt.ess, opt.max_parents, opt.exact_order, &es));
+  struct Guard {
+    obn_es* e;
+    ~Guard() { obn_es_end(e); }
+  } guard{es};
+  using clk = std::chrono::steady_clock;
+  auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+  const size_t n_rows = obn_dataset_n_rows(ds);
+  const size_t max_varset = opt.max_parents + 1;
+  std::vector<uint64_t> masks;
+  for (size_t size = 0; size <= n; ++size) {                        // exhaustive_search.cpp:47
+    const auto t0 = clk::now();
+    masks.clear();
+    uint64_t W = ((uint64_t)1 << size) - 1;                          // :51
+    do masks.push_back(W); while (next_combmask(W, (int)n));         // :129 (Gosper order)
+    const size_t T = masks.size();
+    const bool calc_ls = size <= max_varset && size > 0;             // :48
+    const bool sharded = comm.world > 1 && calc_ls &&
+                         (double)T * (double)size * (double)n_rows >= opt.shard_min_bytes && T >= (size_t)comm.world;
+    const size_t chunk = sharded ? (T + comm.world - 1) / comm.world : T;
+    check(obn_es_level_begin(es, masks.data(), T, (int)size, sharded ? chunk * comm.world : T));
+    const auto t1 = clk::now();
+    if (calc_ls) {
+      if (sharded) check(obn_es_level_scores(es, std::min(T, chunk * comm.rank), std::min(T, chunk * (comm.rank + 1))));
+      else check(obn_es_level_scores(es, 0, T));
+    }
+    const auto t2 = clk::now();
+    if (sharded) {
+      void* p = nullptr;
+      size_t nd = 0;
+      check(obn_es_level_buffer(es, &p, &nd));
+      comm.allgather_dev((uintptr_t)p, chunk * size * sizeof(double));
+    }
+    const auto t3 = clk::now();
+    check(obn_es_level_dp(es));                                       // :59-116
+    const auto t4 = clk::now();
+    if (stats) {
+      if (size <= max_varset) {
+        stats->tables += T;
+        stats->scores += T * size;
+      }
+      stats->enumerate_ms += ms(t0, t1);
+      stats->score_ms += ms(t1, t2);
+      stats->gather_ms += ms(t2, t3);
+      stats->dp_ms += ms(t3, t4);
+    }
+  }
+  std::vector<uint64_t> pm(n, 0);
+  double best = 0;
+  check(obn_es_finish(es, pm.data(), &best));                         // :133-148
+  PDAG g(n);
+  for (size_t v = 0; v < n; ++v)
+    for (size_t j = 0; j < n; ++j)
+      if ((pm[v] >> j) & 1u) g.add_edge(j, v);
+  if (stats) stats->best_score = best;
   return g;
 }
 

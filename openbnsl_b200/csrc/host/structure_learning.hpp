@@ -53,13 +53,21 @@ struct EsOptions {
   double ess = 1.0;
   size_t max_parents = 0;
   int exact_order = 2;            // 0 fast, 1 exact (error if tables do not fit), 2 auto
+  double shard_min_bytes = 0;     // multi-GPU: shard a level only if it has this many algorithmic bytes
 };
 struct EsStats {
   uint64_t tables = 0, scores = 0;
   double best_score = 0.0;
+  double enumerate_ms = 0, score_ms = 0, gather_ms = 0, dp_ms = 0;
 };
 
 PDAG exhaustive_search_driver(size_t n_vars, Evaluator& ev, const Comm& comm, const EsOptions& opt,
                               EsStats* stats);
+
+// The product path: scores AND the DP tables stay in HBM (obn_es_* in the C ABI); the host only
+// enumerates the subsets of each level and backtracks at the end.  Multi-GPU: the level's subsets
+// are split into `world` equal ranges, each rank scores its range, one in-place all-gather of the
+// level's score buffer over NVLink, then every rank runs the (cheap) DP for the whole level.
+PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions& opt, EsStats* stats);
 
 }  // namespace obn

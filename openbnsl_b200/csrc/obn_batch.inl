@@ -22,6 +22,7 @@ struct BatchSpec {
   uint64_t* dof = nullptr;
   double* p = nullptr;
   double* scores = nullptr;
+  double* scores_dev = nullptr;   // BDEU_ALL: leave the scores on the device at this address (no D2H)
   int32_t* counts = nullptr;
   const uint64_t* counts_off = nullptr;
 };
@@ -49,11 +50,13 @@ static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, siz
     if (e != cudaSuccess) return e;
     configured = smem;
   }
+  (void)cudaGetLastError();      // a launch reports only its own error, not a stale one
   count_kernel<KW, TIER, SCALE4><<<grid, nthr, smem, s>>>(a);
   return cudaGetLastError();
 }
 
 static const size_t kScratchMaxBytes = (size_t)8 << 30;
+static const size_t kLutMaxBytes = (size_t)2 << 30;
 
 static int env_int(const char* name, int dflt) {
   const char* v = std::getenv(name);
@@ -118,53 +121,52 @@ static int run_batch(BatchSpec& S) {
     alg_bytes += (double)k * (double)ds->n_rows;
   }
 
-  // ---- exact-order BDeu: host-libm lgamma tables ----------------------------
+  // ---- exact-order BDeu: host-libm lgamma tables, cached in the ctx across calls ------------
   const bool bdeu = (S.mode == MODE_BDEU_ONE || S.mode == MODE_BDEU_ALL);
   bool exact = bdeu && S.exact;   // 1 = required, 2 = if the tables fit
   std::vector<uint32_t> lut_ijk, lut_ij;
-  size_t lut_stride = 0, n_luts = 0;
-  std::vector<double> avals;
+  const size_t lut_stride = ds->n_rows + 1;
   if (exact) {
-    std::map<uint64_t, uint32_t> ids;
+    LutCache& lc = c->lut;
+    if (lc.stride != lut_stride) lc.clear();                 // another sample count: other tables
+    lc.stride = lut_stride;
+    std::vector<double> pending;
+    std::map<uint64_t, uint32_t> pending_ids;
     auto id_of = [&](double a) {
       uint64_t bits;
       memcpy(&bits, &a, 8);
-      auto it = ids.find(bits);
-      if (it != ids.end()) return it->second;
-      const uint32_t id = (uint32_t)avals.size();
-      ids[bits] = id;
-      avals.push_back(a);
+      auto it = lc.ids.find(bits);
+      if (it != lc.ids.end()) return it->second;
+      auto jt = pending_ids.find(bits);
+      if (jt != pending_ids.end()) return jt->second;
+      const uint32_t id = (uint32_t)(lc.rows + pending.size());
+      pending_ids[bits] = id;
+      pending.push_back(a);
       return id;
     };
     lut_ijk.resize(n);
     lut_ij.assign(total_vars, 0);
+    uint32_t last_cells = 0, last_ijk = 0;
     for (size_t t = 0; t < n; ++t) {
       const double a_ijk = S.ess / (double)(size_t)cells[t];      // local_score.h:41
-      lut_ijk[t] = id_of(a_ijk);
-      for (uint64_t i = S.offsets[t]; i < S.offsets[t + 1]; ++i)
-        lut_ij[i] = id_of(a_ijk * (double)(size_t)ds->cards[S.var_ids[i]]);   // :45
+      if (cells[t] != last_cells) { last_ijk = id_of(a_ijk); last_cells = cells[t]; }
+      lut_ijk[t] = last_ijk;
+      uint32_t last_card = 0, last_id = 0;
+      for (uint64_t i = S.offsets[t]; i < S.offsets[t + 1]; ++i) {
+        const uint32_t cd = ds->cards[S.var_ids[i]];
+        if (cd != last_card) { last_id = id_of(a_ijk * (double)(size_t)cd); last_card = cd; }   // :45
+        lut_ij[i] = last_id;
+      }
     }
-    n_luts = avals.size();
-    lut_stride = ds->n_rows + 1;
-    const size_t bytes = n_luts * lut_stride * sizeof(double);
-    if (bytes > ((size_t)2 << 30)) {
+    const size_t want_rows = lc.rows + pending.size();
+    if (want_rows * lut_stride * sizeof(double) > kLutMaxBytes) {
       if (S.exact != 2)
-        return fail(OBN_ERR_UNSUPPORTED, "exact_order needs %zu lgamma tables of %zu entries", n_luts, lut_stride);
+        return fail(OBN_ERR_UNSUPPORTED, "exact_order needs %zu lgamma tables of %zu entries", want_rows, lut_stride);
       exact = false;
+    } else if (!pending.empty()) {
+      if (int rc = lc.append(c, pending)) return rc;
+      for (auto& kv : pending_ids) lc.ids[kv.first] = kv.second;
     }
-  }
-  if (exact) {
-    const size_t bytes = n_luts * lut_stride * sizeof(double);
-    std::vector<double> lut(n_luts * lut_stride);
-    for (size_t j = 0; j < n_luts; ++j) {
-      const double a = avals[j];
-      const double lg_a = std::lgamma(a);
-      double* row = lut.data() + j * lut_stride;
-      for (size_t m = 0; m < lut_stride; ++m) row[m] = std::lgamma((double)m + a) - lg_a;   // :53,:59
-    }
-    if (int rc = c->d_lut.reserve(bytes)) return rc;
-    OBN_CUDA(cudaMemcpyAsync(c->d_lut.p, lut.data(), bytes, cudaMemcpyHostToDevice, c->stream));
-    OBN_CUDA(cudaStreamSynchronize(c->stream));
   }
 
   // ---- packed input buffer ---------------------------------------------------
@@ -220,7 +222,7 @@ static int run_batch(BatchSpec& S) {
   size_t out_bytes = 0, counts_total = 0;
   if (S.mode == MODE_CI) out_bytes = n * 24;
   else if (S.mode == MODE_BDEU_ONE) out_bytes = n * 8;
-  else if (S.mode == MODE_BDEU_ALL) out_bytes = total_vars * 8;
+  else if (S.mode == MODE_BDEU_ALL) out_bytes = S.scores_dev ? 0 : total_vars * 8;
   else {
     uint64_t* coff = reinterpret_cast<uint64_t*>(hin + o_coff);
     for (size_t t = 0; t < n; ++t) { coff[t] = counts_total; counts_total += cells[t]; }
@@ -316,7 +318,7 @@ static int run_batch(BatchSpec& S) {
   a.desc = reinterpret_cast<const uint32_t*>(din + o_var);
   a.mode = S.mode; a.kind = S.kind; a.ess = S.ess;
   if (exact) {
-    a.lut = c->d_lut.as<double>(); a.lut_stride = lut_stride;
+    a.lut = c->lut.dev; a.lut_stride = lut_stride;
     a.lut_ijk = reinterpret_cast<const uint32_t*>(din + o_lijk);
     a.lut_ij = reinterpret_cast<const uint32_t*>(din + o_lij);
   }
@@ -324,7 +326,7 @@ static int run_batch(BatchSpec& S) {
   unsigned long long* d_dof = reinterpret_cast<unsigned long long*>(dout + n * 8);
   double* d_p = reinterpret_cast<double*>(dout + n * 16);
   if (S.mode == MODE_CI) { a.stat = d_stat; a.dof = d_dof; a.pval = S.p ? d_p : nullptr; }
-  else if (bdeu) a.scores = reinterpret_cast<double*>(dout);
+  else if (bdeu) a.scores = S.scores_dev ? S.scores_dev : reinterpret_cast<double*>(dout);
   else { a.counts_out = reinterpret_cast<int32_t*>(dout); a.counts_off = reinterpret_cast<const uint64_t*>(din + o_coff); }
   a.scratch = c->d_scratch.as<int32_t>();
   a.tickets = c->d_tickets.as<unsigned int>();
@@ -412,7 +414,7 @@ static int run_batch(BatchSpec& S) {
   } else if (S.mode == MODE_BDEU_ONE) {
     memcpy(S.scores, hout, n * 8);
   } else if (S.mode == MODE_BDEU_ALL) {
-    if (total_vars) memcpy(S.scores, hout, total_vars * 8);
+    if (total_vars && !S.scores_dev) memcpy(S.scores, hout, total_vars * 8);
   } else {
     const int32_t* src = reinterpret_cast<const int32_t*>(hout);
     size_t o = 0;

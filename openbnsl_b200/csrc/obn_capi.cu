@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <thread>
 
 #include "obn_count_kernel.cuh"
 #include "obn_host.hpp"
@@ -14,6 +15,47 @@ namespace obn {
 thread_local std::string g_last_error;
 }
 using namespace obn;
+
+// Fill the new rows on the host (glibc lgamma, the reference's libm; threaded for long tables),
+// grow the device table if needed, and upload.
+int obn::LutCache::append(obn_ctx* c, const std::vector<double>& avals) {
+  const size_t add = avals.size();
+  std::vector<double> host(add * stride);
+  const size_t total = add * stride;
+  auto fill = [&](size_t lo, size_t hi) {
+    for (size_t q = lo; q < hi; ++q) {
+      const size_t j = q / stride, m = q - j * stride;
+      int sg;
+      const double a = avals[j];
+      host[q] = lgamma_r((double)m + a, &sg) - lgamma_r(a, &sg);      // local_score.h:53,:59
+    }
+  };
+  unsigned nt = total > (1u << 16) ? std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+  if (nt <= 1) {
+    fill(0, total);
+  } else {
+    std::vector<std::thread> th;
+    const size_t step = (total + nt - 1) / nt;
+    for (unsigned i = 0; i < nt; ++i) th.emplace_back(fill, std::min(total, i * step), std::min(total, (i + 1) * step));
+    for (auto& t : th) t.join();
+  }
+  if (rows + add > cap_rows || lut_stride_of_alloc != stride) {
+    const size_t new_cap = std::max(rows + add, cap_rows * 2);
+    double* nd = nullptr;
+    OBN_CUDA(cudaMalloc((void**)&nd, new_cap * stride * sizeof(double)));
+    if (dev && rows && lut_stride_of_alloc == stride)
+      OBN_CUDA(cudaMemcpyAsync(nd, dev, rows * stride * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+    OBN_CUDA(cudaStreamSynchronize(c->stream));
+    if (dev) cudaFree(dev);
+    dev = nd;
+    cap_rows = new_cap;
+    lut_stride_of_alloc = stride;
+  }
+  OBN_CUDA(cudaMemcpyAsync(dev + rows * stride, host.data(), total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  rows += add;
+  return OBN_OK;
+}
 
 extern "C" {
 
@@ -54,7 +96,8 @@ void obn_ctx_destroy(obn_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_lut, &c->d_scratch, &c->d_tickets}) b->release();
+  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_scratch, &c->d_tickets}) b->release();
+  c->lut.release();
   if (c->ds_cache) cudaFree(c->ds_cache);
   c->h_in.release();
   c->h_out.release();
@@ -176,3 +219,4 @@ int obn_profile_read(obn_ctx* c, obn_profile* out, int reset) {
 }  // extern "C"
 
 #include "obn_batch.inl"
+#include "obn_es.inl"

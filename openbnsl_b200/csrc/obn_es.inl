@@ -1,0 +1,202 @@
+// obn_es.inl -- exhaustive search with the DP tables resident in HBM
+// (include/openbnsl_b200.h, "exhaustive search on the device").  Included at the
+// end of obn_capi.cu, after obn_batch.inl.
+
+struct obn_es {
+  obn_ctx* c = nullptr;
+  const obn_dataset* ds = nullptr;
+  int n = 0;
+  double ess = 1.0;
+  size_t max_parents = 0;
+  int exact = 0;
+  // DP tables (device).  bl_* are indexed [parent_set_mask * n + child].
+  double* bl_score = nullptr;
+  uint32_t* bl_ps = nullptr;
+  double* best_gs = nullptr;
+  uint8_t* best_ch = nullptr;
+  // current level
+  obn::DevBuf d_masks, d_level;
+  std::vector<uint64_t> masks;
+  size_t T = 0, buffer_doubles = 0;
+  int k = 0;
+  bool calc = false;
+};
+
+namespace obn {
+
+// exhaustive_search.cpp:59-116 for one subset W per thread.  Reads only entries of the
+// previous level (parent sets of size k-2 / k-1), writes entries of this one.
+__global__ void es_dp_kernel(const unsigned long long* masks, size_t T, int k, int n, const double* scores,
+                             double* bl_score, uint32_t* bl_ps, double* best_gs, uint8_t* best_ch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  const uint32_t W = (uint32_t)masks[t];
+  double bgs = 0.0;
+  int bch = -1;
+  int ci = 0;
+  for (uint32_t m = W; m; m &= m - 1, ++ci) {
+    const int child = __ffs((int)m) - 1;
+    const uint32_t pa = W & ~(1u << child);
+    const double ls = scores ? scores[t * (size_t)k + ci] : -INFINITY;          // :65-73
+    double bls = ls;
+    uint32_t bps = pa;
+    for (uint32_t q = pa; q; q &= q - 1) {                                       // :75-87
+      const uint32_t sub = pa & ~(q & (0u - q));
+      const double s = bl_score[(size_t)sub * n + child];
+      if (s >= bls) {
+        bls = s;
+        bps = bl_ps[(size_t)sub * n + child];
+      }
+    }
+    bl_score[(size_t)pa * n + child] = bls;
+    bl_ps[(size_t)pa * n + child] = bps;
+    const double gs = best_gs[pa] + bls;                                         // :89-94
+    if (bgs >= 0 || gs > bgs) {
+      bgs = gs;
+      bch = child;
+    }
+  }
+  best_gs[W] = bgs;                                                              // :115-116
+  best_ch[W] = (uint8_t)bch;
+}
+
+}  // namespace obn
+
+extern "C" {
+
+int obn_es_begin(obn_ctx* c, const obn_dataset* ds, double ess, size_t max_parents, int exact_order, obn_es** out) {
+  if (!c || !ds || !out) return fail(OBN_ERR_INVALID, "obn_es_begin: NULL argument");
+  *out = nullptr;
+  if (ds->ctx != c) return fail(OBN_ERR_INVALID, "dataset belongs to another ctx");
+  const size_t n = ds->n_vars;
+  if (n == 0) return fail(OBN_ERR_INVALID, "exhaustive search needs at least one variable");
+  if (max_parents > n - 1) return fail(OBN_ERR_INVALID, "max_parents must be in [0, num_of_vars-1]");   // :18-19
+  if (n > 64) return fail(OBN_ERR_INVALID, "num_of_vars must be in [0, 64]");                          // :22-23
+  if (n > 28) return fail(OBN_ERR_UNSUPPORTED, "exhaustive search: the n * 2^n DP tables for n > 28 exceed HBM");
+  OBN_CUDA(cudaSetDevice(c->device));
+  obn_es* e = new obn_es();
+  e->c = c;
+  e->ds = ds;
+  e->n = (int)n;
+  e->ess = ess;
+  e->max_parents = max_parents;
+  e->exact = exact_order;
+  const size_t combs = (size_t)1 << n;
+  cudaError_t err = cudaMalloc((void**)&e->bl_score, combs * n * sizeof(double));
+  if (err == cudaSuccess) err = cudaMalloc((void**)&e->bl_ps, combs * n * sizeof(uint32_t));
+  if (err == cudaSuccess) err = cudaMalloc((void**)&e->best_gs, combs * sizeof(double));
+  if (err == cudaSuccess) err = cudaMalloc((void**)&e->best_ch, combs);
+  if (err != cudaSuccess) {
+    cudaGetLastError();
+    obn_es_end(e);
+    return fail(OBN_ERR_OOM, "exhaustive search: DP tables for %zu variables do not fit (%s)", n, cudaGetErrorString(err));
+  }
+  *out = e;
+  return OBN_OK;
+}
+
+void obn_es_end(obn_es* e) {
+  if (!e) return;
+  cudaSetDevice(e->c->device);
+  cudaStreamSynchronize(e->c->stream);
+  for (void* p : {(void*)e->bl_score, (void*)e->bl_ps, (void*)e->best_gs, (void*)e->best_ch})
+    if (p) cudaFree(p);
+  e->d_masks.release();
+  e->d_level.release();
+  delete e;
+}
+
+int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k, size_t buffer_subsets) {
+  if (!e || (!masks && n_subsets)) return fail(OBN_ERR_INVALID, "obn_es_level_begin: NULL argument");
+  if (k < 0 || k > e->n) return fail(OBN_ERR_INVALID, "subset size %d out of range", k);
+  if (buffer_subsets < n_subsets) buffer_subsets = n_subsets;
+  obn_ctx* c = e->c;
+  OBN_CUDA(cudaSetDevice(c->device));
+  e->masks.assign(masks, masks + n_subsets);
+  e->T = n_subsets;
+  e->k = k;
+  e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
+  e->buffer_doubles = buffer_subsets * (size_t)std::max(k, 1);
+  if (int rc = e->d_masks.reserve(std::max<size_t>(n_subsets * 8, 16))) return rc;
+  if (int rc = e->d_level.reserve(std::max<size_t>(e->buffer_doubles * 8, 16))) return rc;
+  if (n_subsets)
+    OBN_CUDA(cudaMemcpyAsync(e->d_masks.p, e->masks.data(), n_subsets * 8, cudaMemcpyHostToDevice, c->stream));
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  c->prof.h2d_bytes += (double)(n_subsets * 8);
+  return OBN_OK;
+}
+
+int obn_es_level_scores(obn_es* e, size_t begin, size_t end) {
+  if (!e) return fail(OBN_ERR_INVALID, "obn_es_level_scores: NULL argument");
+  if (end > e->T) end = e->T;
+  if (begin >= end || !e->calc || e->k == 0) return OBN_OK;
+  const size_t k = (size_t)e->k;
+  const size_t chunk = std::max<size_t>(1, ((size_t)1 << 21) / k);      // ~2M variable slots per batch
+  std::vector<uint32_t> var_ids;
+  std::vector<uint64_t> offsets;
+  for (size_t b = begin; b < end; b += chunk) {
+    const size_t m = std::min(chunk, end - b);
+    var_ids.resize(m * k);
+    offsets.resize(m + 1);
+    size_t o = 0;
+    for (size_t t = 0; t < m; ++t) {
+      offsets[t] = o;
+      for (uint64_t w = e->masks[b + t]; w; w &= w - 1) var_ids[o++] = (uint32_t)__builtin_ctzll(w);
+      if (o != (t + 1) * k) return fail(OBN_ERR_INVALID, "subset %zu of the level does not have %zu variables", b + t, k);
+    }
+    offsets[m] = o;
+    BatchSpec S{e->c, e->ds, var_ids.data(), offsets.data(), m, MODE_BDEU_ALL};
+    S.ess = e->ess;
+    S.exact = e->exact;
+    S.scores_dev = e->d_level.as<double>() + b * k;
+    if (int rc = run_batch(S)) return rc;
+  }
+  return OBN_OK;
+}
+
+int obn_es_level_buffer(obn_es* e, void** scores_dev, size_t* n_doubles) {
+  if (!e || !scores_dev || !n_doubles) return fail(OBN_ERR_INVALID, "obn_es_level_buffer: NULL argument");
+  *scores_dev = e->d_level.p;
+  *n_doubles = e->buffer_doubles;
+  return OBN_OK;
+}
+
+int obn_es_level_dp(obn_es* e) {
+  if (!e) return fail(OBN_ERR_INVALID, "obn_es_level_dp: NULL argument");
+  if (!e->T) return OBN_OK;
+  obn_ctx* c = e->c;
+  OBN_CUDA(cudaSetDevice(c->device));
+  const unsigned grid = (unsigned)((e->T + 127) / 128);
+  (void)cudaGetLastError();
+  es_dp_kernel<<<grid, 128, 0, c->stream>>>(e->d_masks.as<unsigned long long>(), e->T, e->k, e->n,
+                                             (e->calc && e->k) ? e->d_level.as<double>() : nullptr, e->bl_score,
+                                             e->bl_ps, e->best_gs, e->best_ch);
+  OBN_CUDA(cudaGetLastError());
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  ++c->prof.total_launches;
+  return OBN_OK;
+}
+
+int obn_es_finish(obn_es* e, uint64_t* parent_masks, double* best_score) {
+  if (!e || !parent_masks) return fail(OBN_ERR_INVALID, "obn_es_finish: NULL argument");
+  obn_ctx* c = e->c;
+  OBN_CUDA(cudaSetDevice(c->device));
+  const int n = e->n;
+  for (int v = 0; v < n; ++v) parent_masks[v] = 0;
+  uint32_t W = (uint32_t)(((uint64_t)1 << n) - 1);
+  if (best_score)
+    OBN_CUDA(cudaMemcpy(best_score, e->best_gs + W, sizeof(double), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < n; ++i) {                                                   // :133-148
+    uint8_t ch = 0;
+    OBN_CUDA(cudaMemcpy(&ch, e->best_ch + W, 1, cudaMemcpyDeviceToHost));
+    if (ch >= n) return fail(OBN_ERR_INVALID, "obn_es_finish called before every level was processed");
+    const uint32_t pa = W & ~(1u << ch);
+    uint32_t ps = 0;
+    OBN_CUDA(cudaMemcpy(&ps, e->bl_ps + (size_t)pa * n + ch, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    parent_masks[ch] = ps;
+    W = pa;
+  }
+  return OBN_OK;
+}
+
+}  // extern "C"

@@ -5,6 +5,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -85,6 +86,27 @@ struct PinBuf {
 
 }  // namespace obn
 
+namespace obn {
+// Host-libm tables lut[id][m] = lgamma(m + a) - lgamma(a), m = 0..n_rows, for the exact-order
+// BDeu epilogue (local_score.h:53,59); kept on the device across calls, keyed by the bits of a.
+struct LutCache {
+  std::map<uint64_t, uint32_t> ids;
+  size_t stride = 0, rows = 0, cap_rows = 0, lut_stride_of_alloc = 0;
+  double* dev = nullptr;
+  void clear() {
+    ids.clear();
+    rows = 0;
+  }
+  int append(obn_ctx* c, const std::vector<double>& avals);   // obn_capi.cu
+  void release() {
+    if (dev) cudaFree(dev);
+    dev = nullptr;
+    cap_rows = rows = 0;
+    ids.clear();
+  }
+};
+}  // namespace obn
+
 struct obn_dataset {
   obn_ctx* ctx = nullptr;
   uint8_t* data = nullptr;      // device, column-major, padded
@@ -104,7 +126,8 @@ struct obn_ctx {
   cudaEvent_t ev_fork = nullptr, ev_join[kAuxStreams] = {};
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // batch staging: one packed upload and one packed download per batch
-  obn::DevBuf d_in, d_out, d_lut;
+  obn::DevBuf d_in, d_out;
+  obn::LutCache lut;
   obn::DevBuf d_scratch;   // int32, kept all-zero between launches
   obn::DevBuf d_tickets;   // uint32, kept all-zero between launches
   obn::PinBuf h_in, h_out;

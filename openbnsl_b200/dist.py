@@ -48,3 +48,23 @@ class TorchComm:
         else:
             dist.all_gather_into_tensor(r, s, group=self.group)
         self.n_collectives += 1
+
+    def allgather_dev(self, ptr: int, bytes_per_rank: int) -> None:
+        """In-place all-gather of a device buffer of world * bytes_per_rank bytes (rank r owns
+        slice r).  The buffer belongs to libopenbnsl_b200; it is wrapped zero-copy through
+        __cuda_array_interface__ and handed to NCCL."""
+        torch, dist = self._torch, self._dist
+        if self.device.type != "cuda":
+            raise RuntimeError("allgather_dev needs the nccl backend")
+
+        class _Buf:
+            pass
+        b = _Buf()
+        b.__cuda_array_interface__ = {"shape": (self.world * bytes_per_rank,), "typestr": "|u1",
+                                      "data": (int(ptr), False), "version": 2}
+        full = torch.as_tensor(b, device=self.device)
+        mine = full[self.rank * bytes_per_rank:(self.rank + 1) * bytes_per_rank]
+        torch.cuda.current_stream().synchronize()
+        dist.all_gather_into_tensor(full, mine, group=self.group)
+        torch.cuda.current_stream().synchronize()
+        self.n_collectives += 1

@@ -135,3 +135,21 @@ def test_config1_alarm_pc_full_size():
         s, d, pv = oracle.citest(ods, a, b, [v for v in t if v not in (a, b)], 1)
         assert d == int(dof[i]) and close(stat[i], s, 1e-9, 1e-9) and close(p[i], pv, 1e-9, 1e-12)
     ctx.close()
+
+
+@pytest.mark.parametrize("max_parents,exact", [(11, 2), (3, 2), (11, 0)])
+def test_exhaustive_search_device_dp_equals_host_dp(max_parents, exact):
+    """The HBM-resident DP (obn_es_*) and the host DP over GPU scores pick the same DAG and score."""
+    net = nw.random_binary(12, seed=7)
+    codes, cards = ranked(net.sample(20000, 2))
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+    a = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=exact)
+    sa = L.structure_learning.last_es_stats()
+    b = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=exact, host_dp=True)
+    sb = L.structure_learning.last_es_stats()
+    assert np.array_equal(pdag_to_adj(a, net.n), pdag_to_adj(b, net.n))
+    assert sa["best_score"] == sb["best_score"]
+    assert sa["tables"] == sb["tables"] and sa["scores"] == sb["scores"]
+    if exact:                                   # bit-exact scores => the oracle's DAG, not just its CPDAG
+        ods = oracle.Dataset(codes, cards)
+        assert np.array_equal(pdag_to_adj(a, net.n), oracle.exhaustive_search(ods, 1.0, max_parents))
