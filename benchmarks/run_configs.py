@@ -93,7 +93,8 @@ def run_es(name, net, n_rows, max_parents, what, exact=2):
     st = L.structure_learning.last_es_stats()
     report(name, what, st["scores"], "local_scores", secs, prof,
            {"tables": int(st["tables"]), "n_vars": net.n, "n_rows": n_rows, "max_parents": max_parents,
-            "exact_order": exact, "data_gen_s": t_gen})
+            "exact_order": exact, "data_gen_s": t_gen, "enumerate_ms": st["enumerate_ms"], "score_ms": st["score_ms"],
+            "gather_ms": st["gather_ms"], "dp_ms": st["dp_ms"]})
 
 
 def main():
@@ -108,6 +109,12 @@ def main():
         net = nw.random_binary(24)
         run_es("C3", net, 1_000_000, 3, "exhaustive search BDeu, 24 binary vars, 1M rows, max_parents=3 (12 951 tables)", exact=0)
         run_es("C3", net, 1_000_000, 5, "exhaustive search BDeu, 24 binary vars, 1M rows, max_parents=5 (190 051 tables)", exact=0)
+    for w in which:                       # c3mp<k>[x]: C3 with max_parents=k (x = exact-order scores)
+        if w.startswith("c3mp"):
+            ex = 2 if w.endswith("x") else 0
+            mp = int(w[4:].rstrip("x"))
+            run_es("C3", nw.random_binary(24), 1_000_000, mp,
+                   "exhaustive search BDeu, 24 binary vars, 1M rows, max_parents=%d%s" % (mp, " exact-order" if ex else ""), exact=ex)
     if "c4" in which:
         run_pc("C4", nw.hepar2_like(), 1_000_000, L.citest.GSquare(0.05), 4,
                "PC-stable G2, Hepar2-like, 70 vars, 1M rows, depth<=4")

@@ -144,6 +144,16 @@ OBN_API int obn_es_level_begin(obn_es* es, const uint64_t* masks, size_t n_subse
 OBN_API int obn_es_level_scores(obn_es* es, size_t begin, size_t end);
 OBN_API int obn_es_level_buffer(obn_es* es, void** scores_dev, size_t* n_doubles);
 OBN_API int obn_es_level_dp(obn_es* es);
+/* Fast mode for deep searches: instead of steps 2 of every level, compute
+ *   F(S) = sum over the cells of S of lgamma(N_c + ess/cells(S)) - lgamma(ess/cells(S))
+ * for ALL subsets at once by a marginalisation lattice over the joint table
+ * (one pass over the data; see csrc/obn_lattice.cuh); the DP then uses
+ * score(child | pa) = F(pa + child) - F(pa)  (local_score.h:38-61 regrouped; 1e-9
+ * relative, not exact-order).  Rank r of `world` computes its share of the
+ * blocks; obn_es_f_buffer exposes F for the in-place all-gather
+ * (world * doubles_per_rank doubles, rank r owns slice r). */
+OBN_API int obn_es_lattice(obn_es* es, int rank, int world);
+OBN_API int obn_es_f_buffer(obn_es* es, void** f_dev, size_t* doubles_per_rank);
 OBN_API int obn_es_finish(obn_es* es, uint64_t* parent_masks, double* best_score);
 OBN_API void obn_es_end(obn_es* es);
 

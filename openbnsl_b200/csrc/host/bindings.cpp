@@ -261,6 +261,7 @@ PYBIND11_MODULE(openbnsllib, m) {
            o.ess = std::get<BDeu>(st).ess;
            o.max_parents = max_parents;
            o.exact_order = exact_order;
+           o.cards.assign(df.num_of_values.begin(), df.num_of_values.end());
            const char* e = std::getenv("OBN_SHARD_MIN_BYTES");
            o.shard_min_bytes = e && *e ? std::atof(e) : 4e9;
            const Comm c = make_comm(comm);
@@ -319,6 +320,7 @@ PYBIND11_MODULE(openbnsllib, m) {
     d["score_ms"] = g_last_es_stats.score_ms;
     d["gather_ms"] = g_last_es_stats.gather_ms;
     d["dp_ms"] = g_last_es_stats.dp_ms;
+    d["lattice"] = g_last_es_stats.lattice;
     return d;
   });
 

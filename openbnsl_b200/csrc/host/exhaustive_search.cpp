@@ -6,6 +6,7 @@
 // Gosper order and the scores are all-gathered once per level.
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -143,6 +144,40 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
   auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
   const size_t n_rows = obn_dataset_n_rows(ds);
   const size_t max_varset = opt.max_parents + 1;
+  // Fast mode for deep searches: every F(S) from the marginalisation lattice over the joint table
+  // (one pass over the data) instead of one counted table per subset.  Chosen when exact-order
+  // scores are not demanded and the lattice (~12 bytes per cell of every table) is cheaper than
+  // counting (~1 row visit per row per table at ~1e12 /s).
+  bool lattice = false;
+  if (opt.exact_order != 1 && opt.cards.size() == n) {
+    double count_s = 0, binom = 1, lat_cells = 1;
+    for (size_t k = 0; k <= std::min(n, max_varset); ++k) {
+      if (k) binom = binom * (double)(n - k + 1) / (double)k;
+      count_s += binom * (double)n_rows / 1e12;
+    }
+    for (size_t v = 0; v < n; ++v) lat_cells *= 1.0 + (double)opt.cards[v];
+    const double lattice_s = lat_cells * 12.0 / 3e12 + 0.05;
+    lattice = lattice_s < count_s && (opt.exact_order == 0 || count_s > 2.0);
+    if (const char* f = std::getenv("OBN_ES_LATTICE")) lattice = *f == '1';   // tests / A-B runs
+  }
+  if (lattice) {
+    const auto t0 = clk::now();
+    const int rc = obn_es_lattice(es, comm.rank, comm.world);
+    if (rc == OBN_ERR_UNSUPPORTED) lattice = false;            // joint table too large: count per subset
+    else check(rc);
+    if (lattice && comm.world > 1) {
+      const auto t1 = clk::now();
+      void* p = nullptr;
+      size_t per = 0;
+      check(obn_es_f_buffer(es, &p, &per));
+      comm.allgather_dev((uintptr_t)p, per * sizeof(double));
+      if (stats) stats->gather_ms += ms(t1, clk::now());
+    }
+    if (stats) {
+      stats->score_ms += ms(t0, clk::now());
+      stats->lattice = lattice;
+    }
+  }
   std::vector<uint64_t> masks;
   for (size_t size = 0; size <= n; ++size) {                        // exhaustive_search.cpp:47
     const auto t0 = clk::now();
@@ -151,7 +186,7 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
     do masks.push_back(W); while (next_combmask(W, (int)n));         // :129 (Gosper order)
     const size_t T = masks.size();
     const bool calc_ls = size <= max_varset && size > 0;             // :48
-    const bool sharded = comm.world > 1 && calc_ls &&
+    const bool sharded = comm.world > 1 && calc_ls && !lattice &&
                          (double)T * (double)size * (double)n_rows >= opt.shard_min_bytes && T >= (size_t)comm.world;
     const size_t chunk = sharded ? (T + comm.world - 1) / comm.world : T;
     check(obn_es_level_begin(es, masks.data(), T, (int)size, sharded ? chunk * comm.world : T));

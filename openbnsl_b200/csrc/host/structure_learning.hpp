@@ -53,12 +53,14 @@ struct EsOptions {
   double ess = 1.0;
   size_t max_parents = 0;
   int exact_order = 2;            // 0 fast, 1 exact (error if tables do not fit), 2 auto
+  std::vector<uint32_t> cards;    // cardinalities (device driver: cost model of the lattice mode)
   double shard_min_bytes = 0;     // multi-GPU: shard a level only if it has this many algorithmic bytes
 };
 struct EsStats {
   uint64_t tables = 0, scores = 0;
   double best_score = 0.0;
   double enumerate_ms = 0, score_ms = 0, gather_ms = 0, dp_ms = 0;
+  bool lattice = false;           // scores came from the marginalisation lattice (fast mode)
 };
 
 PDAG exhaustive_search_driver(size_t n_vars, Evaluator& ev, const Comm& comm, const EsOptions& opt,

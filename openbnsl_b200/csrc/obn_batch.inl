@@ -24,6 +24,7 @@ struct BatchSpec {
   double* scores = nullptr;
   double* scores_dev = nullptr;   // BDEU_ALL: leave the scores on the device at this address (no D2H)
   int32_t* counts = nullptr;
+  int32_t* counts_dev = nullptr;  // COUNTS: leave the dense tables on the device at this address (no D2H)
   const uint64_t* counts_off = nullptr;
 };
 
@@ -226,7 +227,7 @@ static int run_batch(BatchSpec& S) {
   else {
     uint64_t* coff = reinterpret_cast<uint64_t*>(hin + o_coff);
     for (size_t t = 0; t < n; ++t) { coff[t] = counts_total; counts_total += cells[t]; }
-    out_bytes = counts_total * 4;
+    out_bytes = S.counts_dev ? 0 : counts_total * 4;
   }
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
@@ -327,7 +328,7 @@ static int run_batch(BatchSpec& S) {
   double* d_p = reinterpret_cast<double*>(dout + n * 16);
   if (S.mode == MODE_CI) { a.stat = d_stat; a.dof = d_dof; a.pval = S.p ? d_p : nullptr; }
   else if (bdeu) a.scores = S.scores_dev ? S.scores_dev : reinterpret_cast<double*>(dout);
-  else { a.counts_out = reinterpret_cast<int32_t*>(dout); a.counts_off = reinterpret_cast<const uint64_t*>(din + o_coff); }
+  else { a.counts_out = S.counts_dev ? S.counts_dev : reinterpret_cast<int32_t*>(dout); a.counts_off = reinterpret_cast<const uint64_t*>(din + o_coff); }
   a.scratch = c->d_scratch.as<int32_t>();
   a.tickets = c->d_tickets.as<unsigned int>();
 
@@ -418,7 +419,7 @@ static int run_batch(BatchSpec& S) {
   } else {
     const int32_t* src = reinterpret_cast<const int32_t*>(hout);
     size_t o = 0;
-    for (size_t t = 0; t < n; ++t) {
+    for (size_t t = 0; t < n && !S.counts_dev; ++t) {
       memcpy(S.counts + S.counts_off[t], src + o, (size_t)cells[t] * 4);
       o += cells[t];
     }

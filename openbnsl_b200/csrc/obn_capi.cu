@@ -9,6 +9,7 @@
 #include <thread>
 
 #include "obn_count_kernel.cuh"
+#include "obn_lattice.cuh"
 #include "obn_host.hpp"
 
 namespace obn {
@@ -220,3 +221,4 @@ int obn_profile_read(obn_ctx* c, obn_profile* out, int reset) {
 
 #include "obn_batch.inl"
 #include "obn_es.inl"
+#include "obn_lattice.inl"

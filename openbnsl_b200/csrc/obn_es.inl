@@ -14,6 +14,12 @@ struct obn_es {
   uint32_t* bl_ps = nullptr;
   double* best_gs = nullptr;
   uint8_t* best_ch = nullptr;
+  // marginalisation lattice (fast mode): F(S) per subset, block-major (obn_lattice.inl)
+  double* F = nullptr;
+  bool use_F = false;
+  int h = 0, L = 0;
+  size_t f_per_rank = 0;
+  obn::DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF;
   // current level
   obn::DevBuf d_masks, d_level;
   std::vector<uint64_t> masks;
@@ -60,6 +66,44 @@ __global__ void es_dp_kernel(const unsigned long long* masks, size_t T, int k, i
   best_ch[W] = (uint8_t)bch;
 }
 
+// Same DP with the local scores taken from the lattice: ls(child | pa) = F(pa + child) - F(pa).
+// F is block-major: index = slot[S & (2^h - 1)] << L | S >> h.
+__global__ void es_dp_f_kernel(const unsigned long long* masks, size_t T, int k, int n, bool calc, const double* F,
+                               const uint32_t* slot, int h, int L, double* bl_score, uint32_t* bl_ps, double* best_gs,
+                               uint8_t* best_ch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  const uint32_t W = (uint32_t)masks[t];
+  const uint32_t hm = (1u << h) - 1u;
+  const double fW = calc ? F[((size_t)slot[W & hm] << L) | (W >> h)] : 0.0;
+  double bgs = 0.0;
+  int bch = -1;
+  for (uint32_t m = W; m; m &= m - 1) {
+    const int child = __ffs((int)m) - 1;
+    const uint32_t pa = W & ~(1u << child);
+    const double ls = calc ? fW - F[((size_t)slot[pa & hm] << L) | (pa >> h)] : -INFINITY;
+    double bls = ls;
+    uint32_t bps = pa;
+    for (uint32_t q = pa; q; q &= q - 1) {
+      const uint32_t sub = pa & ~(q & (0u - q));
+      const double s = bl_score[(size_t)sub * n + child];
+      if (s >= bls) {
+        bls = s;
+        bps = bl_ps[(size_t)sub * n + child];
+      }
+    }
+    bl_score[(size_t)pa * n + child] = bls;
+    bl_ps[(size_t)pa * n + child] = bps;
+    const double gs = best_gs[pa] + bls;
+    if (bgs >= 0 || gs > bgs) {
+      bgs = gs;
+      bch = child;
+    }
+  }
+  best_gs[W] = bgs;
+  best_ch[W] = (uint8_t)bch;
+}
+
 }  // namespace obn
 
 extern "C" {
@@ -101,8 +145,10 @@ void obn_es_end(obn_es* e) {
   cudaStreamSynchronize(e->c->stream);
   for (void* p : {(void*)e->bl_score, (void*)e->bl_ps, (void*)e->best_gs, (void*)e->best_ch})
     if (p) cudaFree(p);
-  e->d_masks.release();
-  e->d_level.release();
+  if (e->F) cudaFree(e->F);
+  for (obn::DevBuf* b : {&e->d_root, &e->d_pp[0], &e->d_pp[1], &e->d_tasks, &e->d_slot, &e->d_partials, &e->d_lut_a,
+                         &e->d_lutF, &e->d_masks, &e->d_level})
+    b->release();
   delete e;
 }
 
@@ -129,7 +175,7 @@ int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k
 int obn_es_level_scores(obn_es* e, size_t begin, size_t end) {
   if (!e) return fail(OBN_ERR_INVALID, "obn_es_level_scores: NULL argument");
   if (end > e->T) end = e->T;
-  if (begin >= end || !e->calc || e->k == 0) return OBN_OK;
+  if (begin >= end || !e->calc || e->k == 0 || e->use_F) return OBN_OK;
   const size_t k = (size_t)e->k;
   const size_t chunk = std::max<size_t>(1, ((size_t)1 << 21) / k);      // ~2M variable slots per batch
   std::vector<uint32_t> var_ids;
@@ -168,9 +214,14 @@ int obn_es_level_dp(obn_es* e) {
   OBN_CUDA(cudaSetDevice(c->device));
   const unsigned grid = (unsigned)((e->T + 127) / 128);
   (void)cudaGetLastError();
-  es_dp_kernel<<<grid, 128, 0, c->stream>>>(e->d_masks.as<unsigned long long>(), e->T, e->k, e->n,
-                                             (e->calc && e->k) ? e->d_level.as<double>() : nullptr, e->bl_score,
-                                             e->bl_ps, e->best_gs, e->best_ch);
+  if (e->use_F)
+    es_dp_f_kernel<<<grid, 128, 0, c->stream>>>(e->d_masks.as<unsigned long long>(), e->T, e->k, e->n, e->calc, e->F,
+                                                 e->d_slot.as<uint32_t>(), e->h, e->L, e->bl_score, e->bl_ps, e->best_gs,
+                                                 e->best_ch);
+  else
+    es_dp_kernel<<<grid, 128, 0, c->stream>>>(e->d_masks.as<unsigned long long>(), e->T, e->k, e->n,
+                                               (e->calc && e->k) ? e->d_level.as<double>() : nullptr, e->bl_score,
+                                               e->bl_ps, e->best_gs, e->best_ch);
   OBN_CUDA(cudaGetLastError());
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   ++c->prof.total_launches;

@@ -153,3 +153,34 @@ def test_exhaustive_search_device_dp_equals_host_dp(max_parents, exact):
     if exact:                                   # bit-exact scores => the oracle's DAG, not just its CPDAG
         ods = oracle.Dataset(codes, cards)
         assert np.array_equal(pdag_to_adj(a, net.n), oracle.exhaustive_search(ods, 1.0, max_parents))
+
+
+@pytest.mark.parametrize("which,max_parents", [("mixed", 9), ("mixed", 3), ("binary", 11)])
+def test_exhaustive_search_lattice_mode(which, max_parents, monkeypatch):
+    """Fast mode: every local score is F(pa + child) - F(pa) with F from the marginalisation lattice
+    over the joint table.  The optimum must equal the exact-order path's within 1e-9 relative, and
+    the DAG it returns must really have that score (recomputed with the oracle's BDeu)."""
+    if which == "mixed":
+        net = nw.random_network(10, 14, 3, [2, 3, 4, 2, 3, 2, 4, 2, 3, 2], seed=11)
+    else:
+        net = nw.random_binary(12, seed=9)
+    codes, cards = ranked(net.sample(6000, 3))
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+    monkeypatch.setenv("OBN_ES_LATTICE", "0")
+    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=1)
+    want = L.structure_learning.last_es_stats()
+    assert not want["lattice"]
+    monkeypatch.setenv("OBN_ES_LATTICE", "1")
+    g = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=0)
+    got = L.structure_learning.last_es_stats()
+    assert got["lattice"]
+    assert got["tables"] == want["tables"] and got["scores"] == want["scores"]
+    assert got["best_score"] == pytest.approx(want["best_score"], rel=1e-9)
+    ods = oracle.Dataset(codes, cards)
+    adj = pdag_to_adj(g, net.n)
+    total = 0.0
+    for v in range(net.n):
+        pa = [int(p) for p in np.nonzero(adj[:, v])[0]]
+        assert len(pa) <= max_parents
+        total += oracle.bdeu_local_score(ods, v, pa, 1.0)
+    assert total == pytest.approx(got["best_score"], rel=1e-9)
