@@ -22,6 +22,8 @@ import openbnsl_b200  # noqa: E402
 from openbnsl_b200 import networks as nw  # noqa: E402
 
 L = openbnsl_b200.openbnsllib
+COMM = None          # set in main() when launched under torchrun (one rank per GPU)
+RANK = 0
 
 
 def peak():
@@ -56,7 +58,10 @@ def report(name, what, units, unit_name, secs, prof, extra=None):
             "host_wait_ms": prof["host_wait_ms"]}
     if extra:
         line.update(extra)
-    print(json.dumps(line), flush=True)
+    if COMM is not None:
+        line["n_gpus"] = COMM.world
+    if RANK == 0:
+        print(json.dumps(line), flush=True)
 
 
 def run_pc(name, net, n_rows, test, depth, what, reps=1):
@@ -67,7 +72,7 @@ def run_pc(name, net, n_rows, test, depth, what, reps=1):
     L.profile_read(True)
     t0 = time.perf_counter()
     for _ in range(reps):
-        g = L.structure_learning.pc(df, test, depth, True)
+        g = L.structure_learning.pc(df, test, depth, True, comm=COMM)
     secs = (time.perf_counter() - t0) / reps
     prof = L.profile_read(True)
     for key in ("count_kernel_ms", "algorithmic_bytes", "host_prep_ms", "host_wait_ms", "count_launches"):
@@ -86,8 +91,11 @@ def run_es(name, net, n_rows, max_parents, what, exact=2):
     df.to_device()
     L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 0, exact_order=exact)
     L.profile_read(True)
+    if COMM is not None:
+        import torch.distributed as dist
+        dist.barrier()
     t0 = time.perf_counter()
-    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=exact)
+    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=exact, comm=COMM)
     secs = time.perf_counter() - t0
     prof = L.profile_read(True)
     st = L.structure_learning.last_es_stats()
@@ -98,6 +106,17 @@ def run_es(name, net, n_rows, max_parents, what, exact=2):
 
 
 def main():
+    global COMM, RANK
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        import torch
+        import torch.distributed as dist
+        from openbnsl_b200.dist import TorchComm
+        local = int(os.environ["LOCAL_RANK"])
+        os.environ["OBN_DEVICE"] = str(local)
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        COMM = TorchComm()
+        RANK = COMM.rank
     which = [a.lower() for a in sys.argv[1:]] or ["c1", "c2", "c3", "c4", "c5"]
     if "c1" in which:
         run_es("C1", nw.asia(), 10_000, 7, "exhaustive search BDeu, Asia, 8 vars, 10k rows, full lattice")

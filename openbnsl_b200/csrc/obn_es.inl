@@ -158,7 +158,8 @@ int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k
   if (buffer_subsets < n_subsets) buffer_subsets = n_subsets;
   obn_ctx* c = e->c;
   OBN_CUDA(cudaSetDevice(c->device));
-  e->masks.assign(masks, masks + n_subsets);
+  if (e->use_F) e->masks.clear();            // lattice mode never re-reads the masks on the host
+  else e->masks.assign(masks, masks + n_subsets);
   e->T = n_subsets;
   e->k = k;
   e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
@@ -166,7 +167,7 @@ int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k
   if (int rc = e->d_masks.reserve(std::max<size_t>(n_subsets * 8, 16))) return rc;
   if (int rc = e->d_level.reserve(std::max<size_t>(e->buffer_doubles * 8, 16))) return rc;
   if (n_subsets)
-    OBN_CUDA(cudaMemcpyAsync(e->d_masks.p, e->masks.data(), n_subsets * 8, cudaMemcpyHostToDevice, c->stream));
+    OBN_CUDA(cudaMemcpyAsync(e->d_masks.p, masks, n_subsets * 8, cudaMemcpyHostToDevice, c->stream));
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   c->prof.h2d_bytes += (double)(n_subsets * 8);
   return OBN_OK;

@@ -123,6 +123,7 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
     t.r = card[h + i];
     t.lo = lo;
     t.f_index = T;
+    t.lo_shift = (t.r == 2 && lo >= 4 && (lo & (lo - 1)) == 0) ? __builtin_ctz(lo) : -1;
     P.level_tasks[k].push_back(t);
   }
   // root lattice (offsets in cells, mul = 1; hi/lo include the low variables' cells in lo)
@@ -146,6 +147,7 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
     t.r = card[i];
     t.lo = (uint32_t)lo;
     t.f_index = P.slot[H] * NT + (NT - 1);
+    t.lo_shift = (t.r == 2 && lo >= 4 && (lo & (lo - 1)) == 0) ? __builtin_ctzll(lo) : -1;
     P.root_tasks[k].push_back(t);
   }
   return true;
@@ -213,6 +215,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   {
     MargTask t{};
     t.f_index = P.slot[B - 1] * NT + (NT - 1);
+    t.lo_shift = -1;
     all.push_back(t);
   }
   if (int rc = e->d_tasks.reserve(all.size() * sizeof(MargTask))) return rc;
@@ -225,15 +228,16 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   // ---- term tables: one per distinct cell count (device libm; this is the fast mode) ---------
   TermTable tt{nullptr, nullptr, 0, 0};
   {
-    std::vector<uint32_t> cells(combs);
-    cells[0] = 1;
-    std::vector<uint32_t> distinct;
-    for (size_t S = 1; S < combs; ++S) cells[S] = cells[S & (S - 1)] * ds->cards[__builtin_ctzll(S)];
-    {
-      std::vector<uint32_t> tmp(cells);
-      std::sort(tmp.begin(), tmp.end());
-      tmp.erase(std::unique(tmp.begin(), tmp.end()), tmp.end());
-      distinct.swap(tmp);
+    // distinct cell counts of all subsets = distinct products over sub-multisets of the cards
+    std::vector<uint32_t> distinct{1};
+    for (int v = 0; v < n && distinct.size() <= 4096; ++v) {
+      const size_t m = distinct.size();
+      for (size_t i = 0; i < m; ++i) {
+        const uint64_t p = (uint64_t)distinct[i] * ds->cards[v];
+        if (p < ((uint64_t)1 << 31)) distinct.push_back((uint32_t)p);
+      }
+      std::sort(distinct.begin(), distinct.end());
+      distinct.erase(std::unique(distinct.begin(), distinct.end()), distinct.end());
     }
     const size_t stride = ds->n_rows + 1;
     if (distinct.size() <= 256 && distinct.size() * stride * 8 <= ((size_t)2 << 30)) {
@@ -249,11 +253,12 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
       OBN_CUDA(cudaGetLastError());
       tt = TermTable{e->d_lutF.as<double>(), e->d_lut_a.as<double>(), (int)a.size(), stride};
     }
-    // accounting: what the reference would have read for the subsets whose scores are used
-    double alg = 0;
-    for (size_t S = 0; S < combs; ++S) {
-      const int k = __builtin_popcountll(S);
-      if ((size_t)k <= e->max_parents + 1) alg += (double)k * (double)ds->n_rows;
+    // accounting: what the reference would have read for the subsets whose scores are used:
+    // sum over k <= max_parents+1 of C(n,k) * k * N bytes
+    double alg = 0, binom = 1;
+    for (int k = 1; k <= n && (size_t)k <= e->max_parents + 1; ++k) {
+      binom = binom * (double)(n - k + 1) / (double)k;
+      alg += binom * (double)k * (double)ds->n_rows;
     }
     c->prof.algorithmic_bytes += alg / world;
   }
