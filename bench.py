@@ -236,6 +236,47 @@ def run_reference_arm(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def secondary_metrics(L, comm, world):
+    """BASELINE.json's other metric, local scores/s, on its two exhaustive-search configurations
+    (not the headline line: reported beside it).  C1 = Asia, 8 vars, 10k rows, exact-order scores
+    (bit-identical to the reference); C3 = 24 binary vars, 1M rows, the FULL 2^24-subset lattice in
+    fast mode (marginalisation lattice over the joint table), subsets sharded over the GPUs."""
+    import torch
+    from openbnsl_b200 import networks as nw
+    out = []
+    for name, net, rows, mp, exact, reps in (("C1_asia8_10k_full_lattice_exact", nw.asia(), 10_000, 7, 1, 20),
+                                            ("C3_bin24_1M_full_lattice_fast", nw.random_binary(24), 1_000_000, 23, 0, 1)):
+        codes = net.sample(rows, 0)
+        cards = [int(codes[:, v].max()) + 1 for v in range(net.n)]
+        df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+        df.to_device()
+        kw = {"comm": comm} if (comm is not None and name.startswith("C3")) else {}
+        L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), min(mp, 2), exact_order=exact)   # warm-up
+        L.profile_read(True)
+        torch.cuda.synchronize()
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), mp, exact_order=exact, **kw)
+        dt = (time.perf_counter() - t0) / reps
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        st = L.structure_learning.last_es_stats()
+        prof = L.profile_read(True)
+        k_s = prof["count_kernel_ms"] * 1e-3 / reps
+        out.append({"workload": name, "metric": "local scores/s", "value": st["scores"] / dt, "learn_time_s": dt,
+                    "local_scores": int(st["scores"]), "tables": int(st["tables"]), "lattice_mode": bool(st["lattice"]),
+                    "n_gpus": world if kw else 1, "kernel_s": k_s,
+                    "algorithmic_GBps_of_kernels": prof["algorithmic_bytes"] / reps / k_s / 1e9 if k_s > 0 else None})
+        del df
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import openbnsl_b200
@@ -304,6 +345,10 @@ def run_ours(args, rank, world, local_rank):
     prof_e2e = L.profile_read(True)
     clk = clocks.stop() if rank == 0 else None
 
+    secondary = None
+    if not args.no_secondary:
+        secondary = secondary_metrics(L, comm, world)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         L.structure_learning.pc(df, test, MAX_COND, True, record_tests=True)
@@ -336,6 +381,7 @@ def run_ours(args, rank, world, local_rank):
                      "kernel_share_of_step": kernel_s / total_s,
                      "algorithmic_bytes_per_step": prof["algorithmic_bytes"] / args.steps},
         "clocks": clk, "cpu_baseline": cpu,
+        "secondary": secondary,
     }
     print(json.dumps(line), flush=True)
 
@@ -347,6 +393,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the local-scores/s measurements")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

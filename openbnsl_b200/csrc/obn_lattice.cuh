@@ -51,11 +51,10 @@ __device__ __forceinline__ int find_lut(const TermTable& tt, double a) {
 }
 
 // grid = (chunks of the largest destination table, tasks).  partials[task * gridDim.x + chunk].
-__global__ void __launch_bounds__(kMargThreads) marg_kernel(const MargTask* tasks, uint64_t mul, const int32_t* src_base,
+__global__ void __launch_bounds__(kMargThreads, 8) marg_kernel(const MargTask* tasks, uint64_t mul, const int32_t* src_base,
                                                             int32_t* dst_base, double ess, TermTable tt,
                                                             double* partials) {
   __shared__ double red[32];
-  __shared__ int s_lut;
   const MargTask T = tasks[blockIdx.y];
   const uint64_t hi = (uint64_t)T.hi * mul, lo = T.lo, r = T.r;
   const uint64_t cells = hi * lo;
@@ -65,8 +64,7 @@ __global__ void __launch_bounds__(kMargThreads) marg_kernel(const MargTask* task
     const int32_t* src = src_base + (uint64_t)T.src_off * mul;
     int32_t* dst = dst_base + (uint64_t)T.dst_off * mul;
     const double a = ess / (double)cells;                       // local_score.h:41 for the table `dst`
-    if (threadIdx.x == 0) s_lut = find_lut(tt, a);
-    __syncthreads();
+    const int s_lut = find_lut(tt, a);                          // uniform over the CTA
     const double* lut = s_lut >= 0 ? tt.lut + (size_t)s_lut * tt.stride : nullptr;
     const double lg_a = lut ? 0.0 : lgamma(a);
     if (T.lo_shift >= 2 && (cells & 3) == 0 && (((uintptr_t)src | (uintptr_t)dst) & 15) == 0) {
