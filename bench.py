@@ -101,6 +101,15 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """DRAM bytes per counting-kernel launch from the committed ncu --set full capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            return float(json.load(f)["count_kernel_dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -376,7 +385,11 @@ def run_ours(args, rank, world, local_rank):
                 "ms_per_step": 1e3 * sum(e2e_times) / n_e2e},
         "gpu_launches": int(prof["total_launches"]),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
+                     "traffic_note": "dram bytes read+written per launch (ncu --set full, profiles/r1_traffic.json); the "
+                                     "3.7 MB dataset is L2-resident, so DRAM sees it about once per launch while the "
+                                     "algorithmic bytes (k*N per test) are served from L2",
+                     "algorithmic_bytes_per_launch": prof["algorithmic_bytes"] / max(1, prof["count_launches"]),
                      "kernel": "obn::count_kernel (all tiers)", "kernel_ms_per_step": prof["count_kernel_ms"] / args.steps,
                      "kernel_share_of_step": kernel_s / total_s,
                      "algorithmic_bytes_per_step": prof["algorithmic_bytes"] / args.steps},
