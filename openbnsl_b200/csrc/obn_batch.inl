@@ -259,7 +259,8 @@ static int run_batch(BatchSpec& S) {
       int nthr = (int)p2;
       int splits = 1;
       if (nthr == 256) {
-        const uint32_t min_vps = std::max<uint32_t>(1024u, max_cells / 4u);
+        // global tier: every CTA adds straight into the one global table, a split costs no merge
+        const uint32_t min_vps = global_tier ? 256u : std::max<uint32_t>(1024u, max_cells / 4u);
         splits = (int)std::min<size_t>(tpt / 256, std::max<uint32_t>(1u, n_vec / min_vps));
         splits = std::max(1, splits);
       }

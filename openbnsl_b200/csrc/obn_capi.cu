@@ -8,7 +8,6 @@
 #include <map>
 #include <thread>
 
-#include "obn_count_kernel.cuh"
 #include "obn_lattice.cuh"
 #include "obn_host.hpp"
 

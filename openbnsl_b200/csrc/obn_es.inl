@@ -68,12 +68,14 @@ __global__ void es_dp_kernel(const unsigned long long* masks, size_t T, int k, i
 
 // Same DP with the local scores taken from the lattice: ls(child | pa) = F(pa + child) - F(pa).
 // F is block-major: index = slot[S & (2^h - 1)] << L | S >> h.
-__global__ void es_dp_f_kernel(const unsigned long long* masks, size_t T, int k, int n, bool calc, const double* F,
+// No mask list: thread W handles subset W if it belongs to the level (|W| == k).
+__global__ void es_dp_f_kernel(size_t T, int k, int n, bool calc, const double* F,
                                const uint32_t* slot, int h, int L, double* bl_score, uint32_t* bl_ps, double* best_gs,
                                uint8_t* best_ch) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= T) return;
-  const uint32_t W = (uint32_t)masks[t];
+  const uint32_t W = (uint32_t)t;
+  if (__popc(W) != k) return;
   const uint32_t hm = (1u << h) - 1u;
   const double fW = calc ? F[((size_t)slot[W & hm] << L) | (W >> h)] : 0.0;
   double bgs = 0.0;
@@ -153,14 +155,16 @@ void obn_es_end(obn_es* e) {
 }
 
 int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k, size_t buffer_subsets) {
-  if (!e || (!masks && n_subsets)) return fail(OBN_ERR_INVALID, "obn_es_level_begin: NULL argument");
+  if (!e || (!masks && n_subsets && !e->use_F)) return fail(OBN_ERR_INVALID, "obn_es_level_begin: NULL argument");
   if (k < 0 || k > e->n) return fail(OBN_ERR_INVALID, "subset size %d out of range", k);
   if (buffer_subsets < n_subsets) buffer_subsets = n_subsets;
   obn_ctx* c = e->c;
   OBN_CUDA(cudaSetDevice(c->device));
-  if (e->use_F) e->masks.clear();            // lattice mode never re-reads the masks on the host
-  else e->masks.assign(masks, masks + n_subsets);
   e->T = n_subsets;
+  e->k = k;
+  e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
+  if (e->use_F) return OBN_OK;                 // lattice mode: the DP kernel finds the level by popcount
+  e->masks.assign(masks, masks + n_subsets);
   e->k = k;
   e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
   e->buffer_doubles = buffer_subsets * (size_t)std::max(k, 1);
@@ -215,10 +219,12 @@ int obn_es_level_dp(obn_es* e) {
   OBN_CUDA(cudaSetDevice(c->device));
   const unsigned grid = (unsigned)((e->T + 127) / 128);
   (void)cudaGetLastError();
-  if (e->use_F)
-    es_dp_f_kernel<<<grid, 128, 0, c->stream>>>(e->d_masks.as<unsigned long long>(), e->T, e->k, e->n, e->calc, e->F,
-                                                 e->d_slot.as<uint32_t>(), e->h, e->L, e->bl_score, e->bl_ps, e->best_gs,
-                                                 e->best_ch);
+  if (e->use_F) {
+    const size_t combs = (size_t)1 << e->n;
+    es_dp_f_kernel<<<(unsigned)((combs + 127) / 128), 128, 0, c->stream>>>(combs, e->k, e->n, e->calc, e->F,
+                                                                            e->d_slot.as<uint32_t>(), e->h, e->L, e->bl_score,
+                                                                            e->bl_ps, e->best_gs, e->best_ch);
+  }
   else
     es_dp_kernel<<<grid, 128, 0, c->stream>>>(e->d_masks.as<unsigned long long>(), e->T, e->k, e->n,
                                                (e->calc && e->k) ? e->d_level.as<double>() : nullptr, e->bl_score,

@@ -14,7 +14,7 @@
 // table.  (The association of the fp64 sum differs from the reference's sequential order:
 // this is the 1e-9-relative "fast" mode; exact-order mode keeps the counting path.)
 #pragma once
-#include "obn_device.cuh"
+#include "obn_count_kernel.cuh"
 
 namespace obn {
 
@@ -154,6 +154,26 @@ __global__ void marg_reduce_kernel(const MargTask* tasks, uint32_t n_tasks, uint
   double s = 0.0;
   for (uint32_t i = 0; i < chunks; ++i) s += p[i];
   F[f_base + tasks[t].f_index] = s;
+}
+
+// The joint table of all n variables, counted straight into its final place (zeroed by the
+// caller): one thread per 16-row vector, RED.E.ADD into L2.  Padding rows are all-zero codes.
+struct JointCards { uint32_t c[kMaxTupleVars]; };
+__global__ void joint_count_kernel(const uint8_t* data, size_t stride, uint32_t n_rows, int n, JointCards cards,
+                                   int32_t* tab) {
+  const uint32_t n_vec = (n_rows + 15u) >> 4;
+  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < n_vec) {
+    const size_t off = (size_t)v << 4;
+    KeyVec<32> key;
+    key.init(ld_codes16(data + off));
+    for (int i = 1; i < n; ++i) key.push(ld_codes16(data + (size_t)i * stride + off), cards.c[i]);
+    count16<32, TIER_GLOBAL, false>(key, reinterpret_cast<unsigned char*>(tab));
+  }
+  if (v == 0) {
+    const int pad = (int)((n_vec << 4) - n_rows);
+    if (pad) atomicAdd(&tab[0], -pad);
+  }
 }
 
 // lut[id][m] = lgamma(m + a_id) - lgamma(a_id), m = 0 .. stride-1 (device libm: fast mode only)

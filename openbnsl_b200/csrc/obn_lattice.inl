@@ -92,39 +92,38 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
       P.slot[order[i]] = r * per + fill[r]++;
     }
   }
-  // low lattice
+  // low lattice: O(1) work per subset (products by peeling the lowest bit, tasks placed by rank)
   const uint32_t NT = 1u << L;
   std::vector<uint32_t> cl(NT, 1), off(NT, 0);
-  for (uint32_t T = 0; T < NT; ++T)
-    for (int i = 0; i < L; ++i)
-      if (T >> i & 1) cl[T] *= card[h + i];
+  for (uint32_t T = 1; T < NT; ++T) cl[T] = cl[T & (T - 1)] * card[h + __builtin_ctz(T)];
   P.level_units.assign(L + 1, 0);
   P.level_max_units.assign(L + 1, 0);
+  std::vector<uint32_t> level_count(L + 1, 0);
   for (uint32_t T = 0; T < NT; ++T) {
     const int k = __builtin_popcount(T);
     off[T] = (uint32_t)P.level_units[k];
     P.level_units[k] += cl[T];
     P.level_max_units[k] = std::max(P.level_max_units[k], cl[T]);
+    ++level_count[k];
   }
+  std::vector<uint32_t> pre(L + 1, 1);                              // pre[i] = prod of the first i low cards
+  for (int i = 0; i < L; ++i) pre[i + 1] = pre[i] * card[h + i];
   P.level_tasks.assign(L, {});
-  for (uint32_t T = 0; T < NT; ++T) {
+  for (int k = 0; k < L; ++k) P.level_tasks[k].resize(level_count[k]);
+  std::vector<uint32_t> fill(L + 1, 0);
+  for (uint32_t T = 0; T + 1 < NT; ++T) {
     const int k = __builtin_popcount(T);
-    if (k == L) continue;
     const int i = __builtin_ctz(~T);                                // lowest absent low variable
-    const uint32_t S = T | (1u << i);
-    MargTask t{};
-    t.src_off = off[S];
+    MargTask& t = P.level_tasks[k][fill[k]++];
+    t.src_off = off[T | (1u << i)];
     t.dst_off = off[T];
-    uint32_t hi = 1, lo = 1;
-    for (int j = 0; j < i; ++j) hi *= card[h + j];                  // bits below i are all present in T
-    for (int j = i + 1; j < L; ++j)
-      if (T >> j & 1) lo *= card[h + j];
-    t.hi = hi;
+    t.hi = pre[i];                                                  // bits below i are all present in T
     t.r = card[h + i];
+    const uint32_t lo = cl[T & ~((2u << i) - 1u)];                  // T's variables above i
     t.lo = lo;
     t.f_index = T;
     t.lo_shift = (t.r == 2 && lo >= 4 && (lo & (lo - 1)) == 0) ? __builtin_ctz(lo) : -1;
-    P.level_tasks[k].push_back(t);
+    t.pad1 = 0;
   }
   // root lattice (offsets in cells, mul = 1; hi/lo include the low variables' cells in lo)
   P.root_tasks.assign(std::max(h, 1), {});
@@ -188,12 +187,23 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   const int n = e->n;
   size_t free_b = 0, total_b = 0;
   OBN_CUDA(cudaMemGetInfo(&free_b, &total_b));
-  const size_t budget = std::min<size_t>((size_t)(free_b * 0.7), (size_t)96 << 30);
+  const size_t budget = std::min<size_t>((size_t)(free_b * 0.7), (size_t)env_int("OBN_LATTICE_BUDGET_GB", 96) << 30);
+  const bool dbg = env_int("OBN_DEBUG", 0) != 0;
+  auto t_dbg = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!dbg) return;
+    cudaStreamSynchronize(c->stream);
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[obn_es_lattice] %-14s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_dbg).count());
+    t_dbg = now;
+  };
   LatticePlan P;
   if (!plan_lattice(ds->cards, budget, world, P))
     return fail(OBN_ERR_UNSUPPORTED, "marginalisation lattice does not fit (joint table >= 2^31 cells or too little memory)");
+  lap("plan");
   const int h = P.h, L = P.L;
   const uint32_t B = 1u << h, NT = 1u << L;
+  if (dbg) fprintf(stderr, "[obn_es_lattice] n=%d h=%d L=%d budget=%.1f GB\n", n, h, L, budget / 1073741824.0);
   const size_t combs = (size_t)1 << n;
 
   // ---- device buffers ---------------------------------------------------------------------
@@ -206,25 +216,34 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   if (int rc = e->d_root.reserve(std::max<uint64_t>(P.root_cells, 4) * 4)) return rc;
   for (int i = 0; i < 2; ++i)
     if (int rc = e->d_pp[i].reserve(std::max<uint64_t>(buf_units * cells_all_high, 4) * 4)) return rc;
+  lap("alloc");
   // tasks: low levels then root levels, one upload
-  std::vector<MargTask> all;
+  size_t n_all = 1;
   std::vector<size_t> low_at(L + 1, 0), root_at(h + 1, 0);
-  for (int k = 0; k < L; ++k) { low_at[k] = all.size(); all.insert(all.end(), P.level_tasks[k].begin(), P.level_tasks[k].end()); }
-  for (int k = 0; k < h; ++k) { root_at[k] = all.size(); all.insert(all.end(), P.root_tasks[k].begin(), P.root_tasks[k].end()); }
-  const size_t joint_task_at = all.size();
+  for (int k = 0; k < L; ++k) { low_at[k] = n_all; n_all += P.level_tasks[k].size(); }
+  for (int k = 0; k < h; ++k) { root_at[k] = n_all; n_all += P.root_tasks[k].size(); }
+  const size_t joint_task_at = 0;
+  if (int rc = e->d_tasks.reserve(n_all * sizeof(MargTask))) return rc;
+  if (int rc = c->h_in.reserve(n_all * sizeof(MargTask))) return rc;               // page-locked staging
   {
+    MargTask* all = c->h_in.as<MargTask>();
     MargTask t{};
     t.f_index = P.slot[B - 1] * NT + (NT - 1);
     t.lo_shift = -1;
-    all.push_back(t);
+    all[0] = t;
+    for (int k = 0; k < L; ++k)
+      if (!P.level_tasks[k].empty()) memcpy(all + low_at[k], P.level_tasks[k].data(), P.level_tasks[k].size() * sizeof(MargTask));
+    for (int k = 0; k < h; ++k)
+      if (!P.root_tasks[k].empty()) memcpy(all + root_at[k], P.root_tasks[k].data(), P.root_tasks[k].size() * sizeof(MargTask));
   }
-  if (int rc = e->d_tasks.reserve(all.size() * sizeof(MargTask))) return rc;
-  OBN_CUDA(cudaMemcpyAsync(e->d_tasks.p, all.data(), all.size() * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
+  OBN_CUDA(cudaMemcpyAsync(e->d_tasks.p, c->h_in.p, n_all * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
+  OBN_CUDA(cudaStreamSynchronize(c->stream));                                        // h_in is reused by run_batch
   if (int rc = e->d_slot.reserve(B * 4)) return rc;
   OBN_CUDA(cudaMemcpyAsync(e->d_slot.p, P.slot.data(), B * 4, cudaMemcpyHostToDevice, c->stream));
   e->h = h;
   e->L = L;
 
+  lap("tasks upload");
   // ---- term tables: one per distinct cell count (device libm; this is the fast mode) ---------
   TermTable tt{nullptr, nullptr, 0, 0};
   {
@@ -263,19 +282,21 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     c->prof.algorithmic_bytes += alg / world;
   }
 
+  lap("term tables");
   // ---- 1. joint table (the only pass over the data) -------------------------------------------
   int32_t* root = e->d_root.as<int32_t>();
   {
-    std::vector<uint32_t> vars(n);
-    for (int v = 0; v < n; ++v) vars[v] = (uint32_t)v;
-    const uint64_t offs[2] = {0, (uint64_t)n};
-    const uint64_t zero = 0;
-    BatchSpec S{c, ds, vars.data(), offs, 1, MODE_COUNTS};
-    S.counts_dev = root + P.root_off[B - 1];
-    S.counts_off = &zero;
-    const double alg_before = c->prof.algorithmic_bytes;
-    if (int rc = run_batch(S)) return rc;
-    c->prof.algorithmic_bytes = alg_before;                  // already accounted above
+    const uint64_t cells = P.cells_high[B - 1] * P.cells_low;
+    int32_t* J = root + P.root_off[B - 1];
+    OBN_CUDA(cudaMemsetAsync(J, 0, cells * 4, c->stream));
+    JointCards jc{};
+    for (int v = 0; v < n; ++v) jc.c[v] = ds->cards[v];
+    const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
+    (void)cudaGetLastError();
+    joint_count_kernel<<<std::max(1u, (n_vec + 127) / 128), 128, 0, c->stream>>>(ds->data, ds->stride, (uint32_t)ds->n_rows, n, jc, J);
+    OBN_CUDA(cudaGetLastError());
+    ++c->prof.total_launches;
+    ++c->prof.count_launches;
   }
   cudaEvent_t e0 = c->ev0, e1 = c->ev1;
   OBN_CUDA(cudaEventRecord(e0, c->stream));
@@ -290,11 +311,13 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     marg_reduce_kernel<<<1, 128, 0, c->stream>>>(d_tasks + joint_task_at, 1, chunks, e->d_partials.as<double>(), e->F, 0);
     OBN_CUDA(cudaGetLastError());
   }
+  lap("joint");
   // ---- 2. root lattice --------------------------------------------------------------------------
   for (int k = h - 1; k >= 0; --k)
     if (int rc = launch_marg_level(c, d_tasks + root_at[k], P.root_tasks[k].size(), (uint64_t)P.root_level_max[k] * P.cells_low,
                                    1, root, root, e->ess, tt, e->d_partials, e->F, 0))
       return rc;
+  lap("roots");
   // ---- 3. blocks of this rank ---------------------------------------------------------------------
   const uint32_t per = B / (uint32_t)world;
   for (uint32_t H = 0; H < B; ++H) {
@@ -310,6 +333,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   }
   OBN_CUDA(cudaEventRecord(e1, c->stream));
   OBN_CUDA(cudaStreamSynchronize(c->stream));
+  lap("blocks");
   float ms = 0;
   cudaEventElapsedTime(&ms, e0, e1);
   c->prof.count_kernel_ms += ms;
