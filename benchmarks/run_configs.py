@@ -68,7 +68,7 @@ def run_pc(name, net, n_rows, test, depth, what, reps=1):
     df, cards, t_gen = frame(net, n_rows, 0)
     L.profile_enable(True)
     df.to_device()
-    L.structure_learning.pc(df, test, min(depth, 1), True)          # warm-up (allocations, first launches)
+    L.structure_learning.pc(df, test, min(depth, 1), True, comm=COMM)   # warm-up (allocations, first launches, NCCL)
     L.profile_read(True)
     t0 = time.perf_counter()
     for _ in range(reps):
@@ -89,7 +89,7 @@ def run_es(name, net, n_rows, max_parents, what, exact=2):
     df, cards, t_gen = frame(net, n_rows, 0)
     L.profile_enable(True)
     df.to_device()
-    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 0, exact_order=exact)
+    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 0, exact_order=exact, comm=COMM)
     L.profile_read(True)
     if COMM is not None:
         import torch.distributed as dist

@@ -98,6 +98,7 @@ void obn_ctx_destroy(obn_ctx* c) {
   cudaStreamSynchronize(c->stream);
   for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_scratch, &c->d_tickets}) b->release();
   c->lut.release();
+  c->es_pool.release();
   if (c->ds_cache) cudaFree(c->ds_cache);
   c->h_in.release();
   c->h_out.release();

@@ -19,9 +19,7 @@ struct obn_es {
   bool use_F = false;
   int h = 0, L = 0;
   size_t f_per_rank = 0;
-  obn::DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF;
-  // current level
-  obn::DevBuf d_masks, d_level;
+  // all device buffers of a session come from c->es_pool (reused by the next session)
   std::vector<uint64_t> masks;
   size_t T = 0, buffer_doubles = 0;
   int k = 0;
@@ -128,15 +126,26 @@ int obn_es_begin(obn_ctx* c, const obn_dataset* ds, double ess, size_t max_paren
   e->max_parents = max_parents;
   e->exact = exact_order;
   const size_t combs = (size_t)1 << n;
-  cudaError_t err = cudaMalloc((void**)&e->bl_score, combs * n * sizeof(double));
-  if (err == cudaSuccess) err = cudaMalloc((void**)&e->bl_ps, combs * n * sizeof(uint32_t));
-  if (err == cudaSuccess) err = cudaMalloc((void**)&e->best_gs, combs * sizeof(double));
-  if (err == cudaSuccess) err = cudaMalloc((void**)&e->best_ch, combs);
-  if (err != cudaSuccess) {
-    cudaGetLastError();
-    obn_es_end(e);
-    return fail(OBN_ERR_OOM, "exhaustive search: DP tables for %zu variables do not fit (%s)", n, cudaGetErrorString(err));
+  EsPool& P = c->es_pool;
+  if (P.in_use) {
+    delete e;
+    return fail(OBN_ERR_INVALID, "another exhaustive-search session is open on this ctx");
   }
+  int rc = P.d_bl_score.reserve(combs * n * sizeof(double));
+  if (!rc) rc = P.d_bl_ps.reserve(combs * n * sizeof(uint32_t));
+  if (!rc) rc = P.d_best_gs.reserve(combs * sizeof(double));
+  if (!rc) rc = P.d_best_ch.reserve(combs);
+  if (rc) {
+    delete e;
+    return rc == OBN_ERR_OOM ? fail(OBN_ERR_OOM, "exhaustive search: DP tables for %zu variables do not fit in HBM", n) : rc;
+  }
+  P.in_use = true;
+  e->bl_score = P.d_bl_score.as<double>();
+  e->bl_ps = P.d_bl_ps.as<uint32_t>();
+  e->best_gs = P.d_best_gs.as<double>();
+  e->best_ch = P.d_best_ch.as<uint8_t>();
+  OBN_CUDA(cudaMemsetAsync(e->best_gs, 0, sizeof(double), c->stream));      // best_gs_tbl[empty] = 0 (:42-44)
+  OBN_CUDA(cudaMemsetAsync(e->best_ch, 0xff, combs, c->stream));            // "not processed yet" marker for finish
   *out = e;
   return OBN_OK;
 }
@@ -145,12 +154,7 @@ void obn_es_end(obn_es* e) {
   if (!e) return;
   cudaSetDevice(e->c->device);
   cudaStreamSynchronize(e->c->stream);
-  for (void* p : {(void*)e->bl_score, (void*)e->bl_ps, (void*)e->best_gs, (void*)e->best_ch})
-    if (p) cudaFree(p);
-  if (e->F) cudaFree(e->F);
-  for (obn::DevBuf* b : {&e->d_root, &e->d_pp[0], &e->d_pp[1], &e->d_tasks, &e->d_slot, &e->d_partials, &e->d_lut_a,
-                         &e->d_lutF, &e->d_masks, &e->d_level})
-    b->release();
+  e->c->es_pool.in_use = false;          // the buffers stay with the ctx for the next session
   delete e;
 }
 
@@ -168,10 +172,10 @@ int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k
   e->k = k;
   e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
   e->buffer_doubles = buffer_subsets * (size_t)std::max(k, 1);
-  if (int rc = e->d_masks.reserve(std::max<size_t>(n_subsets * 8, 16))) return rc;
-  if (int rc = e->d_level.reserve(std::max<size_t>(e->buffer_doubles * 8, 16))) return rc;
+  if (int rc = c->es_pool.d_masks.reserve(std::max<size_t>(n_subsets * 8, 16))) return rc;
+  if (int rc = c->es_pool.d_level.reserve(std::max<size_t>(e->buffer_doubles * 8, 16))) return rc;
   if (n_subsets)
-    OBN_CUDA(cudaMemcpyAsync(e->d_masks.p, masks, n_subsets * 8, cudaMemcpyHostToDevice, c->stream));
+    OBN_CUDA(cudaMemcpyAsync(c->es_pool.d_masks.p, masks, n_subsets * 8, cudaMemcpyHostToDevice, c->stream));
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   c->prof.h2d_bytes += (double)(n_subsets * 8);
   return OBN_OK;
@@ -199,7 +203,7 @@ int obn_es_level_scores(obn_es* e, size_t begin, size_t end) {
     BatchSpec S{e->c, e->ds, var_ids.data(), offsets.data(), m, MODE_BDEU_ALL};
     S.ess = e->ess;
     S.exact = e->exact;
-    S.scores_dev = e->d_level.as<double>() + b * k;
+    S.scores_dev = e->c->es_pool.d_level.as<double>() + b * k;
     if (int rc = run_batch(S)) return rc;
   }
   return OBN_OK;
@@ -207,7 +211,7 @@ int obn_es_level_scores(obn_es* e, size_t begin, size_t end) {
 
 int obn_es_level_buffer(obn_es* e, void** scores_dev, size_t* n_doubles) {
   if (!e || !scores_dev || !n_doubles) return fail(OBN_ERR_INVALID, "obn_es_level_buffer: NULL argument");
-  *scores_dev = e->d_level.p;
+  *scores_dev = e->c->es_pool.d_level.p;
   *n_doubles = e->buffer_doubles;
   return OBN_OK;
 }
@@ -222,12 +226,12 @@ int obn_es_level_dp(obn_es* e) {
   if (e->use_F) {
     const size_t combs = (size_t)1 << e->n;
     es_dp_f_kernel<<<(unsigned)((combs + 127) / 128), 128, 0, c->stream>>>(combs, e->k, e->n, e->calc, e->F,
-                                                                            e->d_slot.as<uint32_t>(), e->h, e->L, e->bl_score,
+                                                                            c->es_pool.d_slot.as<uint32_t>(), e->h, e->L, e->bl_score,
                                                                             e->bl_ps, e->best_gs, e->best_ch);
   }
   else
-    es_dp_kernel<<<grid, 128, 0, c->stream>>>(e->d_masks.as<unsigned long long>(), e->T, e->k, e->n,
-                                               (e->calc && e->k) ? e->d_level.as<double>() : nullptr, e->bl_score,
+    es_dp_kernel<<<grid, 128, 0, c->stream>>>(c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n,
+                                               (e->calc && e->k) ? c->es_pool.d_level.as<double>() : nullptr, e->bl_score,
                                                e->bl_ps, e->best_gs, e->best_ch);
   OBN_CUDA(cudaGetLastError());
   OBN_CUDA(cudaStreamSynchronize(c->stream));

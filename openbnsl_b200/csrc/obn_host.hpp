@@ -107,6 +107,29 @@ struct LutCache {
 };
 }  // namespace obn
 
+namespace obn {
+// Device buffers of exhaustive-search sessions (obn_es.inl, obn_lattice.inl).  They belong to the
+// ctx, grow only, and are reused by the next session: a search does not pay cudaMalloc / cudaFree
+// of tens of GB (which also serialise between the per-GPU processes of one box).
+struct EsPool {
+  bool in_use = false;
+  DevBuf d_bl_score, d_bl_ps, d_best_gs, d_best_ch, d_F;
+  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level;
+  void release() {
+    for (DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks, &d_slot,
+                      &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level})
+      b->release();
+  }
+  size_t bytes() const {
+    size_t s = 0;
+    for (const DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks,
+                            &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level})
+      s += b->cap;
+    return s;
+  }
+};
+}  // namespace obn
+
 struct obn_dataset {
   obn_ctx* ctx = nullptr;
   uint8_t* data = nullptr;      // device, column-major, padded
@@ -128,6 +151,7 @@ struct obn_ctx {
   // batch staging: one packed upload and one packed download per batch
   obn::DevBuf d_in, d_out;
   obn::LutCache lut;
+  obn::EsPool es_pool;
   obn::DevBuf d_scratch;   // int32, kept all-zero between launches
   obn::DevBuf d_tickets;   // uint32, kept all-zero between launches
   obn::PinBuf h_in, h_out;

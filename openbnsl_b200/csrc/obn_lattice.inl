@@ -43,6 +43,13 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
     const int h = n - L;
     if (h > 16) break;
     if (world > 1 && ((1 << h) % world != 0 || (1 << h) < world)) continue;
+    // multi-GPU balance: blocks are dealt whole, so the heaviest block (all high variables
+    // present) must be a small share of the total: prod c_high / prod (1 + c_high) <= 1 / (2 world)
+    if (world > 1 && L > 1) {
+      double heavy = 1, total = 1;
+      for (int v = 0; v < h; ++v) { heavy *= card[v]; total *= 1.0 + card[v]; }
+      if (heavy / total > 1.0 / (2.0 * world)) continue;
+    }
     // units per level by DP over the low variables: poly = prod (1 + c x)
     std::vector<double> lvl(L + 1, 0.0);
     lvl[0] = 1;
@@ -187,7 +194,8 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   const int n = e->n;
   size_t free_b = 0, total_b = 0;
   OBN_CUDA(cudaMemGetInfo(&free_b, &total_b));
-  const size_t budget = std::min<size_t>((size_t)(free_b * 0.7), (size_t)env_int("OBN_LATTICE_BUDGET_GB", 96) << 30);
+  const size_t pooled = c->es_pool.d_root.cap + c->es_pool.d_pp[0].cap + c->es_pool.d_pp[1].cap;   // reusable
+  const size_t budget = std::min<size_t>((size_t)((free_b + pooled) * 0.7), (size_t)env_int("OBN_LATTICE_BUDGET_GB", 24) << 30);
   const bool dbg = env_int("OBN_DEBUG", 0) != 0;
   auto t_dbg = std::chrono::steady_clock::now();
   auto lap = [&](const char* what) {
@@ -209,13 +217,11 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   // ---- device buffers ---------------------------------------------------------------------
   uint64_t cells_all_high = P.cells_high[B - 1], buf_units = 0;
   for (int k = 0; k < L; ++k) buf_units = std::max<uint64_t>(buf_units, P.level_units[k]);
-  if (!e->F) {
-    cudaError_t err = cudaMalloc((void**)&e->F, combs * sizeof(double));
-    if (err != cudaSuccess) return fail(OBN_ERR_OOM, "F table: %s", cudaGetErrorString(err));
-  }
-  if (int rc = e->d_root.reserve(std::max<uint64_t>(P.root_cells, 4) * 4)) return rc;
+  if (int rc = c->es_pool.d_F.reserve(combs * sizeof(double))) return rc;
+  e->F = c->es_pool.d_F.as<double>();
+  if (int rc = c->es_pool.d_root.reserve(std::max<uint64_t>(P.root_cells, 4) * 4)) return rc;
   for (int i = 0; i < 2; ++i)
-    if (int rc = e->d_pp[i].reserve(std::max<uint64_t>(buf_units * cells_all_high, 4) * 4)) return rc;
+    if (int rc = c->es_pool.d_pp[i].reserve(std::max<uint64_t>(buf_units * cells_all_high, 4) * 4)) return rc;
   lap("alloc");
   // tasks: low levels then root levels, one upload
   size_t n_all = 1;
@@ -223,7 +229,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   for (int k = 0; k < L; ++k) { low_at[k] = n_all; n_all += P.level_tasks[k].size(); }
   for (int k = 0; k < h; ++k) { root_at[k] = n_all; n_all += P.root_tasks[k].size(); }
   const size_t joint_task_at = 0;
-  if (int rc = e->d_tasks.reserve(n_all * sizeof(MargTask))) return rc;
+  if (int rc = c->es_pool.d_tasks.reserve(n_all * sizeof(MargTask))) return rc;
   if (int rc = c->h_in.reserve(n_all * sizeof(MargTask))) return rc;               // page-locked staging
   {
     MargTask* all = c->h_in.as<MargTask>();
@@ -236,10 +242,10 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     for (int k = 0; k < h; ++k)
       if (!P.root_tasks[k].empty()) memcpy(all + root_at[k], P.root_tasks[k].data(), P.root_tasks[k].size() * sizeof(MargTask));
   }
-  OBN_CUDA(cudaMemcpyAsync(e->d_tasks.p, c->h_in.p, n_all * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
+  OBN_CUDA(cudaMemcpyAsync(c->es_pool.d_tasks.p, c->h_in.p, n_all * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
   OBN_CUDA(cudaStreamSynchronize(c->stream));                                        // h_in is reused by run_batch
-  if (int rc = e->d_slot.reserve(B * 4)) return rc;
-  OBN_CUDA(cudaMemcpyAsync(e->d_slot.p, P.slot.data(), B * 4, cudaMemcpyHostToDevice, c->stream));
+  if (int rc = c->es_pool.d_slot.reserve(B * 4)) return rc;
+  OBN_CUDA(cudaMemcpyAsync(c->es_pool.d_slot.p, P.slot.data(), B * 4, cudaMemcpyHostToDevice, c->stream));
   e->h = h;
   e->L = L;
 
@@ -262,15 +268,15 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     if (distinct.size() <= 256 && distinct.size() * stride * 8 <= ((size_t)2 << 30)) {
       std::vector<double> a(distinct.size());
       for (size_t i = 0; i < distinct.size(); ++i) a[i] = e->ess / (double)(size_t)distinct[i];
-      if (int rc = e->d_lut_a.reserve(a.size() * 8)) return rc;
-      if (int rc = e->d_lutF.reserve(a.size() * stride * 8)) return rc;
-      OBN_CUDA(cudaMemcpyAsync(e->d_lut_a.p, a.data(), a.size() * 8, cudaMemcpyHostToDevice, c->stream));
+      if (int rc = c->es_pool.d_lut_a.reserve(a.size() * 8)) return rc;
+      if (int rc = c->es_pool.d_lutF.reserve(a.size() * stride * 8)) return rc;
+      OBN_CUDA(cudaMemcpyAsync(c->es_pool.d_lut_a.p, a.data(), a.size() * 8, cudaMemcpyHostToDevice, c->stream));
       OBN_CUDA(cudaStreamSynchronize(c->stream));          // `a` leaves scope
       (void)cudaGetLastError();
       lut_fill_kernel<<<dim3((unsigned)((stride + 255) / 256), (unsigned)a.size()), 256, 0, c->stream>>>(
-          e->d_lutF.as<double>(), e->d_lut_a.as<double>(), stride);
+          c->es_pool.d_lutF.as<double>(), c->es_pool.d_lut_a.as<double>(), stride);
       OBN_CUDA(cudaGetLastError());
-      tt = TermTable{e->d_lutF.as<double>(), e->d_lut_a.as<double>(), (int)a.size(), stride};
+      tt = TermTable{c->es_pool.d_lutF.as<double>(), c->es_pool.d_lut_a.as<double>(), (int)a.size(), stride};
     }
     // accounting: what the reference would have read for the subsets whose scores are used:
     // sum over k <= max_parents+1 of C(n,k) * k * N bytes
@@ -284,7 +290,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
 
   lap("term tables");
   // ---- 1. joint table (the only pass over the data) -------------------------------------------
-  int32_t* root = e->d_root.as<int32_t>();
+  int32_t* root = c->es_pool.d_root.as<int32_t>();
   {
     const uint64_t cells = P.cells_high[B - 1] * P.cells_low;
     int32_t* J = root + P.root_off[B - 1];
@@ -300,22 +306,22 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   }
   cudaEvent_t e0 = c->ev0, e1 = c->ev1;
   OBN_CUDA(cudaEventRecord(e0, c->stream));
-  const MargTask* d_tasks = e->d_tasks.as<MargTask>();
+  const MargTask* d_tasks = c->es_pool.d_tasks.as<MargTask>();
   {
     const uint64_t cells = P.cells_high[B - 1] * P.cells_low;
     const uint32_t chunks = (uint32_t)((cells + kMargChunk - 1) / kMargChunk);
-    if (int rc = e->d_partials.reserve((size_t)chunks * 8)) return rc;
+    if (int rc = c->es_pool.d_partials.reserve((size_t)chunks * 8)) return rc;
     (void)cudaGetLastError();
-    table_f_kernel<<<chunks, kMargThreads, 0, c->stream>>>(root + P.root_off[B - 1], cells, e->ess, tt, e->d_partials.as<double>());
+    table_f_kernel<<<chunks, kMargThreads, 0, c->stream>>>(root + P.root_off[B - 1], cells, e->ess, tt, c->es_pool.d_partials.as<double>());
     OBN_CUDA(cudaGetLastError());
-    marg_reduce_kernel<<<1, 128, 0, c->stream>>>(d_tasks + joint_task_at, 1, chunks, e->d_partials.as<double>(), e->F, 0);
+    marg_reduce_kernel<<<1, 128, 0, c->stream>>>(d_tasks + joint_task_at, 1, chunks, c->es_pool.d_partials.as<double>(), e->F, 0);
     OBN_CUDA(cudaGetLastError());
   }
   lap("joint");
   // ---- 2. root lattice --------------------------------------------------------------------------
   for (int k = h - 1; k >= 0; --k)
     if (int rc = launch_marg_level(c, d_tasks + root_at[k], P.root_tasks[k].size(), (uint64_t)P.root_level_max[k] * P.cells_low,
-                                   1, root, root, e->ess, tt, e->d_partials, e->F, 0))
+                                   1, root, root, e->ess, tt, c->es_pool.d_partials, e->F, 0))
       return rc;
   lap("roots");
   // ---- 3. blocks of this rank ---------------------------------------------------------------------
@@ -325,9 +331,9 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     if (s / per != (uint32_t)rank) continue;
     const uint64_t mul = P.cells_high[H];
     for (int k = L - 1; k >= 0; --k) {
-      const int32_t* src = (k == L - 1) ? root + P.root_off[H] : e->d_pp[(k + 1) & 1].as<int32_t>();
+      const int32_t* src = (k == L - 1) ? root + P.root_off[H] : c->es_pool.d_pp[(k + 1) & 1].as<int32_t>();
       if (int rc = launch_marg_level(c, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul,
-                                     src, e->d_pp[k & 1].as<int32_t>(), e->ess, tt, e->d_partials, e->F, (uint64_t)s * NT))
+                                     src, c->es_pool.d_pp[k & 1].as<int32_t>(), e->ess, tt, c->es_pool.d_partials, e->F, (uint64_t)s * NT))
         return rc;
     }
   }
