@@ -343,20 +343,39 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
 PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, const PcOptions& opt,
                                PcStats* stats) {
   std::vector<double> p;
+  TupleBatch mine;                   // this rank's share of a sharded round
   DecideFn decide = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
                         std::vector<int32_t>& first) {
     first.assign(n_slots, INT_MAX);
-    size_t begin = 0, end = b.size();
     const bool sharded = comm.world > 1 && b.var_ids.size() >= opt.shard_min_slots;
-    if (sharded) shard_range(b.size(), comm.rank, comm.world, &begin, &end);
-    p.resize(end - begin);
-    ev.ci_pvalues(b, begin, end, opt.kind, p.data());
-    for (size_t t = begin; t < end; ++t)
-      if (p[t - begin] >= opt.level) {                      // citest.h:147
+    if (!sharded) {
+      p.resize(b.size());
+      ev.ci_pvalues(b, 0, b.size(), opt.kind, p.data());
+      for (size_t t = 0; t < b.size(); ++t)
+        if (p[t] >= opt.level) {                              // citest.h:147
+          int32_t& f = first[pair_of_test[t]];
+          if ((int32_t)t < f) f = (int32_t)t;
+        }
+      return;
+    }
+    // Interleaved shares (test t belongs to rank t mod world): neighbouring tests have similar
+    // table sizes, so every rank gets the same mix; contiguous ranges would not.
+    mine.clear();
+    for (size_t t = (size_t)comm.rank; t < b.size(); t += (size_t)comm.world) {
+      mine.var_ids.insert(mine.var_ids.end(), b.var_ids.begin() + b.offsets[t], b.var_ids.begin() + b.offsets[t + 1]);
+      mine.offsets.push_back(mine.var_ids.size());
+      mine.x.push_back(b.x[t]);
+      mine.y.push_back(b.y[t]);
+    }
+    p.resize(mine.size());
+    ev.ci_pvalues(mine, 0, mine.size(), opt.kind, p.data());
+    for (size_t i = 0; i < mine.size(); ++i)
+      if (p[i] >= opt.level) {
+        const size_t t = (size_t)comm.rank + i * (size_t)comm.world;
         int32_t& f = first[pair_of_test[t]];
         if ((int32_t)t < f) f = (int32_t)t;
       }
-    if (sharded) comm.allreduce_min_i32(first.data(), first.size());
+    comm.allreduce_min_i32(first.data(), first.size());
   };
   return run_pc(n_vars, opt.max_cond_vars, opt.stable, opt.target_batch, decide, stats);
 }

@@ -32,6 +32,9 @@ struct CtaTuple {            // per-CTA tuple description in shared memory
   const uint8_t* col[kMaxTupleVars];   // column pointers in KERNEL digit order
   uint32_t card[kMaxTupleVars];        // cards in kernel digit order
   uint32_t ref_card[kMaxTupleVars];    // cards in ascending-var (reference) order
+  // column groups (kernel order): consecutive columns whose cards multiply to <= 256 are folded
+  // with packed 8-bit arithmetic (4 rows per IMAD) and only the group keys are widened
+  uint32_t gcells[kMaxTupleVars];      // cells of the group that ends at column i (0: not a group end)
   uint32_t rx, ry;
   int child_pos;             // BDEU_ONE: position of the child in reference order
   unsigned int ticket;
@@ -42,6 +45,11 @@ struct KeyVec;               // keys of 16 consecutive rows
 template <>
 struct KeyVec<8> {
   uint32_t w[4];
+  __device__ __forceinline__ void from8(const KeyVec<8>& p) { *this = p; }
+  __device__ __forceinline__ void push8(const KeyVec<8>& p, uint32_t cells) {      // only one group when KW == 8
+#pragma unroll
+    for (int i = 0; i < 4; ++i) w[i] = w[i] * cells + p.w[i];
+  }
   __device__ __forceinline__ void init(const uint4& c) { w[0] = c.x; w[1] = c.y; w[2] = c.z; w[3] = c.w; }
   __device__ __forceinline__ void push(const uint4& c, uint32_t card) {
     w[0] = w[0] * card + c.x; w[1] = w[1] * card + c.y;
@@ -76,6 +84,20 @@ struct KeyVec<16> {
 #pragma unroll
     for (int i = 0; i < 8; ++i) w[i] <<= 2;
   }
+  __device__ __forceinline__ void from8(const KeyVec<8>& p) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      w[2 * i] = __byte_perm(p.w[i], 0, 0x4140);
+      w[2 * i + 1] = __byte_perm(p.w[i], 0, 0x4342);
+    }
+  }
+  __device__ __forceinline__ void push8(const KeyVec<8>& p, uint32_t cells) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      w[2 * i] = w[2 * i] * cells + __byte_perm(p.w[i], 0, 0x4140);
+      w[2 * i + 1] = w[2 * i + 1] * cells + __byte_perm(p.w[i], 0, 0x4342);
+    }
+  }
   __device__ __forceinline__ uint32_t get(int r) const { return (r & 1) ? (w[r >> 1] >> 16) : (w[r >> 1] & 0xffffu); }
 };
 template <>
@@ -95,6 +117,14 @@ struct KeyVec<32> {
 #pragma unroll
     for (int i = 0; i < 16; ++i) w[i] <<= 2;
   }
+  __device__ __forceinline__ void from8(const KeyVec<8>& p) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = __byte_perm(p.w[i >> 2], 0, 0x4440 + (i & 3));
+  }
+  __device__ __forceinline__ void push8(const KeyVec<8>& p, uint32_t cells) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = w[i] * cells + __byte_perm(p.w[i >> 2], 0, 0x4440 + (i & 3));
+  }
   __device__ __forceinline__ uint32_t get(int r) const { return w[r]; }
 };
 
@@ -110,6 +140,28 @@ __device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* base) {
   }
 }
 
+// Fold one column into the running key: inside a group with packed 8-bit arithmetic, across
+// groups in the key's own width.
+template <int KW>
+__device__ __forceinline__ void fold_column(KeyVec<8>& part, KeyVec<KW>& key, bool& have_part, bool& have_key,
+                                            const uint4& c, uint32_t card, uint32_t gcells) {
+  if (!have_part) {
+    part.init(c);
+    have_part = true;
+  } else {
+    part.push(c, card);
+  }
+  if (gcells) {                       // this column closes its group
+    if (!have_key) {
+      key.from8(part);
+      have_key = true;
+    } else {
+      key.push8(part, gcells);
+    }
+    have_part = false;
+  }
+}
+
 // Row scan with the column count known at compile time: column pointers and
 // cards live in registers, and the loads of the NEXT 16-row vector are issued
 // before the increments of the current one (register double buffering).
@@ -117,9 +169,9 @@ template <int KW, int TIER, bool SCALE4, int K>
 __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, uint32_t v_begin,
                                             uint32_t v_end, uint32_t tid, uint32_t nthr) {
   const uint8_t* col[K];
-  uint32_t card[K];
+  uint32_t card[K], gcells[K];
 #pragma unroll
-  for (int i = 0; i < K; ++i) { col[i] = T.col[i]; card[i] = T.card[i]; }
+  for (int i = 0; i < K; ++i) { col[i] = T.col[i]; card[i] = T.card[i]; gcells[i] = T.gcells[i]; }
   uint4 cur[K], nxt[K];
   uint32_t v = v_begin + tid;
   if (v < v_end) {
@@ -133,30 +185,47 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
       for (int i = 0; i < K; ++i) nxt[i] = ld_codes16(col[i] + ((size_t)vn << 4));
     }
     KeyVec<KW> key;
-    key.init(cur[0]);
+    if (KW == 8) {                    // tables of <= 256 cells: one group, all packed
+      key.init(cur[0]);
 #pragma unroll
-    for (int i = 1; i < K; ++i) key.push(cur[i], card[i]);
+      for (int i = 1; i < K; ++i) key.push(cur[i], card[i]);
+    } else {
+      KeyVec<8> part;
+      bool have_part = false, have_key = false;
+#pragma unroll
+      for (int i = 0; i < K; ++i) fold_column<KW>(part, key, have_part, have_key, cur[i], card[i], gcells[i]);
+    }
     count16<KW, TIER, SCALE4>(key, base);
 #pragma unroll
     for (int i = 0; i < K; ++i) cur[i] = nxt[i];
   }
 }
 
-// Any column count (descriptors stay in shared memory).
+// Any column count (descriptors stay in shared memory): columns are loaded four at a time so
+// that four 16-byte loads are in flight per thread.
 template <int KW, int TIER, bool SCALE4>
 __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
                                               uint32_t v_end, uint32_t tid, uint32_t nthr) {
   for (uint32_t v = v_begin + tid; v < v_end; v += nthr) {
     const size_t off = (size_t)v << 4;
     KeyVec<KW> key;
-    key.init(ld_codes16(T.col[0] + off));
-    for (int i = 1; i < k; ++i) key.push(ld_codes16(T.col[i] + off), T.card[i]);
+    KeyVec<8> part;
+    bool have_part = false, have_key = false;
+    for (int i = 0; i < k; i += 4) {
+      uint4 c[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (i + j < k) c[j] = ld_codes16(T.col[i + j] + off);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
+    }
     count16<KW, TIER, SCALE4>(key, base);
   }
 }
 
 template <int KW, int TIER, bool SCALE4>
-__global__ void __launch_bounds__(256, 4) count_kernel(const BatchArgs A) {
+__global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ CtaTuple T;
   __shared__ double red_d[32];
@@ -202,7 +271,17 @@ __global__ void __launch_bounds__(256, 4) count_kernel(const BatchArgs A) {
       if (is_y) T.ry = c;
     }
     const unsigned m_child = __ballot_sync(0xffffffffu, live && v == child);
-    if (tid == 0) T.child_pos = m_child ? (__ffs(m_child) - 1) : -1;
+    __syncwarp();
+    if (tid == 0) {
+      T.child_pos = m_child ? (__ffs(m_child) - 1) : -1;
+      uint32_t g = 1;                              // greedy groups of <= 256 cells
+      for (int i = 0; i < k; ++i) {
+        g *= T.card[i];
+        const bool close = (i + 1 == k) || g * T.card[i + 1] > 256u;
+        T.gcells[i] = close ? g : 0u;
+        if (close) g = 1;
+      }
+    }
   }
 
   // ---- table + epilogue scratch (zeroed while the descriptor loads are in flight)

@@ -2,6 +2,10 @@
 // (include/openbnsl_b200.h, "exhaustive search on the device").  Included at the
 // end of obn_capi.cu, after obn_batch.inl.
 
+namespace obn {
+struct EsLevels { uint64_t off[34]; };     // off[k] = number of subsets with fewer than k variables, k = 0 .. n+1
+}
+
 struct obn_es {
   obn_ctx* c = nullptr;
   const obn_dataset* ds = nullptr;
@@ -17,6 +21,7 @@ struct obn_es {
   // marginalisation lattice (fast mode): F(S) per subset, block-major (obn_lattice.inl)
   double* F = nullptr;
   bool use_F = false;
+  obn::EsLevels levels{};
   int h = 0, L = 0;
   size_t f_per_rank = 0;
   // all device buffers of a session come from c->es_pool (reused by the next session)
@@ -66,14 +71,33 @@ __global__ void es_dp_kernel(const unsigned long long* masks, size_t T, int k, i
 
 // Same DP with the local scores taken from the lattice: ls(child | pa) = F(pa + child) - F(pa).
 // F is block-major: index = slot[S & (2^h - 1)] << L | S >> h.
-// No mask list: thread W handles subset W if it belongs to the level (|W| == k).
-__global__ void es_dp_f_kernel(size_t T, int k, int n, bool calc, const double* F,
+// lists[off[k] + rank] = W for every subset W: rank = position of W among the k-subsets in
+// increasing numeric order = sum_i C(p_i, i+1) over its set bits p_0 < p_1 < ... (combinatorial
+// number system), which is also the reference's Gosper order (next_combmask.h:41-46).
+__global__ void es_level_lists_kernel(size_t combs, int n, EsLevels lv, uint32_t* lists) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= combs) return;
+  const uint32_t W = (uint32_t)t;
+  uint64_t rank = 0;
+  int i = 0;
+  for (uint32_t m = W; m; m &= m - 1) {
+    const int p = __ffs((int)m) - 1;
+    ++i;                                           // C(p, i)
+    uint64_t c = 1;
+    if (i > p) c = 0;
+    else
+      for (int j = 1; j <= i; ++j) c = c * (uint64_t)(p - i + j) / (uint64_t)j;
+    rank += c;
+  }
+  lists[lv.off[__popc(W)] + rank] = W;
+}
+
+__global__ void es_dp_f_kernel(const uint32_t* level_list, size_t T, int k, int n, bool calc, const double* F,
                                const uint32_t* slot, int h, int L, double* bl_score, uint32_t* bl_ps, double* best_gs,
                                uint8_t* best_ch) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= T) return;
-  const uint32_t W = (uint32_t)t;
-  if (__popc(W) != k) return;
+  const uint32_t W = level_list[t];
   const uint32_t hm = (1u << h) - 1u;
   const double fW = calc ? F[((size_t)slot[W & hm] << L) | (W >> h)] : 0.0;
   double bgs = 0.0;
@@ -224,10 +248,10 @@ int obn_es_level_dp(obn_es* e) {
   const unsigned grid = (unsigned)((e->T + 127) / 128);
   (void)cudaGetLastError();
   if (e->use_F) {
-    const size_t combs = (size_t)1 << e->n;
-    es_dp_f_kernel<<<(unsigned)((combs + 127) / 128), 128, 0, c->stream>>>(combs, e->k, e->n, e->calc, e->F,
-                                                                            c->es_pool.d_slot.as<uint32_t>(), e->h, e->L, e->bl_score,
-                                                                            e->bl_ps, e->best_gs, e->best_ch);
+    const size_t Tk = (size_t)(e->levels.off[e->k + 1] - e->levels.off[e->k]);
+    es_dp_f_kernel<<<(unsigned)((Tk + 127) / 128), 128, 0, c->stream>>>(
+        c->es_pool.d_masks.as<uint32_t>() + e->levels.off[e->k], Tk, e->k, e->n, e->calc, e->F,
+        c->es_pool.d_slot.as<uint32_t>(), e->h, e->L, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
   }
   else
     es_dp_kernel<<<grid, 128, 0, c->stream>>>(c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n,

@@ -94,8 +94,9 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
     P.slot.assign(B, 0);
     const uint32_t per = B / (uint32_t)world;
     std::vector<uint32_t> fill(world, 0);
-    for (uint32_t i = 0; i < B; ++i) {
-      const uint32_t r = i % (uint32_t)world;
+    for (uint32_t i = 0; i < B; ++i) {                      // snake order: 0..w-1, w-1..0, ... (no rank always first)
+      const uint32_t round = i / (uint32_t)world, pos = i % (uint32_t)world;
+      const uint32_t r = (round & 1u) ? (uint32_t)world - 1u - pos : pos;
       P.slot[order[i]] = r * per + fill[r]++;
     }
   }
@@ -305,8 +306,27 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     ++c->prof.count_launches;
   }
   cudaEvent_t e0 = c->ev0, e1 = c->ev1;
-  OBN_CUDA(cudaEventRecord(e0, c->stream));
   const MargTask* d_tasks = c->es_pool.d_tasks.as<MargTask>();
+  // The lattice is thousands of small dependent launches (blocks x levels x 2): capture them into
+  // ONE CUDA graph so that the GPU never waits for the host thread (which shares its cores with
+  // the other ranks' processes).  All buffers are reserved before the capture starts.
+  {
+    size_t need = (size_t)((P.cells_high[B - 1] * P.cells_low + kMargChunk - 1) / kMargChunk);
+    for (int k = 0; k < h; ++k)
+      need = std::max(need, std::min<size_t>(65535, P.root_tasks[k].size()) *
+                                (size_t)(((uint64_t)P.root_level_max[k] * P.cells_low + kMargChunk - 1) / kMargChunk));
+    for (int k = 0; k < L; ++k)
+      need = std::max(need, std::min<size_t>(65535, P.level_tasks[k].size()) *
+                                (size_t)(((uint64_t)P.level_max_units[k] * cells_all_high + kMargChunk - 1) / kMargChunk));
+    if (int rc = c->es_pool.d_partials.reserve(need * sizeof(double))) return rc;
+  }
+  const bool use_graph = env_int("OBN_LATTICE_GRAPH", 1) != 0;
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  if (use_graph) OBN_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+  else OBN_CUDA(cudaEventRecord(e0, c->stream));
+  const bool dbg_saved = dbg;
+  auto lap_if = [&](const char* what) { if (!use_graph) lap(what); };
+  (void)dbg_saved;
   {
     const uint64_t cells = P.cells_high[B - 1] * P.cells_low;
     const uint32_t chunks = (uint32_t)((cells + kMargChunk - 1) / kMargChunk);
@@ -317,13 +337,15 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     marg_reduce_kernel<<<1, 128, 0, c->stream>>>(d_tasks + joint_task_at, 1, chunks, c->es_pool.d_partials.as<double>(), e->F, 0);
     OBN_CUDA(cudaGetLastError());
   }
-  lap("joint");
+  lap_if("joint");
   // ---- 2. root lattice --------------------------------------------------------------------------
   for (int k = h - 1; k >= 0; --k)
     if (int rc = launch_marg_level(c, d_tasks + root_at[k], P.root_tasks[k].size(), (uint64_t)P.root_level_max[k] * P.cells_low,
-                                   1, root, root, e->ess, tt, c->es_pool.d_partials, e->F, 0))
+                                   1, root, root, e->ess, tt, c->es_pool.d_partials, e->F, 0)) {
+      if (use_graph) { cudaGraph_t g = nullptr; cudaStreamEndCapture(c->stream, &g); if (g) cudaGraphDestroy(g); }
       return rc;
-  lap("roots");
+    }
+  lap_if("roots");
   // ---- 3. blocks of this rank ---------------------------------------------------------------------
   const uint32_t per = B / (uint32_t)world;
   for (uint32_t H = 0; H < B; ++H) {
@@ -333,16 +355,55 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     for (int k = L - 1; k >= 0; --k) {
       const int32_t* src = (k == L - 1) ? root + P.root_off[H] : c->es_pool.d_pp[(k + 1) & 1].as<int32_t>();
       if (int rc = launch_marg_level(c, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul,
-                                     src, c->es_pool.d_pp[k & 1].as<int32_t>(), e->ess, tt, c->es_pool.d_partials, e->F, (uint64_t)s * NT))
+                                     src, c->es_pool.d_pp[k & 1].as<int32_t>(), e->ess, tt, c->es_pool.d_partials, e->F, (uint64_t)s * NT)) {
+        if (use_graph) { cudaGraph_t g = nullptr; cudaStreamEndCapture(c->stream, &g); if (g) cudaGraphDestroy(g); }
         return rc;
+      }
     }
   }
-  OBN_CUDA(cudaEventRecord(e1, c->stream));
-  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  if (use_graph) {
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    OBN_CUDA(cudaStreamEndCapture(c->stream, &graph));
+    cudaError_t ge = cudaGraphInstantiate(&exec, graph, 0);
+    if (ge != cudaSuccess) {
+      cudaGraphDestroy(graph);
+      return fail(OBN_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ge));
+    }
+    lap("graph build");
+    OBN_CUDA(cudaEventRecord(e0, c->stream));
+    ge = cudaGraphLaunch(exec, c->stream);
+    if (ge == cudaSuccess) ge = cudaEventRecord(e1, c->stream);
+    if (ge == cudaSuccess) ge = cudaStreamSynchronize(c->stream);
+    cudaGraphExecDestroy(exec);
+    cudaGraphDestroy(graph);
+    if (ge != cudaSuccess) return fail(OBN_ERR_CUDA, "lattice graph launch failed: %s", cudaGetErrorString(ge));
+  } else {
+    OBN_CUDA(cudaEventRecord(e1, c->stream));
+    OBN_CUDA(cudaStreamSynchronize(c->stream));
+  }
   lap("blocks");
   float ms = 0;
   cudaEventElapsedTime(&ms, e0, e1);
   c->prof.count_kernel_ms += ms;
+  // level lists for the DP: subsets grouped by size, ascending inside a level (= Gosper order)
+  {
+    if (int rc = c->es_pool.d_masks.reserve(combs * sizeof(uint32_t))) return rc;
+    EsLevels lv{};
+    uint64_t off = 0, binom = 1;
+    for (int k = 0; k <= n; ++k) {
+      if (k) binom = binom * (uint64_t)(n - k + 1) / (uint64_t)k;
+      lv.off[k] = off;
+      off += binom;
+    }
+    lv.off[n + 1] = off;
+    e->levels = lv;
+    (void)cudaGetLastError();
+    es_level_lists_kernel<<<(unsigned)((combs + 255) / 256), 256, 0, c->stream>>>(combs, n, lv, c->es_pool.d_masks.as<uint32_t>());
+    OBN_CUDA(cudaGetLastError());
+    OBN_CUDA(cudaStreamSynchronize(c->stream));
+    ++c->prof.total_launches;
+  }
   e->use_F = true;
   e->f_per_rank = (size_t)per * NT;
   return OBN_OK;
