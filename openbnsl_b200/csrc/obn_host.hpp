@@ -111,19 +111,37 @@ namespace obn {
 // Device buffers of exhaustive-search sessions (obn_es.inl, obn_lattice.inl).  They belong to the
 // ctx, grow only, and are reused by the next session: a search does not pay cudaMalloc / cudaFree
 // of tens of GB (which also serialise between the per-GPU processes of one box).
+// The instantiated lattice graph of the last search shape (cards, rows, ess, rank/world): a repeated
+// search on the same ctx (bootstrap resampling, ess sweeps re-key it) skips plan, uploads and capture.
+struct LatticeGraphCache {
+  std::vector<uint64_t> key;
+  cudaGraphExec_t exec = nullptr;
+  int h = 0, L = 0;
+  uint32_t per = 0;
+  uint64_t joint_off = 0, joint_cells = 0;
+  uint64_t launches = 0;
+  void clear() {
+    if (exec) cudaGraphExecDestroy(exec);
+    exec = nullptr;
+    key.clear();
+  }
+};
+
 struct EsPool {
   bool in_use = false;
+  LatticeGraphCache lattice;
   DevBuf d_bl_score, d_bl_ps, d_best_gs, d_best_ch, d_F;
-  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level;
+  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog;
   void release() {
+    lattice.clear();
     for (DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks, &d_slot,
-                      &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level})
+                      &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog})
       b->release();
   }
   size_t bytes() const {
     size_t s = 0;
     for (const DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks,
-                            &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level})
+                            &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog})
       s += b->cap;
     return s;
   }

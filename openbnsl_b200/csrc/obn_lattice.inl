@@ -15,6 +15,8 @@ namespace obn {
 
 struct LatticePlan {
   int n = 0, h = 0, L = 0;
+  int bot = 0, Lm = 0;                    // the last `bot` low variables live in shared memory (0 or kBotL); Lm = L - bot
+  uint64_t cells_bot = 1;                 // prod cards of the bottom variables (a factor of every mid-tier unit)
   std::vector<uint32_t> card;
   uint64_t cells_low = 1;                 // prod cards of the low variables
   std::vector<uint64_t> cells_high;       // [2^h] prod cards of the block's high variables
@@ -30,17 +32,25 @@ struct LatticePlan {
   std::vector<uint32_t> root_level_max;   // [h+1] max cells of a root at level k, in units of cells_low
 };
 
-static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes, int world, LatticePlan& P) {
+static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes, int world, bool allow_bottom, LatticePlan& P) {
   const int n = (int)card.size();
   P.n = n;
   P.card = card;
+  // bottom tier: the last kBotL variables, when they are all binary
+  int bot = (allow_bottom && n >= kBotL) ? kBotL : 0;
+  for (int v = n - bot; v < n; ++v)
+    if (card[v] != 2) bot = 0;
+  const int max_L = std::min(n, std::max(1, env_int("OBN_LATTICE_MAX_L", 20)));
+  if (max_L < bot) bot = 0;
+  const double cells_bot = bot ? (double)kBotCells : 1.0;
   double joint = 1;
   for (int v = 0; v < n; ++v) joint *= card[v];
   if (joint >= 2147483648.0) return false;                          // dense joint table must fit int32 indexing
   // the largest L whose two largest adjacent levels (times all high cells) fit the budget
   int best_L = -1;
-  for (int L = std::min(n, 20); L >= 1; --L) {
+  for (int L = max_L; L >= std::max(1, bot); --L) {
     const int h = n - L;
+    const int Lm = L - bot;
     if (h > 16) break;
     if (world > 1 && ((1 << h) % world != 0 || (1 << h) < world)) continue;
     // multi-GPU balance: blocks are dealt whole, so the heaviest block (all high variables
@@ -50,10 +60,10 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
       for (int v = 0; v < h; ++v) { heavy *= card[v]; total *= 1.0 + card[v]; }
       if (heavy / total > 1.0 / (2.0 * world)) continue;
     }
-    // units per level by DP over the low variables: poly = prod (1 + c x)
+    // units per level by DP over the low (mid-tier) variables: poly = cells_bot * prod (1 + c x)
     std::vector<double> lvl(L + 1, 0.0);
-    lvl[0] = 1;
-    for (int i = 0; i < L; ++i)
+    lvl[0] = cells_bot;
+    for (int i = 0; i < Lm; ++i)
       for (int k = i + 1; k >= 1; --k) lvl[k] += lvl[k - 1] * card[h + i];
     double cells_all_high = 1, roots = 1, low = 1;
     for (int v = 0; v < h; ++v) { cells_all_high *= card[v]; roots *= 1.0 + card[v]; }
@@ -66,9 +76,12 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
     if (bytes <= (double)budget_bytes) { best_L = L; break; }
   }
   if (best_L < 0) return false;
-  const int L = best_L, h = n - L;
+  const int L = best_L, h = n - L, Lm = L - bot;
   P.L = L;
   P.h = h;
+  P.bot = bot;
+  P.Lm = Lm;
+  P.cells_bot = bot ? kBotCells : 1;
   P.cells_low = 1;
   for (int v = h; v < n; ++v) P.cells_low *= card[v];
   const uint32_t B = 1u << h;
@@ -100,26 +113,28 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
       P.slot[order[i]] = r * per + fill[r]++;
     }
   }
-  // low lattice: O(1) work per subset (products by peeling the lowest bit, tasks placed by rank)
-  const uint32_t NT = 1u << L;
-  std::vector<uint32_t> cl(NT, 1), off(NT, 0);
-  for (uint32_t T = 1; T < NT; ++T) cl[T] = cl[T & (T - 1)] * card[h + __builtin_ctz(T)];
-  P.level_units.assign(L + 1, 0);
-  P.level_max_units.assign(L + 1, 0);
-  std::vector<uint32_t> level_count(L + 1, 0);
-  for (uint32_t T = 0; T < NT; ++T) {
+  // low lattice over the mid-tier variables h..h+Lm-1; every table also holds all bottom variables
+  // (a factor cells_bot on the fast side).  O(1) work per subset.
+  const uint32_t NT = 1u << L, NM = 1u << Lm;
+  const uint32_t cb = (uint32_t)P.cells_bot;
+  std::vector<uint32_t> cl(NM, cb), off(NM, 0);
+  for (uint32_t T = 1; T < NM; ++T) cl[T] = cl[T & (T - 1)] * card[h + __builtin_ctz(T)];
+  P.level_units.assign(Lm + 1, 0);
+  P.level_max_units.assign(Lm + 1, 0);
+  std::vector<uint32_t> level_count(Lm + 1, 0);
+  for (uint32_t T = 0; T < NM; ++T) {
     const int k = __builtin_popcount(T);
     off[T] = (uint32_t)P.level_units[k];
     P.level_units[k] += cl[T];
     P.level_max_units[k] = std::max(P.level_max_units[k], cl[T]);
     ++level_count[k];
   }
-  std::vector<uint32_t> pre(L + 1, 1);                              // pre[i] = prod of the first i low cards
-  for (int i = 0; i < L; ++i) pre[i + 1] = pre[i] * card[h + i];
-  P.level_tasks.assign(L, {});
-  for (int k = 0; k < L; ++k) P.level_tasks[k].resize(level_count[k]);
-  std::vector<uint32_t> fill(L + 1, 0);
-  for (uint32_t T = 0; T + 1 < NT; ++T) {
+  std::vector<uint32_t> pre(Lm + 1, 1);                             // pre[i] = prod of the first i low cards
+  for (int i = 0; i < Lm; ++i) pre[i + 1] = pre[i] * card[h + i];
+  P.level_tasks.assign(std::max(Lm, 1), {});
+  for (int k = 0; k < Lm; ++k) P.level_tasks[k].resize(level_count[k]);
+  std::vector<uint32_t> fill(Lm + 1, 0);
+  for (uint32_t T = 0; T + 1 < NM; ++T) {
     const int k = __builtin_popcount(T);
     const int i = __builtin_ctz(~T);                                // lowest absent low variable
     MargTask& t = P.level_tasks[k][fill[k]++];
@@ -127,7 +142,7 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
     t.dst_off = off[T];
     t.hi = pre[i];                                                  // bits below i are all present in T
     t.r = card[h + i];
-    const uint32_t lo = cl[T & ~((2u << i) - 1u)];                  // T's variables above i
+    const uint32_t lo = cl[T & ~((2u << i) - 1u)];                  // T's variables above i (and the bottom tier)
     t.lo = lo;
     t.f_index = T;
     t.lo_shift = (t.r == 2 && lo >= 4 && (lo & (lo - 1)) == 0) ? __builtin_ctz(lo) : -1;
@@ -170,8 +185,15 @@ static int launch_marg_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks
   const uint32_t chunks = (uint32_t)((max_cells + kMargChunk - 1) / kMargChunk);
   for (size_t b = 0; b < n_tasks; b += 65535) {
     const uint32_t m = (uint32_t)std::min<size_t>(65535, n_tasks - b);
-    if (int rc = partials.reserve((size_t)m * chunks * sizeof(double))) return rc;
     (void)cudaGetLastError();
+    if (F == nullptr) {                                   // tables only: the bottom tier computes F
+      marg_kernel<<<dim3(chunks, m), kMargThreads, 0, c->stream>>>(d_tasks + b, mul, src, dst, ess, tt, nullptr);
+      OBN_CUDA(cudaGetLastError());
+      c->prof.total_launches += 1;
+      c->prof.count_launches += 1;
+      continue;
+    }
+    if (int rc = partials.reserve((size_t)m * chunks * sizeof(double))) return rc;
     marg_kernel<<<dim3(chunks, m), kMargThreads, 0, c->stream>>>(d_tasks + b, mul, src, dst, ess, tt, partials.as<double>());
     OBN_CUDA(cudaGetLastError());
     marg_reduce_kernel<<<(m + 127) / 128, 128, 0, c->stream>>>(d_tasks + b, m, chunks, partials.as<double>(), F, f_base);
@@ -179,6 +201,134 @@ static int launch_marg_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks
     c->prof.total_launches += 2;
     c->prof.count_launches += 1;
   }
+  return OBN_OK;
+}
+
+// The per-(slot, thread) program of bottom_lattice_kernel (obn_lattice.cuh): where the two sources
+// and the destination of every marginal cell of a 2^8-cell chunk are.  The table of pattern p
+// (bottom variables kept) has 2^popcount(p) cells; tables of one level are stored in ascending
+// pattern order; the parent of p is p with its highest absent bit i set, and digit i sits above
+// sh = popcount(p & (2^i - 1)) kept digits.  Patterns with sh >= 2 are done four cells at a time
+// (quad slots), the rest one cell at a time.  Returns false if the layout does not match the
+// kernel's compile-time slot table.
+struct BottomProgram {
+  std::vector<uint32_t> words;     // [kBotSlots][kBotThreads]
+  std::vector<uint16_t> patterns;  // [kBotSlots][kBotThreads] pattern of the item, kBotNoPattern when idle
+};
+static bool bottom_program(BottomProgram& out) {
+  std::vector<std::vector<uint32_t>> pats(kBotL + 1);
+  for (uint32_t p = 0; p < (uint32_t)kBotCells; ++p) pats[__builtin_popcount(p)].push_back(p);
+  std::vector<uint32_t> off(kBotCells, 0);
+  uint32_t cells_total = 0;
+  for (int k = kBotL; k >= 0; --k) {
+    for (size_t r = 0; r < pats[k].size(); ++r) off[pats[k][r]] = cells_total + (uint32_t)(r << k);
+    cells_total += (uint32_t)(pats[k].size() << k);
+  }
+  if (cells_total != (uint32_t)kBotExpanded) return false;
+  auto pivot = [](uint32_t p, int& i, uint32_t& sh) {
+    i = 31 - __builtin_clz((~p) & (uint32_t)(kBotCells - 1));
+    sh = (uint32_t)__builtin_popcount(p & ((1u << i) - 1u));
+  };
+  // what the kernel was compiled for: {level, quad slots, quad items, scalar slots, scalar items}
+  static const int expect[8][5] = {{7, 1, 192, 1, 256}, {6, 2, 400, 1, 192}, {5, 2, 416, 1, 128}, {4, 1, 256, 1, 96},
+                                   {3, 1, 100, 1, 48},  {2, 0, 0, 1, 112},   {1, 0, 0, 1, 16},    {0, 0, 0, 1, 1}};
+  out.words.assign((size_t)kBotSlots * kBotThreads, kBotIdleCell);
+  out.patterns.assign((size_t)kBotSlots * kBotThreads, kBotNoPattern);
+  for (int t = 0; t < kBotThreads; ++t) out.patterns[t] = (uint16_t)(kBotCells - 1);      // slot 0: the chunk itself
+  int slot = 1;
+  for (int k = kBotL - 1; k >= 0; --k) {
+    std::vector<uint32_t> reg, awk;
+    for (uint32_t p : pats[k]) {
+      int i;
+      uint32_t sh;
+      pivot(p, i, sh);
+      (k >= 2 && sh >= 2 ? reg : awk).push_back(p);
+    }
+    if (!reg.empty()) {
+      // a nearly empty last quad slot costs a whole slot: demote its patterns to the scalar slot
+      const size_t qpp = ((size_t)1 << k) / 4, nq = reg.size() * qpp;
+      if (nq % kBotThreads != 0 && nq % kBotThreads < 32) {
+        const size_t d = (nq % kBotThreads + qpp - 1) / qpp;
+        awk.insert(awk.end(), reg.end() - (ptrdiff_t)d, reg.end());
+        reg.resize(reg.size() - d);
+      }
+    }
+    std::vector<std::pair<uint32_t, uint16_t>> quads, cells;
+    for (uint32_t p : reg) {
+      int i;
+      uint32_t sh;
+      pivot(p, i, sh);
+      for (uint32_t c = 0; c < (1u << k); c += 4)
+        quads.push_back({bot_quad_word(off[p | (1u << i)] + ((c >> sh) << (sh + 1)) + (c & ((1u << sh) - 1u)), sh, off[p] + c), (uint16_t)p});
+    }
+    for (uint32_t p : awk) {
+      int i;
+      uint32_t sh;
+      pivot(p, i, sh);
+      for (uint32_t c = 0; c < (1u << k); ++c)
+        cells.push_back({bot_cell_word(off[p | (1u << i)] + ((c >> sh) << (sh + 1)) + (c & ((1u << sh) - 1u)), sh, off[p] + c), (uint16_t)p});
+    }
+    const int qs = (int)((quads.size() + kBotThreads - 1) / kBotThreads), ss = (int)((cells.size() + kBotThreads - 1) / kBotThreads);
+    const int* ex = expect[kBotL - 1 - k];
+    if (ex[0] != k || ex[1] != qs || ex[2] != (int)quads.size() || ex[3] != ss || ex[4] != (int)cells.size()) return false;
+    if (slot + qs + ss > kBotSlots) return false;
+    for (int it = 0; it < qs; ++it, ++slot)
+      for (int t = 0; t < kBotThreads; ++t) {
+        const size_t e = (size_t)it * kBotThreads + t;
+        out.words[(size_t)slot * kBotThreads + t] = e < quads.size() ? quads[e].first : kBotIdleQuad;
+        if (e < quads.size()) out.patterns[(size_t)slot * kBotThreads + t] = quads[e].second;
+      }
+    for (int it = 0; it < ss; ++it, ++slot)
+      for (int t = 0; t < kBotThreads; ++t) {
+        const size_t e = (size_t)it * kBotThreads + t;
+        if (e < cells.size()) {
+          out.words[(size_t)slot * kBotThreads + t] = cells[e].first;
+          out.patterns[(size_t)slot * kBotThreads + t] = cells[e].second;
+        }
+      }
+  }
+  return slot == kBotSlots;
+}
+
+// F of all 2^8 bottom patterns of every table of one level (the tables are the tasks' `dst`)
+static int launch_bottom_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks, uint64_t max_cells, uint64_t mul,
+                               const int32_t* base, const uint32_t* d_prog, const FixTable& ft, double ess, double* F,
+                               uint64_t f_base, int f_shift) {
+  const uint16_t* d_pat = reinterpret_cast<const uint16_t*>(d_prog + (size_t)kBotSlots * kBotThreads);
+  const uint64_t chunks = max_cells >> kBotL;
+  // enough CTAs to fill the GPU a few times over, as many chunks per CTA as that allows (<= 64)
+  const uint64_t target = (uint64_t)c->sm_count * 16;
+  uint64_t cpc = (chunks * n_tasks + target - 1) / target;
+  cpc = std::max<uint64_t>(1, std::min<uint64_t>({cpc, 64, chunks}));
+  const uint32_t groups = (uint32_t)((chunks + cpc - 1) / cpc);
+  for (size_t b = 0; b < n_tasks; b += 65535) {
+    const uint32_t m = (uint32_t)std::min<size_t>(65535, n_tasks - b);
+    (void)cudaGetLastError();
+    auto* Fx = reinterpret_cast<unsigned long long*>(F);
+    if (ft.lut)
+      bottom_lattice_kernel<true><<<dim3(groups, m), kBotThreads, 0, c->stream>>>(d_tasks + b, mul, base, d_prog, d_pat, ft, ess, Fx,
+                                                                                 f_base, f_shift, (uint32_t)cpc);
+    else
+      bottom_lattice_kernel<false><<<dim3(groups, m), kBotThreads, 0, c->stream>>>(d_tasks + b, mul, base, d_prog, d_pat, ft, ess, Fx,
+                                                                                  f_base, f_shift, (uint32_t)cpc);
+    OBN_CUDA(cudaGetLastError());
+    c->prof.total_launches += 1;
+    c->prof.count_launches += 1;
+  }
+  return OBN_OK;
+}
+
+// The joint table over all variables: the only pass over the data in lattice mode.
+static int joint_count(obn_ctx* c, const obn_dataset* ds, int32_t* J, uint64_t cells) {
+  OBN_CUDA(cudaMemsetAsync(J, 0, cells * 4, c->stream));
+  JointCards jc{};
+  for (size_t v = 0; v < ds->n_vars; ++v) jc.c[v] = ds->cards[v];
+  const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
+  (void)cudaGetLastError();
+  joint_count_kernel<<<std::max(1u, (n_vec + 127) / 128), 128, 0, c->stream>>>(ds->data, ds->stride, (uint32_t)ds->n_rows, (int)ds->n_vars, jc, J);
+  OBN_CUDA(cudaGetLastError());
+  ++c->prof.total_launches;
+  ++c->prof.count_launches;
   return OBN_OK;
 }
 
@@ -206,79 +356,248 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     fprintf(stderr, "[obn_es_lattice] %-14s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_dbg).count());
     t_dbg = now;
   };
-  LatticePlan P;
-  if (!plan_lattice(ds->cards, budget, world, P))
-    return fail(OBN_ERR_UNSUPPORTED, "marginalisation lattice does not fit (joint table >= 2^31 cells or too little memory)");
-  lap("plan");
-  const int h = P.h, L = P.L;
-  const uint32_t B = 1u << h, NT = 1u << L;
-  if (dbg) fprintf(stderr, "[obn_es_lattice] n=%d h=%d L=%d budget=%.1f GB\n", n, h, L, budget / 1073741824.0);
+  const bool use_graph = env_int("OBN_LATTICE_GRAPH", 1) != 0;
   const size_t combs = (size_t)1 << n;
+  EsPool& pool = c->es_pool;
+  LatticeGraphCache& G = pool.lattice;
+  cudaEvent_t e0 = c->ev0, e1 = c->ev1;
+  // what the captured graph depends on: the search shape and every pooled buffer it points into
+  auto make_key = [&]() {
+    std::vector<uint64_t> k;
+    uint64_t ess_bits = 0;
+    memcpy(&ess_bits, &e->ess, 8);
+    k.insert(k.end(), {(uint64_t)n, (uint64_t)ds->n_rows, ess_bits, (uint64_t)rank, (uint64_t)world,
+                       (uint64_t)env_int("OBN_LATTICE_BUDGET_GB", 24), (uint64_t)env_int("OBN_LATTICE_BOTTOM", 1),
+                       (uint64_t)env_int("OBN_LATTICE_MAX_L", 20), (uint64_t)env_int("OBN_LATTICE_NO_LUT", 0)});
+    for (int v = 0; v < n; ++v) k.push_back(ds->cards[v]);
+    for (const DevBuf* d : {&pool.d_F, &pool.d_root, &pool.d_pp[0], &pool.d_pp[1], &pool.d_tasks, &pool.d_partials, &pool.d_lut_a, &pool.d_lutF, &pool.d_prog})
+      k.push_back((uint64_t)(uintptr_t)d->p);
+    return k;
+  };
+  const bool hit = use_graph && G.exec && G.key == make_key();
+  if (dbg) fprintf(stderr, "[obn_es_lattice] graph cache %s\n", hit ? "hit" : "miss");
+  if (!hit) {
+    G.clear();
+    LatticePlan P;
+    if (!plan_lattice(ds->cards, budget, world, env_int("OBN_LATTICE_BOTTOM", 1) != 0, P))
+      return fail(OBN_ERR_UNSUPPORTED, "marginalisation lattice does not fit (joint table >= 2^31 cells or too little memory)");
+    lap("plan");
+    const int h = P.h, L = P.L, Lm = P.Lm;
+    const bool bot = P.bot != 0;
+    const uint32_t B = 1u << h, NT = 1u << L;
+    if (dbg) fprintf(stderr, "[obn_es_lattice] n=%d h=%d L=%d bottom=%d budget=%.1f GB\n", n, h, L, P.bot, budget / 1073741824.0);
 
-  // ---- device buffers ---------------------------------------------------------------------
-  uint64_t cells_all_high = P.cells_high[B - 1], buf_units = 0;
-  for (int k = 0; k < L; ++k) buf_units = std::max<uint64_t>(buf_units, P.level_units[k]);
-  if (int rc = c->es_pool.d_F.reserve(combs * sizeof(double))) return rc;
-  e->F = c->es_pool.d_F.as<double>();
-  if (int rc = c->es_pool.d_root.reserve(std::max<uint64_t>(P.root_cells, 4) * 4)) return rc;
-  for (int i = 0; i < 2; ++i)
-    if (int rc = c->es_pool.d_pp[i].reserve(std::max<uint64_t>(buf_units * cells_all_high, 4) * 4)) return rc;
-  lap("alloc");
-  // tasks: low levels then root levels, one upload
-  size_t n_all = 1;
-  std::vector<size_t> low_at(L + 1, 0), root_at(h + 1, 0);
-  for (int k = 0; k < L; ++k) { low_at[k] = n_all; n_all += P.level_tasks[k].size(); }
-  for (int k = 0; k < h; ++k) { root_at[k] = n_all; n_all += P.root_tasks[k].size(); }
-  const size_t joint_task_at = 0;
-  if (int rc = c->es_pool.d_tasks.reserve(n_all * sizeof(MargTask))) return rc;
-  if (int rc = c->h_in.reserve(n_all * sizeof(MargTask))) return rc;               // page-locked staging
-  {
-    MargTask* all = c->h_in.as<MargTask>();
-    MargTask t{};
-    t.f_index = P.slot[B - 1] * NT + (NT - 1);
-    t.lo_shift = -1;
-    all[0] = t;
-    for (int k = 0; k < L; ++k)
-      if (!P.level_tasks[k].empty()) memcpy(all + low_at[k], P.level_tasks[k].data(), P.level_tasks[k].size() * sizeof(MargTask));
-    for (int k = 0; k < h; ++k)
-      if (!P.root_tasks[k].empty()) memcpy(all + root_at[k], P.root_tasks[k].data(), P.root_tasks[k].size() * sizeof(MargTask));
-  }
-  OBN_CUDA(cudaMemcpyAsync(c->es_pool.d_tasks.p, c->h_in.p, n_all * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
-  OBN_CUDA(cudaStreamSynchronize(c->stream));                                        // h_in is reused by run_batch
-  if (int rc = c->es_pool.d_slot.reserve(B * 4)) return rc;
-  OBN_CUDA(cudaMemcpyAsync(c->es_pool.d_slot.p, P.slot.data(), B * 4, cudaMemcpyHostToDevice, c->stream));
-  e->h = h;
-  e->L = L;
-
-  lap("tasks upload");
-  // ---- term tables: one per distinct cell count (device libm; this is the fast mode) ---------
-  TermTable tt{nullptr, nullptr, 0, 0};
-  {
-    // distinct cell counts of all subsets = distinct products over sub-multisets of the cards
-    std::vector<uint32_t> distinct{1};
-    for (int v = 0; v < n && distinct.size() <= 4096; ++v) {
-      const size_t m = distinct.size();
-      for (size_t i = 0; i < m; ++i) {
-        const uint64_t p = (uint64_t)distinct[i] * ds->cards[v];
-        if (p < ((uint64_t)1 << 31)) distinct.push_back((uint32_t)p);
+    // ---- device buffers (all reserved before the capture starts) ----------------------------
+    uint64_t cells_all_high = P.cells_high[B - 1], buf_units = 0;
+    for (int k = 0; k < Lm; ++k) buf_units = std::max<uint64_t>(buf_units, P.level_units[k]);
+    if (int rc = pool.d_F.reserve(combs * sizeof(double))) return rc;
+    if (int rc = pool.d_root.reserve(std::max<uint64_t>(P.root_cells, 4) * 4)) return rc;
+    for (int i = 0; i < 2; ++i)
+      if (int rc = pool.d_pp[i].reserve(std::max<uint64_t>(buf_units * cells_all_high, 4) * 4)) return rc;
+    if (!bot) {
+      size_t need = (size_t)((P.cells_high[B - 1] * P.cells_low + kMargChunk - 1) / kMargChunk);
+      for (int k = 0; k < h; ++k)
+        need = std::max(need, std::min<size_t>(65535, P.root_tasks[k].size()) *
+                                  (size_t)(((uint64_t)P.root_level_max[k] * P.cells_low + kMargChunk - 1) / kMargChunk));
+      for (int k = 0; k < Lm; ++k)
+        need = std::max(need, std::min<size_t>(65535, P.level_tasks[k].size()) *
+                                  (size_t)(((uint64_t)P.level_max_units[k] * cells_all_high + kMargChunk - 1) / kMargChunk));
+      if (int rc = pool.d_partials.reserve(need * sizeof(double))) return rc;
+    }
+    lap("alloc");
+    // tasks: low levels then root levels, one upload
+    size_t n_all = 1;
+    std::vector<size_t> low_at(Lm + 1, 0), root_at(h + 1, 0);
+    for (int k = 0; k < Lm; ++k) { low_at[k] = n_all; n_all += P.level_tasks[k].size(); }
+    for (int k = 0; k < h; ++k) { root_at[k] = n_all; n_all += P.root_tasks[k].size(); }
+    const size_t joint_task_at = 0;
+    if (int rc = pool.d_tasks.reserve(n_all * sizeof(MargTask))) return rc;
+    if (int rc = c->h_in.reserve(n_all * sizeof(MargTask))) return rc;               // page-locked staging
+    {
+      MargTask* all = c->h_in.as<MargTask>();
+      MargTask t{};
+      t.f_index = P.slot[B - 1] * NT + (NT - 1);
+      t.lo_shift = -1;
+      if (bot) {
+        // bottom tier: task 0 describes a block's root table R_H (base = R_H, mul = cells of H)
+        t.hi = 1;
+        t.lo = (uint32_t)P.cells_low;
+        t.f_index = (1u << Lm) - 1u;
       }
-      std::sort(distinct.begin(), distinct.end());
-      distinct.erase(std::unique(distinct.begin(), distinct.end()), distinct.end());
+      all[0] = t;
+      for (int k = 0; k < Lm; ++k)
+        if (!P.level_tasks[k].empty()) memcpy(all + low_at[k], P.level_tasks[k].data(), P.level_tasks[k].size() * sizeof(MargTask));
+      for (int k = 0; k < h; ++k)
+        if (!P.root_tasks[k].empty()) memcpy(all + root_at[k], P.root_tasks[k].data(), P.root_tasks[k].size() * sizeof(MargTask));
     }
-    const size_t stride = ds->n_rows + 1;
-    if (distinct.size() <= 256 && distinct.size() * stride * 8 <= ((size_t)2 << 30)) {
-      std::vector<double> a(distinct.size());
-      for (size_t i = 0; i < distinct.size(); ++i) a[i] = e->ess / (double)(size_t)distinct[i];
-      if (int rc = c->es_pool.d_lut_a.reserve(a.size() * 8)) return rc;
-      if (int rc = c->es_pool.d_lutF.reserve(a.size() * stride * 8)) return rc;
-      OBN_CUDA(cudaMemcpyAsync(c->es_pool.d_lut_a.p, a.data(), a.size() * 8, cudaMemcpyHostToDevice, c->stream));
-      OBN_CUDA(cudaStreamSynchronize(c->stream));          // `a` leaves scope
+    OBN_CUDA(cudaMemcpyAsync(pool.d_tasks.p, c->h_in.p, n_all * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
+    OBN_CUDA(cudaStreamSynchronize(c->stream));                                        // h_in is reused by run_batch
+    if (int rc = pool.d_slot.reserve(B * 4)) return rc;
+    OBN_CUDA(cudaMemcpyAsync(pool.d_slot.p, P.slot.data(), B * 4, cudaMemcpyHostToDevice, c->stream));
+    OBN_CUDA(cudaStreamSynchronize(c->stream));                                        // P.slot is a local
+    if (bot) {
+      BottomProgram bp;
+      if (!bottom_program(bp)) return fail(OBN_ERR_UNSUPPORTED, "bottom program does not match the kernel's slot table");
+      if (int rc = pool.d_prog.reserve(bp.words.size() * 4 + bp.patterns.size() * 2)) return rc;
+      OBN_CUDA(cudaMemcpy(pool.d_prog.p, bp.words.data(), bp.words.size() * 4, cudaMemcpyHostToDevice));
+      OBN_CUDA(cudaMemcpy(pool.d_prog.as<char>() + bp.words.size() * 4, bp.patterns.data(), bp.patterns.size() * 2, cudaMemcpyHostToDevice));
+    }
+    lap("tasks upload");
+
+    // ---- term tables: one per distinct cell count (device libm; this is the fast mode) -------
+    TermTable tt{nullptr, nullptr, 0, 0};
+    FixTable ft{nullptr, nullptr, 0, 0, 1.0};
+    if (bot) {
+      // fixed-point scale: |F| <= N * (ln(N + ess) + max |lgamma(a)| + 1) must stay below 2^62
+      double joint_cells = 1;
+      for (int v = 0; v < n; ++v) joint_cells *= ds->cards[v];
+      const double lg = std::max(std::fabs(std::lgamma(e->ess / joint_cells)), std::fabs(std::lgamma(e->ess)));
+      const double bound = (double)ds->n_rows * (std::log((double)ds->n_rows + e->ess + 1.0) + lg + 1.0) + 1.0;
+      const int shift = std::max(0, std::min(40, 62 - (int)std::ceil(std::log2(bound))));
+      ft.scale = std::ldexp(1.0, shift);
+    }
+    {
+      // distinct cell counts of all subsets = distinct products over sub-multisets of the cards
+      std::vector<uint32_t> distinct{1};
+      for (int v = 0; v < n && distinct.size() <= 4096; ++v) {
+        const size_t m = distinct.size();
+        for (size_t i = 0; i < m; ++i) {
+          const uint64_t p = (uint64_t)distinct[i] * ds->cards[v];
+          if (p < ((uint64_t)1 << 31)) distinct.push_back((uint32_t)p);
+        }
+        std::sort(distinct.begin(), distinct.end());
+        distinct.erase(std::unique(distinct.begin(), distinct.end()), distinct.end());
+      }
+      const size_t stride = ds->n_rows + 1;
+      if (distinct.size() <= 256 && distinct.size() * stride * 8 <= ((size_t)2 << 30) && !env_int("OBN_LATTICE_NO_LUT", 0)) {
+        std::vector<double> a(distinct.size());
+        for (size_t i = 0; i < distinct.size(); ++i) a[i] = e->ess / (double)(size_t)distinct[i];
+        if (int rc = pool.d_lut_a.reserve(a.size() * 8)) return rc;
+        if (int rc = pool.d_lutF.reserve(a.size() * stride * 8)) return rc;
+        OBN_CUDA(cudaMemcpyAsync(pool.d_lut_a.p, a.data(), a.size() * 8, cudaMemcpyHostToDevice, c->stream));
+        OBN_CUDA(cudaStreamSynchronize(c->stream));          // `a` leaves scope
+        (void)cudaGetLastError();
+        const dim3 grid((unsigned)((stride + 255) / 256), (unsigned)a.size());
+        if (bot) {
+          lut_fill_fix_kernel<<<grid, 256, 0, c->stream>>>(pool.d_lutF.as<long long>(), pool.d_lut_a.as<double>(), stride, ft.scale);
+          ft.lut = pool.d_lutF.as<long long>();
+          ft.lut_a = pool.d_lut_a.as<double>();
+          ft.n_lut = (int)a.size();
+          ft.stride = stride;
+        } else {
+          lut_fill_kernel<<<grid, 256, 0, c->stream>>>(pool.d_lutF.as<double>(), pool.d_lut_a.as<double>(), stride);
+          tt = TermTable{pool.d_lutF.as<double>(), pool.d_lut_a.as<double>(), (int)a.size(), stride};
+        }
+        OBN_CUDA(cudaGetLastError());
+      }
+    }
+    lap("term tables");
+
+    // ---- the lattice itself: thousands of small dependent launches (blocks x levels x 2), captured
+    // into ONE CUDA graph so that the GPU never waits for the host thread (which shares its cores
+    // with the other ranks' processes) ------------------------------------------------------------
+    int32_t* root = pool.d_root.as<int32_t>();
+    double* F = pool.d_F.as<double>();
+    const MargTask* d_tasks = pool.d_tasks.as<MargTask>();
+    const uint64_t launches_before = c->prof.total_launches;
+    OBN_CUDA(cudaStreamSynchronize(c->stream));
+    if (use_graph) OBN_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    else {
+      // eager path (debugging): the joint table has to exist before the first launch
+      if (int rc = joint_count(c, ds, root + P.root_off[B - 1], P.cells_high[B - 1] * P.cells_low)) return rc;
+      OBN_CUDA(cudaEventRecord(e0, c->stream));
+    }
+    auto abort_capture = [&]() {
+      if (!use_graph) return;
+      cudaGraph_t g = nullptr;
+      cudaStreamEndCapture(c->stream, &g);
+      if (g) cudaGraphDestroy(g);
+    };
+    auto lap_if = [&](const char* what) { if (!use_graph) lap(what); };
+    const uint32_t per = B / (uint32_t)world;
+    const size_t slice = (size_t)per * NT;                       // this rank's F words
+    const uint32_t* d_prog = pool.d_prog.as<uint32_t>();
+    if (bot) {
+      if (cudaMemsetAsync(F + (size_t)rank * slice, 0, slice * 8, c->stream) != cudaSuccess) {
+        abort_capture();
+        return fail(OBN_ERR_CUDA, "F memset failed");
+      }
+    } else {
+      const uint64_t cells = P.cells_high[B - 1] * P.cells_low;
+      const uint32_t chunks = (uint32_t)((cells + kMargChunk - 1) / kMargChunk);
       (void)cudaGetLastError();
-      lut_fill_kernel<<<dim3((unsigned)((stride + 255) / 256), (unsigned)a.size()), 256, 0, c->stream>>>(
-          c->es_pool.d_lutF.as<double>(), c->es_pool.d_lut_a.as<double>(), stride);
-      OBN_CUDA(cudaGetLastError());
-      tt = TermTable{c->es_pool.d_lutF.as<double>(), c->es_pool.d_lut_a.as<double>(), (int)a.size(), stride};
+      table_f_kernel<<<chunks, kMargThreads, 0, c->stream>>>(root + P.root_off[B - 1], cells, e->ess, tt, pool.d_partials.as<double>());
+      marg_reduce_kernel<<<1, 128, 0, c->stream>>>(d_tasks + joint_task_at, 1, chunks, pool.d_partials.as<double>(), F, 0);
+      if (cudaGetLastError() != cudaSuccess) { abort_capture(); return fail(OBN_ERR_CUDA, "joint table launch failed"); }
+      c->prof.total_launches += 2;
     }
+    lap_if("joint");
+    // root lattice
+    for (int k = h - 1; k >= 0; --k)
+      if (int rc = launch_marg_level(c, d_tasks + root_at[k], P.root_tasks[k].size(), (uint64_t)P.root_level_max[k] * P.cells_low,
+                                     1, root, root, e->ess, tt, pool.d_partials, bot ? nullptr : F, 0)) {
+        abort_capture();
+        return rc;
+      }
+    lap_if("roots");
+    // blocks of this rank
+    for (uint32_t H = 0; H < B; ++H) {
+      const uint32_t s = P.slot[H];
+      if (s / per != (uint32_t)rank) continue;
+      const uint64_t mul = P.cells_high[H];
+      if (bot)                                                  // F of R_H and of its 255 bottom sub-patterns
+        if (int rc = launch_bottom_level(c, d_tasks, 1, mul * P.cells_low, mul, root + P.root_off[H], d_prog, ft, e->ess, F,
+                                         (uint64_t)s * NT, Lm)) {
+          abort_capture();
+          return rc;
+        }
+      for (int k = Lm - 1; k >= 0; --k) {
+        const int32_t* src = (k == Lm - 1) ? root + P.root_off[H] : pool.d_pp[(k + 1) & 1].as<int32_t>();
+        int rc = launch_marg_level(c, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul, src,
+                                   pool.d_pp[k & 1].as<int32_t>(), e->ess, tt, pool.d_partials, bot ? nullptr : F, (uint64_t)s * NT);
+        if (rc == OBN_OK && bot)
+          rc = launch_bottom_level(c, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul,
+                                   pool.d_pp[k & 1].as<int32_t>(), d_prog, ft, e->ess, F, (uint64_t)s * NT, Lm);
+        if (rc != OBN_OK) {
+          abort_capture();
+          return rc;
+        }
+      }
+    }
+    if (bot) {
+      (void)cudaGetLastError();
+      fix_to_double_kernel<<<(unsigned)((slice + 255) / 256), 256, 0, c->stream>>>(F + (size_t)rank * slice, slice, 1.0 / ft.scale);
+      if (cudaGetLastError() != cudaSuccess) { abort_capture(); return fail(OBN_ERR_CUDA, "fix_to_double launch failed"); }
+      ++c->prof.total_launches;
+    }
+    G.h = h;
+    G.L = L;
+    G.per = per;
+    G.joint_off = P.root_off[B - 1];
+    G.joint_cells = P.cells_high[B - 1] * P.cells_low;
+    G.launches = c->prof.total_launches - launches_before;
+    if (use_graph) {
+      cudaGraph_t graph = nullptr;
+      OBN_CUDA(cudaStreamEndCapture(c->stream, &graph));
+      const cudaError_t ge = cudaGraphInstantiate(&G.exec, graph, 0);
+      cudaGraphDestroy(graph);
+      if (ge != cudaSuccess) {
+        G.exec = nullptr;
+        return fail(OBN_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ge));
+      }
+      G.key = make_key();
+      lap("graph build");
+    } else {
+      OBN_CUDA(cudaEventRecord(e1, c->stream));
+      OBN_CUDA(cudaStreamSynchronize(c->stream));
+    }
+  } else {
+    c->prof.total_launches += G.launches;
+  }
+  e->F = pool.d_F.as<double>();
+  e->h = G.h;
+  e->L = G.L;
+  {
     // accounting: what the reference would have read for the subsets whose scores are used:
     // sum over k <= max_parents+1 of C(n,k) * k * N bytes
     double alg = 0, binom = 1;
@@ -288,99 +607,17 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     }
     c->prof.algorithmic_bytes += alg / world;
   }
-
-  lap("term tables");
-  // ---- 1. joint table (the only pass over the data) -------------------------------------------
-  int32_t* root = c->es_pool.d_root.as<int32_t>();
-  {
-    const uint64_t cells = P.cells_high[B - 1] * P.cells_low;
-    int32_t* J = root + P.root_off[B - 1];
-    OBN_CUDA(cudaMemsetAsync(J, 0, cells * 4, c->stream));
-    JointCards jc{};
-    for (int v = 0; v < n; ++v) jc.c[v] = ds->cards[v];
-    const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
-    (void)cudaGetLastError();
-    joint_count_kernel<<<std::max(1u, (n_vec + 127) / 128), 128, 0, c->stream>>>(ds->data, ds->stride, (uint32_t)ds->n_rows, n, jc, J);
-    OBN_CUDA(cudaGetLastError());
-    ++c->prof.total_launches;
-    ++c->prof.count_launches;
-  }
-  cudaEvent_t e0 = c->ev0, e1 = c->ev1;
-  const MargTask* d_tasks = c->es_pool.d_tasks.as<MargTask>();
-  // The lattice is thousands of small dependent launches (blocks x levels x 2): capture them into
-  // ONE CUDA graph so that the GPU never waits for the host thread (which shares its cores with
-  // the other ranks' processes).  All buffers are reserved before the capture starts.
-  {
-    size_t need = (size_t)((P.cells_high[B - 1] * P.cells_low + kMargChunk - 1) / kMargChunk);
-    for (int k = 0; k < h; ++k)
-      need = std::max(need, std::min<size_t>(65535, P.root_tasks[k].size()) *
-                                (size_t)(((uint64_t)P.root_level_max[k] * P.cells_low + kMargChunk - 1) / kMargChunk));
-    for (int k = 0; k < L; ++k)
-      need = std::max(need, std::min<size_t>(65535, P.level_tasks[k].size()) *
-                                (size_t)(((uint64_t)P.level_max_units[k] * cells_all_high + kMargChunk - 1) / kMargChunk));
-    if (int rc = c->es_pool.d_partials.reserve(need * sizeof(double))) return rc;
-  }
-  const bool use_graph = env_int("OBN_LATTICE_GRAPH", 1) != 0;
-  OBN_CUDA(cudaStreamSynchronize(c->stream));
-  if (use_graph) OBN_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
-  else OBN_CUDA(cudaEventRecord(e0, c->stream));
-  const bool dbg_saved = dbg;
-  auto lap_if = [&](const char* what) { if (!use_graph) lap(what); };
-  (void)dbg_saved;
-  {
-    const uint64_t cells = P.cells_high[B - 1] * P.cells_low;
-    const uint32_t chunks = (uint32_t)((cells + kMargChunk - 1) / kMargChunk);
-    if (int rc = c->es_pool.d_partials.reserve((size_t)chunks * 8)) return rc;
-    (void)cudaGetLastError();
-    table_f_kernel<<<chunks, kMargThreads, 0, c->stream>>>(root + P.root_off[B - 1], cells, e->ess, tt, c->es_pool.d_partials.as<double>());
-    OBN_CUDA(cudaGetLastError());
-    marg_reduce_kernel<<<1, 128, 0, c->stream>>>(d_tasks + joint_task_at, 1, chunks, c->es_pool.d_partials.as<double>(), e->F, 0);
-    OBN_CUDA(cudaGetLastError());
-  }
-  lap_if("joint");
-  // ---- 2. root lattice --------------------------------------------------------------------------
-  for (int k = h - 1; k >= 0; --k)
-    if (int rc = launch_marg_level(c, d_tasks + root_at[k], P.root_tasks[k].size(), (uint64_t)P.root_level_max[k] * P.cells_low,
-                                   1, root, root, e->ess, tt, c->es_pool.d_partials, e->F, 0)) {
-      if (use_graph) { cudaGraph_t g = nullptr; cudaStreamEndCapture(c->stream, &g); if (g) cudaGraphDestroy(g); }
-      return rc;
-    }
-  lap_if("roots");
-  // ---- 3. blocks of this rank ---------------------------------------------------------------------
-  const uint32_t per = B / (uint32_t)world;
-  for (uint32_t H = 0; H < B; ++H) {
-    const uint32_t s = P.slot[H];
-    if (s / per != (uint32_t)rank) continue;
-    const uint64_t mul = P.cells_high[H];
-    for (int k = L - 1; k >= 0; --k) {
-      const int32_t* src = (k == L - 1) ? root + P.root_off[H] : c->es_pool.d_pp[(k + 1) & 1].as<int32_t>();
-      if (int rc = launch_marg_level(c, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul,
-                                     src, c->es_pool.d_pp[k & 1].as<int32_t>(), e->ess, tt, c->es_pool.d_partials, e->F, (uint64_t)s * NT)) {
-        if (use_graph) { cudaGraph_t g = nullptr; cudaStreamEndCapture(c->stream, &g); if (g) cudaGraphDestroy(g); }
-        return rc;
-      }
-    }
-  }
   if (use_graph) {
-    cudaGraph_t graph = nullptr;
-    cudaGraphExec_t exec = nullptr;
-    OBN_CUDA(cudaStreamEndCapture(c->stream, &graph));
-    cudaError_t ge = cudaGraphInstantiate(&exec, graph, 0);
-    if (ge != cudaSuccess) {
-      cudaGraphDestroy(graph);
-      return fail(OBN_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ge));
-    }
-    lap("graph build");
+    // the joint table is the only pass over the data; then the whole lattice is one graph launch
+    if (int rc = joint_count(c, ds, pool.d_root.as<int32_t>() + G.joint_off, G.joint_cells)) return rc;
     OBN_CUDA(cudaEventRecord(e0, c->stream));
-    ge = cudaGraphLaunch(exec, c->stream);
+    cudaError_t ge = cudaGraphLaunch(G.exec, c->stream);
     if (ge == cudaSuccess) ge = cudaEventRecord(e1, c->stream);
     if (ge == cudaSuccess) ge = cudaStreamSynchronize(c->stream);
-    cudaGraphExecDestroy(exec);
-    cudaGraphDestroy(graph);
-    if (ge != cudaSuccess) return fail(OBN_ERR_CUDA, "lattice graph launch failed: %s", cudaGetErrorString(ge));
-  } else {
-    OBN_CUDA(cudaEventRecord(e1, c->stream));
-    OBN_CUDA(cudaStreamSynchronize(c->stream));
+    if (ge != cudaSuccess) {
+      G.clear();
+      return fail(OBN_ERR_CUDA, "lattice graph launch failed: %s", cudaGetErrorString(ge));
+    }
   }
   lap("blocks");
   float ms = 0;
@@ -388,7 +625,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   c->prof.count_kernel_ms += ms;
   // level lists for the DP: subsets grouped by size, ascending inside a level (= Gosper order)
   {
-    if (int rc = c->es_pool.d_masks.reserve(combs * sizeof(uint32_t))) return rc;
+    if (int rc = pool.d_masks.reserve(combs * sizeof(uint32_t))) return rc;
     EsLevels lv{};
     uint64_t off = 0, binom = 1;
     for (int k = 0; k <= n; ++k) {
@@ -405,7 +642,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     ++c->prof.total_launches;
   }
   e->use_F = true;
-  e->f_per_rank = (size_t)per * NT;
+  e->f_per_rank = (size_t)G.per << G.L;
   return OBN_OK;
 }
 

@@ -184,3 +184,37 @@ def test_exhaustive_search_lattice_mode(which, max_parents, monkeypatch):
         assert len(pa) <= max_parents
         total += oracle.bdeu_local_score(ods, v, pa, 1.0)
     assert total == pytest.approx(got["best_score"], rel=1e-9)
+
+
+@pytest.mark.parametrize("cards,max_l,no_lut", [
+    ([2] * 13, 20, 0),                      # one block: h = 0, 5 mid + 8 bottom variables
+    ([2] * 13, 10, 0),                      # 8 blocks of 2 mid + 8 bottom variables
+    ([3, 2, 4, 2, 3] + [2] * 8, 11, 0),     # mixed cardinalities above a binary bottom tier, 4 blocks
+    ([2] * 9, 8, 0),                        # no mid tier at all (Lm = 0), 2 blocks
+    ([2] * 11, 20, 1),                      # no term tables: libm fallback inside the bottom kernel
+])
+def test_lattice_bottom_tier_equals_hbm_tiers(cards, max_l, no_lut, monkeypatch):
+    """The shared-memory bottom tier (last 8 binary variables) and the all-HBM lattice build the same
+    tables; F differs only by summation order (fixed point vs fp64), so the optimum agrees to 1e-11."""
+    n = len(cards)
+    net = nw.random_network(n, n + 4, 3, cards, seed=5)
+    codes, cards_seen = ranked(net.sample(5000, 7))
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards_seen)
+    monkeypatch.setenv("OBN_ES_LATTICE", "1")
+    monkeypatch.setenv("OBN_LATTICE_MAX_L", str(max_l))
+    monkeypatch.setenv("OBN_LATTICE_NO_LUT", str(no_lut))
+    out = {}
+    for bottom in ("0", "1", "1"):          # the second "1" run replays the cached graph
+        monkeypatch.setenv("OBN_LATTICE_BOTTOM", bottom)
+        g = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), n - 1, exact_order=0)
+        st = L.structure_learning.last_es_stats()
+        assert st["lattice"]
+        out.setdefault(bottom, []).append((st["best_score"], pdag_to_adj(g, n).tolist()))
+    (s0, a0), = out["0"]
+    (s1, a1), (s2, a2) = out["1"]
+    assert s1 == s2 and a1 == a2                      # deterministic, cache hit or not
+    assert s1 == pytest.approx(s0, rel=1e-11)
+    ods = oracle.Dataset(codes, cards_seen)            # the DAG really has that score (ties may pick another member
+    adj = np.array(a1)                                 # of the equivalence class than the fp64-order run)
+    total = sum(oracle.bdeu_local_score(ods, v, [int(p) for p in np.nonzero(adj[:, v])[0]], 1.0) for v in range(n))
+    assert total == pytest.approx(s1, rel=1e-9)
