@@ -13,7 +13,7 @@ struct obn_es {
   double ess = 1.0;
   size_t max_parents = 0;
   int exact = 0;
-  // DP tables (device).  bl_* are indexed [parent_set_mask * n + child].
+  // DP tables (device).  bl_* are indexed [(parent candidates + child) mask * n + child] (es_dp_warp_kernel).
   double* bl_score = nullptr;
   uint32_t* bl_ps = nullptr;
   double* best_gs = nullptr;
@@ -33,44 +33,72 @@ struct obn_es {
 
 namespace obn {
 
-// exhaustive_search.cpp:59-116 for one subset W per thread.  Reads only entries of the
-// previous level (parent sets of size k-2 / k-1), writes entries of this one.
-__global__ void es_dp_kernel(const unsigned long long* masks, size_t T, int k, int n, const double* scores,
-                             double* bl_score, uint32_t* bl_ps, double* best_gs, uint8_t* best_ch) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= T) return;
-  const uint32_t W = (uint32_t)masks[t];
-  double bgs = 0.0;
-  int bch = -1;
-  int ci = 0;
-  for (uint32_t m = W; m; m &= m - 1, ++ci) {
-    const int child = __ffs((int)m) - 1;
-    const uint32_t pa = W & ~(1u << child);
-    const double ls = scores ? scores[t * (size_t)k + ci] : -INFINITY;          // :65-73
-    double bls = ls;
-    uint32_t bps = pa;
-    for (uint32_t q = pa; q; q &= q - 1) {                                       // :75-87
-      const uint32_t sub = pa & ~(q & (0u - q));
-      const double s = bl_score[(size_t)sub * n + child];
+// exhaustive_search.cpp:59-116 for one subset W per WARP, lane c = candidate child c.
+//
+// bl_score / bl_ps rows are indexed by the subset that PRODUCED them: entry [W * n + c] is the best
+// (score, parent set) of child c over the parent sets inside W - {c} (the reference keeps the same
+// value under the key (W - {c}, c), :33-36).  The candidates of (W, c) are its own parent set W - {c}
+// and the entries [ (W - {j}) * n + c ] for j in W - {c} (:75-87), so for a fixed j all lanes read ONE
+// row: k coalesced row reads and one row write per subset instead of k (k - 1) scattered sectors.
+// Ties are broken exactly like the serial loops: `>=` in ascending j, then the sink scan in
+// ascending child order with the reference's `bgs >= 0 || gs > bgs`.
+//   LIST   uint32_t (lattice level lists) or unsigned long long (the host's Gosper lists)
+//   USE_F  local scores from the lattice, ls(c | W - c) = F(W) - F(W - c), F block-major:
+//          index = slot[S & (2^h - 1)] << L | S >> h;  else scores[t * k + rank of c in W]
+template <typename LIST, bool USE_F>
+__global__ void __launch_bounds__(128) es_dp_warp_kernel(const LIST* list, size_t T, int k, int n, bool calc, const double* scores,
+                                                       const double* F, const uint32_t* slot, int h, int L, double* bl_score,
+                                                       uint32_t* bl_ps, double* best_gs, uint8_t* best_ch) {
+  const size_t t = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (t >= T) return;                                     // whole warps leave together
+  const int c = threadIdx.x & 31;
+  const uint32_t W = (uint32_t)list[t];
+  const bool active = (W >> c) & 1u;
+  const uint32_t pa = W & ~(1u << c);
+  double bls = -INFINITY;
+  uint32_t bps = pa;
+  if (active && calc) {                                   // :65-73
+    if (USE_F) {
+      const uint32_t hm = (1u << h) - 1u;
+      bls = F[((size_t)slot[W & hm] << L) | (W >> h)] - F[((size_t)slot[pa & hm] << L) | (pa >> h)];
+    } else {
+      bls = scores[t * (size_t)k + __popc(W & ((1u << c) - 1u))];
+    }
+  }
+  for (uint32_t m = W; m; m &= m - 1) {                   // :75-87, the same j for every lane
+    const int j = __ffs((int)m) - 1;
+    if (active && j != c) {
+      const size_t at = (size_t)(W ^ (1u << j)) * n + c;
+      const double s = bl_score[at];
       if (s >= bls) {
         bls = s;
-        bps = bl_ps[(size_t)sub * n + child];
+        bps = bl_ps[at];
       }
     }
-    bl_score[(size_t)pa * n + child] = bls;
-    bl_ps[(size_t)pa * n + child] = bps;
-    const double gs = best_gs[pa] + bls;                                         // :89-94
-    if (bgs >= 0 || gs > bgs) {
-      bgs = gs;
+  }
+  double gs = 0.0;
+  if (active) {
+    bl_score[(size_t)W * n + c] = bls;
+    bl_ps[(size_t)W * n + c] = bps;
+    gs = best_gs[pa] + bls;                               // :89-94
+  }
+  double bgs = 0.0;
+  int bch = -1;
+  for (uint32_t m = W; m; m &= m - 1) {
+    const int child = __ffs((int)m) - 1;
+    const double g = __shfl_sync(0xffffffffu, gs, child);
+    if (bgs >= 0 || g > bgs) {
+      bgs = g;
       bch = child;
     }
   }
-  best_gs[W] = bgs;                                                              // :115-116
-  best_ch[W] = (uint8_t)bch;
+  if (c == 0) {                                           // :115-116
+    best_gs[W] = bgs;
+    best_ch[W] = (uint8_t)bch;
+  }
 }
 
-// Same DP with the local scores taken from the lattice: ls(child | pa) = F(pa + child) - F(pa).
-// F is block-major: index = slot[S & (2^h - 1)] << L | S >> h.
+// Level lists for the lattice mode (no host mask lists there):
 // lists[off[k] + rank] = W for every subset W: rank = position of W among the k-subsets in
 // increasing numeric order = sum_i C(p_i, i+1) over its set bits p_0 < p_1 < ... (combinatorial
 // number system), which is also the reference's Gosper order (next_combmask.h:41-46).
@@ -90,42 +118,6 @@ __global__ void es_level_lists_kernel(size_t combs, int n, EsLevels lv, uint32_t
     rank += c;
   }
   lists[lv.off[__popc(W)] + rank] = W;
-}
-
-__global__ void es_dp_f_kernel(const uint32_t* level_list, size_t T, int k, int n, bool calc, const double* F,
-                               const uint32_t* slot, int h, int L, double* bl_score, uint32_t* bl_ps, double* best_gs,
-                               uint8_t* best_ch) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= T) return;
-  const uint32_t W = level_list[t];
-  const uint32_t hm = (1u << h) - 1u;
-  const double fW = calc ? F[((size_t)slot[W & hm] << L) | (W >> h)] : 0.0;
-  double bgs = 0.0;
-  int bch = -1;
-  for (uint32_t m = W; m; m &= m - 1) {
-    const int child = __ffs((int)m) - 1;
-    const uint32_t pa = W & ~(1u << child);
-    const double ls = calc ? fW - F[((size_t)slot[pa & hm] << L) | (pa >> h)] : -INFINITY;
-    double bls = ls;
-    uint32_t bps = pa;
-    for (uint32_t q = pa; q; q &= q - 1) {
-      const uint32_t sub = pa & ~(q & (0u - q));
-      const double s = bl_score[(size_t)sub * n + child];
-      if (s >= bls) {
-        bls = s;
-        bps = bl_ps[(size_t)sub * n + child];
-      }
-    }
-    bl_score[(size_t)pa * n + child] = bls;
-    bl_ps[(size_t)pa * n + child] = bps;
-    const double gs = best_gs[pa] + bls;
-    if (bgs >= 0 || gs > bgs) {
-      bgs = gs;
-      bch = child;
-    }
-  }
-  best_gs[W] = bgs;
-  best_ch[W] = (uint8_t)bch;
 }
 
 }  // namespace obn
@@ -245,18 +237,17 @@ int obn_es_level_dp(obn_es* e) {
   if (!e->T) return OBN_OK;
   obn_ctx* c = e->c;
   OBN_CUDA(cudaSetDevice(c->device));
-  const unsigned grid = (unsigned)((e->T + 127) / 128);
   (void)cudaGetLastError();
   if (e->use_F) {
     const size_t Tk = (size_t)(e->levels.off[e->k + 1] - e->levels.off[e->k]);
-    es_dp_f_kernel<<<(unsigned)((Tk + 127) / 128), 128, 0, c->stream>>>(
-        c->es_pool.d_masks.as<uint32_t>() + e->levels.off[e->k], Tk, e->k, e->n, e->calc, e->F,
+    es_dp_warp_kernel<uint32_t, true><<<(unsigned)((Tk + 3) / 4), 128, 0, c->stream>>>(
+        c->es_pool.d_masks.as<uint32_t>() + e->levels.off[e->k], Tk, e->k, e->n, e->calc, nullptr, e->F,
         c->es_pool.d_slot.as<uint32_t>(), e->h, e->L, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
+  } else {
+    es_dp_warp_kernel<unsigned long long, false><<<(unsigned)((e->T + 3) / 4), 128, 0, c->stream>>>(
+        c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n, e->calc && e->k, c->es_pool.d_level.as<double>(), nullptr,
+        nullptr, 0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
   }
-  else
-    es_dp_kernel<<<grid, 128, 0, c->stream>>>(c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n,
-                                               (e->calc && e->k) ? c->es_pool.d_level.as<double>() : nullptr, e->bl_score,
-                                               e->bl_ps, e->best_gs, e->best_ch);
   OBN_CUDA(cudaGetLastError());
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   ++c->prof.total_launches;
@@ -278,7 +269,7 @@ int obn_es_finish(obn_es* e, uint64_t* parent_masks, double* best_score) {
     if (ch >= n) return fail(OBN_ERR_INVALID, "obn_es_finish called before every level was processed");
     const uint32_t pa = W & ~(1u << ch);
     uint32_t ps = 0;
-    OBN_CUDA(cudaMemcpy(&ps, e->bl_ps + (size_t)pa * n + ch, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    OBN_CUDA(cudaMemcpy(&ps, e->bl_ps + (size_t)W * n + ch, sizeof(uint32_t), cudaMemcpyDeviceToHost));   // row of W = pa + ch
     parent_masks[ch] = ps;
     W = pa;
   }
