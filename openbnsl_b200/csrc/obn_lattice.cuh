@@ -187,59 +187,47 @@ __global__ void lut_fill_kernel(double* lut, const double* lut_a, size_t stride)
   lut[(size_t)blockIdx.y * stride + m] = m ? lgamma((double)m + a) - lgamma(a) : 0.0;
 }
 
-// ---- bottom tier: the sub-lattice of the last 8 (binary) variables, in shared memory ---------------
+// ---- bottom tier: the sub-lattice of the last 8 (binary) variables, on chip --------------------------
 //
 // Most of the lattice's 3^n cells sit in mid-size tables, and producing every table in HBM costs
 // two reads and one write per cell (3.4 TB for n = 24).  The last kBotL variables are the fastest
 // digits of every key (contingency_table.h:76-85), so a table that contains all of them is a
 // sequence of 2^kBotL-cell CHUNKS, and the tables of its 2^kBotL sub-patterns (which bottom
-// variables stay) are sums inside each chunk.  One CTA therefore streams chunks through shared
-// memory, builds the 3^kBotL = 6561 marginal cells of each chunk with one add per cell (the same
-// "sum out the highest absent digit of the parent" rule as the HBM tiers), and accumulates
-// F(pattern) for all 256 patterns.  Only tables holding all bottom variables ever exist in HBM:
-// 3^(n-8) * 256 cells instead of 3^n.
+// variables stay) are sums inside each chunk.  One CTA streams chunks through the SM and
+// accumulates F(pattern) for all 256 patterns of the table.  Only tables holding all bottom
+// variables ever exist in HBM: 3^(n-8) * 256 cells instead of 3^n.
 //
-// Work of one chunk is a fixed PROGRAM (built on the host, bottom_program() in obn_lattice.inl):
-// level k = 7..0 (bottom variables kept) is a few SLOTS, one item per thread and slot:
-//   quad slot    four consecutive cells of one pattern whose summed-out digit sits above >= 2 kept
-//                digits: two 16-byte LDS, four adds, one 16-byte STS;
-//   scalar slot  one cell (the patterns where that digit is among the two lowest, and levels < 3).
-// Threads without an item read two always-zero cells and write to a dump cell, so a slot is
-// branch-free and the slots of a level pipeline; whole idle warps skip the slot.
+// A chunk's 3^8 = 6561 marginal cells are split by the two fastest digits.  A QUAD is the four
+// cells that differ only in those two digits; there are 3^6 = 729 quads, one per (upper pattern U =
+// which of the other six bottom variables are kept, cell of U's table).  Per chunk:
+//   phase 1  the quads are built level by level in shared memory with the same "sum out the highest
+//            absent digit of the parent" rule as the HBM tiers: two 16-byte LDS, four adds, one
+//            16-byte STS per quad, conflict-free.  Which quad a thread builds at each level is a
+//            fixed PROGRAM (bottom_program() in obn_lattice.inl); idle threads of a partly filled
+//            warp read always-zero quads and store to a dump quad (branch-free), idle warps skip.
+//   phase 2  a flat, barrier-free pass: thread t takes quads t, t+256, t+512, derives the five cells
+//            that sum out one or both of the two fastest digits in registers (nothing depends on
+//            them, so they never touch shared memory) and gathers the nine terms: 27 independent
+//            table lookups per thread in flight, twelve accumulators per thread.
+// The quad buffer is double-buffered, so fast warps start the next chunk while slow ones finish
+// phase 2.
 //
-// F is accumulated in 64-bit FIXED POINT (term * 2^shift, rounded once per term): integer adds are
-// associative, so lane-private accumulators, warp reductions and RED.ADD.64 into the F array give
-// the same bits whatever the chunk -> CTA split or the rank count, and the sum carries no
-// accumulation error at all (better than any fp64 summation order).
 constexpr int kBotL = 8;
-constexpr int kBotCells = 1 << kBotL;      // cells of a chunk = threads of the CTA
-constexpr int kBotThreads = kBotCells;
-constexpr int kBotExpanded = 6561;         // 3^8 marginal cells of one chunk
-constexpr int kBotZero = 6564;             // tab[kBotZero .. +7] stay 0 (sources of idle threads)
-constexpr int kBotDump = 6572;             // tab[kBotDump .. +3]: where idle threads store
-constexpr int kBotTab = 6576;
-constexpr int kBotSlots = 16;
-// slot table (must match bottom_program(); the host checks it):
-//   level  quad slots (items)     scalar slot (items)
-//   8      -                      0 (256, the chunk itself)
-//   7      1 (192)                2 (256)
-//   6      3, 4 (400)             5 (192)
-//   5      6, 7 (416)             8 (128)
-//   4      9 (256)                10 (96)
-//   3      11 (100)               12 (48)
-//   2      -                      13 (112)
-//   1      -                      14 (16)
-//   0      -                      15 (1)
-// quad word:   source quad (11 bits) | log2(distance to the second source) << 11 | destination quad << 14
-// scalar word: source cell (13 bits) | log2(distance) << 13 | destination cell << 16
-__host__ __device__ constexpr uint32_t bot_quad_word(uint32_t src0, uint32_t sh, uint32_t dst) {
-  return (src0 >> 2) | (sh << 11) | ((dst >> 2) << 14);
+constexpr int kBotCells = 1 << kBotL;      // cells of a chunk
+constexpr int kBotThreads = 256;
+constexpr int kBotUpper = kBotL - 2;       // digits handled through shared memory
+constexpr int kBotQuads = 729;             // 3^6 quads of one chunk
+constexpr int kBotZeroQuad = kBotQuads;    // quads 729, 730 stay 0 (sources of idle threads)
+constexpr int kBotDumpQuad = kBotQuads + 2;
+constexpr int kBotTabQuads = kBotQuads + 3;
+constexpr int kBotLevels = kBotUpper + 1;  // j = 6 (the chunk itself) .. 0
+// items of level j = C(6,j) 2^j:  j  6   5    4    3    2   1   0
+//                                    64  192  240  160  60  12  1
+// program word: source quad (10 bits) | log2(distance to the second source quad) << 10 | destination quad << 13
+__host__ __device__ constexpr uint32_t bot_word(uint32_t src0, uint32_t sh, uint32_t dst) {
+  return src0 | (sh << 10) | (dst << 13);
 }
-__host__ __device__ constexpr uint32_t bot_cell_word(uint32_t src0, uint32_t sh, uint32_t dst) {
-  return src0 | (sh << 13) | (dst << 16);
-}
-constexpr uint32_t kBotIdleQuad = bot_quad_word(kBotZero, 2, kBotDump);
-constexpr uint32_t kBotIdleCell = bot_cell_word(kBotZero, 0, kBotDump);
+constexpr uint32_t kBotIdleWord = bot_word(kBotZeroQuad, 0, kBotDumpQuad);
 constexpr uint16_t kBotNoPattern = 0xffff;
 
 struct FixTable {
@@ -254,74 +242,43 @@ __device__ __noinline__ long long fix_term(int n, double a, double scale) {
   return n ? __double2ll_rn((lgamma((double)n + a) - lgamma(a)) * scale) : 0ll;
 }
 
-// true for the warps that hold at least one of the slot's ITEMS items
-#define OBN_BOT_ACTIVE(ITEMS) ((tid & ~31) < (ITEMS))
+constexpr int kBotSlots = 3;               // quads per thread in phase 2: ceil(729 / 256)
 
-template <int SLOT, int ITEMS>
-__device__ __forceinline__ void bot_quad_load(const uint32_t* prog, const int32_t* tab, int tid, int4& x, uint32_t& dst) {
-  x = make_int4(0, 0, 0, 0);
-  dst = kBotDump;
-  if (OBN_BOT_ACTIVE(ITEMS)) {
-    const uint32_t w = prog[SLOT * kBotThreads + tid];
-    const uint32_t s0 = (w & 0x7ffu) << 2;
-    const int4 a = *reinterpret_cast<const int4*>(tab + s0);
-    const int4 b = *reinterpret_cast<const int4*>(tab + s0 + (1u << ((w >> 11) & 7u)));
-    x = make_int4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
-    dst = (w >> 14) << 2;
-  }
+// phase 1, one level: build this thread's quad from its two source quads and store it
+template <int J>
+__device__ __forceinline__ void bot_level(const uint32_t* prog, int4* tab, int tid) {
+  const uint32_t w = prog[(kBotUpper - 1 - J) * kBotThreads + tid];
+  const uint32_t s0 = w & 0x3ffu;
+  const int4 a = tab[s0], b = tab[s0 + (1u << ((w >> 10) & 7u))];
+  tab[w >> 13] = make_int4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
 }
-template <int ITEMS>
-__device__ __forceinline__ void bot_quad_store(int32_t* tab, int tid, const int4& x, uint32_t dst) {
-  if (OBN_BOT_ACTIVE(ITEMS)) *reinterpret_cast<int4*>(tab + dst) = x;
-}
-template <int SLOT, int ITEMS>
-__device__ __forceinline__ void bot_cell_load(const uint32_t* prog, const int32_t* tab, int tid, int& x, uint32_t& dst) {
-  x = 0;
-  dst = kBotDump;
-  if (OBN_BOT_ACTIVE(ITEMS)) {
-    const uint32_t w = prog[SLOT * kBotThreads + tid];
-    const uint32_t s0 = w & 0x1fffu;
-    x = tab[s0] + tab[s0 + (1u << ((w >> 13) & 7u))];
-    dst = w >> 16;
-  }
-}
-template <int ITEMS>
-__device__ __forceinline__ void bot_cell_store(int32_t* tab, int tid, int x, uint32_t dst) {
-  if (OBN_BOT_ACTIVE(ITEMS)) tab[dst] = x;
-}
+#define OBN_BOT_LEVEL(J, ITEMS)                               \
+  if ((tid & ~31) < (ITEMS)) bot_level<J>(prog, tab, tid);    \
+  __syncthreads();
 
-// terms of a slot's cells: table gathers (issued here, added one level later), or libm when this
-// cell count has no table
-template <bool LUT, int ITEMS>
-__device__ __forceinline__ long long bot_quad_terms(const long long* lut, double a, double scale, int tid, const int4& x) {
-  long long g = 0;
-  if (OBN_BOT_ACTIVE(ITEMS)) {
-    if (LUT) {
-      const long long g0 = __ldg(lut + x.x), g1 = __ldg(lut + x.y), g2 = __ldg(lut + x.z), g3 = __ldg(lut + x.w);
-      g = (g0 + g1) + (g2 + g3);
-    } else {
-      g = fix_term(x.x, a, scale) + fix_term(x.y, a, scale) + fix_term(x.z, a, scale) + fix_term(x.w, a, scale);
-    }
-  }
-  return g;
+// phase 2, one quad (cells x = {00, 01, 10, 11} in the two fastest digits; its upper pattern keeps
+// j variables): acc[0] both digits kept (4 cells, level j+2), acc[1] the fastest summed out,
+// acc[2] the second fastest summed out (2 cells each, level j+1), acc[3] both (1 cell, level j).
+// o2/o1/o0 = first element of the term table of level j+2 / j+1 / j.
+__device__ __forceinline__ void bot_quad_lut(const long long* lut, uint32_t o2, uint32_t o1, uint32_t o0, const int4& x,
+                                             long long (&acc)[4]) {
+  const int m0 = x.x + x.y, m1 = x.z + x.w, n0 = x.x + x.z, n1 = x.y + x.w;
+  const long long a0 = __ldg(lut + (o2 + (uint32_t)x.x)), a1 = __ldg(lut + (o2 + (uint32_t)x.y));
+  const long long a2 = __ldg(lut + (o2 + (uint32_t)x.z)), a3 = __ldg(lut + (o2 + (uint32_t)x.w));
+  const long long b0 = __ldg(lut + (o1 + (uint32_t)m0)), b1 = __ldg(lut + (o1 + (uint32_t)m1));
+  const long long c0 = __ldg(lut + (o1 + (uint32_t)n0)), c1 = __ldg(lut + (o1 + (uint32_t)n1));
+  const long long d0 = __ldg(lut + (o0 + (uint32_t)(m0 + m1)));
+  acc[0] += (a0 + a1) + (a2 + a3);
+  acc[1] += b0 + b1;
+  acc[2] += c0 + c1;
+  acc[3] += d0;
 }
-template <bool LUT, int ITEMS>
-__device__ __forceinline__ long long bot_cell_term(const long long* lut, double a, double scale, int tid, int x) {
-  long long g = 0;
-  if (OBN_BOT_ACTIVE(ITEMS)) g = LUT ? __ldg(lut + x) : fix_term(x, a, scale);
-  return g;
-}
-
-// reduce a slot over the W lanes that share a pattern, then one RED.ADD.64 per (slot, pattern)
-template <int SLOT, int ITEMS, int W>
-__device__ __forceinline__ void bot_flush(const uint16_t* g_pat, long long a, unsigned long long* f, int f_shift, int tid) {
-  if (!OBN_BOT_ACTIVE(ITEMS)) return;
-#pragma unroll
-  for (int o = W / 2; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-  const uint32_t pattern = __ldg(g_pat + SLOT * kBotThreads + tid);
-  // pattern bit j = variable n-1-j = bit (L-1-j) of the low mask
-  if (pattern != kBotNoPattern && (tid & (W - 1)) == 0)
-    atomicAdd(f + ((size_t)(__brev(pattern) >> 24) << f_shift), (unsigned long long)a);
+__device__ __forceinline__ void bot_quad_libm(double a2, double a1, double a0, double scale, const int4& x, long long (&acc)[4]) {
+  const int m0 = x.x + x.y, m1 = x.z + x.w, n0 = x.x + x.z, n1 = x.y + x.w;
+  acc[0] += fix_term(x.x, a2, scale) + fix_term(x.y, a2, scale) + fix_term(x.z, a2, scale) + fix_term(x.w, a2, scale);
+  acc[1] += fix_term(m0, a1, scale) + fix_term(m1, a1, scale);
+  acc[2] += fix_term(n0, a1, scale) + fix_term(n1, a1, scale);
+  acc[3] += fix_term(m0 + m1, a0, scale);
 }
 
 // grid = (chunk groups, tasks).  The table of task t is its `dst` (cells = hi * mul * lo, a multiple
@@ -332,9 +289,9 @@ __global__ void __launch_bounds__(kBotThreads, 3) bottom_lattice_kernel(const Ma
                                                                        const uint32_t* g_prog, const uint16_t* g_pat, FixTable ft,
                                                                        double ess, unsigned long long* Fx, uint64_t f_base,
                                                                        int f_shift, uint32_t chunks_per_cta) {
-  __shared__ uint32_t prog[kBotSlots * kBotThreads];
-  __shared__ __align__(16) int32_t tab[kBotTab];
-  __shared__ const long long* s_lut[kBotL + 1];
+  __shared__ uint32_t prog[kBotUpper * kBotThreads];
+  __shared__ int4 tabs[2][kBotTabQuads];
+  __shared__ uint32_t s_off[kBotL + 1];
   __shared__ double s_a[kBotL + 1];
   const int tid = threadIdx.x;
   const MargTask T = tasks[blockIdx.y];
@@ -344,131 +301,94 @@ __global__ void __launch_bounds__(kBotThreads, 3) bottom_lattice_kernel(const Ma
   if (c_begin >= chunks) return;
   const uint64_t c_end = min(chunks, c_begin + chunks_per_cta);
 #pragma unroll
-  for (int s = 1; s < kBotSlots; ++s) prog[s * kBotThreads + tid] = __ldg(g_prog + s * kBotThreads + tid);
-  if (tid < kBotTab - kBotZero) tab[kBotZero + tid] = 0;
+  for (int s = 0; s < kBotUpper; ++s) prog[s * kBotThreads + tid] = __ldg(g_prog + s * kBotThreads + tid);
+  if (tid < 2 * (kBotTabQuads - kBotQuads))
+    tabs[tid / (kBotTabQuads - kBotQuads)][kBotQuads + tid % (kBotTabQuads - kBotQuads)] = make_int4(0, 0, 0, 0);
   if (tid <= kBotL) {
     // pattern of popcount k: cells(table) / 2^(8-k) cells; a = ess / cells (local_score.h:41)
     const double a = ess / (double)(cells >> (kBotL - tid));
-    int id = -1;
+    int id = 0;
     for (int i = 0; i < ft.n_lut; ++i)
       if (ft.lut_a[i] == a) { id = i; break; }
     s_a[tid] = a;
-    s_lut[tid] = id >= 0 ? ft.lut + (size_t)id * ft.stride : nullptr;
+    s_off[tid] = (uint32_t)((size_t)id * ft.stride);
   }
   __syncthreads();
-  const int32_t* src = base + (uint64_t)T.dst_off * mul + (c_begin << kBotL);
-  long long acc[kBotSlots];
+  // phase-2 items of this thread: quads tid, tid + 256, tid + 512 (the last slot is ragged)
+  uint32_t quad[kBotSlots], upper[kBotSlots], o2[kBotSlots], o1[kBotSlots], o0[kBotSlots];
 #pragma unroll
-  for (int s = 0; s < kBotSlots; ++s) acc[s] = 0;
-  int next = __ldg(src + tid);
-  const double scale = ft.scale;
-  for (uint64_t ch = c_begin; ch < c_end; ++ch) {
-    const int c8 = next;
-    src += kBotCells;
-    if (ch + 1 < c_end) next = __ldg(src + tid);
-    tab[tid] = c8;
-    const long long t0 = bot_cell_term<LUT, 256>(s_lut[8], s_a[8], scale, tid, c8);
-    __syncthreads();
-    int4 qa, qb;
-    int ca;
-    uint32_t da, db, dc;
-    // level 7
-    bot_quad_load<1, 192>(prog, tab, tid, qa, da);
-    bot_cell_load<2, 256>(prog, tab, tid, ca, dc);
-    const long long t1 = bot_quad_terms<LUT, 192>(s_lut[7], s_a[7], scale, tid, qa);
-    const long long t2 = bot_cell_term<LUT, 256>(s_lut[7], s_a[7], scale, tid, ca);
-    bot_quad_store<192>(tab, tid, qa, da);
-    bot_cell_store<256>(tab, tid, ca, dc);
-    acc[0] += t0;
-    __syncthreads();
-    // level 6
-    bot_quad_load<3, 256>(prog, tab, tid, qa, da);
-    bot_quad_load<4, 144>(prog, tab, tid, qb, db);
-    bot_cell_load<5, 192>(prog, tab, tid, ca, dc);
-    const long long t3 = bot_quad_terms<LUT, 256>(s_lut[6], s_a[6], scale, tid, qa);
-    const long long t4 = bot_quad_terms<LUT, 144>(s_lut[6], s_a[6], scale, tid, qb);
-    const long long t5 = bot_cell_term<LUT, 192>(s_lut[6], s_a[6], scale, tid, ca);
-    bot_quad_store<256>(tab, tid, qa, da);
-    bot_quad_store<144>(tab, tid, qb, db);
-    bot_cell_store<192>(tab, tid, ca, dc);
-    acc[1] += t1;
-    acc[2] += t2;
-    __syncthreads();
-    // level 5
-    bot_quad_load<6, 256>(prog, tab, tid, qa, da);
-    bot_quad_load<7, 160>(prog, tab, tid, qb, db);
-    bot_cell_load<8, 128>(prog, tab, tid, ca, dc);
-    const long long t6 = bot_quad_terms<LUT, 256>(s_lut[5], s_a[5], scale, tid, qa);
-    const long long t7 = bot_quad_terms<LUT, 160>(s_lut[5], s_a[5], scale, tid, qb);
-    const long long t8 = bot_cell_term<LUT, 128>(s_lut[5], s_a[5], scale, tid, ca);
-    bot_quad_store<256>(tab, tid, qa, da);
-    bot_quad_store<160>(tab, tid, qb, db);
-    bot_cell_store<128>(tab, tid, ca, dc);
-    acc[3] += t3;
-    acc[4] += t4;
-    acc[5] += t5;
-    __syncthreads();
-    // level 4
-    bot_quad_load<9, 256>(prog, tab, tid, qa, da);
-    bot_cell_load<10, 96>(prog, tab, tid, ca, dc);
-    const long long t9 = bot_quad_terms<LUT, 256>(s_lut[4], s_a[4], scale, tid, qa);
-    const long long t10 = bot_cell_term<LUT, 96>(s_lut[4], s_a[4], scale, tid, ca);
-    bot_quad_store<256>(tab, tid, qa, da);
-    bot_cell_store<96>(tab, tid, ca, dc);
-    acc[6] += t6;
-    acc[7] += t7;
-    acc[8] += t8;
-    __syncthreads();
-    // level 3
-    bot_quad_load<11, 100>(prog, tab, tid, qa, da);
-    bot_cell_load<12, 48>(prog, tab, tid, ca, dc);
-    const long long t11 = bot_quad_terms<LUT, 100>(s_lut[3], s_a[3], scale, tid, qa);
-    const long long t12 = bot_cell_term<LUT, 48>(s_lut[3], s_a[3], scale, tid, ca);
-    bot_quad_store<100>(tab, tid, qa, da);
-    bot_cell_store<48>(tab, tid, ca, dc);
-    acc[9] += t9;
-    acc[10] += t10;
-    __syncthreads();
-    // level 2
-    bot_cell_load<13, 112>(prog, tab, tid, ca, dc);
-    const long long t13 = bot_cell_term<LUT, 112>(s_lut[2], s_a[2], scale, tid, ca);
-    bot_cell_store<112>(tab, tid, ca, dc);
-    acc[11] += t11;
-    acc[12] += t12;
-    __syncthreads();
-    // level 1
-    bot_cell_load<14, 16>(prog, tab, tid, ca, dc);
-    const long long t14 = bot_cell_term<LUT, 16>(s_lut[1], s_a[1], scale, tid, ca);
-    bot_cell_store<16>(tab, tid, ca, dc);
-    acc[13] += t13;
-    __syncthreads();
-    // level 0
-    bot_cell_load<15, 1>(prog, tab, tid, ca, dc);
-    const long long t15 = bot_cell_term<LUT, 1>(s_lut[0], s_a[0], scale, tid, ca);
-    acc[14] += t14;
-    acc[15] += t15;
-    // (the next chunk's first store is tab[0..255]; level 0 read level 1's cells only, and a
-    // barrier separates that store from the next level-7 loads)
+  for (int s = 0; s < kBotSlots; ++s) {
+    const uint32_t q = (uint32_t)(s * kBotThreads + tid);
+    upper[s] = q < (uint32_t)kBotQuads ? __ldg(g_pat + q) : (uint32_t)kBotNoPattern;
+    quad[s] = q < (uint32_t)kBotQuads ? q : (uint32_t)kBotZeroQuad;
+    const int j = upper[s] == kBotNoPattern ? 0 : __popc(upper[s]);
+    o2[s] = s_off[j + 2];
+    o1[s] = s_off[j + 1];
+    o0[s] = s_off[j];
   }
+  const int4* src = reinterpret_cast<const int4*>(base + (uint64_t)T.dst_off * mul + (c_begin << kBotL));
+  long long acc[kBotSlots][4];
+#pragma unroll
+  for (int s = 0; s < kBotSlots; ++s)
+#pragma unroll
+    for (int l = 0; l < 4; ++l) acc[s][l] = 0;
+  const double scale = ft.scale;
+  int4 next = make_int4(0, 0, 0, 0);
+  if (tid < 64) next = __ldg(src + tid);
+  for (uint64_t ch = c_begin; ch < c_end; ++ch) {
+    int4* tab = tabs[(ch - c_begin) & 1];
+    if (tid < 64) {                       // level 6: the chunk itself
+      tab[tid] = next;
+      src += kBotCells / 4;
+      if (ch + 1 < c_end) next = __ldg(src + tid);
+    }
+    __syncthreads();
+    OBN_BOT_LEVEL(5, 192)
+    OBN_BOT_LEVEL(4, 240)
+    OBN_BOT_LEVEL(3, 160)
+    OBN_BOT_LEVEL(2, 60)
+    OBN_BOT_LEVEL(1, 12)
+    OBN_BOT_LEVEL(0, 1)
+    // phase 2 (no barrier after it: the next chunk builds in the other buffer, and the one after
+    // that is at least seven barriers away)
+#pragma unroll
+    for (int s = 0; s < kBotSlots; ++s) {
+      const int4 x = tab[quad[s]];
+      if (LUT) {
+        bot_quad_lut(ft.lut, o2[s], o1[s], o0[s], x, acc[s]);
+      } else {
+        const int j = upper[s] == kBotNoPattern ? 0 : __popc(upper[s]);
+        bot_quad_libm(s_a[j + 2], s_a[j + 1], s_a[j], scale, x, acc[s]);
+      }
+    }
+  }
+  // flush: quads of one upper pattern are an aligned power-of-two run of lanes, so a butterfly that
+  // only adds partners of the same pattern leaves the run's total in every lane of the run
   unsigned long long* f = Fx + f_base + T.f_index;
-  bot_flush<0, 256, 32>(g_pat, acc[0], f, f_shift, tid);
-  bot_flush<1, 192, 32>(g_pat, acc[1], f, f_shift, tid);      // level 7 quads: 32 quads per pattern
-  bot_flush<2, 256, 32>(g_pat, acc[2], f, f_shift, tid);
-  bot_flush<3, 256, 16>(g_pat, acc[3], f, f_shift, tid);      // level 6 quads: 16 per pattern
-  bot_flush<4, 144, 16>(g_pat, acc[4], f, f_shift, tid);
-  bot_flush<5, 192, 32>(g_pat, acc[5], f, f_shift, tid);
-  bot_flush<6, 256, 8>(g_pat, acc[6], f, f_shift, tid);       // level 5 quads: 8 per pattern
-  bot_flush<7, 160, 8>(g_pat, acc[7], f, f_shift, tid);
-  bot_flush<8, 128, 32>(g_pat, acc[8], f, f_shift, tid);
-  bot_flush<9, 256, 4>(g_pat, acc[9], f, f_shift, tid);       // level 4 quads: 4 per pattern
-  bot_flush<10, 96, 16>(g_pat, acc[10], f, f_shift, tid);
-  bot_flush<11, 100, 2>(g_pat, acc[11], f, f_shift, tid);     // level 3 quads: 2 per pattern
-  bot_flush<12, 48, 8>(g_pat, acc[12], f, f_shift, tid);
-  bot_flush<13, 112, 4>(g_pat, acc[13], f, f_shift, tid);
-  bot_flush<14, 16, 2>(g_pat, acc[14], f, f_shift, tid);
-  bot_flush<15, 1, 1>(g_pat, acc[15], f, f_shift, tid);
+#pragma unroll
+  for (int s = 0; s < kBotSlots; ++s) {
+    const uint32_t U = upper[s];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const bool same = __shfl_xor_sync(0xffffffffu, U, o) == U;
+#pragma unroll
+      for (int l = 0; l < 4; ++l) {
+        const long long other = __shfl_xor_sync(0xffffffffu, acc[s][l], o);
+        if (same) acc[s][l] += other;
+      }
+    }
+    const uint32_t left = __shfl_up_sync(0xffffffffu, U, 1);
+    if (U != kBotNoPattern && ((tid & 31) == 0 || left != U)) {
+      // pattern bit b = variable n-1-b = bit (L-1-b) of the low mask; bits 1, 0 are the two fastest digits
+      const uint32_t p = U << 2;
+      atomicAdd(f + ((size_t)(__brev(p | 3u) >> 24) << f_shift), (unsigned long long)acc[s][0]);
+      atomicAdd(f + ((size_t)(__brev(p | 2u) >> 24) << f_shift), (unsigned long long)acc[s][1]);   // fastest digit summed out
+      atomicAdd(f + ((size_t)(__brev(p | 1u) >> 24) << f_shift), (unsigned long long)acc[s][2]);
+      atomicAdd(f + ((size_t)(__brev(p) >> 24) << f_shift), (unsigned long long)acc[s][3]);
+    }
+  }
 }
-#undef OBN_BOT_ACTIVE
+#undef OBN_BOT_LEVEL
 
 // F words of one rank's slice: fixed point -> double, in place
 __global__ void fix_to_double_kernel(double* F, size_t n, double inv_scale) {

@@ -204,97 +204,50 @@ static int launch_marg_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks
   return OBN_OK;
 }
 
-// The per-(slot, thread) program of bottom_lattice_kernel (obn_lattice.cuh): where the two sources
-// and the destination of every marginal cell of a 2^8-cell chunk are.  The table of pattern p
-// (bottom variables kept) has 2^popcount(p) cells; tables of one level are stored in ascending
-// pattern order; the parent of p is p with its highest absent bit i set, and digit i sits above
-// sh = popcount(p & (2^i - 1)) kept digits.  Patterns with sh >= 2 are done four cells at a time
-// (quad slots), the rest one cell at a time.  Returns false if the layout does not match the
-// kernel's compile-time slot table.
+// The per-(level, thread) program of bottom_lattice_kernel (obn_lattice.cuh): which two source quads
+// a thread adds and where the result goes.  A quad = the four cells that differ in the two fastest
+// digits; quads are indexed by (upper pattern U = which of the other six bottom variables are kept,
+// cell of U's table).  Tables are stored by level (popcount of U) descending, patterns ascending;
+// the parent of U is U with its highest absent bit i set, and digit i sits above
+// sh = popcount(U & (2^i - 1)) kept digits.
 struct BottomProgram {
-  std::vector<uint32_t> words;     // [kBotSlots][kBotThreads]
-  std::vector<uint16_t> patterns;  // [kBotSlots][kBotThreads] pattern of the item, kBotNoPattern when idle
+  std::vector<uint32_t> words;     // [kBotUpper][kBotThreads] levels 5..0
+  std::vector<uint16_t> patterns;  // [kBotSlots * kBotThreads] U of quad q (phase 2 takes quads tid, tid+256, tid+512)
 };
 static bool bottom_program(BottomProgram& out) {
-  std::vector<std::vector<uint32_t>> pats(kBotL + 1);
-  for (uint32_t p = 0; p < (uint32_t)kBotCells; ++p) pats[__builtin_popcount(p)].push_back(p);
-  std::vector<uint32_t> off(kBotCells, 0);
-  uint32_t cells_total = 0;
-  for (int k = kBotL; k >= 0; --k) {
-    for (size_t r = 0; r < pats[k].size(); ++r) off[pats[k][r]] = cells_total + (uint32_t)(r << k);
-    cells_total += (uint32_t)(pats[k].size() << k);
+  const uint32_t NU = 1u << kBotUpper;
+  std::vector<std::vector<uint32_t>> pats(kBotUpper + 1);
+  for (uint32_t U = 0; U < NU; ++U) pats[__builtin_popcount(U)].push_back(U);
+  std::vector<uint32_t> qoff(NU, 0);
+  uint32_t quads = 0;
+  for (int j = kBotUpper; j >= 0; --j) {
+    for (size_t r = 0; r < pats[j].size(); ++r) qoff[pats[j][r]] = quads + (uint32_t)(r << j);
+    quads += (uint32_t)(pats[j].size() << j);
   }
-  if (cells_total != (uint32_t)kBotExpanded) return false;
-  auto pivot = [](uint32_t p, int& i, uint32_t& sh) {
-    i = 31 - __builtin_clz((~p) & (uint32_t)(kBotCells - 1));
-    sh = (uint32_t)__builtin_popcount(p & ((1u << i) - 1u));
-  };
-  // what the kernel was compiled for: {level, quad slots, quad items, scalar slots, scalar items}
-  static const int expect[8][5] = {{7, 1, 192, 1, 256}, {6, 2, 400, 1, 192}, {5, 2, 416, 1, 128}, {4, 1, 256, 1, 96},
-                                   {3, 1, 100, 1, 48},  {2, 0, 0, 1, 112},   {1, 0, 0, 1, 16},    {0, 0, 0, 1, 1}};
-  out.words.assign((size_t)kBotSlots * kBotThreads, kBotIdleCell);
+  if (quads != (uint32_t)kBotQuads) return false;
+  out.words.assign((size_t)kBotUpper * kBotThreads, kBotIdleWord);
   out.patterns.assign((size_t)kBotSlots * kBotThreads, kBotNoPattern);
-  for (int t = 0; t < kBotThreads; ++t) out.patterns[t] = (uint16_t)(kBotCells - 1);      // slot 0: the chunk itself
-  int slot = 1;
-  for (int k = kBotL - 1; k >= 0; --k) {
-    std::vector<uint32_t> reg, awk;
-    for (uint32_t p : pats[k]) {
-      int i;
-      uint32_t sh;
-      pivot(p, i, sh);
-      (k >= 2 && sh >= 2 ? reg : awk).push_back(p);
+  for (int j = kBotUpper; j >= 0; --j) {
+    const size_t items = pats[j].size() << j;
+    if (items > (size_t)kBotThreads) return false;
+    for (size_t e = 0; e < items; ++e) {
+      const uint32_t U = pats[j][e >> j], cidx = (uint32_t)(e & (((size_t)1 << j) - 1));
+      out.patterns[qoff[U] + cidx] = (uint16_t)U;
+      if (j == kBotUpper) continue;                                   // level 6 is the chunk itself
+      const int i = 31 - __builtin_clz((~U) & (NU - 1u));
+      const uint32_t sh = (uint32_t)__builtin_popcount(U & ((1u << i) - 1u));
+      const uint32_t src0 = qoff[U | (1u << i)] + ((cidx >> sh) << (sh + 1)) + (cidx & ((1u << sh) - 1u));
+      out.words[(size_t)(kBotUpper - 1 - j) * kBotThreads + e] = bot_word(src0, sh, qoff[U] + cidx);
     }
-    if (!reg.empty()) {
-      // a nearly empty last quad slot costs a whole slot: demote its patterns to the scalar slot
-      const size_t qpp = ((size_t)1 << k) / 4, nq = reg.size() * qpp;
-      if (nq % kBotThreads != 0 && nq % kBotThreads < 32) {
-        const size_t d = (nq % kBotThreads + qpp - 1) / qpp;
-        awk.insert(awk.end(), reg.end() - (ptrdiff_t)d, reg.end());
-        reg.resize(reg.size() - d);
-      }
-    }
-    std::vector<std::pair<uint32_t, uint16_t>> quads, cells;
-    for (uint32_t p : reg) {
-      int i;
-      uint32_t sh;
-      pivot(p, i, sh);
-      for (uint32_t c = 0; c < (1u << k); c += 4)
-        quads.push_back({bot_quad_word(off[p | (1u << i)] + ((c >> sh) << (sh + 1)) + (c & ((1u << sh) - 1u)), sh, off[p] + c), (uint16_t)p});
-    }
-    for (uint32_t p : awk) {
-      int i;
-      uint32_t sh;
-      pivot(p, i, sh);
-      for (uint32_t c = 0; c < (1u << k); ++c)
-        cells.push_back({bot_cell_word(off[p | (1u << i)] + ((c >> sh) << (sh + 1)) + (c & ((1u << sh) - 1u)), sh, off[p] + c), (uint16_t)p});
-    }
-    const int qs = (int)((quads.size() + kBotThreads - 1) / kBotThreads), ss = (int)((cells.size() + kBotThreads - 1) / kBotThreads);
-    const int* ex = expect[kBotL - 1 - k];
-    if (ex[0] != k || ex[1] != qs || ex[2] != (int)quads.size() || ex[3] != ss || ex[4] != (int)cells.size()) return false;
-    if (slot + qs + ss > kBotSlots) return false;
-    for (int it = 0; it < qs; ++it, ++slot)
-      for (int t = 0; t < kBotThreads; ++t) {
-        const size_t e = (size_t)it * kBotThreads + t;
-        out.words[(size_t)slot * kBotThreads + t] = e < quads.size() ? quads[e].first : kBotIdleQuad;
-        if (e < quads.size()) out.patterns[(size_t)slot * kBotThreads + t] = quads[e].second;
-      }
-    for (int it = 0; it < ss; ++it, ++slot)
-      for (int t = 0; t < kBotThreads; ++t) {
-        const size_t e = (size_t)it * kBotThreads + t;
-        if (e < cells.size()) {
-          out.words[(size_t)slot * kBotThreads + t] = cells[e].first;
-          out.patterns[(size_t)slot * kBotThreads + t] = cells[e].second;
-        }
-      }
   }
-  return slot == kBotSlots;
+  return true;
 }
 
 // F of all 2^8 bottom patterns of every table of one level (the tables are the tasks' `dst`)
 static int launch_bottom_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks, uint64_t max_cells, uint64_t mul,
                                const int32_t* base, const uint32_t* d_prog, const FixTable& ft, double ess, double* F,
                                uint64_t f_base, int f_shift) {
-  const uint16_t* d_pat = reinterpret_cast<const uint16_t*>(d_prog + (size_t)kBotSlots * kBotThreads);
+  const uint16_t* d_pat = reinterpret_cast<const uint16_t*>(d_prog + (size_t)kBotUpper * kBotThreads);
   const uint64_t chunks = max_cells >> kBotL;
   // enough CTAs to fill the GPU a few times over, as many chunks per CTA as that allows (<= 64)
   const uint64_t target = (uint64_t)c->sm_count * 16;
@@ -437,7 +390,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     OBN_CUDA(cudaStreamSynchronize(c->stream));                                        // P.slot is a local
     if (bot) {
       BottomProgram bp;
-      if (!bottom_program(bp)) return fail(OBN_ERR_UNSUPPORTED, "bottom program does not match the kernel's slot table");
+      if (!bottom_program(bp)) return fail(OBN_ERR_UNSUPPORTED, "bottom program does not match the kernel's level table");
       if (int rc = pool.d_prog.reserve(bp.words.size() * 4 + bp.patterns.size() * 2)) return rc;
       OBN_CUDA(cudaMemcpy(pool.d_prog.p, bp.words.data(), bp.words.size() * 4, cudaMemcpyHostToDevice));
       OBN_CUDA(cudaMemcpy(pool.d_prog.as<char>() + bp.words.size() * 4, bp.patterns.data(), bp.patterns.size() * 2, cudaMemcpyHostToDevice));
