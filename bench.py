@@ -268,7 +268,7 @@ def secondary_metrics(L, comm, world):
         df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
         df.to_device()
         kw = {"comm": comm} if (comm is not None and name.startswith("C3")) else {}
-        L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), min(mp, 2), exact_order=exact)   # warm-up
+        L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), mp, exact_order=exact, **kw)   # warm-up step (same call)
         L.profile_read(True)
         torch.cuda.synchronize()
         if world > 1:

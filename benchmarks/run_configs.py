@@ -89,7 +89,7 @@ def run_es(name, net, n_rows, max_parents, what, exact=2):
     df, cards, t_gen = frame(net, n_rows, 0)
     L.profile_enable(True)
     df.to_device()
-    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 0, exact_order=exact, comm=COMM)
+    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=exact, comm=COMM)   # warm-up step
     L.profile_read(True)
     if COMM is not None:
         import torch.distributed as dist

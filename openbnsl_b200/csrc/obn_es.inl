@@ -188,6 +188,7 @@ int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k
   e->k = k;
   e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
   e->buffer_doubles = buffer_subsets * (size_t)std::max(k, 1);
+  c->es_pool.lists_n = 0;                     // the level lists of the lattice mode share this buffer
   if (int rc = c->es_pool.d_masks.reserve(std::max<size_t>(n_subsets * 8, 16))) return rc;
   if (int rc = c->es_pool.d_level.reserve(std::max<size_t>(e->buffer_doubles * 8, 16))) return rc;
   if (n_subsets)

@@ -130,6 +130,7 @@ struct LatticeGraphCache {
 struct EsPool {
   bool in_use = false;
   LatticeGraphCache lattice;
+  int lists_n = 0;                 // d_masks holds the lattice-mode level lists of this many variables (0 = not)
   DevBuf d_bl_score, d_bl_ps, d_best_gs, d_best_ch, d_F;
   DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog;
   void release() {
