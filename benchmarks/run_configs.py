@@ -105,6 +105,40 @@ def run_es(name, net, n_rows, max_parents, what, exact=2):
             "gather_ms": st["gather_ms"], "dp_ms": st["dp_ms"]})
 
 
+def run_sa(name, net, n_rows, max_parents, iters, chains, what):
+    """Multi-chain simulated annealing: lockstep chains, one batch of new local
+    scores per step.  Also times the unmodified reference on a bounded sample (2 chains, 100 steps)."""
+    df, cards, t_gen = frame(net, n_rows, 0)
+    L.profile_enable(True)
+    df.to_device()
+    L.structure_learning.simulated_annealing(df, L.score.BDeu(1.0), max_parents, 50, 1.0, 0.9995, False, 0, chains, comm=COMM)
+    L.profile_read(True)
+    t0 = time.perf_counter()
+    L.structure_learning.simulated_annealing(df, L.score.BDeu(1.0), max_parents, iters, 1.0, 0.9995, False, 0, chains, comm=COMM)
+    secs = time.perf_counter() - t0
+    prof = L.profile_read(True)
+    st = L.structure_learning.last_sa_stats()
+    extra = {"chains": chains, "max_iters": iters, "proposals": int(st["proposals"]), "gpu_scores": int(st["evaluated"]),
+             "batches": int(st["batches"]), "evaluate_ms": st["evaluate_ms"], "best_score": st["best_score"],
+             "proposals_per_s": st["proposals"] * (COMM.world if COMM is not None else 1) / secs,
+             "n_vars": net.n, "n_rows": n_rows, "max_parents": max_parents, "data_gen_s": t_gen}
+    if RANK == 0:
+        try:
+            import oracle
+            ref, _ = oracle.reference_modules()
+            if ref is not None:
+                codes = net.sample(n_rows, 0)
+                rdf = ref.base.DataframeWrapper(nw.to_reference_frame(codes, net.names, cards))
+                t0 = time.perf_counter()
+                ref.structure_learning.simulated_annealing(rdf, ref.score.BDeu(1.0), max_parents, 100, 1.0, 0.9995, False, 0, 2)
+                dt = time.perf_counter() - t0
+                extra["reference_cpu_proposals_per_s_per_chain_thread"] = 100.0 / dt * 2 / min(2, os.cpu_count() or 1)
+                extra["reference_sample"] = "2 chains x 100 steps of the unmodified reference (one OpenMP thread per chain)"
+        except Exception as e:                      # the checker is optional here
+            extra["reference_error"] = str(e)[:200]
+    report(name, what, st["proposals"], "sa_proposals", secs, prof, extra)
+
+
 def main():
     global COMM, RANK
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
@@ -118,6 +152,9 @@ def main():
         COMM = TorchComm()
         RANK = COMM.rank
     which = [a.lower() for a in sys.argv[1:]] or ["c1", "c2", "c3", "c4", "c5"]
+    if "sa" in which:
+        run_sa("SA", nw.alarm(), 100_000, 3, 2000, 64,
+               "simulated annealing BDeu, Alarm structure, 37 vars, 100k rows, 64 chains x 2000 steps, max_parents=3")
     if "c1" in which:
         run_es("C1", nw.asia(), 10_000, 7, "exhaustive search BDeu, Asia, 8 vars, 10k rows, full lattice")
         run_es("C1", nw.asia(), 10_000, 3, "exhaustive search BDeu, Asia, 8 vars, 10k rows, max_parents=3")

@@ -72,6 +72,14 @@ struct PyEvaluator : Evaluator {
     if ((size_t)r.size() != nv) throw std::runtime_error("evaluator returned a wrong-sized array");
     std::memcpy(out, r.data(), nv * sizeof(double));
   }
+  void child_scores(const TupleBatch& b, const uint32_t* child, double ess, int exact, double* out) override {
+    if (!b.size()) return;
+    py::array_t<double> r = obj.attr("child_scores")(view<uint32_t>(b.var_ids.data(), b.var_ids.size()),
+                                                     view<uint64_t>(b.offsets.data(), b.offsets.size()),
+                                                     view<uint32_t>(child, b.size()), ess, exact);
+    if ((size_t)r.size() != b.size()) throw std::runtime_error("evaluator returned a wrong-sized array");
+    std::memcpy(out, r.data(), b.size() * sizeof(double));
+  }
 };
 
 PDAG run_pc(size_t n_vars, Evaluator* ev, const CITestType& test, size_t max_cond_vars, bool stable,
@@ -105,6 +113,25 @@ PDAG run_es(size_t n_vars, Evaluator* ev, const ScoreType& score, size_t max_par
   const Comm c = make_comm(comm);
   g_last_es_stats = EsStats{};
   return exhaustive_search_driver(n_vars, *ev, c, o, &g_last_es_stats);
+}
+
+SaStats g_last_sa_stats;
+PDAG run_sa(size_t n_vars, Evaluator* ev, const ScoreType& score, size_t max_parents, size_t max_iters, double init_temp,
+            double cooling_rate, bool is_deterministic, uint64_t seed, size_t num_chains, const py::object& comm) {
+  if (max_parents >= n_vars) throw std::invalid_argument("max_parents out of range");     // simulated_annealing.cpp:109-111
+  if (!std::holds_alternative<BDeu>(score)) throw std::invalid_argument("Unsupported score type.");   // local_score.h:43
+  SaOptions o;
+  o.ess = std::get<BDeu>(score).ess;
+  o.max_parents = max_parents;
+  o.max_iters = max_iters;
+  o.init_temp = init_temp;
+  o.cooling_rate = cooling_rate;
+  o.deterministic = is_deterministic;
+  o.seed = seed;
+  o.num_chains = num_chains;
+  const Comm c = make_comm(comm);
+  g_last_sa_stats = SaStats{};
+  return simulated_annealing_driver(n_vars, *ev, c, o, &g_last_sa_stats);
 }
 
 }  // namespace
@@ -295,8 +322,29 @@ PYBIND11_MODULE(openbnsllib, m) {
                                   py::array_t<T> a(v.size()); if (v.size()) std::memcpy(a.mutable_data(), v.data(), v.size() * sizeof(T)); return a; };
     return py::make_tuple(cp(r.var_ids), cp(r.offsets), cp(r.x), cp(r.y));
   }, "(var_ids, offsets, x, y) of every CI test the last pc(record_tests=True) evaluated");
-  sl.def("simulated_annealing", [](py::args, py::kwargs) -> PDAG {
-    throw std::runtime_error("simulated_annealing is outside the B200 hot-path scope (SURVEY.md section 8f)");
+  sl.def("simulated_annealing",
+         [](const DataframeWrapper& df, const ScoreType& st, size_t max_parents, size_t max_iters, double init_temp,
+            double cooling_rate, bool is_deterministic, uint64_t seed, size_t num_chains, const py::object& comm) {
+           if (max_parents >= df.num_of_vars) throw std::invalid_argument("max_parents out of range");
+           if (!std::holds_alternative<BDeu>(st)) throw std::invalid_argument("Unsupported score type.");
+           GpuEvaluator ev(df.device());
+           return run_sa(df.num_of_vars, &ev, st, max_parents, max_iters, init_temp, cooling_rate, is_deterministic, seed,
+                         num_chains, comm);
+         },
+         "Run simulated annealing algorithm", py::arg("df"), py::arg("score_type"), py::arg("max_parents"),
+         py::arg("max_iters") = 10000, py::arg("init_temp") = 1.0, py::arg("cooling_rate") = 0.9995,
+         py::arg("is_deterministic") = false, py::arg("seed") = 0, py::arg("num_chains") = 0, py::kw_only(),
+         py::arg("comm") = py::none());
+  sl.def("last_sa_stats", []() {
+    py::dict d;
+    d["chains"] = g_last_sa_stats.chains;
+    d["proposals"] = g_last_sa_stats.proposals;
+    d["evaluated"] = g_last_sa_stats.evaluated;
+    d["batches"] = g_last_sa_stats.batches;
+    d["best_chain"] = g_last_sa_stats.best_chain;
+    d["best_score"] = g_last_sa_stats.best_score;
+    d["evaluate_ms"] = g_last_sa_stats.evaluate_ms;
+    return d;
   });
   sl.def("rai", [](py::args, py::kwargs) -> PDAG {
     throw std::runtime_error("rai is an unimplemented stub upstream and outside the B200 hot-path scope");
@@ -339,4 +387,12 @@ PYBIND11_MODULE(openbnsllib, m) {
     return run_es(n_vars, &ev, st, max_parents, exact_order, comm);
   }, py::arg("n_vars"), py::arg("evaluator"), py::arg("score_type"), py::arg("max_parents"),
      py::arg("exact_order") = 2, py::arg("comm") = py::none());
+  ts.def("simulated_annealing", [](size_t n_vars, py::object evaluator, const ScoreType& st, size_t max_parents,
+                                   size_t max_iters, double init_temp, double cooling_rate, bool is_deterministic,
+                                   uint64_t seed, size_t num_chains, const py::object& comm) {
+    PyEvaluator ev(std::move(evaluator));
+    return run_sa(n_vars, &ev, st, max_parents, max_iters, init_temp, cooling_rate, is_deterministic, seed, num_chains, comm);
+  }, py::arg("n_vars"), py::arg("evaluator"), py::arg("score_type"), py::arg("max_parents"), py::arg("max_iters") = 10000,
+     py::arg("init_temp") = 1.0, py::arg("cooling_rate") = 0.9995, py::arg("is_deterministic") = false,
+     py::arg("seed") = 0, py::arg("num_chains") = 0, py::arg("comm") = py::none());
 }

@@ -50,4 +50,10 @@ void GpuEvaluator::subset_scores(const TupleBatch& b, size_t begin, size_t end, 
                                end - begin, ess, exact_order, out));
 }
 
+void GpuEvaluator::child_scores(const TupleBatch& b, const uint32_t* child, double ess, int exact_order, double* out) {
+  if (!b.size()) return;
+  check(obn_bdeu_scores(Engine::instance().ctx(), ds_, b.var_ids.data(), b.offsets.data(), b.size(), child, ess,
+                        exact_order, out));
+}
+
 }  // namespace obn

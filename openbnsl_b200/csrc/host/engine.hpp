@@ -77,6 +77,8 @@ struct Evaluator {
   // scores of every child of tuples [begin, end) -> out[offsets[t]-offsets[begin] + i]
   virtual void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                              double* out) = 0;
+  // out[t] = BDeu score of child[t] given the other variables of tuple t, for every tuple of the batch
+  virtual void child_scores(const TupleBatch& b, const uint32_t* child, double ess, int exact_order, double* out) = 0;
 };
 
 class GpuEvaluator : public Evaluator {
@@ -85,6 +87,7 @@ class GpuEvaluator : public Evaluator {
   void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) override;
   void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                      double* out) override;
+  void child_scores(const TupleBatch& b, const uint32_t* child, double ess, int exact_order, double* out) override;
 
  private:
   obn_dataset* ds_;

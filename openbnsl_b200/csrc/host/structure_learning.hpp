@@ -72,4 +72,22 @@ PDAG exhaustive_search_driver(size_t n_vars, Evaluator& ev, const Comm& comm, co
 // level's score buffer over NVLink, then every rank runs the (cheap) DP for the whole level.
 PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions& opt, EsStats* stats);
 
+// Multi-chain simulated annealing (src/structure_learning/simulated_annealing.cpp:15-159): all
+// chains in lockstep, one batch of new (child, parent set) scores per step (simulated_annealing.cpp).
+struct SaOptions {
+  double ess = 1.0;
+  size_t max_parents = 0;
+  size_t max_iters = 10000;
+  double init_temp = 1.0;
+  double cooling_rate = 0.9995;
+  bool deterministic = false;     // std::set vs std::unordered_set parent sets (iteration order feeds the moves)
+  uint64_t seed = 0;
+  size_t num_chains = 0;          // 0 = one per host thread, like the reference's omp_get_max_threads()
+};
+struct SaStats {
+  size_t chains = 0, proposals = 0, evaluated = 0, batches = 0, best_chain = 0;
+  double best_score = 0.0, evaluate_ms = 0.0;
+};
+PDAG simulated_annealing_driver(size_t n_vars, Evaluator& ev, const Comm& comm, const SaOptions& opt, SaStats* stats);
+
 }  // namespace obn

@@ -34,9 +34,43 @@ def dataset_cases():
     yield "munin_like_2k_s2", nw.munin1_like(), 2000, 2
 
 
+SA_CASES = [  # max_parents, max_iters, init_temp, cooling_rate, is_deterministic, seed, num_chains
+    (3, 800, 1.0, 0.9995, False, 0, 3), (3, 800, 1.0, 0.9995, True, 0, 3), (2, 500, 5.0, 0.99, False, 7, 4),
+    (1, 400, 0.5, 0.999, True, 123, 2), (0, 60, 1.0, 0.9995, False, 1, 2)]
+
+
+def make_sa(ref):
+    """simulated_annealing.json: the reference's simulated_annealing() on two of the golden datasets
+    (SURVEY.md section 8f rank 1).  Kept in its own file so the other fixtures stay byte-identical."""
+    out = {}
+    for name, net, n_rows, seed in dataset_cases():
+        if net.n > 40:
+            continue
+        codes = net.sample(n_rows, seed)
+        cols, cards = [], []
+        for v in range(net.n):
+            u, inv = np.unique(codes[:, v], return_inverse=True)
+            cols.append(inv.astype(np.uint8)); cards.append(len(u))
+        codes = np.stack(cols, axis=1)
+        df = ref.base.DataframeWrapper(nw.to_reference_frame(codes, net.names, cards))
+        runs = []
+        for mp, iters, t0, cr, det, sd, chains in SA_CASES:
+            g = ref.structure_learning.simulated_annealing(df, ref.score.BDeu(1.0), mp, iters, t0, cr, det, sd, chains)
+            runs.append({"max_parents": mp, "max_iters": iters, "init_temp": t0, "cooling_rate": cr,
+                         "is_deterministic": det, "seed": sd, "num_chains": chains, "ess": 1.0, "adj": adj_of(g, net.n)})
+        out[name] = runs
+    with open(os.path.join(HERE, "simulated_annealing.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote simulated_annealing.json", os.path.getsize(os.path.join(HERE, "simulated_annealing.json")), "bytes")
+
+
 def main():
     ref, har = oracle.reference_modules()
     assert ref is not None, "build oracle/_ref first (python oracle/build_ref.py)"
+    if "--sa" in sys.argv:
+        make_sa(ref)
+        return
+    make_sa(ref)
     for name, net, n_rows, seed in dataset_cases():
         codes = net.sample(n_rows, seed)
         # ranks of observed states, as DataframeWrapper would compute them

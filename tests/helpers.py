@@ -29,6 +29,14 @@ class OracleEvaluator:
         self.n_sc += len(var_ids)
         return out
 
+    def child_scores(self, var_ids, offsets, child, ess, exact):
+        out = np.zeros(len(child), dtype=np.float64)
+        for t in range(len(child)):
+            vs = [int(v) for v in var_ids[int(offsets[t]):int(offsets[t + 1])]]
+            out[t] = oracle.bdeu_local_score(self.ods, int(child[t]), [v for v in vs if v != int(child[t])], ess)
+        self.n_sc += len(child)
+        return out
+
 
 def pdag_to_adj(g, n):
     return np.array([[1 if g.has_edge(p, v) else 0 for v in range(n)] for p in range(n)], dtype=np.uint8)

@@ -51,6 +51,19 @@ def _worker(rank, world, port, q):
         got = L._testing.exhaustive_search(net.n, ev, L.score.BDeu(e["ess"]), e["max_parents"], 2, comm)
         out[("es", e["max_parents"])] = (pdag_to_adj(got, net.n).tolist() == e["adj"], ev.n_sc,
                                          L.structure_learning.last_es_stats()["scores"])
+    # simulated annealing: chains are dealt to ranks (rank r runs chains r, r + world, ...); one
+    # all-gather of (best score, adjacency) picks the winner, which must be the reference's graph
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "simulated_annealing.json")) as f:
+        sa = json.load(f)["asia_10k_s0"]
+    sa_out = []
+    for e in sa:
+        ev = OracleEvaluator(ods)
+        got = L._testing.simulated_annealing(net.n, ev, L.score.BDeu(e["ess"]), e["max_parents"], e["max_iters"],
+                                             e["init_temp"], e["cooling_rate"], e["is_deterministic"], e["seed"],
+                                             e["num_chains"], comm)
+        sa_out.append((pdag_to_adj(got, net.n).tolist() == e["adj"], ev.n_sc, e["num_chains"]))
+    out["sa"] = sa_out
     out["collectives"] = comm.n_collectives
     q.put((rank, out))
     dist.barrier()
@@ -70,7 +83,7 @@ def test_world2_sharded_drivers():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    keys = [k for k in res[0] if k != "collectives"]
+    keys = [k for k in res[0] if k not in ("collectives", "sa")]
     assert keys
     for k in keys:
         ok0, mine0, total0 = res[0][k]
@@ -80,3 +93,6 @@ def test_world2_sharded_drivers():
         assert mine0 + mine1 == total0, k             # the work was split, not replicated
         assert abs(mine0 - mine1) <= max(16, total0 // 4), k
     assert res[0]["collectives"] == res[1]["collectives"] > 0
+    for (ok0, n0, chains), (ok1, n1, _) in zip(res[0]["sa"], res[1]["sa"]):
+        assert ok0 and ok1                            # every rank returns the reference's DAG
+        assert n0 > 0 and n1 > 0                      # and both scored their own chains
