@@ -128,7 +128,11 @@ OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
  * (best_ls_tbl: n * 2^n (score, parent set); best_gs_tbl / best_ch_tbl: 2^n,
  * :33-40) live in HBM for the whole search.  Per lattice level the caller
  *   1. obn_es_level_begin   hands over the level's subsets (bit masks, all of
- *                           size k, in the reference's Gosper order, :51,:129),
+ *                           size k, in the reference's Gosper order, :51,:129);
+ *                           masks may be NULL for a level that needs no scores
+ *                           (k = 0, k > max_parents + 1, or after obn_es_lattice):
+ *                           n_subsets must then be C(n, k) and the DP walks
+ *                           level lists built on the device,
  *   2. obn_es_level_scores  has the |W| local scores of the subsets
  *                           [begin, end) computed (one table per subset, :55-72)
  *                           into the level buffer -- a multi-GPU caller gives

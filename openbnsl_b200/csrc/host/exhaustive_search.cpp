@@ -183,7 +183,8 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
     const auto t0 = clk::now();
     masks.clear();
     size_t T = 1;
-    if (lattice) {                        // the device DP finds the level's subsets by popcount
+    const bool scored = size <= max_varset && size > 0;              // :48
+    if (lattice || !scored) {             // the device DP walks its own level lists: nothing to enumerate
       for (size_t i = 1; i <= size; ++i) T = T * (n - size + i) / i;             // C(n, size), exact stepwise
     } else {
       uint64_t W = ((uint64_t)1 << size) - 1;                          // :51
@@ -194,7 +195,7 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
     const bool sharded = comm.world > 1 && calc_ls && !lattice &&
                          (double)T * (double)size * (double)n_rows >= opt.shard_min_bytes && T >= (size_t)comm.world;
     const size_t chunk = sharded ? (T + comm.world - 1) / comm.world : T;
-    check(obn_es_level_begin(es, lattice ? nullptr : masks.data(), T, (int)size, sharded ? chunk * comm.world : T));
+    check(obn_es_level_begin(es, (lattice || !scored) ? nullptr : masks.data(), T, (int)size, sharded ? chunk * comm.world : T));
     const auto t1 = clk::now();
     if (calc_ls) {
       if (sharded) check(obn_es_level_scores(es, std::min(T, chunk * comm.rank), std::min(T, chunk * (comm.rank + 1))));

@@ -29,6 +29,7 @@ struct obn_es {
   size_t T = 0, buffer_doubles = 0;
   int k = 0;
   bool calc = false;
+  bool from_lists = false;        // this level's subsets come from the device level lists (no host masks)
 };
 
 namespace obn {
@@ -120,6 +121,36 @@ __global__ void es_level_lists_kernel(size_t combs, int n, EsLevels lv, uint32_t
   lists[lv.off[__popc(W)] + rank] = W;
 }
 
+
+// Level lists on the device (they depend on n only; kept in the ctx pool for the next search).
+static int es_ensure_lists(obn_es* e) {
+  obn_ctx* c = e->c;
+  EsPool& pool = c->es_pool;
+  const int n = e->n;
+  const size_t combs = (size_t)1 << n;
+  const void* before = pool.d_lists.p;
+  if (int rc = pool.d_lists.reserve(combs * sizeof(uint32_t))) return rc;
+  if (pool.d_lists.p != before) pool.lists_n = 0;
+  EsLevels lv{};
+  uint64_t off = 0, binom = 1;
+  for (int k = 0; k <= n; ++k) {
+    if (k) binom = binom * (uint64_t)(n - k + 1) / (uint64_t)k;
+    lv.off[k] = off;
+    off += binom;
+  }
+  lv.off[n + 1] = off;
+  e->levels = lv;
+  if (pool.lists_n != n) {
+    (void)cudaGetLastError();
+    es_level_lists_kernel<<<(unsigned)((combs + 255) / 256), 256, 0, c->stream>>>(combs, n, lv, pool.d_lists.as<uint32_t>());
+    OBN_CUDA(cudaGetLastError());
+    OBN_CUDA(cudaStreamSynchronize(c->stream));
+    ++c->prof.total_launches;
+    pool.lists_n = n;
+  }
+  return OBN_OK;
+}
+
 }  // namespace obn
 
 extern "C" {
@@ -175,7 +206,7 @@ void obn_es_end(obn_es* e) {
 }
 
 int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k, size_t buffer_subsets) {
-  if (!e || (!masks && n_subsets && !e->use_F)) return fail(OBN_ERR_INVALID, "obn_es_level_begin: NULL argument");
+  if (!e) return fail(OBN_ERR_INVALID, "obn_es_level_begin: NULL argument");
   if (k < 0 || k > e->n) return fail(OBN_ERR_INVALID, "subset size %d out of range", k);
   if (buffer_subsets < n_subsets) buffer_subsets = n_subsets;
   obn_ctx* c = e->c;
@@ -183,12 +214,24 @@ int obn_es_level_begin(obn_es* e, const uint64_t* masks, size_t n_subsets, int k
   e->T = n_subsets;
   e->k = k;
   e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
-  if (e->use_F) return OBN_OK;                 // lattice mode: the DP kernel finds the level by popcount
+  e->from_lists = false;
+  if (e->use_F) return OBN_OK;                 // lattice mode: F and the level lists are already on the device
+  if (!masks) {
+    // a level that needs no scores (k = 0 or k > max_parents + 1, exhaustive_search.cpp:48,65): the DP
+    // walks the device level list, nothing to enumerate or upload
+    if (e->calc && k > 0) return fail(OBN_ERR_INVALID, "obn_es_level_begin: masks are required for a scored level");
+    if (int rc = es_ensure_lists(e)) return rc;
+    if (n_subsets != (size_t)(e->levels.off[k + 1] - e->levels.off[k]))
+      return fail(OBN_ERR_INVALID, "obn_es_level_begin: level %d has %llu subsets", k,
+                  (unsigned long long)(e->levels.off[k + 1] - e->levels.off[k]));
+    e->from_lists = true;
+    e->masks.clear();
+    return OBN_OK;
+  }
   e->masks.assign(masks, masks + n_subsets);
   e->k = k;
   e->calc = (size_t)k <= e->max_parents + 1;                                      // :48
   e->buffer_doubles = buffer_subsets * (size_t)std::max(k, 1);
-  c->es_pool.lists_n = 0;                     // the level lists of the lattice mode share this buffer
   if (int rc = c->es_pool.d_masks.reserve(std::max<size_t>(n_subsets * 8, 16))) return rc;
   if (int rc = c->es_pool.d_level.reserve(std::max<size_t>(e->buffer_doubles * 8, 16))) return rc;
   if (n_subsets)
@@ -242,8 +285,12 @@ int obn_es_level_dp(obn_es* e) {
   if (e->use_F) {
     const size_t Tk = (size_t)(e->levels.off[e->k + 1] - e->levels.off[e->k]);
     es_dp_warp_kernel<uint32_t, true><<<(unsigned)((Tk + 3) / 4), 128, 0, c->stream>>>(
-        c->es_pool.d_masks.as<uint32_t>() + e->levels.off[e->k], Tk, e->k, e->n, e->calc, nullptr, e->F,
+        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], Tk, e->k, e->n, e->calc, nullptr, e->F,
         c->es_pool.d_slot.as<uint32_t>(), e->h, e->L, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
+  } else if (e->from_lists) {
+    es_dp_warp_kernel<uint32_t, false><<<(unsigned)((e->T + 3) / 4), 128, 0, c->stream>>>(
+        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], e->T, e->k, e->n, false, nullptr, nullptr, nullptr, 0, 0,
+        e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
   } else {
     es_dp_warp_kernel<unsigned long long, false><<<(unsigned)((e->T + 3) / 4), 128, 0, c->stream>>>(
         c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n, e->calc && e->k, c->es_pool.d_level.as<double>(), nullptr,

@@ -130,19 +130,19 @@ struct LatticeGraphCache {
 struct EsPool {
   bool in_use = false;
   LatticeGraphCache lattice;
-  int lists_n = 0;                 // d_masks holds the lattice-mode level lists of this many variables (0 = not)
+  int lists_n = 0;                 // d_lists holds the level lists (subsets grouped by size) of this many variables
   DevBuf d_bl_score, d_bl_ps, d_best_gs, d_best_ch, d_F;
-  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog;
+  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog, d_lists;
   void release() {
     lattice.clear();
     for (DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks, &d_slot,
-                      &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog})
+                      &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists})
       b->release();
   }
   size_t bytes() const {
     size_t s = 0;
     for (const DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks,
-                            &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog})
+                            &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists})
       s += b->cap;
     return s;
   }

@@ -577,28 +577,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   cudaEventElapsedTime(&ms, e0, e1);
   c->prof.count_kernel_ms += ms;
   // level lists for the DP: subsets grouped by size, ascending inside a level (= Gosper order)
-  {
-    const void* before = pool.d_masks.p;
-    if (int rc = pool.d_masks.reserve(combs * sizeof(uint32_t))) return rc;
-    if (pool.d_masks.p != before) pool.lists_n = 0;
-    EsLevels lv{};
-    uint64_t off = 0, binom = 1;
-    for (int k = 0; k <= n; ++k) {
-      if (k) binom = binom * (uint64_t)(n - k + 1) / (uint64_t)k;
-      lv.off[k] = off;
-      off += binom;
-    }
-    lv.off[n + 1] = off;
-    e->levels = lv;
-    if (pool.lists_n != n) {                  // they depend on n only: kept for the next search
-      (void)cudaGetLastError();
-      es_level_lists_kernel<<<(unsigned)((combs + 255) / 256), 256, 0, c->stream>>>(combs, n, lv, pool.d_masks.as<uint32_t>());
-      OBN_CUDA(cudaGetLastError());
-      OBN_CUDA(cudaStreamSynchronize(c->stream));
-      ++c->prof.total_launches;
-      pool.lists_n = n;
-    }
-  }
+  if (int rc = es_ensure_lists(e)) return rc;
   e->use_F = true;
   e->f_per_rank = (size_t)G.per << G.L;
   return OBN_OK;
