@@ -24,6 +24,8 @@ struct obn_es {
   obn::EsLevels levels{};
   int h = 0, L = 0;
   size_t f_per_rank = 0;
+  const uint32_t* perm = nullptr;   // lattice digit order != variable order: three 1024-entry tables, subset mask ->
+                                    // mask in digit order = perm[m & 1023] | perm[1024 + (m >> 10 & 1023)] | perm[2048 + (m >> 20)]
   // all device buffers of a session come from c->es_pool (reused by the next session)
   std::vector<uint64_t> masks;
   size_t T = 0, buffer_doubles = 0;
@@ -46,10 +48,15 @@ namespace obn {
 //   LIST   uint32_t (lattice level lists) or unsigned long long (the host's Gosper lists)
 //   USE_F  local scores from the lattice, ls(c | W - c) = F(W) - F(W - c), F block-major:
 //          index = slot[S & (2^h - 1)] << L | S >> h;  else scores[t * k + rank of c in W]
+__device__ __forceinline__ size_t es_f_index(uint32_t S, const uint32_t* perm, const uint32_t* slot, int h, int L) {
+  if (perm) S = __ldg(perm + (S & 1023u)) | __ldg(perm + 1024 + ((S >> 10) & 1023u)) | __ldg(perm + 2048 + (S >> 20));
+  return ((size_t)slot[S & ((1u << h) - 1u)] << L) | (S >> h);
+}
+
 template <typename LIST, bool USE_F>
 __global__ void __launch_bounds__(128) es_dp_warp_kernel(const LIST* list, size_t T, int k, int n, bool calc, const double* scores,
-                                                       const double* F, const uint32_t* slot, int h, int L, double* bl_score,
-                                                       uint32_t* bl_ps, double* best_gs, uint8_t* best_ch) {
+                                                       const double* F, const uint32_t* slot, const uint32_t* perm, int h, int L,
+                                                       double* bl_score, uint32_t* bl_ps, double* best_gs, uint8_t* best_ch) {
   const size_t t = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (t >= T) return;                                     // whole warps leave together
   const int c = threadIdx.x & 31;
@@ -60,8 +67,7 @@ __global__ void __launch_bounds__(128) es_dp_warp_kernel(const LIST* list, size_
   uint32_t bps = pa;
   if (active && calc) {                                   // :65-73
     if (USE_F) {
-      const uint32_t hm = (1u << h) - 1u;
-      bls = F[((size_t)slot[W & hm] << L) | (W >> h)] - F[((size_t)slot[pa & hm] << L) | (pa >> h)];
+      bls = F[es_f_index(W, perm, slot, h, L)] - F[es_f_index(pa, perm, slot, h, L)];
     } else {
       bls = scores[t * (size_t)k + __popc(W & ((1u << c) - 1u))];
     }
@@ -286,15 +292,15 @@ int obn_es_level_dp(obn_es* e) {
     const size_t Tk = (size_t)(e->levels.off[e->k + 1] - e->levels.off[e->k]);
     es_dp_warp_kernel<uint32_t, true><<<(unsigned)((Tk + 3) / 4), 128, 0, c->stream>>>(
         c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], Tk, e->k, e->n, e->calc, nullptr, e->F,
-        c->es_pool.d_slot.as<uint32_t>(), e->h, e->L, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
+        c->es_pool.d_slot.as<uint32_t>(), e->perm, e->h, e->L, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
   } else if (e->from_lists) {
     es_dp_warp_kernel<uint32_t, false><<<(unsigned)((e->T + 3) / 4), 128, 0, c->stream>>>(
-        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], e->T, e->k, e->n, false, nullptr, nullptr, nullptr, 0, 0,
-        e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
+        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], e->T, e->k, e->n, false, nullptr, nullptr, nullptr, nullptr,
+        0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
   } else {
     es_dp_warp_kernel<unsigned long long, false><<<(unsigned)((e->T + 3) / 4), 128, 0, c->stream>>>(
         c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n, e->calc && e->k, c->es_pool.d_level.as<double>(), nullptr,
-        nullptr, 0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
+        nullptr, nullptr, 0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
   }
   OBN_CUDA(cudaGetLastError());
   OBN_CUDA(cudaStreamSynchronize(c->stream));

@@ -120,6 +120,8 @@ struct LatticeGraphCache {
   uint32_t per = 0;
   uint64_t joint_off = 0, joint_cells = 0;
   uint64_t launches = 0;
+  bool permuted = false;           // digit order differs from the variable order (d_perm holds the mask translation)
+  std::vector<uint32_t> order;     // order[i] = variable at digit i
   void clear() {
     if (exec) cudaGraphExecDestroy(exec);
     exec = nullptr;
@@ -132,17 +134,17 @@ struct EsPool {
   LatticeGraphCache lattice;
   int lists_n = 0;                 // d_lists holds the level lists (subsets grouped by size) of this many variables
   DevBuf d_bl_score, d_bl_ps, d_best_gs, d_best_ch, d_F;
-  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog, d_lists;
+  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog, d_lists, d_perm;
   void release() {
     lattice.clear();
     for (DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks, &d_slot,
-                      &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists})
+                      &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists, &d_perm})
       b->release();
   }
   size_t bytes() const {
     size_t s = 0;
     for (const DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks,
-                            &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists})
+                            &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists, &d_perm})
       s += b->cap;
     return s;
   }

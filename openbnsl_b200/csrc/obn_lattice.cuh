@@ -161,7 +161,8 @@ __global__ void marg_reduce_kernel(const MargTask* tasks, uint32_t n_tasks, uint
 
 // The joint table of all n variables, counted straight into its final place (zeroed by the
 // caller): one thread per 16-row vector, RED.E.ADD into L2.  Padding rows are all-zero codes.
-struct JointCards { uint32_t c[kMaxTupleVars]; };
+// c[i] / v[i]: cardinality / dataset column of the variable at digit i (digit 0 most significant)
+struct JointCards { uint32_t c[kMaxTupleVars]; uint32_t v[kMaxTupleVars]; };
 __global__ void joint_count_kernel(const uint8_t* data, size_t stride, uint32_t n_rows, int n, JointCards cards,
                                    int32_t* tab) {
   const uint32_t n_vec = (n_rows + 15u) >> 4;
@@ -169,8 +170,8 @@ __global__ void joint_count_kernel(const uint8_t* data, size_t stride, uint32_t 
   if (v < n_vec) {
     const size_t off = (size_t)v << 4;
     KeyVec<32> key;
-    key.init(ld_codes16(data + off));
-    for (int i = 1; i < n; ++i) key.push(ld_codes16(data + (size_t)i * stride + off), cards.c[i]);
+    key.init(ld_codes16(data + (size_t)cards.v[0] * stride + off));
+    for (int i = 1; i < n; ++i) key.push(ld_codes16(data + (size_t)cards.v[i] * stride + off), cards.c[i]);
     count16<32, TIER_GLOBAL, false>(key, reinterpret_cast<unsigned char*>(tab));
   }
   if (v == 0) {

@@ -272,10 +272,13 @@ static int launch_bottom_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tas
 }
 
 // The joint table over all variables: the only pass over the data in lattice mode.
-static int joint_count(obn_ctx* c, const obn_dataset* ds, int32_t* J, uint64_t cells) {
+static int joint_count(obn_ctx* c, const obn_dataset* ds, const std::vector<uint32_t>& order, int32_t* J, uint64_t cells) {
   OBN_CUDA(cudaMemsetAsync(J, 0, cells * 4, c->stream));
   JointCards jc{};
-  for (size_t v = 0; v < ds->n_vars; ++v) jc.c[v] = ds->cards[v];
+  for (size_t i = 0; i < ds->n_vars; ++i) {
+    jc.v[i] = order[i];
+    jc.c[i] = ds->cards[order[i]];
+  }
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
   (void)cudaGetLastError();
   joint_count_kernel<<<std::max(1u, (n_vec + 127) / 128), 128, 0, c->stream>>>(ds->data, ds->stride, (uint32_t)ds->n_rows, (int)ds->n_vars, jc, J);
@@ -321,18 +324,41 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     memcpy(&ess_bits, &e->ess, 8);
     k.insert(k.end(), {(uint64_t)n, (uint64_t)ds->n_rows, ess_bits, (uint64_t)rank, (uint64_t)world,
                        (uint64_t)env_int("OBN_LATTICE_BUDGET_GB", 24), (uint64_t)env_int("OBN_LATTICE_BOTTOM", 1),
-                       (uint64_t)env_int("OBN_LATTICE_MAX_L", 20), (uint64_t)env_int("OBN_LATTICE_NO_LUT", 0)});
+                       (uint64_t)env_int("OBN_LATTICE_MAX_L", 20), (uint64_t)env_int("OBN_LATTICE_NO_LUT", 0),
+                       (uint64_t)env_int("OBN_LATTICE_REORDER", 1)});
     for (int v = 0; v < n; ++v) k.push_back(ds->cards[v]);
     for (const DevBuf* d : {&pool.d_F, &pool.d_root, &pool.d_pp[0], &pool.d_pp[1], &pool.d_tasks, &pool.d_partials, &pool.d_lut_a, &pool.d_lutF, &pool.d_prog})
       k.push_back((uint64_t)(uintptr_t)d->p);
     return k;
   };
+  // Digit order of the joint table.  The bottom tier needs the 8 fastest digits binary: when the last
+  // 8 variables are not all binary but the data set has 8 binary variables, the 8 highest-numbered
+  // binary variables become the fastest digits (everything else keeps its relative order).  Subset
+  // masks are translated to digit order by three small tables (es_f_index in obn_es.inl).
+  std::vector<uint32_t> order(n);
+  for (int v = 0; v < n; ++v) order[v] = (uint32_t)v;
+  if (env_int("OBN_LATTICE_BOTTOM", 1) != 0 && env_int("OBN_LATTICE_REORDER", 1) != 0 && n >= kBotL) {
+    bool tail_binary = true;
+    for (int v = n - kBotL; v < n; ++v) tail_binary &= ds->cards[v] == 2;
+    std::vector<uint32_t> bin;
+    for (int v = n - 1; v >= 0 && bin.size() < (size_t)kBotL; --v)
+      if (ds->cards[v] == 2) bin.push_back((uint32_t)v);
+    if (!tail_binary && bin.size() == (size_t)kBotL) {
+      std::sort(bin.begin(), bin.end());
+      order.clear();
+      for (int v = 0; v < n; ++v)
+        if (!std::binary_search(bin.begin(), bin.end(), (uint32_t)v)) order.push_back((uint32_t)v);
+      order.insert(order.end(), bin.begin(), bin.end());
+    }
+  }
+  std::vector<uint32_t> cards_p(n);
+  for (int i = 0; i < n; ++i) cards_p[i] = ds->cards[order[i]];
   const bool hit = use_graph && G.exec && G.key == make_key();
   if (dbg) fprintf(stderr, "[obn_es_lattice] graph cache %s\n", hit ? "hit" : "miss");
   if (!hit) {
     G.clear();
     LatticePlan P;
-    if (!plan_lattice(ds->cards, budget, world, env_int("OBN_LATTICE_BOTTOM", 1) != 0, P))
+    if (!plan_lattice(cards_p, budget, world, env_int("OBN_LATTICE_BOTTOM", 1) != 0, P))
       return fail(OBN_ERR_UNSUPPORTED, "marginalisation lattice does not fit (joint table >= 2^31 cells or too little memory)");
     lap("plan");
     const int h = P.h, L = P.L, Lm = P.Lm;
@@ -394,6 +420,22 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
       if (int rc = pool.d_prog.reserve(bp.words.size() * 4 + bp.patterns.size() * 2)) return rc;
       OBN_CUDA(cudaMemcpy(pool.d_prog.p, bp.words.data(), bp.words.size() * 4, cudaMemcpyHostToDevice));
       OBN_CUDA(cudaMemcpy(pool.d_prog.as<char>() + bp.words.size() * 4, bp.patterns.data(), bp.patterns.size() * 2, cudaMemcpyHostToDevice));
+    }
+    bool permuted = false;
+    for (int i = 0; i < n; ++i) permuted |= order[i] != (uint32_t)i;
+    if (permuted) {
+      // mask translation tables: bit v of a subset mask -> bit (digit of variable v)
+      std::vector<uint32_t> digit_of(n), tab(3 * 1024, 0);
+      for (int i = 0; i < n; ++i) digit_of[order[i]] = (uint32_t)i;
+      for (int t = 0; t < 3; ++t)
+        for (uint32_t m = 0; m < 1024; ++m) {
+          uint32_t out = 0;
+          for (int b = 0; b < 10; ++b)
+            if ((m >> b & 1u) && t * 10 + b < n) out |= 1u << digit_of[t * 10 + b];
+          tab[t * 1024 + m] = out;
+        }
+      if (int rc = pool.d_perm.reserve(tab.size() * 4)) return rc;
+      OBN_CUDA(cudaMemcpy(pool.d_perm.p, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice));
     }
     lap("tasks upload");
 
@@ -457,7 +499,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     if (use_graph) OBN_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
     else {
       // eager path (debugging): the joint table has to exist before the first launch
-      if (int rc = joint_count(c, ds, root + P.root_off[B - 1], P.cells_high[B - 1] * P.cells_low)) return rc;
+      if (int rc = joint_count(c, ds, order, root + P.root_off[B - 1], P.cells_high[B - 1] * P.cells_low)) return rc;
       OBN_CUDA(cudaEventRecord(e0, c->stream));
     }
     auto abort_capture = [&]() {
@@ -526,6 +568,8 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     G.h = h;
     G.L = L;
     G.per = per;
+    G.order = order;
+    G.permuted = permuted;
     G.joint_off = P.root_off[B - 1];
     G.joint_cells = P.cells_high[B - 1] * P.cells_low;
     G.launches = c->prof.total_launches - launches_before;
@@ -550,6 +594,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   e->F = pool.d_F.as<double>();
   e->h = G.h;
   e->L = G.L;
+  e->perm = G.permuted ? pool.d_perm.as<uint32_t>() : nullptr;
   {
     // accounting: what the reference would have read for the subsets whose scores are used:
     // sum over k <= max_parents+1 of C(n,k) * k * N bytes
@@ -562,7 +607,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   }
   if (use_graph) {
     // the joint table is the only pass over the data; then the whole lattice is one graph launch
-    if (int rc = joint_count(c, ds, pool.d_root.as<int32_t>() + G.joint_off, G.joint_cells)) return rc;
+    if (int rc = joint_count(c, ds, G.order, pool.d_root.as<int32_t>() + G.joint_off, G.joint_cells)) return rc;
     OBN_CUDA(cudaEventRecord(e0, c->stream));
     cudaError_t ge = cudaGraphLaunch(G.exec, c->stream);
     if (ge == cudaSuccess) ge = cudaEventRecord(e1, c->stream);

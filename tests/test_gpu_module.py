@@ -192,6 +192,8 @@ def test_exhaustive_search_lattice_mode(which, max_parents, monkeypatch):
     ([3, 2, 4, 2, 3] + [2] * 8, 11, 0),     # mixed cardinalities above a binary bottom tier, 4 blocks
     ([2] * 9, 8, 0),                        # no mid tier at all (Lm = 0), 2 blocks
     ([2] * 11, 20, 1),                      # no term tables: libm fallback inside the bottom kernel
+    ([2, 3, 2, 2, 4, 2, 2, 3, 2, 2, 2], 20, 0),          # exactly 8 binary variables, scattered: digit order != variable order
+    ([2, 2, 3, 2, 2, 2, 4, 2, 2, 2, 3, 2, 3], 11, 0),    # 9 binary variables, the last one is not binary; 4 blocks
 ])
 def test_lattice_bottom_tier_equals_hbm_tiers(cards, max_l, no_lut, monkeypatch):
     """The shared-memory bottom tier (last 8 binary variables) and the all-HBM lattice build the same
