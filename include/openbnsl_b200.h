@@ -148,6 +148,17 @@ OBN_API int obn_es_level_begin(obn_es* es, const uint64_t* masks, size_t n_subse
 OBN_API int obn_es_level_scores(obn_es* es, size_t begin, size_t end);
 OBN_API int obn_es_level_buffer(obn_es* es, void** scores_dev, size_t* n_doubles);
 OBN_API int obn_es_level_dp(obn_es* es);
+/* Multi-GPU, after obn_es_lattice: the DP sharded by child.  The best-parent-set entry of (W, c)
+ * (:75-87) depends only on entries of the same child c, so rank r of `world` keeps the DP columns
+ * of children [n r / world, n (r+1) / world) and never needs the others.  Only the sink choice
+ * (:89-94) needs every child: obn_es_level_dp_part runs the level for this rank's children and
+ * writes (best sum, child) per subset into slice `rank` of a device buffer of world * bytes_per_rank
+ * bytes, the caller all-gathers that buffer in place, obn_es_level_dp_commit takes the reference's
+ * choice (largest sum, earliest child) and writes best_gs / best_ch on every rank.  Once a level
+ * has been done this way the rest of the search must be too; obn_es_finish then fills only this
+ * rank's children in parent_masks (zero elsewhere: OR the ranks' arrays). */
+OBN_API int obn_es_level_dp_part(obn_es* es, int rank, int world, void** parts_dev, size_t* bytes_per_rank);
+OBN_API int obn_es_level_dp_commit(obn_es* es, int world);
 /* Fast mode for deep searches: instead of steps 2 of every level, compute
  *   F(S) = sum over the cells of S of lgamma(N_c + ess/cells(S)) - lgamma(ess/cells(S))
  * for ALL subsets at once by a marginalisation lattice over the joint table

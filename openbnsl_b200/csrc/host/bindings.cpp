@@ -291,6 +291,7 @@ PYBIND11_MODULE(openbnsllib, m) {
            o.cards.assign(df.num_of_values.begin(), df.num_of_values.end());
            const char* e = std::getenv("OBN_SHARD_MIN_BYTES");
            o.shard_min_bytes = e && *e ? std::atof(e) : 4e9;
+           if (const char* d = std::getenv("OBN_ES_DP_SHARD_MIN")) o.dp_shard_min_subsets = (size_t)std::atoll(d);
            const Comm c = make_comm(comm);
            if (c.world > 1 && !c.allgather_dev) throw std::invalid_argument("comm lacks allgather_dev");
            g_last_es_stats = EsStats{};

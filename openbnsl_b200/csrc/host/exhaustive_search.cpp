@@ -179,6 +179,7 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
     }
   }
   std::vector<uint64_t> masks;
+  bool dp_by_child = false;             // lattice mode on several GPUs: the DP columns are sharded by child
   for (size_t size = 0; size <= n; ++size) {                        // exhaustive_search.cpp:47
     const auto t0 = clk::now();
     masks.clear();
@@ -209,7 +210,19 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
       comm.allgather_dev((uintptr_t)p, chunk * size * sizeof(double));
     }
     const auto t3 = clk::now();
-    check(obn_es_level_dp(es));                                       // :59-116
+    // :59-116.  Lattice mode on several GPUs: from the first level that is worth a collective on,
+    // every rank runs the DP for its own children only and the sink choice merges through one
+    // all-gather of (sum, child) per level (obn_es_level_dp_part).
+    if (lattice && comm.world > 1 && (dp_by_child || T >= opt.dp_shard_min_subsets)) {
+      dp_by_child = true;
+      void* parts = nullptr;
+      size_t per = 0;
+      check(obn_es_level_dp_part(es, comm.rank, comm.world, &parts, &per));
+      comm.allgather_dev((uintptr_t)parts, per);
+      check(obn_es_level_dp_commit(es, comm.world));
+    } else {
+      check(obn_es_level_dp(es));
+    }
     const auto t4 = clk::now();
     if (stats) {
       if (size <= max_varset) {
@@ -225,6 +238,14 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
   std::vector<uint64_t> pm(n, 0);
   double best = 0;
   check(obn_es_finish(es, pm.data(), &best));                         // :133-148
+  if (dp_by_child) {                    // every rank reported the parent sets of its own children
+    std::vector<uint64_t> all(n * (size_t)comm.world, 0);
+    comm.allgather(pm.data(), all.data(), n * sizeof(uint64_t));
+    for (size_t v = 0; v < n; ++v) {
+      pm[v] = 0;
+      for (int r = 0; r < comm.world; ++r) pm[v] |= all[(size_t)r * n + v];
+    }
+  }
   PDAG g(n);
   for (size_t v = 0; v < n; ++v)
     for (size_t j = 0; j < n; ++j)

@@ -55,6 +55,7 @@ struct EsOptions {
   int exact_order = 2;            // 0 fast, 1 exact (error if tables do not fit), 2 auto
   std::vector<uint32_t> cards;    // cardinalities (device driver: cost model of the lattice mode)
   double shard_min_bytes = 0;     // multi-GPU: shard a level only if it has this many algorithmic bytes
+  size_t dp_shard_min_subsets = 4096;   // multi-GPU lattice mode: shard the DP by child from the first level this large
 };
 struct EsStats {
   uint64_t tables = 0, scores = 0;

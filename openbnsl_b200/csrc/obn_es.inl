@@ -32,6 +32,7 @@ struct obn_es {
   int k = 0;
   bool calc = false;
   bool from_lists = false;        // this level's subsets come from the device level lists (no host masks)
+  int own_first = 0, own_end = 64;  // children whose DP columns this rank holds (obn_es_level_dp_part)
 };
 
 namespace obn {
@@ -53,15 +54,29 @@ __device__ __forceinline__ size_t es_f_index(uint32_t S, const uint32_t* perm, c
   return ((size_t)slot[S & ((1u << h) - 1u)] << L) | (S >> h);
 }
 
+// Multi-GPU: the DP shards by CHILD.  Entry [W * n + c] depends only on entries of the same child, so
+// rank r keeps the columns of its children (a contiguous range) and never needs the others'; only
+// the sink choice needs every child, and it merges through one all-gather of (best own sum, child)
+// per level (EsPart) followed by es_dp_commit_kernel.  A group of 2^gshift lanes handles one subset,
+// lane q = child own_first + q; unsharded: one warp per subset, all n children.
+struct EsPart {
+  double gs;      // best best_gs[W - c] + bls over this rank's children of W (-inf if it has none)
+  int32_t ch;     // that child (INT_MAX if none)
+  int32_t pad;
+};
+
 template <typename LIST, bool USE_F>
 __global__ void __launch_bounds__(128) es_dp_warp_kernel(const LIST* list, size_t T, int k, int n, bool calc, const double* scores,
                                                        const double* F, const uint32_t* slot, const uint32_t* perm, int h, int L,
-                                                       double* bl_score, uint32_t* bl_ps, double* best_gs, uint8_t* best_ch) {
-  const size_t t = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (t >= T) return;                                     // whole warps leave together
-  const int c = threadIdx.x & 31;
-  const uint32_t W = (uint32_t)list[t];
-  const bool active = (W >> c) & 1u;
+                                                       double* bl_score, uint32_t* bl_ps, double* best_gs, uint8_t* best_ch,
+                                                       int own_first, int own_count, int gshift, EsPart* part) {
+  const int lane = threadIdx.x & 31, width = 1 << gshift, q = lane & (width - 1);
+  const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const size_t t = warp * (size_t)(32 >> gshift) + (size_t)(lane >> gshift);
+  const bool in_range = t < T;                            // (no early return: the sink scan shuffles over full warps)
+  const uint32_t W = in_range ? (uint32_t)list[t] : 0u;
+  const int c = own_first + q;
+  const bool active = in_range && q < own_count && ((W >> c) & 1u);
   const uint32_t pa = W & ~(1u << c);
   double bls = -INFINITY;
   uint32_t bps = pa;
@@ -72,7 +87,7 @@ __global__ void __launch_bounds__(128) es_dp_warp_kernel(const LIST* list, size_
       bls = scores[t * (size_t)k + __popc(W & ((1u << c) - 1u))];
     }
   }
-  for (uint32_t m = W; m; m &= m - 1) {                   // :75-87, the same j for every lane
+  for (uint32_t m = W; m; m &= m - 1) {                   // :75-87, the same j for every lane of the subset
     const int j = __ffs((int)m) - 1;
     if (active && j != c) {
       const size_t at = (size_t)(W ^ (1u << j)) * n + c;
@@ -91,18 +106,43 @@ __global__ void __launch_bounds__(128) es_dp_warp_kernel(const LIST* list, size_
   }
   double bgs = 0.0;
   int bch = -1;
-  for (uint32_t m = W; m; m &= m - 1) {
-    const int child = __ffs((int)m) - 1;
-    const double g = __shfl_sync(0xffffffffu, gs, child);
-    if (bgs >= 0 || g > bgs) {
+  const int base = lane & ~(width - 1);
+  const uint32_t act = __ballot_sync(0xffffffffu, active);
+  for (int qq = 0; qq < own_count; ++qq) {                // ascending child order
+    const double g = __shfl_sync(0xffffffffu, gs, base + qq);
+    if (((act >> (base + qq)) & 1u) && (bgs >= 0 || g > bgs)) {
       bgs = g;
-      bch = child;
+      bch = own_first + qq;
     }
   }
-  if (c == 0) {                                           // :115-116
-    best_gs[W] = bgs;
-    best_ch[W] = (uint8_t)bch;
+  if (q == 0 && in_range) {                               // :115-116
+    if (part) {
+      part[t] = EsPart{bch >= 0 ? bgs : -INFINITY, bch >= 0 ? bch : INT_MAX, 0};
+    } else {
+      best_gs[W] = bgs;
+      best_ch[W] = (uint8_t)bch;
+    }
   }
+}
+
+// parts[r * T + t] = rank r's (sum, child) for subset list[t]; ranks own ascending child ranges, so the
+// serial scan over children (:89-94) is a scan over ranks that only replaces on a strictly larger sum.
+template <typename LIST>
+__global__ void es_dp_commit_kernel(const LIST* list, size_t T, int world, const EsPart* parts, double* best_gs, uint8_t* best_ch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  double bgs = 0.0;
+  int bch = -1;
+  for (int r = 0; r < world; ++r) {
+    const EsPart p = parts[(size_t)r * T + t];
+    if (p.ch != INT_MAX && (bgs >= 0 || p.gs > bgs)) {
+      bgs = p.gs;
+      bch = p.ch;
+    }
+  }
+  const uint32_t W = (uint32_t)list[t];
+  best_gs[W] = bgs;
+  best_ch[W] = (uint8_t)bch;
 }
 
 // Level lists for the lattice mode (no host mask lists there):
@@ -282,26 +322,79 @@ int obn_es_level_buffer(obn_es* e, void** scores_dev, size_t* n_doubles) {
   return OBN_OK;
 }
 
+// one DP launch for the level: children [own_first, own_first + own_count), results to the tables
+// (part == nullptr) or to `part` (child-sharded)
+static int es_launch_dp(obn_es* e, int own_first, int own_count, obn::EsPart* part) {
+  obn_ctx* c = e->c;
+  int gshift = 0;
+  while ((1 << gshift) < own_count) ++gshift;
+  const size_t per_cta = (size_t)4 * (32 >> gshift);                 // subsets per 128-thread CTA
+  const unsigned grid = (unsigned)((e->T + per_cta - 1) / per_cta);
+  (void)cudaGetLastError();
+  if (e->use_F) {
+    es_dp_warp_kernel<uint32_t, true><<<grid, 128, 0, c->stream>>>(
+        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], e->T, e->k, e->n, e->calc, nullptr, e->F,
+        c->es_pool.d_slot.as<uint32_t>(), e->perm, e->h, e->L, e->bl_score, e->bl_ps, e->best_gs, e->best_ch, own_first, own_count,
+        gshift, part);
+  } else if (e->from_lists) {
+    es_dp_warp_kernel<uint32_t, false><<<grid, 128, 0, c->stream>>>(
+        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], e->T, e->k, e->n, false, nullptr, nullptr, nullptr, nullptr,
+        0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch, own_first, own_count, gshift, part);
+  } else {
+    es_dp_warp_kernel<unsigned long long, false><<<grid, 128, 0, c->stream>>>(
+        c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n, e->calc && e->k, c->es_pool.d_level.as<double>(), nullptr,
+        nullptr, nullptr, 0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch, own_first, own_count, gshift, part);
+  }
+  OBN_CUDA(cudaGetLastError());
+  ++c->prof.total_launches;
+  return OBN_OK;
+}
+
 int obn_es_level_dp(obn_es* e) {
   if (!e) return fail(OBN_ERR_INVALID, "obn_es_level_dp: NULL argument");
   if (!e->T) return OBN_OK;
   obn_ctx* c = e->c;
   OBN_CUDA(cudaSetDevice(c->device));
-  (void)cudaGetLastError();
-  if (e->use_F) {
-    const size_t Tk = (size_t)(e->levels.off[e->k + 1] - e->levels.off[e->k]);
-    es_dp_warp_kernel<uint32_t, true><<<(unsigned)((Tk + 3) / 4), 128, 0, c->stream>>>(
-        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], Tk, e->k, e->n, e->calc, nullptr, e->F,
-        c->es_pool.d_slot.as<uint32_t>(), e->perm, e->h, e->L, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
-  } else if (e->from_lists) {
-    es_dp_warp_kernel<uint32_t, false><<<(unsigned)((e->T + 3) / 4), 128, 0, c->stream>>>(
-        c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], e->T, e->k, e->n, false, nullptr, nullptr, nullptr, nullptr,
-        0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
-  } else {
-    es_dp_warp_kernel<unsigned long long, false><<<(unsigned)((e->T + 3) / 4), 128, 0, c->stream>>>(
-        c->es_pool.d_masks.as<unsigned long long>(), e->T, e->k, e->n, e->calc && e->k, c->es_pool.d_level.as<double>(), nullptr,
-        nullptr, nullptr, 0, 0, e->bl_score, e->bl_ps, e->best_gs, e->best_ch);
+  if (e->own_first != 0 || e->own_end < e->n)
+    return fail(OBN_ERR_INVALID, "obn_es_level_dp after obn_es_level_dp_part: the DP columns are sharded by child");
+  if (int rc = es_launch_dp(e, 0, e->n, nullptr)) return rc;
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  return OBN_OK;
+}
+
+int obn_es_level_dp_part(obn_es* e, int rank, int world, void** parts_dev, size_t* bytes_per_rank) {
+  if (!e || !parts_dev || !bytes_per_rank) return fail(OBN_ERR_INVALID, "obn_es_level_dp_part: NULL argument");
+  if (world < 1 || rank < 0 || rank >= world) return fail(OBN_ERR_INVALID, "bad rank/world");
+  if (!e->use_F) return fail(OBN_ERR_UNSUPPORTED, "the child-sharded DP needs the lattice mode (obn_es_lattice)");
+  obn_ctx* c = e->c;
+  OBN_CUDA(cudaSetDevice(c->device));
+  const int first = (int)((size_t)e->n * (size_t)rank / (size_t)world), end = (int)((size_t)e->n * (size_t)(rank + 1) / (size_t)world);
+  if (e->own_first != 0 || e->own_end < e->n) {
+    if (e->own_first != first || e->own_end != end) return fail(OBN_ERR_INVALID, "rank/world changed inside a search");
   }
+  e->own_first = first;
+  e->own_end = end;
+  const size_t bytes = std::max<size_t>(e->T, 1) * sizeof(obn::EsPart);
+  if (int rc = c->es_pool.d_level.reserve(bytes * (size_t)world)) return rc;
+  *parts_dev = c->es_pool.d_level.p;
+  *bytes_per_rank = e->T * sizeof(obn::EsPart);
+  if (!e->T) return OBN_OK;
+  obn::EsPart* mine = reinterpret_cast<obn::EsPart*>(c->es_pool.d_level.as<char>() + (size_t)rank * e->T * sizeof(obn::EsPart));
+  if (int rc = es_launch_dp(e, first, end - first, mine)) return rc;
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  return OBN_OK;
+}
+
+int obn_es_level_dp_commit(obn_es* e, int world) {
+  if (!e) return fail(OBN_ERR_INVALID, "obn_es_level_dp_commit: NULL argument");
+  if (!e->use_F || world < 1) return fail(OBN_ERR_INVALID, "obn_es_level_dp_commit without obn_es_level_dp_part");
+  if (!e->T) return OBN_OK;
+  obn_ctx* c = e->c;
+  OBN_CUDA(cudaSetDevice(c->device));
+  (void)cudaGetLastError();
+  es_dp_commit_kernel<uint32_t><<<(unsigned)((e->T + 255) / 256), 256, 0, c->stream>>>(
+      c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], e->T, world, c->es_pool.d_level.as<obn::EsPart>(), e->best_gs,
+      e->best_ch);
   OBN_CUDA(cudaGetLastError());
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   ++c->prof.total_launches;
@@ -323,8 +416,10 @@ int obn_es_finish(obn_es* e, uint64_t* parent_masks, double* best_score) {
     if (ch >= n) return fail(OBN_ERR_INVALID, "obn_es_finish called before every level was processed");
     const uint32_t pa = W & ~(1u << ch);
     uint32_t ps = 0;
-    OBN_CUDA(cudaMemcpy(&ps, e->bl_ps + (size_t)W * n + ch, sizeof(uint32_t), cudaMemcpyDeviceToHost));   // row of W = pa + ch
-    parent_masks[ch] = ps;
+    if ((int)ch >= e->own_first && (int)ch < e->own_end) {      // child-sharded DP: the other ranks report theirs (OR them)
+      OBN_CUDA(cudaMemcpy(&ps, e->bl_ps + (size_t)W * n + ch, sizeof(uint32_t), cudaMemcpyDeviceToHost));   // row of W = pa + ch
+      parent_masks[ch] = ps;
+    }
     W = pa;
   }
   return OBN_OK;

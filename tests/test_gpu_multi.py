@@ -54,6 +54,17 @@ b = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 11, exact_orde
 sb = L.structure_learning.last_es_stats()
 ok &= sa["lattice"] and sb["lattice"] and sa["best_score"] == sb["best_score"]
 ok &= pdag_to_adj(a, net.n).tolist() == pdag_to_adj(b, net.n).tolist()
+# the same with the DP sharded by child from the very first level (every rank keeps its children's
+# columns only; (sum, child) merged by one all-gather per level), and from a middle level on
+for dp_min in ("1", "200"):
+    os.environ["OBN_ES_DP_SHARD_MIN"] = dp_min
+    before = comm.n_collectives
+    a2 = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), 11, exact_order=0, comm=comm)
+    s2 = L.structure_learning.last_es_stats()
+    ok &= s2["lattice"] and s2["best_score"] == sb["best_score"]
+    ok &= pdag_to_adj(a2, net.n).tolist() == pdag_to_adj(b, net.n).tolist()
+    ok &= comm.n_collectives - before > 8
+os.environ["OBN_ES_DP_SHARD_MIN"] = "1000000000"
 t = torch.tensor([int(ok), comm.n_collectives], device="cuda")
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
 if rank == 0:
