@@ -134,16 +134,16 @@ struct EsPool {
   LatticeGraphCache lattice;
   int lists_n = 0;                 // d_lists holds the level lists (subsets grouped by size) of this many variables
   DevBuf d_bl_score, d_bl_ps, d_best_gs, d_best_ch, d_F;
-  DevBuf d_root, d_pp[2], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog, d_lists, d_perm;
+  DevBuf d_root, d_pp[4], d_tasks, d_slot, d_partials, d_lut_a, d_lutF, d_masks, d_level, d_prog, d_lists, d_perm;
   void release() {
     lattice.clear();
-    for (DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks, &d_slot,
+    for (DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_pp[2], &d_pp[3], &d_tasks, &d_slot,
                       &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists, &d_perm})
       b->release();
   }
   size_t bytes() const {
     size_t s = 0;
-    for (const DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_tasks,
+    for (const DevBuf* b : {&d_bl_score, &d_bl_ps, &d_best_gs, &d_best_ch, &d_F, &d_root, &d_pp[0], &d_pp[1], &d_pp[2], &d_pp[3], &d_tasks,
                             &d_slot, &d_partials, &d_lut_a, &d_lutF, &d_masks, &d_level, &d_prog, &d_lists, &d_perm})
       s += b->cap;
     return s;

@@ -179,7 +179,7 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
 
 namespace obn {
 
-static int launch_marg_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks, uint64_t max_cells, uint64_t mul,
+static int launch_marg_level(obn_ctx* c, cudaStream_t st, const MargTask* d_tasks, size_t n_tasks, uint64_t max_cells, uint64_t mul,
                              const int32_t* src, int32_t* dst, double ess, const TermTable& tt, DevBuf& partials,
                              double* F, uint64_t f_base) {
   const uint32_t chunks = (uint32_t)((max_cells + kMargChunk - 1) / kMargChunk);
@@ -187,16 +187,16 @@ static int launch_marg_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks
     const uint32_t m = (uint32_t)std::min<size_t>(65535, n_tasks - b);
     (void)cudaGetLastError();
     if (F == nullptr) {                                   // tables only: the bottom tier computes F
-      marg_kernel<<<dim3(chunks, m), kMargThreads, 0, c->stream>>>(d_tasks + b, mul, src, dst, ess, tt, nullptr);
+      marg_kernel<<<dim3(chunks, m), kMargThreads, 0, st>>>(d_tasks + b, mul, src, dst, ess, tt, nullptr);
       OBN_CUDA(cudaGetLastError());
       c->prof.total_launches += 1;
       c->prof.count_launches += 1;
       continue;
     }
     if (int rc = partials.reserve((size_t)m * chunks * sizeof(double))) return rc;
-    marg_kernel<<<dim3(chunks, m), kMargThreads, 0, c->stream>>>(d_tasks + b, mul, src, dst, ess, tt, partials.as<double>());
+    marg_kernel<<<dim3(chunks, m), kMargThreads, 0, st>>>(d_tasks + b, mul, src, dst, ess, tt, partials.as<double>());
     OBN_CUDA(cudaGetLastError());
-    marg_reduce_kernel<<<(m + 127) / 128, 128, 0, c->stream>>>(d_tasks + b, m, chunks, partials.as<double>(), F, f_base);
+    marg_reduce_kernel<<<(m + 127) / 128, 128, 0, st>>>(d_tasks + b, m, chunks, partials.as<double>(), F, f_base);
     OBN_CUDA(cudaGetLastError());
     c->prof.total_launches += 2;
     c->prof.count_launches += 1;
@@ -244,25 +244,35 @@ static bool bottom_program(BottomProgram& out) {
 }
 
 // F of all 2^8 bottom patterns of every table of one level (the tables are the tasks' `dst`)
-static int launch_bottom_level(obn_ctx* c, const MargTask* d_tasks, size_t n_tasks, uint64_t max_cells, uint64_t mul,
+static int launch_bottom_level(obn_ctx* c, cudaStream_t st, const MargTask* d_tasks, size_t n_tasks, uint64_t max_cells, uint64_t mul,
                                const int32_t* base, const uint32_t* d_prog, const FixTable& ft, double ess, double* F,
                                uint64_t f_base, int f_shift) {
   const uint16_t* d_pat = reinterpret_cast<const uint16_t*>(d_prog + (size_t)kBotUpper * kBotThreads);
   const uint64_t chunks = max_cells >> kBotL;
-  // enough CTAs to fill the GPU a few times over, as many chunks per CTA as that allows (<= 64)
-  const uint64_t target = (uint64_t)c->sm_count * 16;
-  uint64_t cpc = (chunks * n_tasks + target - 1) / target;
-  cpc = std::max<uint64_t>(1, std::min<uint64_t>({cpc, 64, chunks}));
+  // chunks per CTA: a CTA costs about 1.3 chunks of fixed work (program copy, term-table lookup,
+  // the flush of its twelve sums), so one-chunk CTAs more than double the cost of a small table.
+  // Pick the power of two that minimises waves x (chunks per CTA + fixed cost), 3 CTAs per SM.
+  const double resident = (double)c->sm_count * 3.0;
+  uint64_t cpc = 1;
+  double best_cost = 1e300;
+  for (uint64_t cand = 1; cand <= 64 && cand <= std::max<uint64_t>(chunks, 1); cand <<= 1) {
+    const double ctas = (double)n_tasks * (double)((chunks + cand - 1) / cand);
+    const double cost = std::ceil(ctas / resident) * ((double)cand + 1.3);
+    if (cost < best_cost * 0.999) {
+      best_cost = cost;
+      cpc = cand;
+    }
+  }
   const uint32_t groups = (uint32_t)((chunks + cpc - 1) / cpc);
   for (size_t b = 0; b < n_tasks; b += 65535) {
     const uint32_t m = (uint32_t)std::min<size_t>(65535, n_tasks - b);
     (void)cudaGetLastError();
     auto* Fx = reinterpret_cast<unsigned long long*>(F);
     if (ft.lut)
-      bottom_lattice_kernel<true><<<dim3(groups, m), kBotThreads, 0, c->stream>>>(d_tasks + b, mul, base, d_prog, d_pat, ft, ess, Fx,
+      bottom_lattice_kernel<true><<<dim3(groups, m), kBotThreads, 0, st>>>(d_tasks + b, mul, base, d_prog, d_pat, ft, ess, Fx,
                                                                                  f_base, f_shift, (uint32_t)cpc);
     else
-      bottom_lattice_kernel<false><<<dim3(groups, m), kBotThreads, 0, c->stream>>>(d_tasks + b, mul, base, d_prog, d_pat, ft, ess, Fx,
+      bottom_lattice_kernel<false><<<dim3(groups, m), kBotThreads, 0, st>>>(d_tasks + b, mul, base, d_prog, d_pat, ft, ess, Fx,
                                                                                   f_base, f_shift, (uint32_t)cpc);
     OBN_CUDA(cudaGetLastError());
     c->prof.total_launches += 1;
@@ -301,7 +311,8 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   const int n = e->n;
   size_t free_b = 0, total_b = 0;
   OBN_CUDA(cudaMemGetInfo(&free_b, &total_b));
-  const size_t pooled = c->es_pool.d_root.cap + c->es_pool.d_pp[0].cap + c->es_pool.d_pp[1].cap;   // reusable
+  const size_t pooled = c->es_pool.d_root.cap + c->es_pool.d_pp[0].cap + c->es_pool.d_pp[1].cap + c->es_pool.d_pp[2].cap +
+                        c->es_pool.d_pp[3].cap;   // reusable
   const size_t budget = std::min<size_t>((size_t)((free_b + pooled) * 0.7), (size_t)env_int("OBN_LATTICE_BUDGET_GB", 24) << 30);
   const bool dbg = env_int("OBN_DEBUG", 0) != 0;
   auto t_dbg = std::chrono::steady_clock::now();
@@ -325,9 +336,9 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     k.insert(k.end(), {(uint64_t)n, (uint64_t)ds->n_rows, ess_bits, (uint64_t)rank, (uint64_t)world,
                        (uint64_t)env_int("OBN_LATTICE_BUDGET_GB", 24), (uint64_t)env_int("OBN_LATTICE_BOTTOM", 1),
                        (uint64_t)env_int("OBN_LATTICE_MAX_L", 20), (uint64_t)env_int("OBN_LATTICE_NO_LUT", 0),
-                       (uint64_t)env_int("OBN_LATTICE_REORDER", 1)});
+                       (uint64_t)env_int("OBN_LATTICE_REORDER", 1), (uint64_t)env_int("OBN_LATTICE_LANES", 2)});
     for (int v = 0; v < n; ++v) k.push_back(ds->cards[v]);
-    for (const DevBuf* d : {&pool.d_F, &pool.d_root, &pool.d_pp[0], &pool.d_pp[1], &pool.d_tasks, &pool.d_partials, &pool.d_lut_a, &pool.d_lutF, &pool.d_prog})
+    for (const DevBuf* d : {&pool.d_F, &pool.d_root, &pool.d_pp[0], &pool.d_pp[1], &pool.d_pp[2], &pool.d_pp[3], &pool.d_tasks, &pool.d_partials, &pool.d_lut_a, &pool.d_lutF, &pool.d_prog})
       k.push_back((uint64_t)(uintptr_t)d->p);
     return k;
   };
@@ -371,8 +382,14 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     for (int k = 0; k < Lm; ++k) buf_units = std::max<uint64_t>(buf_units, P.level_units[k]);
     if (int rc = pool.d_F.reserve(combs * sizeof(double))) return rc;
     if (int rc = pool.d_root.reserve(std::max<uint64_t>(P.root_cells, 4) * 4)) return rc;
-    for (int i = 0; i < 2; ++i)
-      if (int rc = pool.d_pp[i].reserve(std::max<uint64_t>(buf_units * cells_all_high, 4) * 4)) return rc;
+    // Blocks are independent once their roots exist: with the bottom tier they alternate between two
+    // stream lanes (own ping-pong pair each), so the small launches at the ends of one block's levels
+    // overlap with the other lane's (matters when there are many small blocks, i.e. on several GPUs).
+    const uint64_t pp_bytes = std::max<uint64_t>(buf_units * cells_all_high, 4) * 4;
+    const int lanes = (bot && env_int("OBN_LATTICE_LANES", 2) >= 2 && B / (uint32_t)world >= 2 &&
+                       4 * pp_bytes + P.root_cells * 4 <= budget) ? 2 : 1;
+    for (int i = 0; i < 2 * lanes; ++i)
+      if (int rc = pool.d_pp[i].reserve(pp_bytes)) return rc;
     if (!bot) {
       size_t need = (size_t)((P.cells_high[B - 1] * P.cells_low + kMargChunk - 1) / kMargChunk);
       for (int k = 0; k < h; ++k)
@@ -529,34 +546,50 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     lap_if("joint");
     // root lattice
     for (int k = h - 1; k >= 0; --k)
-      if (int rc = launch_marg_level(c, d_tasks + root_at[k], P.root_tasks[k].size(), (uint64_t)P.root_level_max[k] * P.cells_low,
+      if (int rc = launch_marg_level(c, c->stream, d_tasks + root_at[k], P.root_tasks[k].size(), (uint64_t)P.root_level_max[k] * P.cells_low,
                                      1, root, root, e->ess, tt, pool.d_partials, bot ? nullptr : F, 0)) {
         abort_capture();
         return rc;
       }
     lap_if("roots");
     // blocks of this rank
+    if (lanes > 1) {                                            // fork the second lane
+      if (cudaEventRecord(c->ev_fork, c->stream) != cudaSuccess || cudaStreamWaitEvent(c->aux[0], c->ev_fork, 0) != cudaSuccess) {
+        abort_capture();
+        return fail(OBN_ERR_CUDA, "lattice lane fork failed");
+      }
+    }
+    uint32_t n_mine = 0;
     for (uint32_t H = 0; H < B; ++H) {
       const uint32_t s = P.slot[H];
       if (s / per != (uint32_t)rank) continue;
+      const int lane = (int)(n_mine++ % (uint32_t)lanes);
+      cudaStream_t st = lane ? c->aux[0] : c->stream;
+      DevBuf* pp = &pool.d_pp[2 * lane];
       const uint64_t mul = P.cells_high[H];
       if (bot)                                                  // F of R_H and of its 255 bottom sub-patterns
-        if (int rc = launch_bottom_level(c, d_tasks, 1, mul * P.cells_low, mul, root + P.root_off[H], d_prog, ft, e->ess, F,
+        if (int rc = launch_bottom_level(c, st, d_tasks, 1, mul * P.cells_low, mul, root + P.root_off[H], d_prog, ft, e->ess, F,
                                          (uint64_t)s * NT, Lm)) {
           abort_capture();
           return rc;
         }
       for (int k = Lm - 1; k >= 0; --k) {
-        const int32_t* src = (k == Lm - 1) ? root + P.root_off[H] : pool.d_pp[(k + 1) & 1].as<int32_t>();
-        int rc = launch_marg_level(c, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul, src,
-                                   pool.d_pp[k & 1].as<int32_t>(), e->ess, tt, pool.d_partials, bot ? nullptr : F, (uint64_t)s * NT);
+        const int32_t* src = (k == Lm - 1) ? root + P.root_off[H] : pp[(k + 1) & 1].as<int32_t>();
+        int rc = launch_marg_level(c, st, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul, src,
+                                   pp[k & 1].as<int32_t>(), e->ess, tt, pool.d_partials, bot ? nullptr : F, (uint64_t)s * NT);
         if (rc == OBN_OK && bot)
-          rc = launch_bottom_level(c, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul,
-                                   pool.d_pp[k & 1].as<int32_t>(), d_prog, ft, e->ess, F, (uint64_t)s * NT, Lm);
+          rc = launch_bottom_level(c, st, d_tasks + low_at[k], P.level_tasks[k].size(), (uint64_t)P.level_max_units[k] * mul, mul,
+                                   pp[k & 1].as<int32_t>(), d_prog, ft, e->ess, F, (uint64_t)s * NT, Lm);
         if (rc != OBN_OK) {
           abort_capture();
           return rc;
         }
+      }
+    }
+    if (lanes > 1) {                                            // join
+      if (cudaEventRecord(c->ev_join[0], c->aux[0]) != cudaSuccess || cudaStreamWaitEvent(c->stream, c->ev_join[0], 0) != cudaSuccess) {
+        abort_capture();
+        return fail(OBN_ERR_CUDA, "lattice lane join failed");
       }
     }
     if (bot) {
