@@ -169,6 +169,16 @@ OBN_API int obn_es_level_dp_commit(obn_es* es, int world);
  * (world * doubles_per_rank doubles, rank r owns slice r). */
 OBN_API int obn_es_lattice(obn_es* es, int rank, int world);
 OBN_API int obn_es_f_buffer(obn_es* es, void** f_dev, size_t* doubles_per_rank);
+/* Diagnostics (host only, needs no device): the per-thread program of the lattice's bottom-tier
+ * kernel (csrc/obn_lattice.cuh).  geometry[6] = {bottom variables, threads, quads per chunk, quad
+ * buffer size, upper variables, phase-2 quads per thread}; words[upper variables][threads]: source
+ * quad | log2(distance to the second source) << 10 | destination quad << 13 for levels
+ * upper-1 .. 0; patterns[slots * threads]: upper pattern of quad q (0xffff = none).  words /
+ * patterns may be NULL to query the geometry only.  The CPU test-suite replays the program in
+ * numpy against directly computed marginals. */
+OBN_API int obn_lattice_bottom_program(uint32_t* words, size_t n_words, uint16_t* patterns, size_t n_patterns,
+                                       int* geometry);
+
 OBN_API int obn_es_finish(obn_es* es, uint64_t* parent_masks, double* best_score);
 OBN_API void obn_es_end(obn_es* es);
 

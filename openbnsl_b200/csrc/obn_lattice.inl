@@ -661,6 +661,24 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   return OBN_OK;
 }
 
+int obn_lattice_bottom_program(uint32_t* words, size_t n_words, uint16_t* patterns, size_t n_patterns, int* geometry) {
+  if (!geometry) return fail(OBN_ERR_INVALID, "obn_lattice_bottom_program: NULL argument");
+  geometry[0] = kBotL;
+  geometry[1] = kBotThreads;
+  geometry[2] = kBotQuads;
+  geometry[3] = kBotTabQuads;
+  geometry[4] = kBotUpper;
+  geometry[5] = kBotSlots;
+  BottomProgram bp;
+  if (!bottom_program(bp)) return fail(OBN_ERR_UNSUPPORTED, "bottom program does not match the kernel's level table");
+  if ((words && n_words < bp.words.size()) || (patterns && n_patterns < bp.patterns.size()))
+    return fail(OBN_ERR_INVALID, "obn_lattice_bottom_program: buffers too small (%zu words, %zu patterns)", bp.words.size(),
+                bp.patterns.size());
+  if (words) std::memcpy(words, bp.words.data(), bp.words.size() * 4);
+  if (patterns) std::memcpy(patterns, bp.patterns.data(), bp.patterns.size() * 2);
+  return OBN_OK;
+}
+
 int obn_es_f_buffer(obn_es* e, void** f_dev, size_t* doubles_per_rank) {
   if (!e || !f_dev || !doubles_per_rank) return fail(OBN_ERR_INVALID, "obn_es_f_buffer: NULL argument");
   *f_dev = e->F;

@@ -55,6 +55,30 @@ def test_driver_matches_compiled_reference_live():
         assert (pdag_to_adj(got, net.n) == pdag_to_adj(want, net.n)).all()
 
 
+@pytest.mark.parametrize("case", range(8))
+def test_driver_matches_compiled_reference_random_settings(case):
+    """Random (max_parents, temperature schedule, seed, chains, container mode, ess) on a small Alarm sample."""
+    ref, _ = oracle.reference_modules()
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(100 + case)
+    net = nw.alarm()
+    codes, cards = ranked(net.sample(int(rng.integers(300, 1500)), int(rng.integers(0, 50))))
+    ods = oracle.Dataset(codes, cards)
+    rdf = ref.base.DataframeWrapper(nw.to_reference_frame(codes, net.names, cards))
+    mp = int(rng.integers(1, 6))
+    iters = int(rng.integers(50, 400))
+    t0 = float(rng.choice([0.1, 1.0, 10.0, 100.0]))
+    cr = float(rng.choice([0.9, 0.99, 0.9995, 1.0]))
+    det = bool(rng.integers(0, 2))
+    seed = int(rng.integers(0, 2 ** 31))
+    chains = int(rng.integers(1, 6))
+    ess = float(rng.choice([0.5, 1.0, 10.0]))
+    want = ref.structure_learning.simulated_annealing(rdf, ref.score.BDeu(ess), mp, iters, t0, cr, det, seed, chains)
+    got = L._testing.simulated_annealing(net.n, OracleEvaluator(ods), L.score.BDeu(ess), mp, iters, t0, cr, det, seed, chains)
+    assert (pdag_to_adj(got, net.n) == pdag_to_adj(want, net.n)).all(), (mp, iters, t0, cr, det, seed, chains, ess)
+
+
 def test_errors_like_the_reference():
     g, net, codes, cards = load_golden("asia_10k_s0")
     ev = OracleEvaluator(oracle.Dataset(codes, cards))
