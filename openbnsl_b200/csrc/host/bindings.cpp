@@ -140,6 +140,8 @@ PYBIND11_MODULE(openbnsllib, m) {
   m.doc() = "B200-native drop-in for OpenBNSL's contingency-counting hot path.";
   m.attr("cuda_enabled") = true;
   m.def("device", []() { return Engine::instance().device(); }, "CUDA device of this process (creates the context)");
+  m.def("stream_handle", []() { return (uintptr_t)obn_ctx_stream(Engine::instance().ctx()); },
+        "cudaStream_t of the library's main stream (for CUDA-event timing from Python, e.g. torch.cuda.ExternalStream)");
 
   m.def("profile_enable", [](bool on) { check(obn_profile_enable(Engine::instance().ctx(), on ? 1 : 0)); });
   m.def("profile_read", [](bool reset) {
