@@ -304,21 +304,33 @@ PYBIND11_MODULE(openbnsllib, m) {
          py::arg("comm") = py::none(), py::arg("host_dp") = false);
   sl.def("pc",
          [](const DataframeWrapper& df, const CITestType& test, size_t max_cond_vars, bool stable,
-            const py::object& comm, size_t target_batch, bool record_tests) {
+            const py::object& comm, size_t target_batch, bool record_tests, bool apply_meek, bool complete_cpdag) {
+           // apply_meek: what un-commenting pc.cpp:84 would do; complete_cpdag: the published rules
+           auto finish = [&](PDAG g) {
+             if (apply_meek) g = apply_meeks_rules(g, false, false);
+             return complete_cpdag ? apply_meeks_rules(g, false, true) : g;
+           };
            if (std::holds_alternative<OracleGraph>(test))
-             return run_pc(df.num_of_vars, nullptr, test, max_cond_vars, stable, comm, target_batch);
+             return finish(run_pc(df.num_of_vars, nullptr, test, max_cond_vars, stable, comm, target_batch));
            GpuEvaluator ev(df.device());
            // shard a round over the GPUs only when it is worth a collective: >= 4 GB of algorithmic
            // bytes (about 0.6 ms of one B200) unless OBN_SHARD_MIN_BYTES says otherwise
            const char* e = std::getenv("OBN_SHARD_MIN_BYTES");
            const double min_bytes = e && *e ? std::atof(e) : 4e9;
            const size_t min_slots = (size_t)(min_bytes / (double)std::max<size_t>(1, df.num_of_datapoints));
-           return run_pc(df.num_of_vars, &ev, test, max_cond_vars, stable, comm, target_batch, record_tests,
-                         min_slots);
+           return finish(run_pc(df.num_of_vars, &ev, test, max_cond_vars, stable, comm, target_batch, record_tests,
+                                min_slots));
          },
          "Run PC algorithm", py::arg("df"), py::arg("ci_test_type"), py::arg("max_cond_vars"),
          py::arg("stable") = true, py::kw_only(), py::arg("comm") = py::none(), py::arg("target_batch") = 0,
-         py::arg("record_tests") = false);
+         py::arg("record_tests") = false, py::arg("apply_meek") = false, py::arg("complete_cpdag") = false);
+  // the reference's Meek rules (pdag_with_adjmat.cpp:215-279) exist but pc() leaves them
+  // switched off (pc.cpp:84) and PDAGwithAdjMat is not bound; here they are reachable, off by default.
+  sl.def("apply_meeks_rules",
+         [](const PDAG& g, bool apply_r4, bool textbook) { return apply_meeks_rules(g, apply_r4, textbook); },
+         "Meek's orientation rules as PDAGwithAdjMat::apply_meeks_rules states them (textbook=False), or as "
+         "published, which completes a pattern to its CPDAG (textbook=True); returns a new PDAG",
+         py::arg("pdag"), py::arg("apply_r4") = false, py::arg("textbook") = false);
   sl.def("last_pc_tests", []() {
     const TupleBatch& r = g_last_pc_stats.recorded;
     auto cp = [](const auto& v) { using T = typename std::decay_t<decltype(v)>::value_type;

@@ -68,7 +68,7 @@ def build(verbose=False):
     if not _newer(mod, mod_src + shim):
         jobs.append(flags + inc + mod_src + ["-o", mod])
     har = os.path.join(OUT, "obn_refharness" + EXT)
-    har_src = [os.path.join(HERE, "ref_harness.cpp")]
+    har_src = [os.path.join(HERE, "ref_harness.cpp"), os.path.join(REF, "src/graph/pdag_with_adjmat.cpp")]
     if not _newer(har, har_src + shim):
         jobs.append(flags + inc + har_src + ["-o", har])
     procs = [subprocess.Popen(j, stdout=subprocess.PIPE, stderr=subprocess.STDOUT) for j in jobs]

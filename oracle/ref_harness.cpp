@@ -9,7 +9,10 @@
 //      `#pragma omp parallel for` -- the "constructed OpenMP CPU baseline" of
 //      BASELINE.md section 3 (the reference has no OpenMP on this path);
 //   2. read back the statistic and dof that citest<>() keeps as locals
-//      (citest.h:86-87,139) through the recorder in the Boost shim.
+//      (citest.h:86-87,139) through the recorder in the Boost shim;
+//   3. call PDAGwithAdjMat::apply_meeks_rules (src/graph/pdag_with_adjmat.cpp:215-279),
+//      which the reference compiles but neither binds nor calls (pc.cpp:84), on an
+//      arbitrary adjacency matrix.
 // Nothing here re-implements reference arithmetic; it only calls it.
 #include <omp.h>
 #include <pybind11/numpy.h>
@@ -24,6 +27,7 @@
 #include "base/contingency_table.h"
 #include "base/dataframe_wrapper.h"
 #include "citest/citest.h"
+#include "graph/pdag_with_adjmat.h"
 #include "score/local_score.h"
 
 namespace py = pybind11;
@@ -163,11 +167,29 @@ static py::dict subset_score_batch(const DataframeWrapper& df,
   return out;
 }
 
+// adj[u][v] != 0 <=> arc u -> v (undirected = both).  Built by deleting arcs from the complete
+// graph the constructor makes, since that is the only public way in.
+static py::array_t<uint8_t> meek(py::array_t<uint8_t, py::array::c_style> adj, bool apply_r4) {
+  const size_t n = (size_t)adj.shape(0);
+  auto a = adj.unchecked<2>();
+  PDAGwithAdjMat g(n);
+  for (size_t u = 0; u < n; ++u)
+    for (size_t v = 0; v < n; ++v)
+      if (u != v && !a(u, v)) g.remove_directed_edge(u, v);
+  g.apply_meeks_rules(apply_r4);
+  py::array_t<uint8_t> out({n, n});
+  auto o = out.mutable_unchecked<2>();
+  for (size_t u = 0; u < n; ++u)
+    for (size_t v = 0; v < n; ++v) o(u, v) = (u != v && g.has_directed_edge(u, v)) ? 1 : 0;
+  return out;
+}
+
 PYBIND11_MODULE(obn_refharness, m) {
   m.doc() = "OpenMP batch harness around the unmodified reference functions";
   m.def("ci_batch", &ci_batch);
   m.def("score_batch", &score_batch);
   m.def("subset_score_batch", &subset_score_batch);
+  m.def("meek", &meek, py::arg("adj"), py::arg("apply_r4") = false);
   m.def("max_threads", []() { return omp_get_max_threads(); });
   m.def("pchisq", [](double x, size_t dof) { return pchisq(x, dof); });
 }

@@ -64,13 +64,113 @@ def make_sa(ref):
     print("wrote simulated_annealing.json", os.path.getsize(os.path.join(HERE, "simulated_annealing.json")), "bytes")
 
 
+def random_pdag(rng, n, dens, pdir):
+    adj = np.zeros((n, n), dtype=np.uint8)
+    for u in range(n):
+        for v in range(u + 1, n):
+            if rng.random() < dens:
+                r = rng.random()
+                if r < pdir / 2:
+                    adj[u, v] = 1
+                elif r < pdir:
+                    adj[v, u] = 1
+                else:
+                    adj[u, v] = adj[v, u] = 1
+    return adj
+
+
+def load_reference_structural_distance():
+    """helpers/structural_distance.py of the reference, imported from where it lies.  Its only
+    non-stdlib imports are networkx (present) and pgmpy.base.PDAG (absent): pgmpy's PDAG is a
+    networkx.DiGraph subclass and the helper uses DiGraph methods only, so a two-line stand-in
+    module is enough -- the helper's own code runs unmodified."""
+    import importlib.util
+    import types
+    import networkx as nx
+    pg, base = types.ModuleType("pgmpy"), types.ModuleType("pgmpy.base")
+    base.PDAG = type("PDAG", (nx.DiGraph,), {})
+    pg.base = base
+    sys.modules.setdefault("pgmpy", pg)
+    sys.modules.setdefault("pgmpy.base", base)
+    spec = importlib.util.spec_from_file_location(
+        "ref_structural_distance", os.path.join(os.environ.get("OBN_REFERENCE_DIR", "/root/reference"),
+                                                "helpers", "structural_distance.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod, base.PDAG
+
+
+def make_graphs(har):
+    """graph_kat.json: Meek's rules from the reference's own
+    PDAGwithAdjMat::apply_meeks_rules (through oracle/ref_harness.cpp) and PDAG2CPDAG /
+    structural_errors from the reference's helpers/structural_distance.py, on seeded random PDAGs
+    and on the true DAGs of the example networks."""
+    sd, RefPDAG = load_reference_structural_distance()
+
+    def to_ref(adj):
+        g = RefPDAG()
+        g.add_nodes_from(range(len(adj)))
+        g.add_edges_from((int(u), int(v)) for u, v in zip(*np.nonzero(adj)))
+        return g
+
+    def from_ref(g, n):
+        a = np.zeros((n, n), dtype=np.uint8)
+        for u, v in g.edges():
+            a[u, v] = 1
+        return a
+
+    rng = np.random.default_rng(20260)
+    graphs = []
+    for i in range(48):
+        n = int(rng.integers(2, 11))
+        graphs.append(random_pdag(rng, n, rng.uniform(0.15, 0.7), rng.uniform(0.0, 0.9)))
+    for net in (nw.asia(), nw.alarm()):
+        a = np.zeros((net.n, net.n), dtype=np.uint8)
+        for v, ps in enumerate(net.parents):
+            for p_ in ps:
+                a[p_, v] = 1
+        graphs.append(a)
+        graphs.append(from_ref(sd.PDAG2CPDAG(to_ref(a)), net.n))     # pattern of the true DAG: Meek has work to do
+    cases = []
+    for a in graphs:
+        n = len(a)
+        cases.append({"n": n, "adj": a.tolist(), "meek": har.meek(a, False).tolist(),
+                      "meek_r4": har.meek(a, True).tolist(), "cpdag": from_ref(sd.PDAG2CPDAG(to_ref(a)), n).tolist()})
+    pairs = []
+    for i in range(40):
+        n = int(rng.integers(3, 10))
+        gt = random_pdag(rng, n, rng.uniform(0.2, 0.6), rng.uniform(0.3, 1.0))
+        pr = gt.copy()
+        for _ in range(int(rng.integers(0, 6))):                        # perturb: drop / add / flip / undirect
+            u, v = rng.choice(n, size=2, replace=False)
+            op = int(rng.integers(0, 4))
+            if op == 0:
+                pr[u, v] = pr[v, u] = 0
+            elif op == 1:
+                pr[u, v] = 1
+            elif op == 2:
+                pr[u, v], pr[v, u] = pr[v, u], pr[u, v]
+            else:
+                if pr[u, v] or pr[v, u]:
+                    pr[u, v] = pr[v, u] = 1
+        pairs.append({"n": n, "truth": gt.tolist(), "pred": pr.tolist(),
+                      "errors": sd.structural_errors(to_ref(gt), to_ref(pr))})
+    with open(os.path.join(HERE, "graph_kat.json"), "w") as f:
+        json.dump({"meek_cpdag": cases, "structural_errors": pairs}, f)
+    print("wrote graph_kat.json", os.path.getsize(os.path.join(HERE, "graph_kat.json")), "bytes")
+
+
 def main():
     ref, har = oracle.reference_modules()
     assert ref is not None, "build oracle/_ref first (python oracle/build_ref.py)"
     if "--sa" in sys.argv:
         make_sa(ref)
         return
+    if "--graphs" in sys.argv:
+        make_graphs(har)
+        return
     make_sa(ref)
+    make_graphs(har)
     for name, net, n_rows, seed in dataset_cases():
         codes = net.sample(n_rows, seed)
         # ranks of observed states, as DataframeWrapper would compute them
