@@ -122,6 +122,25 @@ OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
                          int kind, double* stat_out, uint64_t* dof_out,
                          double* p_out);
 
+/* Diagnostics of the CI-test pooling inside obn_ci_tests (host only, need no device; DESIGN.md
+ * 3.5).  Tests of one (x, y) pair whose conditioning sets come from one neighbourhood -- the shape
+ * of the PC frontier, src/structure_learning/pc.cpp:27-47 -- share ONE joint table over (union of
+ * the conditioning sets, x, y); each test's own table is summed out of it on the device.
+ * obn_ci_pool_plan returns the plan for a batch given as for obn_ci_tests: the pools in CSR form
+ * (pool_var_ids needs room for offsets[n_tests] ids, pool_offsets for n_tests + 1), the pool of
+ * every test and its keep mask (bit i = i-th conditioning variable of the pool, ascending ids;
+ * 0xffffffff = the test is passed through as it is).  Any output pointer but n_pools may be NULL.
+ * obn_ci_pool_marginalise runs the kernel's marginalisation passes on the host: `joint` is a
+ * dense table in kernel digit order (n_z conditioning digits, most significant first, then x, y;
+ * cards_kernel_order[0 .. n_z) their cardinalities), `keep` a mask as above; `out` needs room for
+ * `cells` ints. */
+OBN_API int obn_ci_pool_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids,
+                             const uint64_t* offsets, size_t n_tests, const uint32_t* x, const uint32_t* y,
+                             uint32_t max_cells, uint32_t* pool_var_ids, uint64_t* pool_offsets,
+                             uint32_t* pool_of_test, uint32_t* keep_of_test, size_t* n_pools);
+OBN_API int obn_ci_pool_marginalise(const int32_t* joint, uint32_t cells, const uint32_t* cards_kernel_order,
+                                    int n_z, uint32_t keep, int32_t* out, uint32_t* out_cells);
+
 /* ---- exhaustive search on the device --------------------------------------
  * Level-synchronous Silander-Myllymaki DP with the reference's tie-breaking
  * (src/structure_learning/exhaustive_search.cpp:47-148).  The DP tables

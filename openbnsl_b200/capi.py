@@ -24,6 +24,7 @@ EXPORTS = [
     "obn_last_error", "obn_version", "obn_ctx_create", "obn_ctx_destroy", "obn_ctx_stream",
     "obn_dataset_upload", "obn_dataset_destroy", "obn_host_pin", "obn_host_unpin", "obn_dataset_n_vars", "obn_dataset_n_rows",
     "obn_count_tables", "obn_bdeu_scores", "obn_bdeu_subset_scores", "obn_ci_tests",
+    "obn_ci_pool_plan", "obn_ci_pool_marginalise",
     "obn_es_begin", "obn_es_level_begin", "obn_es_level_scores", "obn_es_level_buffer", "obn_es_level_dp", "obn_es_level_dp_part", "obn_es_level_dp_commit", "obn_lattice_bottom_program",
     "obn_es_lattice", "obn_es_f_buffer", "obn_es_finish", "obn_es_end",
     "obn_profile_enable", "obn_profile_read",
@@ -71,6 +72,9 @@ def load():
     L.obn_bdeu_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, C.c_double, C.c_int, f64p]
     L.obn_bdeu_subset_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, C.c_double, C.c_int, f64p]
     L.obn_ci_tests.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, f64p, u64p, f64p]
+    L.obn_ci_pool_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, C.c_uint32,
+                                   u32p, u64p, u32p, u32p, C.POINTER(C.c_size_t)]
+    L.obn_ci_pool_marginalise.argtypes = [i32p, C.c_uint32, u32p, C.c_int, C.c_uint32, i32p, u32p]
     L.obn_profile_enable.argtypes = [vp, C.c_int]
     L.obn_profile_read.argtypes = [vp, C.POINTER(Profile), C.c_int]
     _lib = L
@@ -101,6 +105,37 @@ def _csr(tuples):
         offs[1:] = np.cumsum([len(t) for t in tuples])
     flat = np.fromiter((v for t in tuples for v in t), dtype=np.uint32, count=int(offs[-1]))
     return flat, offs
+
+
+def ci_pool_plan(cards, tuples, x, y, max_cells=4096):
+    """The pooling plan obn_ci_tests would use (host only).  Returns (pools, pool_of_test, keep_of_test):
+    pools = list of ascending variable lists (x and y included)."""
+    flat, offs = _csr(tuples)
+    cards = np.ascontiguousarray(np.asarray(cards, dtype=np.uint32))
+    xa = np.ascontiguousarray(np.asarray(x, dtype=np.uint32))
+    ya = np.ascontiguousarray(np.asarray(y, dtype=np.uint32))
+    n = len(tuples)
+    pv = np.zeros(max(1, len(flat)), dtype=np.uint32)
+    po = np.zeros(n + 1, dtype=np.uint64)
+    pool_of, keep = np.zeros(max(1, n), dtype=np.uint32), np.zeros(max(1, n), dtype=np.uint32)
+    n_pools = C.c_size_t(0)
+    _check(load().obn_ci_pool_plan(_ptr(cards, C.c_uint32), len(cards), _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64),
+                                   n, _ptr(xa, C.c_uint32), _ptr(ya, C.c_uint32), int(max_cells),
+                                   _ptr(pv, C.c_uint32), _ptr(po, C.c_uint64), _ptr(pool_of, C.c_uint32),
+                                   _ptr(keep, C.c_uint32), C.byref(n_pools)))
+    pools = [pv[int(po[q]):int(po[q + 1])].tolist() for q in range(n_pools.value)]
+    return pools, pool_of[:n], keep[:n]
+
+
+def ci_pool_marginalise(joint, cards_kernel_order, keep):
+    """The kernel's marginalisation passes, run on the host over a dense joint table in kernel digit order."""
+    joint = np.ascontiguousarray(np.asarray(joint, dtype=np.int32))
+    cards = np.ascontiguousarray(np.asarray(cards_kernel_order, dtype=np.uint32))
+    out = np.zeros(max(1, joint.size), dtype=np.int32)
+    oc = C.c_uint32(0)
+    _check(load().obn_ci_pool_marginalise(_ptr(joint, C.c_int32), joint.size, _ptr(cards, C.c_uint32), len(cards),
+                                          int(keep) & 0xffffffff, _ptr(out, C.c_int32), C.byref(oc)))
+    return out[:oc.value].copy()
 
 
 class Context:

@@ -26,6 +26,13 @@ struct BatchSpec {
   int32_t* counts = nullptr;
   int32_t* counts_dev = nullptr;  // COUNTS: leave the dense tables on the device at this address (no D2H)
   const uint64_t* counts_off = nullptr;
+  // MODE_CI_POOL (obn_ci_tests with pooling on): the tuples are POOLS (obn_ci_pool.inl), the
+  // outputs are per TEST
+  size_t n_out = 0;                 // number of tests
+  const uint32_t* mem_off = nullptr;    // [n + 1]
+  const uint32_t* members = nullptr;    // 2 words per member
+  uint32_t pool_cells = 0;
+  double alg_bytes = 0;             // sum over the TESTS of k * n_rows (the unit is the test)
 };
 
 // Table-size classes.  One launch covers the tuples of one class, so that the
@@ -42,17 +49,17 @@ static const uint32_t kClassCells[kNumClasses - 2] = {64, 256, 1024, 4096, 16384
 
 static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-template <int KW, int TIER, bool SCALE4>
+template <int KW, int TIER, bool SCALE4, bool POOL = false>
 static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, size_t smem, cudaStream_t s) {
   static size_t configured = 0;
   if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4>,
+    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4, POOL>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;
   }
   (void)cudaGetLastError();      // a launch reports only its own error, not a stale one
-  count_kernel<KW, TIER, SCALE4><<<grid, nthr, smem, s>>>(a);
+  count_kernel<KW, TIER, SCALE4, POOL><<<grid, nthr, smem, s>>>(a);
   return cudaGetLastError();
 }
 
@@ -75,7 +82,9 @@ static int run_batch(BatchSpec& S) {
   if (n >= 0xffffffffull) return fail(OBN_ERR_UNSUPPORTED, "more than 2^32-2 tuples in one batch");
   const size_t total_vars = S.offsets[n];
   if (total_vars && !S.var_ids) return fail(OBN_ERR_INVALID, "var_ids is NULL");
-  if ((S.mode == MODE_CI) && (!S.role_a || !S.role_b)) return fail(OBN_ERR_INVALID, "x or y is NULL");
+  const bool ci = (S.mode == MODE_CI || S.mode == MODE_CI_POOL), pooled = (S.mode == MODE_CI_POOL);
+  const size_t n_out = pooled ? S.n_out : n;
+  if (ci && (!S.role_a || !S.role_b)) return fail(OBN_ERR_INVALID, "x or y is NULL");
   if ((S.mode == MODE_BDEU_ONE) && !S.role_a) return fail(OBN_ERR_INVALID, "child is NULL");
   OBN_CUDA(cudaSetDevice(c->device));
   const auto t_begin = std::chrono::steady_clock::now();
@@ -92,27 +101,11 @@ static int run_batch(BatchSpec& S) {
     const uint64_t o0 = S.offsets[t], o1 = S.offsets[t + 1];
     if (o1 < o0) return fail(OBN_ERR_INVALID, "offsets must be non-decreasing");
     const size_t k = o1 - o0;
-    if (k > (size_t)kMaxTupleVars)
-      return fail(OBN_ERR_UNSUPPORTED, "tuple %zu has %zu variables (max %d)", t, k, kMaxTupleVars);
     uint64_t cl = 1;
-    bool has_a = false, has_b = false;
-    for (size_t i = 0; i < k; ++i) {
-      const uint32_t v = S.var_ids[o0 + i];
-      if (v >= ds->n_vars) return fail(OBN_ERR_RANGE, "variable id %u out of range", v);
-      if (i && S.var_ids[o0 + i - 1] > v) return fail(OBN_ERR_INVALID, "var_ids must be sorted");
-      cl *= ds->cards[v];
-      if (cl >= (1ull << 31))
-        return fail(OBN_ERR_UNSUPPORTED, "tuple %zu: dense table has >= 2^31 cells", t);
-      if (S.role_a && v == S.role_a[t]) has_a = true;
-      if (S.role_b && v == S.role_b[t]) has_b = true;
-    }
-    if (S.mode == MODE_CI) {
-      if (S.role_a[t] == S.role_b[t]) return fail(OBN_ERR_INVALID, "x and y must differ");
-      if (!has_a || !has_b) return fail(OBN_ERR_INVALID, "x or y not contained in contingency table");
-      rxy[t] = ds->cards[S.role_a[t]] + ds->cards[S.role_b[t]];
-    } else if (S.mode == MODE_BDEU_ONE && !has_a) {
-      return fail(OBN_ERR_INVALID, "child_var not present in contingency table");
-    }
+    if (int rc = check_tuple(ds->cards.data(), ds->n_vars, S.var_ids + o0, k, t, ci, S.mode == MODE_BDEU_ONE,
+                             S.role_a ? S.role_a[t] : 0xffffffffu, S.role_b ? S.role_b[t] : 0xffffffffu, &cl))
+      return rc;
+    if (ci) rxy[t] = ds->cards[S.role_a[t]] + ds->cards[S.role_b[t]];
     cells[t] = (uint32_t)cl;
     int g = 0;
     while (g < kNumClasses - 2 && cl > kClassCells[g]) ++g;
@@ -179,6 +172,8 @@ static int run_batch(BatchSpec& S) {
   const size_t o_soff = take(n * 8);
   const size_t o_coff = take(S.mode == MODE_COUNTS ? n * 8 : 0);
   const size_t o_lijk = take(exact ? n * 4 : 0), o_lij = take(exact ? total_vars * 4 : 0);
+  const size_t n_members = pooled ? S.mem_off[n] : 0;
+  const size_t o_moff = take(pooled ? (n + 1) * 4 : 0), o_mem = take(n_members * 8);
   const size_t in_bytes = off;
   if (int rc = c->h_in.reserve(in_bytes)) return rc;
   if (int rc = c->d_in.reserve(in_bytes)) return rc;
@@ -186,6 +181,10 @@ static int run_batch(BatchSpec& S) {
   {
     uint32_t* desc = reinterpret_cast<uint32_t*>(hin + o_var);
     for (size_t i = 0; i < total_vars; ++i) desc[i] = S.var_ids[i] | ((ds->cards[S.var_ids[i]] - 1u) << 24);
+  }
+  if (pooled) {
+    memcpy(hin + o_moff, S.mem_off, (n + 1) * 4);
+    memcpy(hin + o_mem, S.members, n_members * 8);
   }
   if (exact) {
     memcpy(hin + o_lijk, lut_ijk.data(), n * 4);
@@ -221,7 +220,7 @@ static int run_batch(BatchSpec& S) {
 
   // ---- output buffer ----------------------------------------------------------
   size_t out_bytes = 0, counts_total = 0;
-  if (S.mode == MODE_CI) out_bytes = n * 24;
+  if (ci) out_bytes = n_out * 24;
   else if (S.mode == MODE_BDEU_ONE) out_bytes = n * 8;
   else if (S.mode == MODE_BDEU_ALL) out_bytes = S.scores_dev ? 0 : total_vars * 8;
   else {
@@ -268,6 +267,18 @@ static int run_batch(BatchSpec& S) {
       if (force_splits) splits = std::max(1, std::min<int>(force_splits, (int)std::max<uint32_t>(1u, n_vec)));
       const int nw = nthr / 32;
       size_t smem = (global_tier ? 0 : align16((size_t)max_cells * 4)) + (size_t)nw * max_rxy * 4;
+      if (pooled && !global_tier) {
+        // per tuple: table + the two pass buffers (cells/2, cells/4 ints) when it is a real pool,
+        // carved up the same way by count_kernel
+        size_t need = 0;
+        for (size_t q = i; q < gstart[g + 1]; ++q) {
+          const size_t cq = cells[perm[q]];
+          size_t b = align16(cq * 4);
+          if (cq <= S.pool_cells) b += align16((cq / 2) * 4) + align16((cq / 4) * 4);
+          need = std::max(need, b);
+        }
+        smem = need + (size_t)nw * max_rxy * 4;
+      }
       smem = std::max<size_t>(align16(smem), 16);
       const bool need_scratch = splits > 1 || global_tier;
       size_t j = i, scratch_ints = 0;
@@ -325,9 +336,16 @@ static int run_batch(BatchSpec& S) {
     a.lut_ij = reinterpret_cast<const uint32_t*>(din + o_lij);
   }
   double* d_stat = reinterpret_cast<double*>(dout);
-  unsigned long long* d_dof = reinterpret_cast<unsigned long long*>(dout + n * 8);
-  double* d_p = reinterpret_cast<double*>(dout + n * 16);
-  if (S.mode == MODE_CI) { a.stat = d_stat; a.dof = d_dof; a.pval = S.p ? d_p : nullptr; }
+  unsigned long long* d_dof = reinterpret_cast<unsigned long long*>(dout + n_out * 8);
+  double* d_p = reinterpret_cast<double*>(dout + n_out * 16);
+  if (ci) {
+    a.stat = d_stat; a.dof = d_dof; a.pval = S.p ? d_p : nullptr;
+    if (pooled) {
+      a.mem_off = reinterpret_cast<const uint32_t*>(din + o_moff);
+      a.members = reinterpret_cast<const uint2*>(din + o_mem);
+      a.pool_cells = S.pool_cells;
+    }
+  }
   else if (bdeu) a.scores = S.scores_dev ? S.scores_dev : reinterpret_cast<double*>(dout);
   else { a.counts_out = S.counts_dev ? S.counts_dev : reinterpret_cast<int32_t*>(dout); a.counts_off = reinterpret_cast<const uint64_t*>(din + o_coff); }
   a.scratch = c->d_scratch.as<int32_t>();
@@ -388,6 +406,13 @@ static int run_batch(BatchSpec& S) {
     a.vec_per_split = L.vps;
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
     cudaError_t e;
+    if (pooled) {
+      if (L.g == 0) e = launch_count<8, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
+      else if (L.g == 1) e = launch_count<8, TIER_SMEM, false, true>(a, grid, L.nthr, L.smem, st);
+      else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
+      else if (L.g == 5) e = launch_count<32, TIER_SMEM, false, true>(a, grid, L.nthr, L.smem, st);
+      else e = launch_count<32, TIER_GLOBAL, false, true>(a, grid, L.nthr, L.smem, st);
+    } else
     if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
     else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
     else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
@@ -409,10 +434,10 @@ static int run_batch(BatchSpec& S) {
   c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
   c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(t_synced - t_packed).count();
   const unsigned char* hout = c->h_out.as<unsigned char>();
-  if (S.mode == MODE_CI) {
-    if (S.stat) memcpy(S.stat, hout, n * 8);
-    if (S.dof) memcpy(S.dof, hout + n * 8, n * 8);
-    if (S.p) memcpy(S.p, hout + n * 16, n * 8);
+  if (ci) {
+    if (S.stat) memcpy(S.stat, hout, n_out * 8);
+    if (S.dof) memcpy(S.dof, hout + n_out * 8, n_out * 8);
+    if (S.p) memcpy(S.p, hout + n_out * 16, n_out * 8);
   } else if (S.mode == MODE_BDEU_ONE) {
     memcpy(S.scores, hout, n * 8);
   } else if (S.mode == MODE_BDEU_ALL) {
@@ -435,8 +460,8 @@ static int run_batch(BatchSpec& S) {
   }
   c->prof.h2d_bytes += (double)in_bytes;
   c->prof.d2h_bytes += (double)out_bytes;
-  c->prof.algorithmic_bytes += alg_bytes;
-  c->prof.tuples += n;
+  c->prof.algorithmic_bytes += pooled ? S.alg_bytes : alg_bytes;
+  c->prof.tuples += n_out;
   return OBN_OK;
 }
 
@@ -479,6 +504,32 @@ int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, con
                  size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
                  uint64_t* dof_out, double* p_out) {
   if (kind != OBN_CI_CHI2 && kind != OBN_CI_G2) return fail(OBN_ERR_INVALID, "Unsupported CI test type");
+  // Count reuse across the tests of one (x, y) pair.  OFF unless OBN_CI_POOL=1:
+  // written in round 1 after the GPU budget was spent -- planner and marginalisation passes are
+  // covered by the CPU tests, the kernel path has not run on a device yet.
+  const uint32_t pool_cells = (uint32_t)std::min(16384, std::max(0, env_int("OBN_CI_POOL_CELLS", 4096)));
+  if (env_int("OBN_CI_POOL", 0) && pool_cells && n_tuples > 1 && c && ds && ds->ctx == c && offsets && x && y &&
+      (var_ids || !offsets[n_tuples]) && n_tuples < 0xffffffffull) {
+    // tables much larger than the row count are not worth sharing (the passes cost ~2 ops per joint cell)
+    const uint32_t cap = (uint32_t)std::min<uint64_t>(pool_cells, std::max<uint64_t>(64, ds->n_rows / 8));
+    CiPoolPlan P;
+    if (int rc = plan_ci_pools(ds->cards.data(), ds->n_vars, var_ids, offsets, n_tuples, x, y, cap, P)) return rc;
+    if (P.pools() < n_tuples) {     // at least one table is shared
+      BatchSpec S{c, ds, P.var_ids.data(), P.offsets.data(), P.pools(), MODE_CI_POOL};
+      S.role_a = P.x.data();
+      S.role_b = P.y.data();
+      S.kind = kind;
+      S.stat = stat_out;
+      S.dof = dof_out;
+      S.p = p_out;
+      S.n_out = n_tuples;
+      S.mem_off = P.mem_off.data();
+      S.members = P.members.data();
+      S.pool_cells = cap;
+      S.alg_bytes = (double)offsets[n_tuples] * (double)ds->n_rows;
+      return run_batch(S);
+    }
+  }
   BatchSpec S{c, ds, var_ids, offsets, n_tuples, MODE_CI};
   S.role_a = x;
   S.role_b = y;

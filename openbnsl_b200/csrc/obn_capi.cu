@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <iterator>
 #include <map>
 #include <thread>
 
@@ -219,6 +220,7 @@ int obn_profile_read(obn_ctx* c, obn_profile* out, int reset) {
 
 }  // extern "C"
 
+#include "obn_ci_pool.inl"
 #include "obn_batch.inl"
 #include "obn_es.inl"
 #include "obn_lattice.inl"

@@ -224,7 +224,9 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
   }
 }
 
-template <int KW, int TIER, bool SCALE4>
+// POOL = true is the MODE_CI_POOL variant (a separate instantiation, so that the default
+// kernels compile exactly as they did without it).
+template <int KW, int TIER, bool SCALE4, bool POOL = false>
 __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ CtaTuple T;
@@ -247,7 +249,7 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   // every Z-slice is a contiguous rx*ry block laid out like citest.h:83.
   if (tid < 32) {
     uint32_t xa = 0xffffffffu, ya = 0xffffffffu, child = 0xffffffffu;
-    if (A.mode == MODE_CI) {
+    if (POOL || A.mode == MODE_CI) {
       const uint2 r = __ldg(&A.roles[lt]);
       xa = r.x; ya = r.y;                                        // host stores x < y (citest.h:48)
     } else if (A.mode == MODE_BDEU_ONE) {
@@ -287,9 +289,18 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   // ---- table + epilogue scratch (zeroed while the descriptor loads are in flight)
   int32_t* tab;
   int32_t* wscratch;                // per-warp epilogue scratch
+  int32_t* mbuf0 = nullptr;         // MODE_CI_POOL: ping-pong buffers of the marginalisation passes
+  int32_t* mbuf1 = nullptr;
   if (TIER == TIER_SMEM) {
     tab = reinterpret_cast<int32_t*>(smem_raw);
-    wscratch = reinterpret_cast<int32_t*>(smem_raw + (((size_t)cells * 4u + 15u) & ~(size_t)15u));
+    size_t o = ((size_t)cells * 4u + 15u) & ~(size_t)15u;
+    if (POOL && cells <= A.pool_cells) {   // cells/2 and cells/4 ints (run_batch sizes the launch the same way)
+      mbuf0 = reinterpret_cast<int32_t*>(smem_raw + o);
+      o += ((size_t)(cells / 2u) * 4u + 15u) & ~(size_t)15u;
+      mbuf1 = reinterpret_cast<int32_t*>(smem_raw + o);
+      o += ((size_t)(cells / 4u) * 4u + 15u) & ~(size_t)15u;
+    }
+    wscratch = reinterpret_cast<int32_t*>(smem_raw + o);
     for (uint32_t i = tid; i < cells; i += nthr) tab[i] = 0;
   } else {
     tab = A.scratch + A.scratch_off[lt];
@@ -353,7 +364,22 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   }
 
   // ---- fused epilogue -------------------------------------------------------
-  if (A.mode == MODE_CI) {
+  if (POOL) {
+    // one joint table, many tests: every member's (Z, x, y) table is summed out of the joint
+    // table in shared memory and goes through the same epilogue as a directly counted one
+    // (tables above A.pool_cells, in particular every global-tier one, are single tests that
+    // keep every digit: plan_ci_pools)
+    const uint32_t m_end = __ldg(&A.mem_off[t + 1]);
+    for (uint32_t m = __ldg(&A.mem_off[t]); m < m_end; ++m) {
+      const uint2 mem = __ldg(&A.members[m]);
+      const int32_t* mt = tab;
+      uint32_t mcells = cells;
+      if (mbuf0) mt = marginalise(tab, cells, T.card, k - 2, mem.y, mbuf0, mbuf1, mcells);
+      epilogue_ci(mt, mcells, T.rx, T.ry, A.kind, wscratch + (tid >> 5) * (T.rx + T.ry),
+                  red_d, red_u, &A.stat[mem.x], &A.dof[mem.x], A.pval ? &A.pval[mem.x] : nullptr);
+      __syncthreads();                // the buffers are rewritten for the next member
+    }
+  } else if (A.mode == MODE_CI) {
     epilogue_ci(tab, cells, T.rx, T.ry, A.kind, wscratch + (tid >> 5) * (T.rx + T.ry),
                 red_d, red_u, &A.stat[t], &A.dof[t], A.pval ? &A.pval[t] : nullptr);
   } else if (A.mode == MODE_BDEU_ONE || A.mode == MODE_BDEU_ALL) {

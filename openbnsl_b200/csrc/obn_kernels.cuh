@@ -10,7 +10,8 @@
 
 namespace obn {
 
-enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3 };
+enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3,
+                  MODE_CI_POOL = 4 };   // CI tests of one (x, y) pair sharing a joint table
 enum Tier : int { TIER_SMEM = 0, TIER_GLOBAL = 1 };
 
 struct BatchArgs {
@@ -43,6 +44,12 @@ struct BatchArgs {
   int32_t* scratch;         // zero on entry, zero on exit
   const uint64_t* scratch_off;  // [launch tuples]
   unsigned int* tickets;        // [launch tuples], zero on entry and exit
+  // MODE_CI_POOL: the launch tuple is a POOL -- the joint table over (union of the members'
+  // conditioning sets, x, y); member m of pool q is the CI test members[m].x whose conditioning
+  // set is the subset members[m].y (bit i = i-th conditioning digit of the pool, kernel order)
+  const uint32_t* mem_off;  // [pools + 1], indexed by pool id (hdr.x)
+  const uint2* members;
+  uint32_t pool_cells;      // joint tables above this size are single tests: no pass buffers
 };
 
 // ---------------------------------------------------------------------------
@@ -164,6 +171,67 @@ __device__ __forceinline__ void epilogue_ci(const int32_t* tab, uint32_t cells, 
     *dof_out = dof;
     if (p_out) *p_out = pchisq(stat, dof);               // citest.h:139
   }
+}
+
+// ---------------------------------------------------------------------------
+// MODE_CI_POOL: the table of (Z, x, y) from the joint table of (P, x, y), Z a subset of P, by
+// summing out the digits of P - Z one at a time, most significant first (so the weight of the
+// digit being removed is still its weight in the joint table).  Integer sums of the same rows:
+// the result IS the table the counting loop would have produced for (Z, x, y).
+// ---------------------------------------------------------------------------
+
+// one output cell of one pass: src viewed as [hi][c][w], out[j] = sum_d src[hi][d][lo], j = hi*w + lo
+__host__ __device__ __forceinline__ int32_t marg_cell(const int32_t* src, uint32_t j, uint32_t w, uint32_t c) {
+  const uint32_t hi = j / w, lo = j - hi * w;
+  const int32_t* p = src + (size_t)hi * c * w + lo;
+  int32_t a = 0;
+  for (uint32_t d = 0; d < c; ++d) a += p[(size_t)d * w];
+  return a;
+}
+
+// The pass schedule, shared by the kernel and its host replay (obn_ci_pool_marginalise).
+// card[0 .. n_z) are the pool's conditioning digits in kernel order; `cells` the joint table's.
+struct MargPasses {
+  uint32_t w, cur;          // weight of the digit last visited in the joint table; cells of the current table
+  int i;
+  __host__ __device__ MargPasses(uint32_t cells) : w(cells), cur(cells), i(0) {}
+  // next removed digit: its weight and cardinality, and the cells of the table after the pass
+  __host__ __device__ bool next(const uint32_t* card, int n_z, uint32_t keep, uint32_t& pw, uint32_t& pc,
+                                uint32_t& n_out) {
+    while (i < n_z) {
+      const uint32_t c = card[i];
+      w /= c;                                 // weight of digit i in the joint table
+      const bool kept = (keep >> i) & 1u;
+      ++i;
+      if (kept || c == 1u) continue;          // summing out a one-state digit changes nothing
+      // the digits removed so far were all more significant, the block below digit i is untouched:
+      // its weight in the current table is still w
+      cur /= c;
+      pw = w; pc = c; n_out = cur;
+      return true;
+    }
+    return false;
+  }
+};
+
+// All threads of the CTA.  buf0 holds >= cells/2 ints, buf1 >= cells/4 (every pass at least halves
+// the table: one-state digits are skipped); returns the table (tab itself when nothing is removed) and its size, visible to
+// every thread.
+__device__ __forceinline__ const int32_t* marginalise(const int32_t* tab, uint32_t cells, const uint32_t* card,
+                                                      int n_z, uint32_t keep, int32_t* buf0, int32_t* buf1,
+                                                      uint32_t& out_cells) {
+  const int32_t* src = tab;
+  int32_t* dst = buf0;
+  MargPasses it(cells);
+  uint32_t w, c, n_out;
+  while (it.next(card, n_z, keep, w, c, n_out)) {
+    for (uint32_t j = threadIdx.x; j < n_out; j += blockDim.x) dst[j] = marg_cell(src, j, w, c);
+    __syncthreads();
+    src = dst;
+    dst = (dst == buf0) ? buf1 : buf0;
+  }
+  out_cells = it.cur;
+  return src;
 }
 
 __device__ __forceinline__ double bdeu_term(int n, double a, double lg_a) {

@@ -1,0 +1,91 @@
+"""GPU parity of the pooled CI path (OBN_CI_POOL=1) against the default path and the
+checker.  OPT-IN (OBN_TEST_CI_POOL=1): the pooled kernel was written in round 1 after the GPU
+budget was spent and has not run on a device yet; the default `-m gpu` run must not depend on it.
+First thing to do in round 2:   OBN_TEST_CI_POOL=1 python -m pytest tests/test_zz_gpu_ci_pool.py -m gpu -x -q
+"""
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from helpers import close, ranked
+from openbnsl_b200 import networks as nw
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("OBN_TEST_CI_POOL", "0") != "1", reason="opt-in: OBN_TEST_CI_POOL=1")]
+
+
+def frontier(rng, n_vars, n_pairs, depth, pool_size):
+    xs, ys, zs = [], [], []
+    for _ in range(n_pairs):
+        x, y = (int(v) for v in rng.choice(n_vars, size=2, replace=False))
+        others = [v for v in range(n_vars) if v not in (x, y)]
+        neigh = sorted(int(v) for v in rng.choice(others, size=min(pool_size, len(others)), replace=False))
+        for z in itertools.combinations(neigh, depth):
+            xs.append(x); ys.append(y); zs.append(list(z))
+    return xs, ys, zs
+
+
+class pooled:
+    def __init__(self, on, cells=None):
+        self.env = {"OBN_CI_POOL": "1" if on else "0"}
+        if cells:
+            self.env["OBN_CI_POOL_CELLS"] = str(cells)
+
+    def __enter__(self):
+        self.old = {k: os.environ.get(k) for k in self.env}
+        os.environ.update(self.env)
+
+    def __exit__(self, *a):
+        for k, v in self.old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+@pytest.mark.parametrize("netf,n_rows,depth,pool_size,cells", [
+    (nw.alarm, 20011, 1, 5, 4096), (nw.alarm, 20011, 2, 6, 4096), (nw.alarm, 100000, 3, 5, 16384),
+    (nw.munin1_like, 30001, 1, 4, 4096), (nw.hepar2_like, 50000, 2, 5, 1024), (nw.asia, 10000, 2, 6, 64)])
+@pytest.mark.parametrize("kind", [0, 1])
+def test_pooled_ci_equals_default_and_checker(gpu_ctx, netf, n_rows, depth, pool_size, cells, kind):
+    net = netf()
+    codes, cards = ranked(net.sample(n_rows, 5))
+    ods = oracle.Dataset(codes, cards)
+    ds = gpu_ctx.upload(codes, cards)
+    rng = np.random.default_rng(7 * depth + pool_size)
+    xs, ys, zs = frontier(rng, net.n, 40, depth, pool_size)
+    with pooled(False):
+        s0, d0, p0 = ds.ci_tests(xs, ys, zs, kind)
+    gpu_ctx.profile_enable(True)
+    gpu_ctx.profile_read(True)
+    with pooled(True, cells):
+        s1, d1, p1 = ds.ci_tests(xs, ys, zs, kind)
+    prof = gpu_ctx.profile_read(True)
+    gpu_ctx.profile_enable(False)
+    assert prof.tuples == len(xs)                              # the unit stays the test
+    assert prof.algorithmic_bytes == sum(len(z) + 2 for z in zs) * float(n_rows)
+    assert np.array_equal(d0, d1)                              # same integer tables => same dof
+    for t in range(len(xs)):
+        assert close(s0[t], s1[t], 1e-12, 1e-12), (t, s0[t], s1[t])
+        assert close(p0[t], p1[t], 1e-9, 1e-300), (t, p0[t], p1[t])
+    for t in rng.choice(len(xs), size=min(60, len(xs)), replace=False):
+        ws, wd, wp = oracle.citest(ods, xs[t], ys[t], zs[t], kind)
+        assert int(d1[t]) == wd and close(s1[t], ws, 1e-9, 1e-12) and close(p1[t], wp, 1e-9, 1e-300)
+    ds.close()
+
+
+def test_pooled_pc_learns_the_same_graph(gpu_ctx):
+    import openbnsl_b200
+    L = openbnsl_b200.openbnsllib
+    net = nw.alarm()
+    codes, cards = ranked(net.sample(100000, 1))
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, [int(c) for c in cards])
+    adj = []
+    for on in (False, True):
+        with pooled(on):
+            g = L.structure_learning.pc(df, L.citest.GSquare(0.05), 4, True)
+        adj.append(np.array([[g.has_edge(a, b) for b in range(net.n)] for a in range(net.n)]))
+    assert (adj[0] == adj[1]).all()
