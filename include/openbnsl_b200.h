@@ -126,7 +126,8 @@ OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
  * 3.5).  Tests of one (x, y) pair whose conditioning sets come from one neighbourhood -- the shape
  * of the PC frontier, src/structure_learning/pc.cpp:27-47 -- share ONE joint table over (union of
  * the conditioning sets, x, y); each test's own table is summed out of it on the device.
- * obn_ci_pool_plan returns the plan for a batch given as for obn_ci_tests: the pools in CSR form
+ * obn_ci_pool_plan returns the plan for a batch given as for obn_ci_tests (joint tables of at most
+ * max_cells cells over at most max_z conditioning variables): the pools in CSR form
  * (pool_var_ids needs room for offsets[n_tests] ids, pool_offsets for n_tests + 1), the pool of
  * every test and its keep mask (bit i = i-th conditioning variable of the pool, ascending ids;
  * 0xffffffff = the test is passed through as it is).  Any output pointer but n_pools may be NULL.
@@ -136,7 +137,7 @@ OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
  * `cells` ints. */
 OBN_API int obn_ci_pool_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids,
                              const uint64_t* offsets, size_t n_tests, const uint32_t* x, const uint32_t* y,
-                             uint32_t max_cells, uint32_t* pool_var_ids, uint64_t* pool_offsets,
+                             uint32_t max_cells, uint32_t max_z, uint32_t* pool_var_ids, uint64_t* pool_offsets,
                              uint32_t* pool_of_test, uint32_t* keep_of_test, size_t* n_pools);
 OBN_API int obn_ci_pool_marginalise(const int32_t* joint, uint32_t cells, const uint32_t* cards_kernel_order,
                                     int n_z, uint32_t keep, int32_t* out, uint32_t* out_cells);

@@ -72,7 +72,7 @@ def load():
     L.obn_bdeu_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, C.c_double, C.c_int, f64p]
     L.obn_bdeu_subset_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, C.c_double, C.c_int, f64p]
     L.obn_ci_tests.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, f64p, u64p, f64p]
-    L.obn_ci_pool_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, C.c_uint32,
+    L.obn_ci_pool_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, C.c_uint32, C.c_uint32,
                                    u32p, u64p, u32p, u32p, C.POINTER(C.c_size_t)]
     L.obn_ci_pool_marginalise.argtypes = [i32p, C.c_uint32, u32p, C.c_int, C.c_uint32, i32p, u32p]
     L.obn_profile_enable.argtypes = [vp, C.c_int]
@@ -107,7 +107,7 @@ def _csr(tuples):
     return flat, offs
 
 
-def ci_pool_plan(cards, tuples, x, y, max_cells=4096):
+def ci_pool_plan(cards, tuples, x, y, max_cells=4096, max_z=30):
     """The pooling plan obn_ci_tests would use (host only).  Returns (pools, pool_of_test, keep_of_test):
     pools = list of ascending variable lists (x and y included)."""
     flat, offs = _csr(tuples)
@@ -120,7 +120,7 @@ def ci_pool_plan(cards, tuples, x, y, max_cells=4096):
     pool_of, keep = np.zeros(max(1, n), dtype=np.uint32), np.zeros(max(1, n), dtype=np.uint32)
     n_pools = C.c_size_t(0)
     _check(load().obn_ci_pool_plan(_ptr(cards, C.c_uint32), len(cards), _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64),
-                                   n, _ptr(xa, C.c_uint32), _ptr(ya, C.c_uint32), int(max_cells),
+                                   n, _ptr(xa, C.c_uint32), _ptr(ya, C.c_uint32), int(max_cells), int(max_z),
                                    _ptr(pv, C.c_uint32), _ptr(po, C.c_uint64), _ptr(pool_of, C.c_uint32),
                                    _ptr(keep, C.c_uint32), C.byref(n_pools)))
     pools = [pv[int(po[q]):int(po[q + 1])].tolist() for q in range(n_pools.value)]

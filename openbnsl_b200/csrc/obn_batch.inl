@@ -513,7 +513,9 @@ int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, con
     // tables much larger than the row count are not worth sharing (the passes cost ~2 ops per joint cell)
     const uint32_t cap = (uint32_t)std::min<uint64_t>(pool_cells, std::max<uint64_t>(64, ds->n_rows / 8));
     CiPoolPlan P;
-    if (int rc = plan_ci_pools(ds->cards.data(), ds->n_vars, var_ids, offsets, n_tuples, x, y, cap, P)) return rc;
+    // pools of <= 4 conditioning variables have <= 6 columns: the row loop specialised on the column count
+    const uint32_t max_z = (uint32_t)std::max(1, env_int("OBN_CI_POOL_VARS", 4));
+    if (int rc = plan_ci_pools(ds->cards.data(), ds->n_vars, var_ids, offsets, n_tuples, x, y, cap, max_z, P)) return rc;
     if (P.pools() < n_tuples) {     // at least one table is shared
       BatchSpec S{c, ds, P.var_ids.data(), P.offsets.data(), P.pools(), MODE_CI_POOL};
       S.role_a = P.x.data();

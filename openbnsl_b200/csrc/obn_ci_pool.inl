@@ -44,12 +44,17 @@ struct CiPoolPlan {
 };
 
 // Greedy, order-preserving: a test joins the open pool of its pair while the union of the
-// conditioning sets keeps the joint table within max_cells (and the mask within 30 bits);
+// conditioning sets keeps the joint table within max_cells, the pool within max_z conditioning variables (<= 30: the
+// mask is a 32-bit word) and kPoolMaxMembers tests;
 // otherwise the pool is closed and the test opens the next one.  A test whose own table exceeds
 // max_cells is a pool of its own (it may use any table tier; nothing is summed out).  Tests with
 // a repeated variable id are left alone as well (the kernel counts such a table as it is given).
+static const uint32_t kPoolMaxMembers = kPoolMembers;   // count_kernel keeps (stat, dof) of a pool's members in shared memory
+
 static int plan_ci_pools(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids, const uint64_t* offsets,
-                         size_t n, const uint32_t* xs, const uint32_t* ys, uint32_t max_cells, CiPoolPlan& P) {
+                         size_t n, const uint32_t* xs, const uint32_t* ys, uint32_t max_cells, uint32_t max_z,
+                         CiPoolPlan& P) {
+  if (max_z > 30) max_z = 30;                 // keep masks are 32-bit words
   struct Pool {
     uint32_t x, y;
     std::vector<uint32_t> z;        // union of the members' conditioning sets, ascending
@@ -57,7 +62,10 @@ static int plan_ci_pools(const uint32_t* cards, size_t n_vars, const uint32_t* v
     bool verbatim;                  // a single test passed through with its own variable list
   };
   std::vector<Pool> pools;
+  pools.reserve(n);
   std::map<uint64_t, size_t> open;  // pair -> index of its open pool
+  uint64_t last_key = ~0ull;        // the tests of a pair arrive back to back (pc.cpp:27-47): skip the map
+  size_t last_pool = 0;
   std::vector<uint32_t> z, u;
   for (size_t t = 0; t < n; ++t) {
     const uint64_t o0 = offsets[t], o1 = offsets[t + 1];
@@ -81,20 +89,30 @@ static int plan_ci_pools(const uint32_t* cards, size_t n_vars, const uint32_t* v
       continue;
     }
     const uint64_t key = (uint64_t)x * n_vars + y;
-    auto it = open.find(key);
-    if (it != open.end()) {
-      Pool& p = pools[it->second];
+    size_t pi = (size_t)-1;
+    if (key == last_key) {
+      pi = last_pool;
+    } else {
+      auto it = open.find(key);
+      if (it != open.end()) pi = it->second;
+    }
+    if (pi != (size_t)-1 && pools[pi].tests.size() < kPoolMaxMembers) {
+      Pool& p = pools[pi];
       u.clear();
       std::set_union(p.z.begin(), p.z.end(), z.begin(), z.end(), std::back_inserter(u));
       uint64_t ucells = (uint64_t)cards[x] * cards[y];
       for (size_t i = 0; i < u.size() && ucells <= max_cells; ++i) ucells *= cards[u[i]];
-      if (ucells <= max_cells && u.size() <= 30) {
-        p.z = u;
+      if (ucells <= max_cells && u.size() <= max_z) {
+        if (u.size() != p.z.size()) p.z = u;
         p.tests.push_back((uint32_t)t);
+        last_key = key;
+        last_pool = pi;
         continue;
       }
     }
     open[key] = pools.size();
+    last_key = key;
+    last_pool = pools.size();
     pools.push_back({x, y, z, {(uint32_t)t}, false});
   }
   // ---- emit ------------------------------------------------------------------------------
@@ -144,12 +162,12 @@ extern "C" {
 
 // Diagnostics, host only (include/openbnsl_b200.h): the plan obn_ci_tests would use.
 int obn_ci_pool_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids, const uint64_t* offsets,
-                     size_t n_tests, const uint32_t* x, const uint32_t* y, uint32_t max_cells,
+                     size_t n_tests, const uint32_t* x, const uint32_t* y, uint32_t max_cells, uint32_t max_z,
                      uint32_t* pool_var_ids, uint64_t* pool_offsets, uint32_t* pool_of_test,
                      uint32_t* keep_of_test, size_t* n_pools) {
   if (!cards || !offsets || !n_pools || (n_tests && (!x || !y))) return fail(OBN_ERR_INVALID, "NULL argument");
   CiPoolPlan P;
-  if (int rc = plan_ci_pools(cards, n_vars, var_ids, offsets, n_tests, x, y, max_cells, P)) return rc;
+  if (int rc = plan_ci_pools(cards, n_vars, var_ids, offsets, n_tests, x, y, max_cells, max_z, P)) return rc;
   *n_pools = P.pools();
   if (pool_offsets) memcpy(pool_offsets, P.offsets.data(), P.offsets.size() * sizeof(uint64_t));
   if (pool_var_ids && !P.var_ids.empty()) memcpy(pool_var_ids, P.var_ids.data(), P.var_ids.size() * sizeof(uint32_t));

@@ -28,6 +28,8 @@
 
 namespace obn {
 
+constexpr int kPoolMembers = 32;   // members of one pool (plan_ci_pools: kPoolMaxMembers)
+
 struct CtaTuple {            // per-CTA tuple description in shared memory
   const uint8_t* col[kMaxTupleVars];   // column pointers in KERNEL digit order
   uint32_t card[kMaxTupleVars];        // cards in kernel digit order
@@ -364,21 +366,31 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   }
 
   // ---- fused epilogue -------------------------------------------------------
-  if (POOL) {
+  if constexpr (POOL) {
     // one joint table, many tests: every member's (Z, x, y) table is summed out of the joint
     // table in shared memory and goes through the same epilogue as a directly counted one
     // (tables above A.pool_cells, in particular every global-tier one, are single tests that
-    // keep every digit: plan_ci_pools)
-    const uint32_t m_end = __ldg(&A.mem_off[t + 1]);
-    for (uint32_t m = __ldg(&A.mem_off[t]); m < m_end; ++m) {
+    // keep every digit: plan_ci_pools).  The p-values wait until every member has its statistic
+    // and are then evaluated by one thread per member instead of serially by thread 0.
+    __shared__ double m_stat[kPoolMembers];
+    __shared__ unsigned long long m_dof[kPoolMembers];
+    __shared__ uint32_t m_id[kPoolMembers];
+    const uint32_t m_begin = __ldg(&A.mem_off[t]), m_end = __ldg(&A.mem_off[t + 1]);
+    for (uint32_t m = m_begin; m < m_end; ++m) {
       const uint2 mem = __ldg(&A.members[m]);
       const int32_t* mt = tab;
       uint32_t mcells = cells;
       if (mbuf0) mt = marginalise(tab, cells, T.card, k - 2, mem.y, mbuf0, mbuf1, mcells);
       epilogue_ci(mt, mcells, T.rx, T.ry, A.kind, wscratch + (tid >> 5) * (T.rx + T.ry),
-                  red_d, red_u, &A.stat[mem.x], &A.dof[mem.x], A.pval ? &A.pval[mem.x] : nullptr);
+                  red_d, red_u, &A.stat[mem.x], &A.dof[mem.x], nullptr);
+      if (tid == 0) {                 // thread 0 wrote them just now
+        m_stat[m - m_begin] = A.stat[mem.x];
+        m_dof[m - m_begin] = A.dof[mem.x];
+        m_id[m - m_begin] = mem.x;
+      }
       __syncthreads();                // the buffers are rewritten for the next member
     }
+    if (A.pval && tid < m_end - m_begin) A.pval[m_id[tid]] = pchisq(m_stat[tid], m_dof[tid]);   // citest.h:139
   } else if (A.mode == MODE_CI) {
     epilogue_ci(tab, cells, T.rx, T.ry, A.kind, wscratch + (tid >> 5) * (T.rx + T.ry),
                 red_d, red_u, &A.stat[t], &A.dof[t], A.pval ? &A.pval[t] : nullptr);

@@ -87,6 +87,13 @@ def test_plan_edge_cases():
     assert pools == [[0, 1, 3, 4], [1, 3, 4], [0, 1, 5]] and pool_of.tolist() == [0, 0, 1, 2, 2]
     pools, pool_of, keep = capi.ci_pool_plan(cards, tuples, xs, ys, 7)
     assert len(pools) == 5 and pool_of.tolist() == [0, 1, 2, 3, 4]       # tables above the cap stay alone, never open a pool
+    # at most max_z conditioning variables per pool
+    pools, pool_of, keep = capi.ci_pool_plan(cards, tuples, xs, ys, 4096, max_z=2)
+    assert pools == [[0, 1, 3, 4], [1, 3, 4], [0, 1, 5]] and pool_of.tolist() == [0, 0, 1, 2, 2]
+    # at most 32 members per pool (the kernel keeps their statistics in shared memory)
+    many = [[0, 1, 3]] * 70
+    pools, pool_of, keep = capi.ci_pool_plan(cards, many, [0] * 70, [1] * 70, 4096)
+    assert len(pools) == 3 and np.bincount(pool_of).tolist() == [32, 32, 6]
     # a repeated id is passed through untouched
     pools, pool_of, keep = capi.ci_pool_plan(cards, [[0, 1, 3, 3], [0, 1, 4]], [0, 0], [1, 1], 4096)
     assert pools == [[0, 1, 3, 3], [0, 1, 4]] and keep.tolist() == [0xffffffff, 1]
