@@ -505,14 +505,14 @@ int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, con
                  uint64_t* dof_out, double* p_out) {
   if (kind != OBN_CI_CHI2 && kind != OBN_CI_G2) return fail(OBN_ERR_INVALID, "Unsupported CI test type");
   // Count reuse across the tests of one (x, y) pair.  OFF unless OBN_CI_POOL=1:
-  // written in round 1 after the GPU budget was spent -- planner and marginalisation passes are
-  // covered by the CPU tests, the kernel path has not run on a device yet.
+  // parity-green on a B200 and 12-25 % faster on the 1M-row configs, but slower at 100k rows and
+  // not yet profiled (profiles/r1_ab_ci_pool_v3.jsonl).
   const uint32_t pool_cells = (uint32_t)std::min(16384, std::max(0, env_int("OBN_CI_POOL_CELLS", 4096)));
   if (env_int("OBN_CI_POOL", 0) && pool_cells && n_tuples > 1 && c && ds && ds->ctx == c && offsets && x && y &&
       (var_ids || !offsets[n_tuples]) && n_tuples < 0xffffffffull) {
     // tables much larger than the row count are not worth sharing (the passes cost ~2 ops per joint cell)
     const uint32_t cap = (uint32_t)std::min<uint64_t>(pool_cells, std::max<uint64_t>(64, ds->n_rows / 8));
-    CiPoolPlan P;
+    static thread_local CiPoolPlan P;           // capacity reused across the rounds of a PC run
     // pools of <= 4 conditioning variables have <= 6 columns: the row loop specialised on the column count
     const uint32_t max_z = (uint32_t)std::max(1, env_int("OBN_CI_POOL_VARS", 4));
     if (int rc = plan_ci_pools(ds->cards.data(), ds->n_vars, var_ids, offsets, n_tuples, x, y, cap, max_z, P)) return rc;

@@ -8,6 +8,7 @@
 #include <iterator>
 #include <map>
 #include <thread>
+#include <unordered_map>
 
 #include "obn_lattice.cuh"
 #include "obn_host.hpp"

@@ -44,114 +44,183 @@ struct CiPoolPlan {
 };
 
 // Greedy, order-preserving: a test joins the open pool of its pair while the union of the
-// conditioning sets keeps the joint table within max_cells, the pool within max_z conditioning variables (<= 30: the
-// mask is a 32-bit word) and kPoolMaxMembers tests;
-// otherwise the pool is closed and the test opens the next one.  A test whose own table exceeds
-// max_cells is a pool of its own (it may use any table tier; nothing is summed out).  Tests with
-// a repeated variable id are left alone as well (the kernel counts such a table as it is given).
+// conditioning sets keeps the joint table within max_cells, the pool within max_z conditioning
+// variables (<= 30: the mask is a 32-bit word) and kPoolMaxMembers tests; otherwise the pool is
+// closed and the test opens the next one.  A test whose own table exceeds max_cells, that is wider
+// than max_z or that repeats a variable id is passed through with its own variable list (it may
+// use any table tier; nothing is summed out).
 static const uint32_t kPoolMaxMembers = kPoolMembers;   // count_kernel keeps (stat, dof) of a pool's members in shared memory
+
+// Working storage of the planner, kept per host thread so that a PC run (one plan per round)
+// does not allocate (about 100 ns per test with per-pool vectors and a std::map, about 40 like this).
+struct CiPoolScratch {
+  struct Pool {
+    uint32_t x, y, nz, head, tail, count;
+    uint64_t zcells;               // product of the cards of z
+    bool single;                   // one test emitted with its own variable list
+  };
+  std::vector<Pool> pools;
+  std::vector<uint32_t> z;         // `stride` slots per pool: its conditioning variables, ascending
+  std::vector<uint32_t> next;      // per test: next member of its pool
+  // pair -> its open pool: open addressing, only consulted when the pair changes
+  std::vector<uint64_t> hkey;
+  std::vector<uint32_t> hval;
+  size_t hmask = 0;
+  void hash_reset(size_t n) {
+    size_t cap = 64;
+    while (cap < 2 * n) cap <<= 1;
+    hkey.assign(cap, ~0ull);
+    hval.resize(cap);
+    hmask = cap - 1;
+  }
+  size_t slot(uint64_t key) const {
+    size_t h = (size_t)((key * 0x9E3779B97F4A7C15ull) >> 20) & hmask;
+    while (hkey[h] != ~0ull && hkey[h] != key) h = (h + 1) & hmask;
+    return h;
+  }
+};
 
 static int plan_ci_pools(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids, const uint64_t* offsets,
                          size_t n, const uint32_t* xs, const uint32_t* ys, uint32_t max_cells, uint32_t max_z,
                          CiPoolPlan& P) {
   if (max_z > 30) max_z = 30;                 // keep masks are 32-bit words
-  struct Pool {
-    uint32_t x, y;
-    std::vector<uint32_t> z;        // union of the members' conditioning sets, ascending
-    std::vector<uint32_t> tests;
-    bool verbatim;                  // a single test passed through with its own variable list
+  if (max_z < 1) max_z = 1;
+  static thread_local CiPoolScratch W;
+  const size_t stride = max_z;
+  W.pools.clear();
+  W.pools.reserve(n);
+  W.hash_reset(n);
+  W.z.resize(n * stride);                     // capacity persists across calls; slots are written before they are read
+  W.next.resize(n);
+  auto new_pool = [&](uint32_t x, uint32_t y, uint32_t t, bool single) -> uint32_t {
+    W.pools.push_back({x, y, 0u, t, t, 1u, 1ull, single});
+    W.next[t] = 0xffffffffu;
+    return (uint32_t)(W.pools.size() - 1);
   };
-  std::vector<Pool> pools;
-  pools.reserve(n);
-  std::map<uint64_t, size_t> open;  // pair -> index of its open pool
-  uint64_t last_key = ~0ull;        // the tests of a pair arrive back to back (pc.cpp:27-47): skip the map
-  size_t last_pool = 0;
-  std::vector<uint32_t> z, u;
+  uint64_t last_key = ~0ull;                  // the tests of a pair arrive back to back (pc.cpp:27-47)
+  uint32_t last_pool = 0;
+  uint32_t zt[kMaxTupleVars], un[2 * kMaxTupleVars];
   for (size_t t = 0; t < n; ++t) {
     const uint64_t o0 = offsets[t], o1 = offsets[t + 1];
     if (o1 < o0) return fail(OBN_ERR_INVALID, "offsets must be non-decreasing");
-    uint64_t cl = 0;
-    if (int rc = check_tuple(cards, n_vars, var_ids + o0, (size_t)(o1 - o0), t, true, false, xs[t], ys[t], &cl))
-      return rc;
+    const uint32_t* ids = var_ids + o0;
+    const size_t k = (size_t)(o1 - o0);
     const uint32_t x = std::min(xs[t], ys[t]), y = std::max(xs[t], ys[t]);
-    z.clear();
-    bool plain = true;              // strictly ascending, x and y once each
-    for (uint64_t i = o0; i < o1; ++i) {
-      if (i > o0 && var_ids[i] == var_ids[i - 1]) plain = false;
-      if (var_ids[i] != x && var_ids[i] != y) z.push_back(var_ids[i]);
+    // one scan: the checks of check_tuple, the test's conditioning set, its table size
+    bool ok = k <= (size_t)kMaxTupleVars && x != y, plain = true, hx = false, hy = false;
+    uint64_t cl = 1;
+    uint32_t nzt = 0;
+    for (size_t i = 0; ok && i < k; ++i) {
+      const uint32_t v = ids[i];
+      if (v >= n_vars || (i && ids[i - 1] > v)) { ok = false; break; }
+      if (i && ids[i - 1] == v) plain = false;
+      cl *= cards[v];
+      if (cl >= (1ull << 31)) { ok = false; break; }
+      if (v == x) hx = true;
+      else if (v == y) hy = true;
+      else zt[nzt++] = v;
     }
-    if (!plain) {
-      pools.push_back({x, y, std::vector<uint32_t>(var_ids + o0, var_ids + o1), {(uint32_t)t}, true});
-      continue;
+    if (!ok || !hx || !hy) {                  // let check_tuple name the problem
+      uint64_t dummy;
+      if (int rc = check_tuple(cards, n_vars, ids, k, t, true, false, xs[t], ys[t], &dummy)) return rc;
+      return fail(OBN_ERR_INVALID, "tuple %zu: inconsistent CI test", t);
     }
-    if (cl > max_cells) {
-      pools.push_back({x, y, z, {(uint32_t)t}, false});
+    if (!plain || cl > max_cells || nzt > max_z) {   // repeated id, too large or too wide to share: passed through
+      new_pool(x, y, (uint32_t)t, true);
       continue;
     }
     const uint64_t key = (uint64_t)x * n_vars + y;
-    size_t pi = (size_t)-1;
+    uint32_t pi = 0xffffffffu;
+    size_t hs = (size_t)-1;
     if (key == last_key) {
       pi = last_pool;
     } else {
-      auto it = open.find(key);
-      if (it != open.end()) pi = it->second;
+      hs = W.slot(key);
+      if (W.hkey[hs] == key) pi = W.hval[hs];
     }
-    if (pi != (size_t)-1 && pools[pi].tests.size() < kPoolMaxMembers) {
-      Pool& p = pools[pi];
-      u.clear();
-      std::set_union(p.z.begin(), p.z.end(), z.begin(), z.end(), std::back_inserter(u));
-      uint64_t ucells = (uint64_t)cards[x] * cards[y];
-      for (size_t i = 0; i < u.size() && ucells <= max_cells; ++i) ucells *= cards[u[i]];
-      if (ucells <= max_cells && u.size() <= max_z) {
-        if (u.size() != p.z.size()) p.z = u;
-        p.tests.push_back((uint32_t)t);
+    if (pi != 0xffffffffu && W.pools[pi].count < kPoolMaxMembers) {
+      // sorted union of the pool's and the test's conditioning sets; the table grows by the new cards
+      CiPoolScratch::Pool& p = W.pools[pi];
+      uint32_t* pz = W.z.data() + (size_t)pi * stride;
+      uint32_t a = 0, b = 0, nu = 0;
+      uint64_t ucells = p.zcells;
+      while (a < p.nz || b < nzt) {
+        if (b == nzt || (a < p.nz && pz[a] < zt[b])) un[nu++] = pz[a++];
+        else if (a == p.nz || zt[b] < pz[a]) { ucells *= cards[zt[b]]; un[nu++] = zt[b++]; }
+        else { un[nu++] = pz[a++]; ++b; }
+      }
+      if (nu <= max_z && ucells * cards[x] * cards[y] <= max_cells) {
+        if (nu != p.nz) {
+          std::copy(un, un + nu, pz);
+          p.nz = nu;
+          p.zcells = ucells;
+        }
+        W.next[p.tail] = (uint32_t)t;
+        W.next[t] = 0xffffffffu;
+        p.tail = (uint32_t)t;
+        ++p.count;
         last_key = key;
         last_pool = pi;
         continue;
       }
     }
-    open[key] = pools.size();
+    pi = new_pool(x, y, (uint32_t)t, false);
+    std::copy(zt, zt + nzt, W.z.data() + (size_t)pi * stride);
+    W.pools[pi].nz = nzt;
+    W.pools[pi].zcells = cl / ((uint64_t)cards[x] * cards[y]);
+    if (hs == (size_t)-1) hs = W.slot(key);
+    W.hkey[hs] = key;
+    W.hval[hs] = pi;
     last_key = key;
-    last_pool = pools.size();
-    pools.push_back({x, y, z, {(uint32_t)t}, false});
+    last_pool = pi;
   }
   // ---- emit ------------------------------------------------------------------------------
-  P = CiPoolPlan{};
+  const size_t n_pools = W.pools.size();
+  P.var_ids.clear(); P.offsets.clear(); P.mem_off.clear();
+  P.x.resize(n_pools);
+  P.y.resize(n_pools);
+  P.members.resize(2 * n);
+  P.var_ids.reserve(offsets[n]);
+  P.offsets.reserve(n_pools + 1);
+  P.mem_off.reserve(n_pools + 1);
   P.offsets.push_back(0);
   P.mem_off.push_back(0);
-  for (const Pool& p : pools) {
-    if (p.verbatim) {               // the test's own variable list, nothing summed out
-      P.var_ids.insert(P.var_ids.end(), p.z.begin(), p.z.end());
-      P.x.push_back(p.x);
-      P.y.push_back(p.y);
-      P.members.push_back(p.tests[0]);
-      P.members.push_back(0xffffffffu);
+  size_t nm = 0;
+  for (size_t q = 0; q < n_pools; ++q) {
+    const CiPoolScratch::Pool& p = W.pools[q];
+    P.x[q] = p.x;
+    P.y[q] = p.y;
+    if (p.single) {                 // the test's own variable list, nothing summed out
+      const uint32_t t = p.head;
+      P.var_ids.insert(P.var_ids.end(), var_ids + offsets[t], var_ids + offsets[t + 1]);
+      P.members[2 * nm] = t;
+      P.members[2 * nm + 1] = 0xffffffffu;
+      ++nm;
     } else {
-      bool px = false, py = false;  // merge x and y into the ascending list
-      for (uint32_t v : p.z) {
-        if (!px && p.x < v) { P.var_ids.push_back(p.x); px = true; }
-        if (!py && p.y < v) { P.var_ids.push_back(p.y); py = true; }
-        P.var_ids.push_back(v);
+      const uint32_t* pz = W.z.data() + q * stride;
+      bool dx = false, dy = false;  // merge x and y into the ascending list
+      for (uint32_t i = 0; i < p.nz; ++i) {
+        if (!dx && p.x < pz[i]) { P.var_ids.push_back(p.x); dx = true; }
+        if (!dy && p.y < pz[i]) { P.var_ids.push_back(p.y); dy = true; }
+        P.var_ids.push_back(pz[i]);
       }
-      if (!px) P.var_ids.push_back(p.x);
-      if (!py) P.var_ids.push_back(p.y);
-      P.x.push_back(p.x);
-      P.y.push_back(p.y);
-      for (uint32_t t : p.tests) {
-        uint32_t mask = 0;
-        size_t j = 0;
+      if (!dx) P.var_ids.push_back(p.x);
+      if (!dy) P.var_ids.push_back(p.y);
+      for (uint32_t t = p.head; t != 0xffffffffu; t = W.next[t]) {
+        uint32_t mask = 0, j = 0;
         for (uint64_t i = offsets[t]; i < offsets[t + 1]; ++i) {
           const uint32_t v = var_ids[i];
           if (v == p.x || v == p.y) continue;
-          while (p.z[j] != v) ++j;  // both ascending, the test's set is contained in the pool's
+          while (pz[j] != v) ++j;   // both ascending, the test's set is contained in the pool's
           mask |= 1u << j;
         }
-        P.members.push_back(t);
-        P.members.push_back(mask);
+        P.members[2 * nm] = t;
+        P.members[2 * nm + 1] = mask;
+        ++nm;
       }
     }
     P.offsets.push_back(P.var_ids.size());
-    P.mem_off.push_back((uint32_t)(P.members.size() / 2));
+    P.mem_off.push_back((uint32_t)nm);
   }
   return OBN_OK;
 }
@@ -166,7 +235,7 @@ int obn_ci_pool_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_i
                      uint32_t* pool_var_ids, uint64_t* pool_offsets, uint32_t* pool_of_test,
                      uint32_t* keep_of_test, size_t* n_pools) {
   if (!cards || !offsets || !n_pools || (n_tests && (!x || !y))) return fail(OBN_ERR_INVALID, "NULL argument");
-  CiPoolPlan P;
+  static thread_local CiPoolPlan P;
   if (int rc = plan_ci_pools(cards, n_vars, var_ids, offsets, n_tests, x, y, max_cells, max_z, P)) return rc;
   *n_pools = P.pools();
   if (pool_offsets) memcpy(pool_offsets, P.offsets.data(), P.offsets.size() * sizeof(uint64_t));

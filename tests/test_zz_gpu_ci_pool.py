@@ -1,7 +1,8 @@
 """GPU parity of the pooled CI path (OBN_CI_POOL=1) against the default path and the
 checker.  OPT-IN (OBN_TEST_CI_POOL=1): the pooled kernel was written in round 1 after the GPU
-budget was spent and has not run on a device yet; the default `-m gpu` run must not depend on it.
-First thing to do in round 2:   OBN_TEST_CI_POOL=1 python -m pytest tests/test_zz_gpu_ci_pool.py -m gpu -x -q
+budget was nearly spent: green on a B200 (profiles/r1_ci_pool_parity_test.log) but the path is off by
+default and has no ncu capture yet, so the default `-m gpu` run does not depend on it.
+Round 2:   OBN_TEST_CI_POOL=1 python -m pytest tests/test_zz_gpu_ci_pool.py -m gpu -x -q
 """
 import itertools
 import os
