@@ -1,6 +1,7 @@
 #include "dataframe_wrapper.hpp"
 
 #include <algorithm>
+#include <cstring>
 #include <set>
 #include <stdexcept>
 
@@ -41,21 +42,108 @@ void alloc(DataframeWrapper& w) {
   w.colmajor.assign(w.num_of_vars * w.num_of_datapoints, 0);
 }
 
+// Ranks of the distinct values of one column.  The reference inserts every cell's string into a
+// std::set and later looks every cell up in a std::map (dataframe_wrapper.cpp:36-70: two string
+// casts and two tree walks per cell); here a cell costs one probe of a small direct-mapped cache
+// keyed by what identifies the value cheaply (the PyObject pointer, the integer itself), the
+// distinct values get first-seen ids, and ONE 256-entry table turns ids into ranks at the end.
+struct ColumnCoder {
+  std::vector<std::string> seen;              // distinct strings in first-seen order (<= 256)
+  int16_t slot[1024];                         // open addressing over `seen`: -1 = empty
+  ColumnCoder() { std::fill(slot, slot + 1024, (int16_t)-1); }
+  uint32_t id(const char* p, size_t len, DataframeWrapper& w, size_t v) {
+    uint64_t h = 1469598103934665603ull;      // FNV-1a
+    for (size_t i = 0; i < len; ++i) h = (h ^ (unsigned char)p[i]) * 1099511628211ull;
+    size_t q = (size_t)(h >> 32) & 1023;
+    for (; slot[q] >= 0; q = (q + 1) & 1023) {
+      const std::string& s = seen[(size_t)slot[q]];
+      if (s.size() == len && std::memcmp(s.data(), p, len) == 0) return (uint32_t)slot[q];
+    }
+    if (seen.size() == 256)
+      throw std::invalid_argument("column '" + w.col_idx2str[v] + "' has more than 256 distinct values (uint8 codes)");
+    slot[q] = (int16_t)seen.size();
+    seen.emplace_back(p, len);
+    return (uint32_t)slot[q];
+  }
+  // col holds first-seen ids; rewrite them as ranks among the sorted distinct strings
+  void finish(DataframeWrapper& w, size_t v, dtype* col, size_t n) {
+    std::set<std::string> uniq(seen.begin(), seen.end());
+    finish_column(w, v, uniq);
+    dtype rank[256];
+    for (size_t i = 0; i < seen.size(); ++i) rank[i] = w.val_str2idx[v][seen[i]];
+    for (size_t r = 0; r < n; ++r) col[r] = rank[col[r]];
+  }
+};
+
+constexpr size_t kCacheSlots = 1024;          // direct-mapped; a miss only costs the slow path
+
 template <typename Int>
 void ingest_integers(DataframeWrapper& w, const py::array& arr) {
   const auto* base = static_cast<const unsigned char*>(arr.data());
   const ssize_t s0 = arr.strides(0), s1 = arr.strides(1);
   const size_t n = w.num_of_datapoints;
+  std::vector<Int> key(kCacheSlots);
+  std::vector<int32_t> val(kCacheSlots);
   for (size_t v = 0; v < w.num_of_vars; ++v) {
-    std::set<long long> vals;
-    for (size_t r = 0; r < n; ++r) vals.insert((long long)*reinterpret_cast<const Int*>(base + r * s0 + v * s1));
-    std::set<std::string> uniq;
-    for (auto x : vals) uniq.insert(std::to_string(x));
-    finish_column(w, v, uniq);
-    std::map<long long, dtype> code;
-    for (auto x : vals) code[x] = w.val_str2idx[v][std::to_string(x)];
+    ColumnCoder cc;
+    std::fill(val.begin(), val.end(), -1);
     dtype* col = w.colmajor.data() + v * n;
-    for (size_t r = 0; r < n; ++r) col[r] = code[(long long)*reinterpret_cast<const Int*>(base + r * s0 + v * s1)];
+    for (size_t r = 0; r < n; ++r) {
+      const Int x = *reinterpret_cast<const Int*>(base + r * s0 + v * s1);
+      const size_t h = (size_t)((uint64_t)x * 0x9E3779B97F4A7C15ull >> 54) & (kCacheSlots - 1);
+      if (val[h] < 0 || key[h] != x) {
+        key[h] = x;
+        const std::string d = std::to_string(x);              // decimal string = .astype(str) of the reference's callers
+        val[h] = (int32_t)cc.id(d.data(), d.size(), w, v);
+      }
+      col[r] = (dtype)val[h];
+    }
+    cc.finish(w, v, col, n);
+  }
+}
+
+// Object cells (dataframe_wrapper.cpp:42,67).  A str is read through its cached UTF-8 form (no
+// copy for ASCII); anything else goes through the same pybind11 string cast as before, so bytes
+// still work and other objects raise the reference's error.  Equal strings are usually the SAME
+// object (a frame built from categories, an interned literal, `table[codes]`), which the pointer
+// cache turns into one pointer compare per cell; distinct objects with equal text still meet in
+// the string table.
+void ingest_objects(DataframeWrapper& w, const py::array& arr) {
+  const auto* base = static_cast<const unsigned char*>(arr.data());
+  const ssize_t s0 = arr.strides(0), s1 = arr.strides(1);
+  const size_t n = w.num_of_datapoints;
+  std::vector<PyObject*> key(kCacheSlots);
+  std::vector<uint32_t> val(kCacheSlots);
+  std::string tmp;
+  for (size_t v = 0; v < w.num_of_vars; ++v) {
+    ColumnCoder cc;
+    std::fill(key.begin(), key.end(), nullptr);
+    dtype* col = w.colmajor.data() + v * n;
+    for (size_t r = 0; r < n; ++r) {
+      PyObject* o = *reinterpret_cast<PyObject* const*>(base + r * s0 + v * s1);
+      const size_t h = (size_t)(((uintptr_t)o >> 4) * 0x9E3779B97F4A7C15ull >> 54) & (kCacheSlots - 1);
+      if (key[h] != o) {
+        if (o && PyUnicode_Check(o)) {
+          Py_ssize_t len = 0;
+          const char* u = PyUnicode_AsUTF8AndSize(o, &len);
+          if (!u) {
+            PyErr_Clear();
+            throw std::invalid_argument("Failed to cast value to string");
+          }
+          val[h] = cc.id(u, (size_t)len, w, v);
+        } else {
+          try {
+            tmp = py::handle(o).cast<std::string>();
+          } catch (const std::exception&) {
+            throw std::invalid_argument("Failed to cast value to string");
+          }
+          val[h] = cc.id(tmp.data(), tmp.size(), w, v);
+        }
+        key[h] = o;                           // the array keeps the object alive for the whole scan
+      }
+      col[r] = (dtype)val[h];
+    }
+    cc.finish(w, v, col, n);
   }
 }
 
@@ -73,27 +161,7 @@ DataframeWrapper::DataframeWrapper(const py::object& dataframe) {
   alloc(*this);
   const char kind = arr.dtype().kind();
   if (kind == 'O') {
-    // Python str cells (dataframe_wrapper.cpp:42,67).  Strides are honoured, so
-    // C- and Fortran-ordered object arrays both work.
-    const auto* base = static_cast<const unsigned char*>(arr.data());
-    const ssize_t s0 = arr.strides(0), s1 = arr.strides(1);
-    const size_t n = num_of_datapoints;
-    for (size_t v = 0; v < num_of_vars; ++v) {
-      std::set<std::string> uniq;
-      std::vector<std::string> cells(n);
-      for (size_t r = 0; r < n; ++r) {
-        PyObject* o = *reinterpret_cast<PyObject* const*>(base + r * s0 + v * s1);
-        try {
-          cells[r] = py::handle(o).cast<std::string>();
-        } catch (const std::exception&) {
-          throw std::invalid_argument("Failed to cast value to string");
-        }
-        uniq.insert(cells[r]);
-      }
-      finish_column(*this, v, uniq);
-      dtype* col = colmajor.data() + v * n;
-      for (size_t r = 0; r < n; ++r) col[r] = val_str2idx[v][cells[r]];
-    }
+    ingest_objects(*this, arr);             // strides are honoured: C- and Fortran-ordered object arrays both work
   } else if (kind == 'i' || kind == 'u' || kind == 'b') {
     // extension: integer-coded frames; values are ranked by their decimal
     // strings, i.e. exactly what the reference computes after .astype(str)

@@ -68,6 +68,47 @@ def test_dataframe_wrapper_semantics():
     assert df.col_idx2str == ["a", "b"] and df.data_column_major == [[1, 1, 0], [0, 1, 0]]
 
 
+def test_dataframe_wrapper_ingest_paths_agree_with_a_plain_ranking():
+    # the ingest is written around a pointer / value cache (dataframe_wrapper.cpp); whatever the cells are --
+    # shared str objects, one object per cell, non-ASCII text, bytes, integers -- the codes must be the ranks of
+    # the sorted distinct strings (src/base/dataframe_wrapper.cpp:36-70)
+    rng = np.random.default_rng(0)
+    states = ["b", "a", "10", "9", "é", "aa", "", "Z", "z0"]
+    idx = rng.integers(0, len(states), size=(500, 3))
+    shared = np.array(states, dtype=object)[idx]                                   # few objects, many references
+    fresh = np.empty(idx.shape, dtype=object)
+    for r in range(idx.shape[0]):
+        for c in range(idx.shape[1]):
+            fresh[r, c] = "".join(list(states[idx[r, c]]))                        # a new object per cell
+    want = []
+    for c in range(3):
+        order = sorted(set(states[i] for i in idx[:, c]), key=lambda t: t.encode("utf-8"))
+        want.append([order.index(states[i]) for i in idx[:, c]])
+    for vals in (shared, fresh, np.asfortranarray(fresh)):
+        df = L.base.DataframeWrapper(types.SimpleNamespace(columns=["x", "y", "z"], values=vals))
+        assert df.data_column_major == want
+        assert df.val_idx2str[0] == sorted(set(states[i] for i in idx[:, 0]), key=lambda t: t.encode("utf-8"))
+    ref = oracle.reference_modules()[0]
+    if ref is not None:                                                            # the unmodified reference agrees
+        r = ref.base.DataframeWrapper(types.SimpleNamespace(columns=["x", "y", "z"], values=np.asfortranarray(fresh)))
+        assert r.data_column_major == want and r.val_idx2str == df.val_idx2str
+    # bytes cells go through the same string cast as in the reference
+    b = np.array([[b"q"], [b"p"], [b"q"]], dtype=object)
+    assert L.base.DataframeWrapper(types.SimpleNamespace(columns=["v"], values=b)).data_column_major == [[1, 0, 1]]
+    # integers rank by their decimal strings, negative ones included; more than 1024 rows cycle the value cache
+    ints = rng.integers(-3, 12, size=(3000, 2))
+    di = L.base.DataframeWrapper(types.SimpleNamespace(columns=["i", "j"], values=ints))
+    for c in range(2):
+        order = sorted(set(str(v) for v in ints[:, c]))
+        assert di.data_column_major[c] == [order.index(str(v)) for v in ints[:, c]]
+    # uint8 codes: the 257th distinct value is an error, not a wrap-around
+    many = np.array([["v%03d" % i] for i in range(257)], dtype=object)
+    with pytest.raises(ValueError, match="more than 256"):
+        L.base.DataframeWrapper(types.SimpleNamespace(columns=["v"], values=many))
+    with pytest.raises(ValueError, match="cast value to string"):
+        L.base.DataframeWrapper(types.SimpleNamespace(columns=["v"], values=np.array([[1.5], [object()]], dtype=object)))
+
+
 def test_no_gpu_fails_loudly():
     import torch
     if torch.cuda.is_available():
