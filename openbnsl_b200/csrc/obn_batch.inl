@@ -508,7 +508,12 @@ int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, con
   // parity-green on a B200 and 12-25 % faster on the 1M-row configs, but slower at 100k rows and
   // not yet profiled (profiles/r1_ab_ci_pool_v3.jsonl).
   const uint32_t pool_cells = (uint32_t)std::min(16384, std::max(0, env_int("OBN_CI_POOL_CELLS", 4096)));
-  if (env_int("OBN_CI_POOL", 0) && pool_cells && n_tuples > 1 && c && ds && ds->ctx == c && offsets && x && y &&
+  // OBN_CI_POOL: 0 off (default), 1 on, 2 on for data sets of at least OBN_CI_POOL_MIN_ROWS rows (the measured
+  // crossover lies between 100k and 1M rows)
+  const int pool_mode = env_int("OBN_CI_POOL", 0);
+  const bool pool_on = pool_mode == 1 ||
+                       (pool_mode == 2 && ds && ds->n_rows >= (size_t)std::max(0, env_int("OBN_CI_POOL_MIN_ROWS", 500000)));
+  if (pool_on && pool_cells && n_tuples > 1 && c && ds && ds->ctx == c && offsets && x && y &&
       (var_ids || !offsets[n_tuples]) && n_tuples < 0xffffffffull) {
     // tables much larger than the row count are not worth sharing (the passes cost ~2 ops per joint cell)
     const uint32_t cap = (uint32_t)std::min<uint64_t>(pool_cells, std::max<uint64_t>(64, ds->n_rows / 8));
