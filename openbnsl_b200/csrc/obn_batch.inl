@@ -344,6 +344,7 @@ static int run_batch(BatchSpec& S) {
       a.mem_off = reinterpret_cast<const uint32_t*>(din + o_moff);
       a.members = reinterpret_cast<const uint2*>(din + o_mem);
       a.pool_cells = S.pool_cells;
+      a.wide_prefetch = env_int("OBN_CI_POOL_WIDE", 0);
     }
   }
   else if (bdeu) a.scores = S.scores_dev ? S.scores_dev : reinterpret_cast<double*>(dout);

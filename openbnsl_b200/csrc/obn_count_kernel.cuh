@@ -226,6 +226,49 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
   }
 }
 
+// Pools of more than six columns (POOL kernels, A.wide_prefetch): like scan_rows_any, but the first
+// eight columns of the NEXT 16-row vector are requested before the increments of the current one,
+// so that their L2 latency hides behind the ATOMS instead of being paid twice per vector (the A/B
+// of round 1 has wide pools 20 % slower than narrow ones on C4: scan_rows_any exposes one load
+// round trip per four columns).  UNMEASURED: written after the round's GPU budget was spent; off
+// unless OBN_CI_POOL_WIDE=1.
+template <int KW, int TIER, bool SCALE4>
+__device__ __forceinline__ void scan_rows_wide(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
+                                               uint32_t v_end, uint32_t tid, uint32_t nthr) {
+  uint4 pre[8];
+  uint32_t v = v_begin + tid;
+  if (v < v_end) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (j < k) pre[j] = ld_codes16(T.col[j] + ((size_t)v << 4));
+  }
+  for (; v < v_end; v += nthr) {
+    const size_t off = (size_t)v << 4;
+    KeyVec<KW> key;
+    KeyVec<8> part;
+    bool have_part = false, have_key = false;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (j < k) fold_column<KW>(part, key, have_part, have_key, pre[j], T.card[j], T.gcells[j]);
+    for (int i = 8; i < k; i += 4) {          // columns beyond the prefetch window (rare)
+      uint4 c[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (i + j < k) c[j] = ld_codes16(T.col[i + j] + off);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
+    }
+    const uint32_t vn = v + nthr;
+    if (vn < v_end) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j < k) pre[j] = ld_codes16(T.col[j] + ((size_t)vn << 4));
+    }
+    count16<KW, TIER, SCALE4>(key, base);
+  }
+}
+
 // POOL = true is the MODE_CI_POOL variant (a separate instantiation, so that the default
 // kernels compile exactly as they did without it).
 template <int KW, int TIER, bool SCALE4, bool POOL = false>
@@ -324,7 +367,10 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     case 4: scan_rows_k<KW, TIER, SCALE4, 4>(T, base, v_begin, v_end, tid, nthr); break;
     case 5: scan_rows_k<KW, TIER, SCALE4, 5>(T, base, v_begin, v_end, tid, nthr); break;
     case 6: scan_rows_k<KW, TIER, SCALE4, 6>(T, base, v_begin, v_end, tid, nthr); break;
-    default: scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr); break;
+    default:
+      if (POOL && KW != 8 && A.wide_prefetch) scan_rows_wide<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
+      else scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
+      break;
   }
   if (tid == 0) {
     if (k == 0) {

@@ -50,6 +50,7 @@ struct BatchArgs {
   const uint32_t* mem_off;  // [pools + 1], indexed by pool id (hdr.x)
   const uint2* members;
   uint32_t pool_cells;      // joint tables above this size are single tests: no pass buffers
+  int wide_prefetch;        // POOL kernels: scan_rows_wide for tuples of more than six columns
 };
 
 // ---------------------------------------------------------------------------
