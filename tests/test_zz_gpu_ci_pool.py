@@ -30,10 +30,11 @@ def frontier(rng, n_vars, n_pairs, depth, pool_size):
 
 
 class pooled:
-    def __init__(self, on, cells=None):
+    def __init__(self, on, cells=None, **extra):
         self.env = {"OBN_CI_POOL": "1" if on else "0"}
         if cells:
             self.env["OBN_CI_POOL_CELLS"] = str(cells)
+        self.env.update({k: str(v) for k, v in extra.items()})
 
     def __enter__(self):
         self.old = {k: os.environ.get(k) for k in self.env}
@@ -90,3 +91,27 @@ def test_pooled_pc_learns_the_same_graph(gpu_ctx):
             g = L.structure_learning.pc(df, L.citest.GSquare(0.05), 4, True)
         adj.append(np.array([[g.has_edge(a, b) for b in range(net.n)] for a in range(net.n)]))
     assert (adj[0] == adj[1]).all()
+
+
+@pytest.mark.skipif(os.environ.get("OBN_TEST_CI_POOL_WIDE", "0") != "1",
+                    reason="opt-in (OBN_TEST_CI_POOL_WIDE=1): scan_rows_wide has never run on a device")
+@pytest.mark.parametrize("wide", [0, 1])
+@pytest.mark.parametrize("kind", [0, 1])
+def test_wide_pools_equal_default(gpu_ctx, kind, wide):
+    net = nw.alarm()
+    codes, cards = ranked(net.sample(50000, 9))
+    ods = oracle.Dataset(codes, cards)
+    ds = gpu_ctx.upload(codes, cards)
+    rng = np.random.default_rng(3)
+    xs, ys, zs = frontier(rng, net.n, 30, 2, 8)          # pools of up to 8 conditioning variables: 10 columns
+    with pooled(False):
+        s0, d0, p0 = ds.ci_tests(xs, ys, zs, kind)
+    with pooled(True, 16384, OBN_CI_POOL_VARS=8, OBN_CI_POOL_WIDE=wide):
+        s1, d1, p1 = ds.ci_tests(xs, ys, zs, kind)
+    assert np.array_equal(d0, d1)
+    for t in range(len(xs)):
+        assert close(s0[t], s1[t], 1e-12, 1e-12) and close(p0[t], p1[t], 1e-9, 1e-300), t
+    for t in rng.choice(len(xs), size=40, replace=False):
+        ws, wd, wp = oracle.citest(ods, xs[t], ys[t], zs[t], kind)
+        assert int(d1[t]) == wd and close(s1[t], ws, 1e-9, 1e-12)
+    ds.close()
