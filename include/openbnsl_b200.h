@@ -115,7 +115,10 @@ OBN_API int obn_bdeu_subset_scores(obn_ctx* ctx, const obn_dataset* ds,
  * tuple t must contain x[t] and y[t]; all its other variables condition.
  * Outputs the statistic, the degrees of freedom and p = pchisq(stat, dof)
  * (citest.h:17-21); the decision p >= level stays with the caller.  Any of
- * the three output pointers may be NULL. */
+ * the three output pointers may be NULL.  With OBN_CI_POOL=1 (or 2: from
+ * OBN_CI_POOL_MIN_ROWS rows up) the tests of one (x, y) pair share one joint
+ * table on the device (see obn_ci_pool_plan below); the results are the same
+ * tables' statistics either way. */
 OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
                          const uint32_t* var_ids, const uint64_t* offsets,
                          size_t n_tuples, const uint32_t* x, const uint32_t* y,
