@@ -125,6 +125,19 @@ OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
                          int kind, double* stat_out, uint64_t* dof_out,
                          double* p_out);
 
+/* obn_ci_tests in two halves, so that the caller's host thread can prepare its next batch while
+ * the device works on this one (the PC driver enumerates round r+1 during round r).  submit
+ * validates, packs, uploads and enqueues everything and returns; the input arrays may be reused
+ * as soon as it has returned.  collect waits for the results and writes them (any pointer may be
+ * NULL; p_out only if want_p was set).  At most one batch is in flight per ctx: until it is
+ * collected every other batch call on the ctx returns OBN_ERR_INVALID.  collect without a
+ * submitted batch (or after submitting zero tuples) is a no-op. */
+OBN_API int obn_ci_tests_submit(obn_ctx* ctx, const obn_dataset* ds,
+                                const uint32_t* var_ids, const uint64_t* offsets,
+                                size_t n_tuples, const uint32_t* x, const uint32_t* y,
+                                int kind, int want_p);
+OBN_API int obn_ci_tests_collect(obn_ctx* ctx, double* stat_out, uint64_t* dof_out, double* p_out);
+
 /* Diagnostics of the CI-test pooling inside obn_ci_tests (host only, need no device; DESIGN.md
  * 3.5).  Tests of one (x, y) pair whose conditioning sets come from one neighbourhood -- the shape
  * of the PC frontier, src/structure_learning/pc.cpp:27-47 -- share ONE joint table over (union of

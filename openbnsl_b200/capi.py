@@ -24,7 +24,7 @@ EXPORTS = [
     "obn_last_error", "obn_version", "obn_ctx_create", "obn_ctx_destroy", "obn_ctx_stream",
     "obn_dataset_upload", "obn_dataset_destroy", "obn_host_pin", "obn_host_unpin", "obn_dataset_n_vars", "obn_dataset_n_rows",
     "obn_count_tables", "obn_bdeu_scores", "obn_bdeu_subset_scores", "obn_ci_tests",
-    "obn_ci_pool_plan", "obn_ci_pool_marginalise",
+    "obn_ci_tests_submit", "obn_ci_tests_collect", "obn_ci_pool_plan", "obn_ci_pool_marginalise",
     "obn_es_begin", "obn_es_level_begin", "obn_es_level_scores", "obn_es_level_buffer", "obn_es_level_dp", "obn_es_level_dp_part", "obn_es_level_dp_commit", "obn_lattice_bottom_program",
     "obn_es_lattice", "obn_es_f_buffer", "obn_es_finish", "obn_es_end",
     "obn_profile_enable", "obn_profile_read",
@@ -72,6 +72,8 @@ def load():
     L.obn_bdeu_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, C.c_double, C.c_int, f64p]
     L.obn_bdeu_subset_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, C.c_double, C.c_int, f64p]
     L.obn_ci_tests.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, f64p, u64p, f64p]
+    L.obn_ci_tests_submit.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, C.c_int]
+    L.obn_ci_tests_collect.argtypes = [vp, f64p, u64p, f64p]
     L.obn_ci_pool_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, C.c_uint32, C.c_uint32,
                                    u32p, u64p, u32p, u32p, C.POINTER(C.c_size_t)]
     L.obn_ci_pool_marginalise.argtypes = [i32p, C.c_uint32, u32p, C.c_int, C.c_uint32, i32p, u32p]
@@ -232,6 +234,19 @@ class Dataset:
         _check(load().obn_ci_tests(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), n,
                                    _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), int(kind),
                                    _ptr(stat, C.c_double), _ptr(dof, C.c_uint64), _ptr(p, C.c_double)))
+        return stat, dof, p
+
+    def ci_tests_submit_collect(self, flat, offs, x, y, kind, between=None):
+        """The same batch through obn_ci_tests_submit / obn_ci_tests_collect; `between` runs while it is in flight."""
+        n = len(offs) - 1
+        _check(load().obn_ci_tests_submit(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), n,
+                                          _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), int(kind), 1))
+        if between is not None:
+            between()
+        stat = np.zeros(n, dtype=np.float64)
+        dof = np.zeros(n, dtype=np.uint64)
+        p = np.zeros(n, dtype=np.float64)
+        _check(load().obn_ci_tests_collect(self.ctx._h, _ptr(stat, C.c_double), _ptr(dof, C.c_uint64), _ptr(p, C.c_double)))
         return stat, dof, p
 
     def ci_tests(self, x, y, zs, kind):

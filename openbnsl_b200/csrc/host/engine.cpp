@@ -42,6 +42,15 @@ void GpuEvaluator::ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int
                      b.x.data() + begin, b.y.data() + begin, kind, nullptr, nullptr, p));
 }
 
+bool GpuEvaluator::ci_submit(const TupleBatch& b, int kind) {
+  check(obn_ci_tests_submit(Engine::instance().ctx(), ds_, b.var_ids.data(), b.offsets.data(), b.size(),
+                            b.x.data(), b.y.data(), kind, 1));
+  return true;
+}
+void GpuEvaluator::ci_collect(double* p) {
+  check(obn_ci_tests_collect(Engine::instance().ctx(), nullptr, nullptr, p));
+}
+
 void GpuEvaluator::subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                                  double* out) {
   if (end <= begin) return;

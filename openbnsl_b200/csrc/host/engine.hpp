@@ -74,6 +74,10 @@ struct Evaluator {
   virtual ~Evaluator() = default;
   // p-values of tuples [begin, end) of the batch -> p[0 .. end-begin)
   virtual void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) = 0;
+  // the same question in two halves (whole batch): submit returns while the answer is being
+  // computed, collect waits for it.  false = not supported, use ci_pvalues.
+  virtual bool ci_submit(const TupleBatch&, int /*kind*/) { return false; }
+  virtual void ci_collect(double* /*p*/) {}
   // scores of every child of tuples [begin, end) -> out[offsets[t]-offsets[begin] + i]
   virtual void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                              double* out) = 0;
@@ -85,6 +89,8 @@ class GpuEvaluator : public Evaluator {
  public:
   explicit GpuEvaluator(obn_dataset* ds) : ds_(ds) {}
   void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) override;
+  bool ci_submit(const TupleBatch& b, int kind) override;
+  void ci_collect(double* p) override;
   void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                      double* out) override;
   void child_scores(const TupleBatch& b, const uint32_t* child, double ess, int exact_order, double* out) override;

@@ -146,8 +146,16 @@ void append_test(TupleBatch& b, uint32_t u, uint32_t v, const std::vector<uint32
   b.y.push_back(v);
 }
 
+// The same decision in two halves (Evaluator::ci_submit / ci_collect): submit returns false when
+// the evaluator cannot work asynchronously, and the driver falls back to `decide`.
+struct AsyncDecide {
+  std::function<bool(const TupleBatch&)> submit;
+  std::function<void(const TupleBatch&, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
+                     std::vector<int32_t>& first)> collect;
+};
+
 PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, const DecideFn& decide,
-            PcStats* stats) {
+            PcStats* stats, const AsyncDecide* async = nullptr) {
   AdjMatGraph g(n);
   Sepsets sep(n * n);
   if (stats) {
@@ -171,11 +179,11 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
   std::vector<FastCursor> cursors;
   std::vector<uint32_t> idx_arena;
   std::vector<std::vector<uint32_t>> adj(n);
-  TupleBatch batch;
-  std::vector<uint32_t> pair_of_test, z, tmp;
+  TupleBatch batch, spec;                     // spec: the next round, built while this one is evaluated
+  std::vector<uint32_t> pair_of_test, pair_of_spec, z, tmp;
   std::vector<std::vector<uint32_t>> z_of_test;
   std::vector<int32_t> first;
-  auto note_batch = [&](size_t k) {
+  auto note_batch = [&](size_t k) {           // accounts `batch`
     if (!stats) return;
     stats->tests_per_depth[k] += batch.size();
     stats->batches_per_depth[k] += 1;
@@ -250,14 +258,15 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         start_dir(cursors[pi], idx, 0);
         settle(cursors[pi], idx);
       }
-      size_t quota = 1;
-      for (;;) {
+      auto count_live = [&]() {
         size_t live = 0;
         for (const auto& c : cursors) live += (!c.done && !c.removed);
-        if (!live) break;
-        quota = std::max<size_t>(quota, target_batch / live);
-        batch.clear();
-        pair_of_test.clear();
+        return live;
+      };
+      // the next `quota` candidates of every undecided edge, in the reference's enumeration order
+      auto build_round = [&](TupleBatch& out, std::vector<uint32_t>& pair_out, size_t quota) {
+        out.clear();
+        pair_out.clear();
         for (size_t pi = 0; pi < cursors.size(); ++pi) {
           FastCursor& c = cursors[pi];
           if (c.done || c.removed) continue;
@@ -268,27 +277,26 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
             int np = 0;
             for (size_t i = 0; i < k; ++i) {
               const uint32_t z = item(c, c.dir, idx[i]);
-              while (np < 2 && pend[np] < z) batch.var_ids.push_back(pend[np++]);
-              batch.var_ids.push_back(z);
+              while (np < 2 && pend[np] < z) out.var_ids.push_back(pend[np++]);
+              out.var_ids.push_back(z);
             }
-            while (np < 2) batch.var_ids.push_back(pend[np++]);
-            batch.offsets.push_back(batch.var_ids.size());
-            batch.x.push_back(c.dir ? c.y : c.x);
-            batch.y.push_back(c.dir ? c.x : c.y);
-            pair_of_test.push_back((uint32_t)pi);
+            while (np < 2) out.var_ids.push_back(pend[np++]);
+            out.offsets.push_back(out.var_ids.size());
+            out.x.push_back(c.dir ? c.y : c.x);
+            out.y.push_back(c.dir ? c.x : c.y);
+            pair_out.push_back((uint32_t)pi);
             next_comb(c, idx);
             settle(c, idx);
           }
         }
-        lap(&PcStats::enumerate_ms);
-        decide(batch, pair_of_test, cursors.size(), first);
-        lap(&PcStats::evaluate_ms);
-        note_batch(k);
+      };
+      // every edge is resolved at its FIRST passing candidate (pc.cpp:40-42)
+      auto resolve_round = [&]() {
         for (size_t pi = 0; pi < cursors.size(); ++pi) {
           if (first[pi] == INT_MAX) continue;
           FastCursor& c = cursors[pi];
           c.removed = true;
-          g.remove_undirected_edge(c.x, c.y);                 // pc.cpp:40-42
+          g.remove_undirected_edge(c.x, c.y);
           std::vector<uint32_t>& sz = sep[(size_t)c.x * n + c.y];
           sz.clear();
           const size_t t = (size_t)first[pi];
@@ -296,8 +304,60 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
             if (batch.var_ids[i] != c.x && batch.var_ids[i] != c.y) sz.push_back(batch.var_ids[i]);
           sep[(size_t)c.y * n + c.x] = sz;
         }
-        lap(&PcStats::resolve_ms);
+      };
+      size_t quota = 1;
+      size_t live = count_live();
+      if (live) {
+        quota = std::max<size_t>(quota, target_batch / live);
+        build_round(batch, pair_of_test, quota);
+      }
+      while (live && batch.size()) {
+        lap(&PcStats::enumerate_ms);
+        // Overlap (async evaluators): the candidates of a depth depend only on the snapshot, so
+        // while the device works on this round the next one is enumerated as if no edge were
+        // removed, and the tests of the edges this round does remove are dropped afterwards.
+        // Batch boundaries do not change what an edge resolves at: its first passing candidate.
+        const bool in_flight = async && async->submit(batch);
         quota *= 2;
+        bool have_spec = false;
+        if (in_flight) {
+          lap(&PcStats::evaluate_ms);
+          const size_t l2 = count_live();
+          if (l2) {
+            quota = std::max<size_t>(quota, target_batch / l2);
+            build_round(spec, pair_of_spec, quota);
+            have_spec = true;
+          }
+          lap(&PcStats::enumerate_ms);
+          async->collect(batch, pair_of_test, cursors.size(), first);
+        } else {
+          decide(batch, pair_of_test, cursors.size(), first);
+        }
+        lap(&PcStats::evaluate_ms);
+        note_batch(k);
+        resolve_round();
+        if (in_flight) {
+          batch.clear();
+          pair_of_test.clear();
+          if (have_spec)
+            for (size_t t = 0; t < spec.size(); ++t) {
+              if (cursors[pair_of_spec[t]].removed) continue;
+              batch.var_ids.insert(batch.var_ids.end(), spec.var_ids.begin() + spec.offsets[t],
+                                   spec.var_ids.begin() + spec.offsets[t + 1]);
+              batch.offsets.push_back(batch.var_ids.size());
+              batch.x.push_back(spec.x[t]);
+              batch.y.push_back(spec.y[t]);
+              pair_of_test.push_back(pair_of_spec[t]);
+            }
+          live = batch.size();      // an edge that is still undecided kept its tests
+        } else {
+          live = count_live();
+          if (live) {
+            quota = std::max<size_t>(quota, target_batch / live);
+            build_round(batch, pair_of_test, quota);
+          }
+        }
+        lap(&PcStats::resolve_ms);
       }
     } else {
       for (size_t x = 0; x < n; ++x)
@@ -377,7 +437,22 @@ PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, c
       }
     comm.allreduce_min_i32(first.data(), first.size());
   };
-  return run_pc(n_vars, opt.max_cond_vars, opt.stable, opt.target_batch, decide, stats);
+  // single rank only: a sharded round ends in a collective, which would need its own split
+  AsyncDecide async;
+  async.submit = [&](const TupleBatch& b) { return ev.ci_submit(b, opt.kind); };
+  async.collect = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
+                      std::vector<int32_t>& first) {
+    first.assign(n_slots, INT_MAX);
+    p.resize(b.size());
+    ev.ci_collect(p.data());
+    for (size_t t = 0; t < b.size(); ++t)
+      if (p[t] >= opt.level) {                                // citest.h:147
+        int32_t& f = first[pair_of_test[t]];
+        if ((int32_t)t < f) f = (int32_t)t;
+      }
+  };
+  const bool overlap = opt.overlap && opt.stable && comm.world == 1;
+  return run_pc(n_vars, opt.max_cond_vars, opt.stable, opt.target_batch, decide, stats, overlap ? &async : nullptr);
 }
 
 PDAG pc_oracle(size_t n_vars, const PDAG& truth, size_t max_cond_vars, bool stable) {

@@ -33,6 +33,9 @@ struct BatchSpec {
   const uint32_t* members = nullptr;    // 2 words per member
   uint32_t pool_cells = 0;
   double alg_bytes = 0;             // sum over the TESTS of k * n_rows (the unit is the test)
+  // CI modes: return once everything is enqueued (obn_ci_tests_submit); obn_ci_tests_collect
+  // waits and hands the results out
+  bool defer = false;
 };
 
 // Table-size classes.  One launch covers the tuples of one class, so that the
@@ -76,6 +79,7 @@ static int run_batch(BatchSpec& S) {
   const obn_dataset* ds = S.ds;
   if (!c || !ds) return fail(OBN_ERR_INVALID, "ctx or dataset is NULL");
   if (ds->ctx != c) return fail(OBN_ERR_INVALID, "dataset belongs to another ctx");
+  if (c->pending.active) return fail(OBN_ERR_INVALID, "a submitted batch is waiting for obn_ci_tests_collect");
   const size_t n = S.n;
   if (n == 0) return OBN_OK;
   if (!S.offsets) return fail(OBN_ERR_INVALID, "offsets is NULL");
@@ -430,6 +434,21 @@ static int run_batch(BatchSpec& S) {
   // ---- download ------------------------------------------------------------------
   if (int rc = c->h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
   if (out_bytes) OBN_CUDA(cudaMemcpyAsync(c->h_out.p, dout, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+  if (S.defer) {                    // CI modes only (obn_ci_tests_submit)
+    obn_ctx::Pending& P = c->pending;
+    P.active = true;
+    P.n_out = n_out;
+    P.out_bytes = out_bytes;
+    P.in_bytes = in_bytes;
+    P.ev_first = ev_first;
+    P.alg_bytes = pooled ? S.alg_bytes : alg_bytes;
+    P.want_p = S.p != nullptr;
+    const auto now = std::chrono::steady_clock::now();
+    P.t_submitted_ms = std::chrono::duration<double, std::milli>(now.time_since_epoch()).count();
+    c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
+    c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(now - t_packed).count();
+    return OBN_OK;
+  }
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   const auto t_synced = std::chrono::steady_clock::now();
   c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
@@ -501,9 +520,9 @@ int obn_bdeu_subset_scores(obn_ctx* c, const obn_dataset* ds, const uint32_t* va
   return run_batch(S);
 }
 
-int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
-                 size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
-                 uint64_t* dof_out, double* p_out) {
+static int ci_tests_impl(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
+                         size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
+                         uint64_t* dof_out, double* p_out, bool defer) {
   if (kind != OBN_CI_CHI2 && kind != OBN_CI_G2) return fail(OBN_ERR_INVALID, "Unsupported CI test type");
   // Count reuse across the tests of one (x, y) pair.  OFF unless OBN_CI_POOL=1:
   // parity-green on a B200 and 12-25 % faster on the 1M-row configs, but slower at 100k rows and
@@ -535,6 +554,7 @@ int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, con
       S.members = P.members.data();
       S.pool_cells = cap;
       S.alg_bytes = (double)offsets[n_tuples] * (double)ds->n_rows;
+      S.defer = defer;
       return run_batch(S);
     }
   }
@@ -545,7 +565,55 @@ int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, con
   S.stat = stat_out;
   S.dof = dof_out;
   S.p = p_out;
+  S.defer = defer;
   return run_batch(S);
 }
+
+int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
+                 size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
+                 uint64_t* dof_out, double* p_out) {
+  return ci_tests_impl(c, ds, var_ids, offsets, n_tuples, x, y, kind, stat_out, dof_out, p_out, false);
+}
+
+// Same work as obn_ci_tests, split in two so that the caller's host thread can prepare its next
+// batch while the device runs this one: submit packs, uploads and enqueues everything (the input
+// arrays may be reused as soon as it returns); collect waits and writes the results.  One batch
+// may be in flight per ctx; every other batch call fails until it is collected.
+int obn_ci_tests_submit(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
+                        size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, int want_p) {
+  static double dummy;              // run_batch only asks whether p is wanted
+  return ci_tests_impl(c, ds, var_ids, offsets, n_tuples, x, y, kind, nullptr, nullptr, want_p ? &dummy : nullptr, true);
+}
+
+int obn_ci_tests_collect(obn_ctx* c, double* stat_out, uint64_t* dof_out, double* p_out) {
+  if (!c) return fail(OBN_ERR_INVALID, "ctx is NULL");
+  obn_ctx::Pending& P = c->pending;
+  if (!P.active) return OBN_OK;     // nothing was submitted (an empty batch): nothing to hand out
+  if (p_out && !P.want_p) return fail(OBN_ERR_INVALID, "p-values were not requested at submit");
+  OBN_CUDA(cudaSetDevice(c->device));
+  const auto t0 = std::chrono::steady_clock::now();
+  P.active = false;
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  const unsigned char* hout = c->h_out.as<unsigned char>();
+  const size_t n = P.n_out;
+  if (stat_out) memcpy(stat_out, hout, n * 8);
+  if (dof_out) memcpy(dof_out, hout + n * 8, n * 8);
+  if (p_out) memcpy(p_out, hout + n * 16, n * 8);
+  if (c->profile_on) {
+    for (size_t i = P.ev_first; i < c->ev_used; ++i) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, c->ev_pool[i].first, c->ev_pool[i].second);
+      c->prof.count_kernel_ms += ms;
+    }
+    c->ev_used = P.ev_first;
+  }
+  c->prof.h2d_bytes += (double)P.in_bytes;
+  c->prof.d2h_bytes += (double)P.out_bytes;
+  c->prof.algorithmic_bytes += P.alg_bytes;
+  c->prof.tuples += n;
+  return OBN_OK;
+}
+
 
 }  // extern "C"

@@ -178,6 +178,15 @@ struct obn_ctx {
   obn::PinBuf h_in, h_out;
   uint8_t* ds_cache = nullptr;  // device buffer of the last destroyed dataset, reused by the next upload
   size_t ds_cache_bytes = 0;
+  // a CI batch submitted with obn_ci_tests_submit whose results are still on their way
+  // (obn_ci_tests_collect waits for them); at most one, it owns the staging buffers until then
+  struct Pending {
+    bool active = false;
+    size_t n_out = 0, out_bytes = 0, in_bytes = 0, ev_first = 0;
+    double alg_bytes = 0;
+    bool want_p = false;
+    double t_submitted_ms = 0;    // host clock at the end of submit (steady_clock, ms)
+  } pending;
   // profiling
   bool profile_on = false;
   obn_profile prof = {};

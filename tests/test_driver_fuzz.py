@@ -25,8 +25,16 @@ def case(seed):
     return net, codes, cards
 
 
+class CountingEvaluator(OracleEvaluator):
+    """Also answers the two-half calls of the test seam (bindings.cpp: PyEvaluator::ci_submit)."""
+    submitted = 0
+
+
 @pytest.mark.parametrize("seed", range(40))
-def test_pc_driver_fuzz(seed):
+@pytest.mark.parametrize("overlap", [0, 1])
+def test_pc_driver_fuzz(seed, overlap, monkeypatch):
+    # overlap = 1: round r+1 is enumerated while round r is "in flight" (OBN_PC_OVERLAP, pc.cpp) -- same graphs
+    monkeypatch.setenv("OBN_PC_OVERLAP", str(overlap))
     net, codes, cards = case(seed)
     ods = oracle.Dataset(codes, cards)
     rng = np.random.default_rng(1000 + seed)
@@ -38,8 +46,10 @@ def test_pc_driver_fuzz(seed):
     for stable in (True, False):
         want = oracle.pc(ods, kind, level, depth, stable)
         for tb in (0, 1, 5):                                     # default rounds, one test per round, tiny rounds
-            got = pdag_to_adj(L._testing.pc(net.n, OracleEvaluator(ods), T, depth, stable, None, tb), net.n)
+            ev = CountingEvaluator(ods)
+            got = pdag_to_adj(L._testing.pc(net.n, ev, T, depth, stable, None, tb), net.n)
             assert (got == want).all(), (seed, stable, tb)
+            assert (ev.submitted > 0) == bool(overlap and stable)    # the overlapped loop really ran
         if rdf is not None:
             RT = REF.citest.ChiSquare(level) if kind == 0 else REF.citest.GSquare(level)
             assert (pdag_to_adj(REF.structure_learning.pc(rdf, RT, depth, stable), net.n) == want).all(), (seed, stable)

@@ -115,3 +115,47 @@ def test_wide_pools_equal_default(gpu_ctx, kind, wide):
         ws, wd, wp = oracle.citest(ods, xs[t], ys[t], zs[t], kind)
         assert int(d1[t]) == wd and close(s1[t], ws, 1e-9, 1e-12)
     ds.close()
+
+
+@pytest.mark.skipif(os.environ.get("OBN_TEST_PC_OVERLAP", "0") != "1",
+                    reason="opt-in (OBN_TEST_PC_OVERLAP=1): obn_ci_tests_submit/collect have never run on a device")
+def test_submit_collect_and_overlapped_pc(gpu_ctx):
+    import openbnsl_b200
+    from openbnsl_b200 import capi
+    L = openbnsl_b200.openbnsllib
+    net = nw.alarm()
+    codes, cards = ranked(net.sample(100000, 1))
+    ds = gpu_ctx.upload(codes, cards)
+    rng = np.random.default_rng(2)
+    xs, ys, zs = frontier(rng, net.n, 50, 2, 5)
+    tuples = [sorted(list(z) + [a, b]) for a, b, z in zip(xs, ys, zs)]
+    flat, offs = capi._csr(tuples)
+    xa, ya = np.asarray(xs, dtype=np.uint32), np.asarray(ys, dtype=np.uint32)
+    for pool in (False, True):
+        with pooled(pool):
+            s0, d0, p0 = ds.ci_tests_csr(flat, offs, xa, ya, 1)
+            busy = []
+            s1, d1, p1 = ds.ci_tests_submit_collect(flat.copy(), offs, xa, ya, 1,
+                                                    between=lambda: busy.append(sum(range(20000))))
+            assert np.array_equal(s0, s1) and np.array_equal(d0, d1) and np.array_equal(p0, p1)
+            # a second batch call while one is in flight is refused, and the ctx recovers after collect
+            lib = capi.load()
+            C = capi.C
+            assert lib.obn_ci_tests_submit(gpu_ctx._h, ds._h, capi._ptr(flat, C.c_uint32), capi._ptr(offs, C.c_uint64),
+                                           len(xs), capi._ptr(xa, C.c_uint32), capi._ptr(ya, C.c_uint32), 1, 1) == 0
+            with pytest.raises(ValueError, match="waiting for obn_ci_tests_collect"):
+                ds.ci_tests_csr(flat, offs, xa, ya, 1)
+            assert lib.obn_ci_tests_collect(gpu_ctx._h, None, None, None) == 0
+            s2, _, _ = ds.ci_tests_csr(flat, offs, xa, ya, 1)
+            assert np.array_equal(s0, s2)
+    ds.close()
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, [int(c) for c in cards])
+    adj = []
+    for ov in ("0", "1"):
+        os.environ["OBN_PC_OVERLAP"] = ov
+        try:
+            g = L.structure_learning.pc(df, L.citest.GSquare(0.05), 4, True)
+        finally:
+            os.environ.pop("OBN_PC_OVERLAP", None)
+        adj.append(np.array([[g.has_edge(a, b) for b in range(net.n)] for a in range(net.n)]))
+    assert (adj[0] == adj[1]).all()
