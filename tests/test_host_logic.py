@@ -28,6 +28,14 @@ def test_c_abi_exports_every_declared_symbol():
     assert b"sm_100a" in capi.load().obn_version()
 
 
+def test_two_half_ci_call_rejects_a_missing_ctx():
+    # obn_ci_tests_submit / _collect validate before touching a device, like every other entry point
+    lib = capi.load()
+    assert lib.obn_ci_tests_collect(None, None, None, None) == capi.OBN_ERR_INVALID
+    assert b"ctx" in lib.obn_last_error()
+    assert lib.obn_ci_tests_submit(None, None, None, None, 0, None, None, 1, 1) == capi.OBN_ERR_INVALID
+
+
 def test_module_surface_matches_reference():
     assert L.cuda_enabled is True
     for sub, names in {"base": ["DataframeWrapper", "ContingencyTable", "PDAG"],
