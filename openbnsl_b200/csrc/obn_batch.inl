@@ -235,11 +235,12 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
-  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; };
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t stage_off = 0; };
   std::vector<Launch> launches;
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
   size_t max_scratch_ints = 0, max_launch_tuples = 0;
   const int force_t = env_int("OBN_FORCE_T", 0), force_splits = env_int("OBN_FORCE_SPLITS", 0);
+  const int pool_wide = pooled ? env_int("OBN_CI_POOL_WIDE", 0) : 0;
   const size_t target_threads = (size_t)c->sm_count * (size_t)env_int("OBN_THREADS_PER_SM", 768);
   for (int g = 0; g < kNumClasses; ++g) {
     if (!group_count[g]) continue;
@@ -284,6 +285,20 @@ static int run_batch(BatchSpec& S) {
         smem = need + (size_t)nw * max_rxy * 4;
       }
       smem = std::max<size_t>(align16(smem), 16);
+      // scan_rows_tma (OBN_CI_POOL_WIDE=2): a ring of kTmaStages tiles of nthr 16-row vectors of every
+      // column behind everything else; used only when it fits next to the table
+      uint32_t stage_off = 0;
+      if (pooled && pool_wide == 2) {
+        size_t max_k = 0;
+        for (size_t q = i; q < gstart[g + 1]; ++q)
+          max_k = std::max<size_t>(max_k, S.offsets[perm[q] + 1] - S.offsets[perm[q]]);
+        const size_t off128 = (smem + 127) & ~(size_t)127;
+        const size_t ring = (size_t)kTmaStages * max_k * 16 * (size_t)nthr;
+        if (max_k > 6 && off128 + ring + 1024 <= budget) {
+          stage_off = (uint32_t)off128;
+          smem = off128 + ring;
+        }
+      }
       const bool need_scratch = splits > 1 || global_tier;
       size_t j = i, scratch_ints = 0;
       if (need_scratch) {
@@ -298,7 +313,7 @@ static int run_batch(BatchSpec& S) {
       }
       uint32_t vps = (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false});
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, stage_off});
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
       max_launch_tuples = std::max(max_launch_tuples, j - i);
       i = j;
@@ -348,7 +363,6 @@ static int run_batch(BatchSpec& S) {
       a.mem_off = reinterpret_cast<const uint32_t*>(din + o_moff);
       a.members = reinterpret_cast<const uint2*>(din + o_mem);
       a.pool_cells = S.pool_cells;
-      a.wide_prefetch = env_int("OBN_CI_POOL_WIDE", 0);
     }
   }
   else if (bdeu) a.scores = S.scores_dev ? S.scores_dev : reinterpret_cast<double*>(dout);
@@ -409,6 +423,8 @@ static int run_batch(BatchSpec& S) {
     a.tickets = c->d_tickets.as<unsigned int>() + L.begin;
     a.splits = L.splits;
     a.vec_per_split = L.vps;
+    a.stage_off = L.stage_off;
+    a.wide_prefetch = (pool_wide == 2 && !L.stage_off) ? 0 : pool_wide;   // no room for the tile ring: plain loop
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
     cudaError_t e;
     if (pooled) {

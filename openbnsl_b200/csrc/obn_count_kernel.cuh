@@ -269,6 +269,74 @@ __device__ __forceinline__ void scan_rows_wide(const CtaTuple& T, int k, unsigne
   }
 }
 
+// Pools of any width, rows staged through shared memory by the TMA engine (POOL kernels,
+// A.wide_prefetch == 2).  A tile is blockDim.x 16-row vectors of every column of the pool: thread 0
+// arms `full[s]` with the tile's byte count and issues one 1-D bulk copy per column
+// (cp.async.bulk ... mbarrier::complete_tx::bytes); every thread then reads its vector of each
+// column with one conflict-free LDS.128, arrives on `empty[s]` as soon as its reads are done (the
+// increments do not need the slot any more) and applies its 16 increments.  kTmaStages tiles are in
+// flight; a slot is refilled one tile late, so that thread 0 rarely waits for the other warps.
+// No registers are spent on prefetch, so the loop does not care how wide the pool is.
+// UNMEASURED and never run: written after round 1's GPU budget was spent (OBN_CI_POOL_WIDE=2).
+constexpr int kTmaStages = 3;
+
+template <int KW, int TIER, bool SCALE4>
+__device__ __forceinline__ void scan_rows_tma(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
+                                              uint32_t v_end, uint32_t tid, uint32_t nthr, unsigned char* stage,
+                                              uint64_t* full, uint64_t* empty) {
+  const uint32_t tv = nthr;                               // vectors per tile
+  const uint32_t col_bytes = tv << 4, stage_bytes = (uint32_t)k * col_bytes;
+  const uint32_t n_tiles = (v_end > v_begin) ? (v_end - v_begin + tv - 1) / tv : 0;
+  if (tid == 0) {
+    for (int s = 0; s < kTmaStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], nthr);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  auto issue = [&](uint32_t tile) {                       // thread 0 only
+    const uint32_t s = tile % kTmaStages;
+    const uint32_t v0 = v_begin + tile * tv;
+    const uint32_t bytes = min(tv, v_end - v0) << 4;
+    mbar_arrive_expect_tx(&full[s], (uint32_t)k * bytes);
+    for (int j = 0; j < k; ++j)
+      bulk_g2s(stage + s * stage_bytes + (uint32_t)j * col_bytes, T.col[j] + ((size_t)v0 << 4), bytes, &full[s]);
+  };
+  if (tid == 0)
+    for (uint32_t t = 0; t < n_tiles && t < (uint32_t)kTmaStages; ++t) issue(t);
+  for (uint32_t tile = 0; tile < n_tiles; ++tile) {
+    const uint32_t s = tile % kTmaStages;
+    mbar_wait(&full[s], (tile / kTmaStages) & 1u);
+    const uint32_t v = v_begin + tile * tv + tid;
+    const bool valid = v < v_end;
+    KeyVec<KW> key;
+    if (valid) {
+      const unsigned char* src = stage + s * stage_bytes + (tid << 4);
+      KeyVec<8> part;
+      bool have_part = false, have_key = false;
+      for (int i = 0; i < k; i += 4) {
+        uint4 c[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (i + j < k) c[j] = *reinterpret_cast<const uint4*>(src + (uint32_t)(i + j) * col_bytes);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
+      }
+    }
+    mbar_arrive(&empty[s]);                               // this thread is done with the slot
+    if (valid) count16<KW, TIER, SCALE4>(key, base);
+    if (tid == 0 && tile >= 1) {                          // refill the slot of the previous tile
+      const uint32_t pt = tile - 1, nt = pt + kTmaStages;
+      if (nt < n_tiles) {
+        mbar_wait(&empty[pt % kTmaStages], (pt / kTmaStages) & 1u);
+        issue(nt);
+      }
+    }
+  }
+}
+
 // POOL = true is the MODE_CI_POOL variant (a separate instantiation, so that the default
 // kernels compile exactly as they did without it).
 template <int KW, int TIER, bool SCALE4, bool POOL = false>
@@ -368,8 +436,18 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     case 5: scan_rows_k<KW, TIER, SCALE4, 5>(T, base, v_begin, v_end, tid, nthr); break;
     case 6: scan_rows_k<KW, TIER, SCALE4, 6>(T, base, v_begin, v_end, tid, nthr); break;
     default:
-      if (POOL && KW != 8 && A.wide_prefetch) scan_rows_wide<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
-      else scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
+      if constexpr (POOL) {
+        __shared__ __align__(8) uint64_t tma_bar[2 * kTmaStages];
+        if (A.wide_prefetch == 2)
+          scan_rows_tma<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr, smem_raw + A.stage_off, tma_bar,
+                                          tma_bar + kTmaStages);
+        else if (KW != 8 && A.wide_prefetch == 1)
+          scan_rows_wide<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
+        else
+          scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
+      } else {
+        scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
+      }
       break;
   }
   if (tid == 0) {

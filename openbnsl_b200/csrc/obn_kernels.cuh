@@ -50,7 +50,8 @@ struct BatchArgs {
   const uint32_t* mem_off;  // [pools + 1], indexed by pool id (hdr.x)
   const uint2* members;
   uint32_t pool_cells;      // joint tables above this size are single tests: no pass buffers
-  int wide_prefetch;        // POOL kernels: scan_rows_wide for tuples of more than six columns
+  int wide_prefetch;        // POOL kernels, tuples of more than six columns: 1 scan_rows_wide, 2 scan_rows_tma
+  uint32_t stage_off;       // scan_rows_tma: byte offset of the tile ring in dynamic shared memory (128-aligned)
 };
 
 // ---------------------------------------------------------------------------

@@ -94,8 +94,9 @@ def test_pooled_pc_learns_the_same_graph(gpu_ctx):
 
 
 @pytest.mark.skipif(os.environ.get("OBN_TEST_CI_POOL_WIDE", "0") != "1",
-                    reason="opt-in (OBN_TEST_CI_POOL_WIDE=1): scan_rows_wide has never run on a device")
-@pytest.mark.parametrize("wide", [0, 1])
+                    reason="opt-in (OBN_TEST_CI_POOL_WIDE=1): scan_rows_wide / scan_rows_tma have never run on a device; "
+                           "run under `timeout`: a wrong mbarrier phase would spin")
+@pytest.mark.parametrize("wide", [0, 1, 2])          # scan_rows_any / scan_rows_wide / scan_rows_tma (TMA-staged tiles)
 @pytest.mark.parametrize("kind", [0, 1])
 def test_wide_pools_equal_default(gpu_ctx, kind, wide):
     net = nw.alarm()
