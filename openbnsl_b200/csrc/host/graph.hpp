@@ -51,6 +51,8 @@ class AdjMatGraph {
   bool has_undirected_edge(std::size_t u, std::size_t v) const {
     return has_directed_edge(u, v) && has_directed_edge(v, u);
   }
+  // the same without the range checks, for inner loops over ids that came out of this graph
+  bool has_undirected_edge_unchecked(std::size_t u, std::size_t v) const { return get(u, v) && get(v, u); }
   bool is_adjacent(std::size_t u, std::size_t v) const {
     return has_directed_edge(u, v) || has_directed_edge(v, u);
   }

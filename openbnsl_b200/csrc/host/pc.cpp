@@ -176,11 +176,26 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
     uint8_t dir = 0;
     bool valid = false, done = false, removed = false;
   };
-  std::vector<FastCursor> cursors;
-  std::vector<uint32_t> idx_arena;
-  std::vector<std::vector<uint32_t>> adj(n);
-  TupleBatch batch, spec;                     // spec: the next round, built while this one is evaluated
-  std::vector<uint32_t> pair_of_test, pair_of_spec, z, tmp;
+  // working storage kept per host thread: a run allocates nothing after the first one of its size
+  // (a C2 run is 0.8 ms in all; growing these vectors from empty was a measurable part of it)
+  struct Scratch {
+    std::vector<FastCursor> cursors;
+    std::vector<uint32_t> idx_arena, pair_of_test, pair_of_spec;
+    std::vector<std::vector<uint32_t>> adj;
+    TupleBatch batch, spec;
+  };
+  static thread_local Scratch W;
+  std::vector<FastCursor>& cursors = W.cursors;
+  std::vector<uint32_t>& idx_arena = W.idx_arena;
+  std::vector<std::vector<uint32_t>>& adj = W.adj;
+  adj.resize(n);
+  TupleBatch& batch = W.batch;                // spec: the next round, built while this one is evaluated
+  TupleBatch& spec = W.spec;
+  std::vector<uint32_t>& pair_of_test = W.pair_of_test;
+  std::vector<uint32_t>& pair_of_spec = W.pair_of_spec;
+  batch.clear();
+  spec.clear();
+  std::vector<uint32_t> z, tmp;
   std::vector<std::vector<uint32_t>> z_of_test;
   std::vector<int32_t> first;
   auto note_batch = [&](size_t k) {           // accounts `batch`
@@ -207,15 +222,17 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
       cursors.clear();
       for (size_t x = 0; x < n; ++x)
         for (size_t y = x + 1; y < n; ++y) {
-          if (!snap.has_undirected_edge(x, y)) continue;
+          if (!snap.has_undirected_edge_unchecked(x, y)) continue;
           FastCursor c;
           c.x = (uint32_t)x;
           c.y = (uint32_t)y;
           c.m[0] = (uint32_t)adj[x].size() - 1;
           c.m[1] = (uint32_t)adj[y].size() - 1;
-          c.skip[0] = (uint32_t)(std::lower_bound(adj[x].begin(), adj[x].end(), (uint32_t)y) - adj[x].begin());
-          c.skip[1] = (uint32_t)(std::lower_bound(adj[y].begin(), adj[y].end(), (uint32_t)x) - adj[y].begin());
           if (c.m[0] < k && c.m[1] < k) continue;
+          if (k) {                          // position of the partner in each list (nothing is indexed at depth 0)
+            c.skip[0] = (uint32_t)(std::lower_bound(adj[x].begin(), adj[x].end(), (uint32_t)y) - adj[x].begin());
+            c.skip[1] = (uint32_t)(std::lower_bound(adj[y].begin(), adj[y].end(), (uint32_t)x) - adj[y].begin());
+          }
           cursors.push_back(c);
         }
       idx_arena.assign(cursors.size() * std::max<size_t>(k, 1), 0);
@@ -247,7 +264,7 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
           }
           if (c.dir == 1 && c.m[0] >= k) {
             bool dup = true;
-            for (size_t i = 0; i < k && dup; ++i) dup = snap.has_undirected_edge(c.x, item(c, 1, idx[i]));
+            for (size_t i = 0; i < k && dup; ++i) dup = snap.has_undirected_edge_unchecked(c.x, item(c, 1, idx[i]));
             if (dup) { next_comb(c, idx); continue; }
           }
           return;
@@ -273,14 +290,19 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
           uint32_t* idx = idx_arena.data() + pi * std::max<size_t>(k, 1);
           for (size_t q = 0; q < quota && !c.done; ++q) {
             // tuple = sort(Z + {x,y}) (pc.cpp:34-37): Z is ascending already, merge x < y into it
+            const uint32_t* a = adj[c.dir ? c.y : c.x].data();
+            const uint32_t skip = c.skip[c.dir];
+            const size_t at = out.var_ids.size();
+            out.var_ids.resize(at + k + 2);
+            uint32_t* w = out.var_ids.data() + at;
             uint32_t pend[2] = {c.x, c.y};
             int np = 0;
             for (size_t i = 0; i < k; ++i) {
-              const uint32_t z = item(c, c.dir, idx[i]);
-              while (np < 2 && pend[np] < z) out.var_ids.push_back(pend[np++]);
-              out.var_ids.push_back(z);
+              const uint32_t z = a[idx[i] + (idx[i] >= skip ? 1u : 0u)];
+              while (np < 2 && pend[np] < z) *w++ = pend[np++];
+              *w++ = z;
             }
-            while (np < 2) out.var_ids.push_back(pend[np++]);
+            while (np < 2) *w++ = pend[np++];
             out.offsets.push_back(out.var_ids.size());
             out.x.push_back(c.dir ? c.y : c.x);
             out.y.push_back(c.dir ? c.x : c.y);
