@@ -218,3 +218,16 @@ def test_pc_oracle_graph_shd_zero_like_the_reference_test(netf, stable):
         assert (full == _brute_force_cpdag(t)).all()
     else:
         assert (full != a).any()                   # Alarm's pattern has edges only the propagation orients
+
+
+def test_exhaustive_search_shd_zero_like_the_reference_test():
+    # pytest/structure_learning/test_exhaustive_search.py:22-30: 1e5 samples, max_parents = 3, judged by
+    # structural_errors against the true graph (here: the Asia structure; the driver runs over the checker seam)
+    import oracle as orc
+    from helpers import OracleEvaluator, ranked
+    net = nw.asia()
+    codes, cards = ranked(net.sample(100000, 0))
+    ods = orc.Dataset(codes, cards)
+    got = L._testing.exhaustive_search(net.n, OracleEvaluator(ods), L.score.BDeu(1.0), 3)
+    err = sd.structural_errors(truth_of(net), got)
+    assert err["SHD"] == 0, err
