@@ -160,3 +160,20 @@ def test_submit_collect_and_overlapped_pc(gpu_ctx):
             os.environ.pop("OBN_PC_OVERLAP", None)
         adj.append(np.array([[g.has_edge(a, b) for b in range(net.n)] for a in range(net.n)]))
     assert (adj[0] == adj[1]).all()
+
+
+@pytest.mark.skipif(os.environ.get("OBN_TEST_CI_ZERO_COPY", "0") != "1",
+                    reason="opt-in (OBN_TEST_CI_ZERO_COPY=1): results written straight to pinned host memory, never run")
+def test_zero_copy_results_equal_default(gpu_ctx):
+    net = nw.alarm()
+    codes, cards = ranked(net.sample(20011, 4))
+    ds = gpu_ctx.upload(codes, cards)
+    rng = np.random.default_rng(8)
+    xs, ys, zs = frontier(rng, net.n, 60, 2, 5)
+    with pooled(False):
+        want = ds.ci_tests(xs, ys, zs, 1)
+        with pooled(False, None, OBN_CI_ZERO_COPY=1):
+            got = ds.ci_tests(xs, ys, zs, 1)
+    for a, b in zip(want, got):
+        assert np.array_equal(a, b)
+    ds.close()
