@@ -24,6 +24,7 @@ from openbnsl_b200 import networks as nw  # noqa: E402
 L = openbnsl_b200.openbnsllib
 COMM = None          # set in main() when launched under torchrun (one rank per GPU)
 RANK = 0
+PC_KW = {}           # extra keyword arguments of pc() from the command line (tb=<target_batch>, overlap=0/1, shard=<bytes>)
 
 
 def peak():
@@ -51,7 +52,7 @@ def frame(net, n_rows, seed):
 def report(name, what, units, unit_name, secs, prof, extra=None):
     k_s = prof["count_kernel_ms"] * 1e-3
     gbs = prof["algorithmic_bytes"] / k_s / 1e9 if k_s > 0 else 0.0
-    line = {"config": name, "what": what, "learn_time_s": secs, unit_name: units, unit_name + "_per_s": units / secs,
+    line = {"config": name, "what": what, "learn_time_s": secs, "learn_ms": secs * 1e3, unit_name: units, unit_name + "_per_s": units / secs,
             "kernel_ms": prof["count_kernel_ms"], "algorithmic_GB": prof["algorithmic_bytes"] / 1e9,
             "kernel_algorithmic_GBps": gbs, "hbm_peak_GBps": peak(), "roofline_frac": gbs / peak(),
             "launches": int(prof["count_launches"]), "host_prep_ms": prof["host_prep_ms"],
@@ -68,21 +69,29 @@ def run_pc(name, net, n_rows, test, depth, what, reps=1):
     df, cards, t_gen = frame(net, n_rows, 0)
     L.profile_enable(True)
     df.to_device()
-    L.structure_learning.pc(df, test, min(depth, 1), True, comm=COMM)   # warm-up (allocations, first launches, NCCL)
+    L.structure_learning.pc(df, test, depth, True, comm=COMM, **PC_KW)   # warm-up (allocations, first launches, NCCL)
     L.profile_read(True)
+    if COMM is not None:
+        import torch.distributed as dist
+        dist.barrier()
     t0 = time.perf_counter()
     for _ in range(reps):
-        g = L.structure_learning.pc(df, test, depth, True, comm=COMM)
+        g = L.structure_learning.pc(df, test, depth, True, comm=COMM, **PC_KW)
     secs = (time.perf_counter() - t0) / reps
     prof = L.profile_read(True)
-    for key in ("count_kernel_ms", "algorithmic_bytes", "host_prep_ms", "host_wait_ms", "count_launches"):
+    for key in ("count_kernel_ms", "algorithmic_bytes", "host_prep_ms", "host_wait_ms", "count_launches", "scanned_bytes",
+                "increments", "tables", "collectives"):
         prof[key] = prof[key] / reps
     st = L.structure_learning.last_pc_stats()
     n_edges = sum(1 for v in range(net.n) for p in range(net.n) if g.has_edge(p, v))
     report(name, what, st["total_tests"], "ci_tests", secs, prof,
            {"tests_per_depth": [int(x) for x in st["tests_per_depth"]], "n_vars": net.n, "n_rows": n_rows,
             "max_card": int(max(cards)), "pdag_arcs": n_edges, "enumerate_ms": st["enumerate_ms"],
-            "evaluate_ms": st["evaluate_ms"], "data_gen_s": t_gen})
+            "evaluate_ms": st["evaluate_ms"], "resolve_ms": st["resolve_ms"], "data_gen_s": t_gen,
+            "batches_per_depth": [int(x) for x in st["batches_per_depth"]], "tables": prof["tables"],
+            "scanned_GB": prof["scanned_bytes"] / 1e9, "atoms_ceiling_ms": prof["increments"] / 4.65e12 * 1e3,
+            "collectives": prof["collectives"], "pc_kwargs": dict(PC_KW),
+            "adj_sha": int(sum((i + 1) * (j + 7) for i in range(net.n) for j in range(net.n) if g.has_edge(i, j)))})
 
 
 def run_es(name, net, n_rows, max_parents, what, exact=2):
@@ -144,14 +153,22 @@ def main():
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
         import torch
         import torch.distributed as dist
-        from openbnsl_b200.dist import TorchComm
+        from openbnsl_b200.dist import TorchComm, init_native_comm
         local = int(os.environ["LOCAL_RANK"])
         os.environ["OBN_DEVICE"] = str(local)
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        COMM = TorchComm()
+        COMM = TorchComm() if "hostcomm" in sys.argv else init_native_comm(L)
         RANK = COMM.rank
-    which = [a.lower() for a in sys.argv[1:]] or ["c1", "c2", "c3", "c4", "c5"]
+    args = [a.lower() for a in sys.argv[1:] if a != "hostcomm"]
+    for a in list(args):
+        if a.startswith("tb="):
+            PC_KW["target_batch"] = int(a[3:]); args.remove(a)
+        elif a.startswith("overlap="):
+            PC_KW["overlap"] = bool(int(a[8:])); args.remove(a)
+        elif a.startswith("shard="):
+            PC_KW["shard_min_bytes"] = float(a[6:]); args.remove(a)
+    which = args or ["c1", "c2", "c3", "c4", "c5"]
     if "sa" in which:
         run_sa("SA", nw.alarm(), 100_000, 3, 2000, 64,
                "simulated annealing BDeu, Alarm structure, 37 vars, 100k rows, 64 chains x 2000 steps, max_parents=3")
@@ -173,10 +190,10 @@ def main():
                    "exhaustive search BDeu, 24 binary vars, 1M rows, max_parents=%d%s" % (mp, " exact-order" if ex else ""), exact=ex)
     if "c4" in which:
         run_pc("C4", nw.hepar2_like(), 1_000_000, L.citest.GSquare(0.05), 4,
-               "PC-stable G2, Hepar2-like, 70 vars, 1M rows, depth<=4")
+               "PC-stable G2, Hepar2-like, 70 vars, 1M rows, depth<=4", reps=5)
     if "c5" in which:
         run_pc("C5", nw.munin1_like(), 1_000_000, L.citest.ChiSquare(0.05), 3,
-               "PC-stable chi2, Munin1-like, 186 vars, cards<=21, 1M rows, depth<=3")
+               "PC-stable chi2, Munin1-like, 186 vars, cards<=21, 1M rows, depth<=3", reps=5)
 
 
 if __name__ == "__main__":

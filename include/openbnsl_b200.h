@@ -18,9 +18,13 @@
  *  - All pointer arguments are HOST pointers unless the name ends in `_dev`.
  *    The library copies; it never keeps a host pointer after returning.
  *  - Calls are synchronous: outputs are valid on return.
- *  - A ctx is bound to ONE CUDA device (one process per GPU is the intended
- *    deployment; multi-GPU sharding happens above this boundary) and must be
- *    used by one host thread at a time.
+ *  - A ctx is bound to ONE CUDA device (one process per GPU) and must be used
+ *    by one host thread at a time.  A multi-GPU job gives every rank's ctx a
+ *    communicator (obn_comm_init, NCCL); the sharded calls (obn_pc_round with
+ *    shard != 0, obn_comm_allgather_inplace) are then COLLECTIVE: every rank
+ *    makes the same call with the same batch.
+ *  - The library reads no environment variables; tuning goes through
+ *    obn_ctx_set_option.
  *  - There is no CPU fallback.  Without a usable CUDA device obn_ctx_create
  *    fails with OBN_ERR_CUDA and nothing else can be called.
  */
@@ -46,7 +50,8 @@ enum {
   OBN_ERR_CUDA = 2,        /* CUDA runtime error / no device               */
   OBN_ERR_OOM = 3,         /* device or host allocation failed             */
   OBN_ERR_UNSUPPORTED = 4, /* e.g. a dense table with more than 2^31 cells */
-  OBN_ERR_RANGE = 5        /* index out of range (maps to std::out_of_range) */
+  OBN_ERR_RANGE = 5,       /* index out of range (maps to std::out_of_range) */
+  OBN_ERR_COMM = 6         /* NCCL error / no communicator                 */
 };
 
 enum { OBN_CI_CHI2 = 0, OBN_CI_G2 = 1 };
@@ -62,6 +67,33 @@ OBN_API int obn_ctx_create(int device, obn_ctx** out);
 OBN_API void obn_ctx_destroy(obn_ctx* ctx);
 /* The CUDA stream (cudaStream_t) all work of this ctx is issued on. */
 OBN_API void* obn_ctx_stream(obn_ctx* ctx);
+/* Tuning knobs for A/B runs and tests (defaults are what the published numbers use):
+ *   "threads_per_sm" (768), "force_threads" (0), "force_splits" (0), "streams" (4)   counting-kernel launch policy
+ *   "lattice_budget_gb" (24), "lattice_max_l" (20), "lattice_bottom" (1), "lattice_reorder" (1),
+ *   "lattice_graph" (1), "lattice_lanes" (2), "lattice_no_lut" (0), "debug" (0)      marginalisation lattice
+ * Unknown names fail with OBN_ERR_INVALID. */
+OBN_API int obn_ctx_set_option(obn_ctx* ctx, const char* name, double value);
+
+/* ---- communicator (multi-GPU jobs, one process per GPU) --------------------
+ * NCCL over NVLink, owned by the ctx, bound at run time (a process that already
+ * holds libnccl.so.2 shares it).  Rank 0 calls obn_comm_unique_id and hands the
+ * OBN_COMM_ID_BYTES bytes to every rank by any host-side means; every rank then
+ * calls obn_comm_init (collective).  The exchanges of the path run on device
+ * buffers of the library: all-reduce(min) of the first passing candidate per
+ * edge inside obn_pc_round, in-place all-gathers of the exhaustive-search
+ * buffers through obn_comm_allgather_inplace. */
+#define OBN_COMM_ID_BYTES 128
+OBN_API int obn_comm_unique_id(uint8_t* id_out);
+OBN_API int obn_comm_init(obn_ctx* ctx, const uint8_t* id_bytes, int rank, int world);
+OBN_API void obn_comm_destroy(obn_ctx* ctx);
+OBN_API int obn_comm_rank(const obn_ctx* ctx);
+OBN_API int obn_comm_world(const obn_ctx* ctx);
+/* dev: DEVICE buffer of world * bytes_per_rank bytes, rank r contributes slice r; synchronous. */
+OBN_API int obn_comm_allgather_inplace(obn_ctx* ctx, void* dev, size_t bytes_per_rank);
+/* All-gather of small HOST payloads (recv: world * bytes_per_rank bytes, rank order), staged through the device. */
+OBN_API int obn_comm_allgather_host(obn_ctx* ctx, const void* send, void* recv, size_t bytes_per_rank);
+/* In-place elementwise MIN over ranks of a HOST int32 array (staged through the device). */
+OBN_API int obn_comm_allreduce_min_i32(obn_ctx* ctx, int32_t* host, size_t count);
 
 /* ---- dataset: replaces DataframeWrapper's two vector<vector<uint8_t>>
  * (include/base/dataframe_wrapper.h:42-45) by ONE padded column-major uint8
@@ -115,21 +147,36 @@ OBN_API int obn_bdeu_subset_scores(obn_ctx* ctx, const obn_dataset* ds,
  * tuple t must contain x[t] and y[t]; all its other variables condition.
  * Outputs the statistic, the degrees of freedom and p = pchisq(stat, dof)
  * (citest.h:17-21); the decision p >= level stays with the caller.  Any of
- * the three output pointers may be NULL.  With OBN_CI_POOL=1 (or 2: from
- * OBN_CI_POOL_MIN_ROWS rows up) the tests of one (x, y) pair share one joint
- * table on the device (see obn_ci_pool_plan below); the results are the same
- * tables' statistics either way. */
+ * the three output pointers may be NULL.
+ * Tests of one batch that are asked over the SAME variable set share one
+ * table on the device (the reference's table does not depend on which two of
+ * its variables are tested, citest.h:63-70; a PC frontier asks every set
+ * |Z|+1 times or more): it is counted once and read once per test. */
 OBN_API int obn_ci_tests(obn_ctx* ctx, const obn_dataset* ds,
                          const uint32_t* var_ids, const uint64_t* offsets,
                          size_t n_tuples, const uint32_t* x, const uint32_t* y,
                          int kind, double* stat_out, uint64_t* dof_out,
                          double* p_out);
 
-/* obn_ci_tests in two halves, so that the caller's host thread can prepare its next batch while
- * the device works on this one (the PC driver enumerates round r+1 during round r).  submit
- * validates, packs, uploads and enqueues everything and returns; the input arrays may be reused
- * as soon as it has returned.  collect waits for the results and writes them (any pointer may be
- * NULL; p_out only if want_p was set).  At most one batch is in flight per ctx: until it is
+/* One round of the PC skeleton search (src/structure_learning/pc.cpp:27-47):
+ * the batch holds candidate tests of n_slots edges, test t belonging to edge
+ * slot_of_test[t], in the reference's enumeration order within every edge.
+ * The decision p >= level (citest.h:147) is taken on the device and
+ * first_out[s] = smallest t of edge s that passed -- the candidate the serial
+ * reference stops at -- or INT32_MAX when none did.  Only that array leaves
+ * the device.  shard != 0 and a communicator on the ctx: COLLECTIVE -- every
+ * rank passes the same batch, evaluates its share of the tables and the
+ * per-edge minima are merged by ncclAllReduce(min) on the device buffer. */
+OBN_API int obn_pc_round(obn_ctx* ctx, const obn_dataset* ds,
+                         const uint32_t* var_ids, const uint64_t* offsets, size_t n_tests,
+                         const uint32_t* x, const uint32_t* y, const uint32_t* slot_of_test,
+                         size_t n_slots, int kind, double level, int shard, int32_t* first_out);
+
+/* obn_ci_tests / obn_pc_round in two halves, so that the caller's host thread can prepare its next
+ * batch while the device works on this one (the PC driver enumerates round r+1 during round r).
+ * submit validates, packs, uploads and enqueues everything and returns; the input arrays may be
+ * reused as soon as it has returned.  collect waits for the results and writes them (any pointer
+ * may be NULL; p_out only if want_p was set).  At most one batch is in flight per ctx: until it is
  * collected every other batch call on the ctx returns OBN_ERR_INVALID.  collect without a
  * submitted batch (or after submitting zero tuples) is a no-op. */
 OBN_API int obn_ci_tests_submit(obn_ctx* ctx, const obn_dataset* ds,
@@ -137,26 +184,20 @@ OBN_API int obn_ci_tests_submit(obn_ctx* ctx, const obn_dataset* ds,
                                 size_t n_tuples, const uint32_t* x, const uint32_t* y,
                                 int kind, int want_p);
 OBN_API int obn_ci_tests_collect(obn_ctx* ctx, double* stat_out, uint64_t* dof_out, double* p_out);
+OBN_API int obn_pc_round_submit(obn_ctx* ctx, const obn_dataset* ds,
+                                const uint32_t* var_ids, const uint64_t* offsets, size_t n_tests,
+                                const uint32_t* x, const uint32_t* y, const uint32_t* slot_of_test,
+                                size_t n_slots, int kind, double level, int shard);
+OBN_API int obn_pc_round_collect(obn_ctx* ctx, int32_t* first_out);
 
-/* Diagnostics of the CI-test pooling inside obn_ci_tests (host only, need no device; DESIGN.md
- * 3.5).  Tests of one (x, y) pair whose conditioning sets come from one neighbourhood -- the shape
- * of the PC frontier, src/structure_learning/pc.cpp:27-47 -- share ONE joint table over (union of
- * the conditioning sets, x, y); each test's own table is summed out of it on the device.
- * obn_ci_pool_plan returns the plan for a batch given as for obn_ci_tests (joint tables of at most
- * max_cells cells over at most max_z conditioning variables): the pools in CSR form
- * (pool_var_ids needs room for offsets[n_tests] ids, pool_offsets for n_tests + 1), the pool of
- * every test and its keep mask (bit i = i-th conditioning variable of the pool, ascending ids;
- * 0xffffffff = the test is passed through as it is).  Any output pointer but n_pools may be NULL.
- * obn_ci_pool_marginalise runs the kernel's marginalisation passes on the host: `joint` is a
- * dense table in kernel digit order (n_z conditioning digits, most significant first, then x, y;
- * cards_kernel_order[0 .. n_z) their cardinalities), `keep` a mask as above; `out` needs room for
- * `cells` ints. */
-OBN_API int obn_ci_pool_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids,
-                             const uint64_t* offsets, size_t n_tests, const uint32_t* x, const uint32_t* y,
-                             uint32_t max_cells, uint32_t max_z, uint32_t* pool_var_ids, uint64_t* pool_offsets,
-                             uint32_t* pool_of_test, uint32_t* keep_of_test, size_t* n_pools);
-OBN_API int obn_ci_pool_marginalise(const int32_t* joint, uint32_t cells, const uint32_t* cards_kernel_order,
-                                    int n_z, uint32_t keep, int32_t* out, uint32_t* out_cells);
+/* Diagnostics (host only, needs no device): the table sharing obn_ci_tests / obn_pc_round use.
+ * Groups in CSR form (group_var_ids needs room for offsets[n_tests] ids, group_offsets for
+ * n_tests + 1), the group of every test and its digits (px | py << 8: positions of x < y in the
+ * group's ascending variable list).  Any output pointer but n_groups may be NULL. */
+OBN_API int obn_ci_group_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids,
+                              const uint64_t* offsets, size_t n_tests, const uint32_t* x, const uint32_t* y,
+                              uint32_t* group_var_ids, uint64_t* group_offsets, uint32_t* group_of_test,
+                              uint32_t* digits_of_test, size_t* n_groups);
 
 /* ---- exhaustive search on the device --------------------------------------
  * Level-synchronous Silander-Myllymaki DP with the reference's tie-breaking
@@ -225,12 +266,18 @@ typedef struct obn_profile {
   double count_kernel_ms;    /* sum of counting-kernel durations            */
   uint64_t count_launches;   /* number of counting-kernel launches          */
   uint64_t total_launches;   /* all kernels launched by this ctx            */
-  double algorithmic_bytes;  /* sum over tuples of k * n_rows               */
-  uint64_t tuples;           /* tuples evaluated                            */
+  double algorithmic_bytes;  /* sum over tuples (CI: tests) of k * n_rows   */
+  uint64_t tuples;           /* tuples (CI: tests) evaluated by this ctx    */
   double h2d_bytes;          /* bytes copied host -> device (batches + datasets) */
   double d2h_bytes;          /* bytes copied device -> host (results)       */
   double host_prep_ms;       /* host: validate + classify + pack the batch  */
   double host_wait_ms;       /* host: enqueue copies/launches + wait for the stream */
+  double scanned_bytes;      /* sum over TABLES of k * n_rows: what the kernels read (tests sharing a table count once) */
+  double increments;         /* sum over tables of n_rows: shared-memory / L2 increments applied */
+  uint64_t tables;           /* contingency tables counted                  */
+  uint64_t collectives;      /* NCCL collectives issued                     */
+  double collective_ms;      /* host wall time of the synchronous collectives (all-gathers) */
+  uint64_t exact_fallbacks;  /* exact_order == 2 batches that fell back to fast mode (lgamma tables over the cap) */
 } obn_profile;
 OBN_API int obn_profile_enable(obn_ctx* ctx, int on);
 OBN_API int obn_profile_read(obn_ctx* ctx, obn_profile* out, int reset);

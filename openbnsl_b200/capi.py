@@ -17,14 +17,18 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libopenbnsl_b200.so")
 
-OBN_OK, OBN_ERR_INVALID, OBN_ERR_CUDA, OBN_ERR_OOM, OBN_ERR_UNSUPPORTED, OBN_ERR_RANGE = range(6)
+OBN_OK, OBN_ERR_INVALID, OBN_ERR_CUDA, OBN_ERR_OOM, OBN_ERR_UNSUPPORTED, OBN_ERR_RANGE, OBN_ERR_COMM = range(7)
+COMM_ID_BYTES = 128
 CI_CHI2, CI_G2 = 0, 1
 
 EXPORTS = [
-    "obn_last_error", "obn_version", "obn_ctx_create", "obn_ctx_destroy", "obn_ctx_stream",
+    "obn_last_error", "obn_version", "obn_ctx_create", "obn_ctx_destroy", "obn_ctx_stream", "obn_ctx_set_option",
+    "obn_comm_unique_id", "obn_comm_init", "obn_comm_destroy", "obn_comm_rank", "obn_comm_world",
+    "obn_comm_allgather_inplace", "obn_comm_allgather_host", "obn_comm_allreduce_min_i32",
     "obn_dataset_upload", "obn_dataset_destroy", "obn_host_pin", "obn_host_unpin", "obn_dataset_n_vars", "obn_dataset_n_rows",
     "obn_count_tables", "obn_bdeu_scores", "obn_bdeu_subset_scores", "obn_ci_tests",
-    "obn_ci_tests_submit", "obn_ci_tests_collect", "obn_ci_pool_plan", "obn_ci_pool_marginalise",
+    "obn_ci_tests_submit", "obn_ci_tests_collect", "obn_pc_round", "obn_pc_round_submit", "obn_pc_round_collect",
+    "obn_ci_group_plan",
     "obn_es_begin", "obn_es_level_begin", "obn_es_level_scores", "obn_es_level_buffer", "obn_es_level_dp", "obn_es_level_dp_part", "obn_es_level_dp_commit", "obn_lattice_bottom_program",
     "obn_es_lattice", "obn_es_f_buffer", "obn_es_finish", "obn_es_end",
     "obn_profile_enable", "obn_profile_read",
@@ -35,7 +39,9 @@ class Profile(C.Structure):
     _fields_ = [("count_kernel_ms", C.c_double), ("count_launches", C.c_uint64),
                 ("total_launches", C.c_uint64), ("algorithmic_bytes", C.c_double),
                 ("tuples", C.c_uint64), ("h2d_bytes", C.c_double), ("d2h_bytes", C.c_double),
-                ("host_prep_ms", C.c_double), ("host_wait_ms", C.c_double)]
+                ("host_prep_ms", C.c_double), ("host_wait_ms", C.c_double),
+                ("scanned_bytes", C.c_double), ("increments", C.c_double), ("tables", C.c_uint64),
+                ("collectives", C.c_uint64), ("collective_ms", C.c_double), ("exact_fallbacks", C.c_uint64)]
 
 
 _lib = None
@@ -74,9 +80,23 @@ def load():
     L.obn_ci_tests.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, f64p, u64p, f64p]
     L.obn_ci_tests_submit.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, C.c_int]
     L.obn_ci_tests_collect.argtypes = [vp, f64p, u64p, f64p]
-    L.obn_ci_pool_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, C.c_uint32, C.c_uint32,
-                                   u32p, u64p, u32p, u32p, C.POINTER(C.c_size_t)]
-    L.obn_ci_pool_marginalise.argtypes = [i32p, C.c_uint32, u32p, C.c_int, C.c_uint32, i32p, u32p]
+    L.obn_pc_round.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, u32p, C.c_size_t, C.c_int, C.c_double,
+                               C.c_int, i32p]
+    L.obn_pc_round_submit.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, u32p, C.c_size_t, C.c_int,
+                                      C.c_double, C.c_int]
+    L.obn_pc_round_collect.argtypes = [vp, i32p]
+    L.obn_ci_group_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, u32p, u64p, u32p, u32p,
+                                    C.POINTER(C.c_size_t)]
+    L.obn_ctx_set_option.argtypes = [vp, C.c_char_p, C.c_double]
+    L.obn_comm_unique_id.argtypes = [u8p]
+    L.obn_comm_init.argtypes = [vp, u8p, C.c_int, C.c_int]
+    L.obn_comm_destroy.argtypes = [vp]
+    L.obn_comm_destroy.restype = None
+    L.obn_comm_rank.argtypes = [vp]
+    L.obn_comm_world.argtypes = [vp]
+    L.obn_comm_allgather_inplace.argtypes = [vp, vp, C.c_size_t]
+    L.obn_comm_allgather_host.argtypes = [vp, vp, vp, C.c_size_t]
+    L.obn_comm_allreduce_min_i32.argtypes = [vp, i32p, C.c_size_t]
     L.obn_profile_enable.argtypes = [vp, C.c_int]
     L.obn_profile_read.argtypes = [vp, C.POINTER(Profile), C.c_int]
     _lib = L
@@ -109,35 +129,30 @@ def _csr(tuples):
     return flat, offs
 
 
-def ci_pool_plan(cards, tuples, x, y, max_cells=4096, max_z=30):
-    """The pooling plan obn_ci_tests would use (host only).  Returns (pools, pool_of_test, keep_of_test):
-    pools = list of ascending variable lists (x and y included)."""
+def ci_group_plan(cards, tuples, x, y):
+    """The table sharing obn_ci_tests / obn_pc_round use (host only).  Returns (groups, group_of_test,
+    digits_of_test): groups = list of ascending variable lists, digits = (px, py) positions of x < y."""
     flat, offs = _csr(tuples)
     cards = np.ascontiguousarray(np.asarray(cards, dtype=np.uint32))
     xa = np.ascontiguousarray(np.asarray(x, dtype=np.uint32))
     ya = np.ascontiguousarray(np.asarray(y, dtype=np.uint32))
     n = len(tuples)
-    pv = np.zeros(max(1, len(flat)), dtype=np.uint32)
-    po = np.zeros(n + 1, dtype=np.uint64)
-    pool_of, keep = np.zeros(max(1, n), dtype=np.uint32), np.zeros(max(1, n), dtype=np.uint32)
-    n_pools = C.c_size_t(0)
-    _check(load().obn_ci_pool_plan(_ptr(cards, C.c_uint32), len(cards), _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64),
-                                   n, _ptr(xa, C.c_uint32), _ptr(ya, C.c_uint32), int(max_cells), int(max_z),
-                                   _ptr(pv, C.c_uint32), _ptr(po, C.c_uint64), _ptr(pool_of, C.c_uint32),
-                                   _ptr(keep, C.c_uint32), C.byref(n_pools)))
-    pools = [pv[int(po[q]):int(po[q + 1])].tolist() for q in range(n_pools.value)]
-    return pools, pool_of[:n], keep[:n]
+    gv = np.zeros(max(1, len(flat)), dtype=np.uint32)
+    go = np.zeros(n + 1, dtype=np.uint64)
+    group_of, digits = np.zeros(max(1, n), dtype=np.uint32), np.zeros(max(1, n), dtype=np.uint32)
+    n_groups = C.c_size_t(0)
+    _check(load().obn_ci_group_plan(_ptr(cards, C.c_uint32), len(cards), _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64),
+                                    n, _ptr(xa, C.c_uint32), _ptr(ya, C.c_uint32), _ptr(gv, C.c_uint32),
+                                    _ptr(go, C.c_uint64), _ptr(group_of, C.c_uint32), _ptr(digits, C.c_uint32),
+                                    C.byref(n_groups)))
+    groups = [gv[int(go[q]):int(go[q + 1])].tolist() for q in range(n_groups.value)]
+    return groups, group_of[:n], [(int(d) & 0xff, (int(d) >> 8) & 0xff) for d in digits[:n]]
 
 
-def ci_pool_marginalise(joint, cards_kernel_order, keep):
-    """The kernel's marginalisation passes, run on the host over a dense joint table in kernel digit order."""
-    joint = np.ascontiguousarray(np.asarray(joint, dtype=np.int32))
-    cards = np.ascontiguousarray(np.asarray(cards_kernel_order, dtype=np.uint32))
-    out = np.zeros(max(1, joint.size), dtype=np.int32)
-    oc = C.c_uint32(0)
-    _check(load().obn_ci_pool_marginalise(_ptr(joint, C.c_int32), joint.size, _ptr(cards, C.c_uint32), len(cards),
-                                          int(keep) & 0xffffffff, _ptr(out, C.c_int32), C.byref(oc)))
-    return out[:oc.value].copy()
+def comm_unique_id() -> bytes:
+    buf = np.zeros(COMM_ID_BYTES, dtype=np.uint8)
+    _check(load().obn_comm_unique_id(_ptr(buf, C.c_uint8)))
+    return buf.tobytes()
 
 
 class Context:
@@ -162,6 +177,13 @@ class Context:
 
     def upload(self, codes_rows_by_vars: np.ndarray, cards) -> "Dataset":
         return Dataset(self, codes_rows_by_vars, cards)
+
+    def set_option(self, name: str, value: float):
+        _check(load().obn_ctx_set_option(self._h, name.encode(), float(value)))
+
+    def comm_init(self, id_bytes: bytes, rank: int, world: int):
+        buf = np.frombuffer(id_bytes, dtype=np.uint8).copy()
+        _check(load().obn_comm_init(self._h, _ptr(buf, C.c_uint8), int(rank), int(world)))
 
     def profile_enable(self, on=True):
         _check(load().obn_profile_enable(self._h, int(on)))
@@ -235,6 +257,22 @@ class Dataset:
                                    _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), int(kind),
                                    _ptr(stat, C.c_double), _ptr(dof, C.c_uint64), _ptr(p, C.c_double)))
         return stat, dof, p
+
+    def pc_round(self, flat, offs, x, y, slot_of_test, n_slots, kind, level, shard=False, split=False):
+        """obn_pc_round (or its submit / collect halves): first passing test index per edge slot."""
+        n = len(offs) - 1
+        slot = np.ascontiguousarray(np.asarray(slot_of_test, dtype=np.uint32))
+        first = np.zeros(max(1, n_slots), dtype=np.int32)
+        if split:
+            _check(load().obn_pc_round_submit(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), n,
+                                              _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), _ptr(slot, C.c_uint32),
+                                              int(n_slots), int(kind), float(level), int(shard)))
+            _check(load().obn_pc_round_collect(self.ctx._h, _ptr(first, C.c_int32)))
+        else:
+            _check(load().obn_pc_round(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), n,
+                                       _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), _ptr(slot, C.c_uint32), int(n_slots),
+                                       int(kind), float(level), int(shard), _ptr(first, C.c_int32)))
+        return first[:n_slots]
 
     def ci_tests_submit_collect(self, flat, offs, x, y, kind, between=None):
         """The same batch through obn_ci_tests_submit / obn_ci_tests_collect; `between` runs while it is in flight."""

@@ -28,9 +28,12 @@ py::array_t<T> view(const T* p, size_t n) {   // zero-copy numpy view over C++ m
 }
 
 // Python object with .rank, .world, .allreduce_min_i32(arr), .allgather(send, recv)
+struct NcclCommTag {};   // Python-side marker: "use the communicator the library owns" (openbnsllib.nccl_comm())
+
 Comm make_comm(const py::object& o) {
   Comm c;
   if (o.is_none()) return c;
+  if (py::isinstance<NcclCommTag>(o)) return native_comm();
   c.rank = o.attr("rank").cast<int>();
   c.world = o.attr("world").cast<int>();
   if (c.world < 1 || c.rank < 0 || c.rank >= c.world) throw std::invalid_argument("bad comm rank/world");
@@ -97,7 +100,8 @@ struct PyEvaluator : Evaluator {
 };
 
 PDAG run_pc(size_t n_vars, Evaluator* ev, const CITestType& test, size_t max_cond_vars, bool stable,
-            const py::object& comm, size_t target_batch, bool record = false, size_t shard_min_slots = 0) {
+            const py::object& comm, size_t target_batch, bool record = false, size_t shard_min_slots = 0,
+            bool overlap = false) {
   g_last_pc_stats.record = record;
   if (std::holds_alternative<OracleGraph>(test))
     return pc_oracle(n_vars, std::get<OracleGraph>(test).graph, max_cond_vars, stable);
@@ -113,8 +117,7 @@ PDAG run_pc(size_t n_vars, Evaluator* ev, const CITestType& test, size_t max_con
   }
   if (target_batch) o.target_batch = target_batch;
   o.shard_min_slots = shard_min_slots;
-  // OBN_PC_OVERLAP=1: written at the end of round 1 without a GPU to time it on; off by default
-  if (const char* e = std::getenv("OBN_PC_OVERLAP")) o.overlap = std::atoi(e) != 0;
+  o.overlap = overlap;
   const Comm c = make_comm(comm);
   return pc_skeleton_and_colliders(n_vars, *ev, c, o, &g_last_pc_stats);
 }
@@ -159,6 +162,27 @@ PYBIND11_MODULE(openbnsllib, m) {
   m.def("stream_handle", []() { return (uintptr_t)obn_ctx_stream(Engine::instance().ctx()); },
         "cudaStream_t of the library's main stream (for CUDA-event timing from Python, e.g. torch.cuda.ExternalStream)");
 
+  // ---- the library's own communicator (NCCL below the C boundary) ----
+  m.def("comm_unique_id", []() {
+    uint8_t id[OBN_COMM_ID_BYTES];
+    check(obn_comm_unique_id(id));
+    return py::bytes(reinterpret_cast<const char*>(id), sizeof(id));
+  }, "rank 0: the id every rank passes to comm_init (hand it over by any host-side means)");
+  m.def("comm_init", [](const py::bytes& id, int rank, int world) {
+    const std::string s = id;
+    if (s.size() != OBN_COMM_ID_BYTES) throw std::invalid_argument("id must be OBN_COMM_ID_BYTES bytes");
+    py::gil_scoped_release nogil;
+    check(obn_comm_init(Engine::instance().ctx(), reinterpret_cast<const uint8_t*>(s.data()), rank, world));
+  }, py::arg("id"), py::arg("rank"), py::arg("world"), "collective: create the NCCL communicator of this process's ctx");
+  m.def("comm_destroy", []() { obn_comm_destroy(Engine::instance().ctx()); });
+  py::class_<NcclCommTag>(m, "NcclComm", "comm= argument selecting the library's own NCCL communicator")
+      .def_property_readonly("rank", [](const NcclCommTag&) { return obn_comm_rank(Engine::instance().ctx()); })
+      .def_property_readonly("world", [](const NcclCommTag&) { return obn_comm_world(Engine::instance().ctx()); });
+  m.def("nccl_comm", []() { return NcclCommTag{}; });
+  m.def("set_option", [](const std::string& name, double value) {
+    check(obn_ctx_set_option(Engine::instance().ctx(), name.c_str(), value));
+  }, py::arg("name"), py::arg("value"), "obn_ctx_set_option on this process's ctx");
+
   m.def("profile_enable", [](bool on) { check(obn_profile_enable(Engine::instance().ctx(), on ? 1 : 0)); });
   m.def("profile_read", [](bool reset) {
     obn_profile p;
@@ -173,6 +197,12 @@ PYBIND11_MODULE(openbnsllib, m) {
     d["host_wait_ms"] = p.host_wait_ms;
     d["h2d_bytes"] = p.h2d_bytes;
     d["d2h_bytes"] = p.d2h_bytes;
+    d["scanned_bytes"] = p.scanned_bytes;
+    d["increments"] = p.increments;
+    d["tables"] = p.tables;
+    d["collectives"] = p.collectives;
+    d["collective_ms"] = p.collective_ms;
+    d["exact_fallbacks"] = p.exact_fallbacks;
     return d;
   }, py::arg("reset") = true);
 
@@ -294,7 +324,8 @@ PYBIND11_MODULE(openbnsllib, m) {
   auto sl = m.def_submodule("structure_learning", "Structure learning submodule");
   sl.def("exhaustive_search",
          [](const DataframeWrapper& df, const ScoreType& st, size_t max_parents, bool /*is_deterministic*/,
-            int exact_order, const py::object& comm, bool host_dp) {
+            int exact_order, const py::object& comm, bool host_dp, const py::object& lattice, double shard_min_bytes,
+            size_t dp_shard_min) {
            if (!std::holds_alternative<BDeu>(st)) throw std::invalid_argument("Unsupported score type.");
            if (df.num_of_vars && max_parents > df.num_of_vars - 1)
              throw std::invalid_argument("max_parents must be in [0, num_of_vars-1]");
@@ -307,9 +338,9 @@ PYBIND11_MODULE(openbnsllib, m) {
            o.max_parents = max_parents;
            o.exact_order = exact_order;
            o.cards.assign(df.num_of_values.begin(), df.num_of_values.end());
-           const char* e = std::getenv("OBN_SHARD_MIN_BYTES");
-           o.shard_min_bytes = e && *e ? std::atof(e) : 4e9;
-           if (const char* d = std::getenv("OBN_ES_DP_SHARD_MIN")) o.dp_shard_min_subsets = (size_t)std::atoll(d);
+           o.shard_min_bytes = shard_min_bytes;
+           o.dp_shard_min_subsets = dp_shard_min;
+           o.force_lattice = lattice.is_none() ? -1 : (lattice.cast<bool>() ? 1 : 0);
            const Comm c = make_comm(comm);
            if (c.world > 1 && !c.allgather_dev) throw std::invalid_argument("comm lacks allgather_dev");
            g_last_es_stats = EsStats{};
@@ -317,10 +348,12 @@ PYBIND11_MODULE(openbnsllib, m) {
          },
          "Run exhaustive search algorithm", py::arg("df"), py::arg("score_type"), py::arg("max_parents"),
          py::arg("is_deterministic") = false, py::kw_only(), py::arg("exact_order") = 2,
-         py::arg("comm") = py::none(), py::arg("host_dp") = false);
+         py::arg("comm") = py::none(), py::arg("host_dp") = false, py::arg("lattice") = py::none(),
+         py::arg("shard_min_bytes") = 4e9, py::arg("dp_shard_min") = 4096);
   sl.def("pc",
          [](const DataframeWrapper& df, const CITestType& test, size_t max_cond_vars, bool stable,
-            const py::object& comm, size_t target_batch, bool record_tests, bool apply_meek, bool complete_cpdag) {
+            const py::object& comm, size_t target_batch, bool record_tests, bool apply_meek, bool complete_cpdag,
+            bool overlap, double shard_min_bytes) {
            // apply_meek: what un-commenting pc.cpp:84 would do; complete_cpdag: the published rules
            auto finish = [&](PDAG g) {
              if (apply_meek) g = apply_meeks_rules(g, false, false);
@@ -329,17 +362,16 @@ PYBIND11_MODULE(openbnsllib, m) {
            if (std::holds_alternative<OracleGraph>(test))
              return finish(run_pc(df.num_of_vars, nullptr, test, max_cond_vars, stable, comm, target_batch));
            GpuEvaluator ev(df.device());
-           // shard a round over the GPUs only when it is worth a collective: >= 4 GB of algorithmic
-           // bytes (about 0.6 ms of one B200) unless OBN_SHARD_MIN_BYTES says otherwise
-           const char* e = std::getenv("OBN_SHARD_MIN_BYTES");
-           const double min_bytes = e && *e ? std::atof(e) : 4e9;
-           const size_t min_slots = (size_t)(min_bytes / (double)std::max<size_t>(1, df.num_of_datapoints));
+           // shard a round over the GPUs only when it is worth a collective: >= shard_min_bytes of
+           // algorithmic bytes (default 1 GB, about 0.15 ms of one B200)
+           const size_t min_slots = (size_t)(shard_min_bytes / (double)std::max<size_t>(1, df.num_of_datapoints));
            return finish(run_pc(df.num_of_vars, &ev, test, max_cond_vars, stable, comm, target_batch, record_tests,
-                                min_slots));
+                                min_slots, overlap));
          },
          "Run PC algorithm", py::arg("df"), py::arg("ci_test_type"), py::arg("max_cond_vars"),
          py::arg("stable") = true, py::kw_only(), py::arg("comm") = py::none(), py::arg("target_batch") = 0,
-         py::arg("record_tests") = false, py::arg("apply_meek") = false, py::arg("complete_cpdag") = false);
+         py::arg("record_tests") = false, py::arg("apply_meek") = false, py::arg("complete_cpdag") = false,
+         py::arg("overlap") = true, py::arg("shard_min_bytes") = 1e9);
   // the reference's Meek rules (pdag_with_adjmat.cpp:215-279) exist but pc() leaves them
   // switched off (pc.cpp:84) and PDAGwithAdjMat is not bound; here they are reachable, off by default.
   sl.def("apply_meeks_rules",
@@ -406,12 +438,12 @@ PYBIND11_MODULE(openbnsllib, m) {
   // ---------------- test seam (drivers over an injected evaluator) -----------
   auto ts = m.def_submodule("_testing", "Driver entry points over an injected evaluator (CPU test-suite only)");
   ts.def("pc", [](size_t n_vars, py::object evaluator, const CITestType& test, size_t max_cond_vars, bool stable,
-                  const py::object& comm, size_t target_batch, bool record_tests) {
+                  const py::object& comm, size_t target_batch, bool record_tests, bool overlap) {
     PyEvaluator ev(std::move(evaluator));
-    return run_pc(n_vars, &ev, test, max_cond_vars, stable, comm, target_batch, record_tests);
+    return run_pc(n_vars, &ev, test, max_cond_vars, stable, comm, target_batch, record_tests, 0, overlap);
   }, py::arg("n_vars"), py::arg("evaluator"), py::arg("ci_test_type"), py::arg("max_cond_vars"),
      py::arg("stable") = true, py::arg("comm") = py::none(), py::arg("target_batch") = 0,
-     py::arg("record_tests") = false);
+     py::arg("record_tests") = false, py::arg("overlap") = false);
   ts.def("exhaustive_search", [](size_t n_vars, py::object evaluator, const ScoreType& st, size_t max_parents,
                                  int exact_order, const py::object& comm) {
     PyEvaluator ev(std::move(evaluator));

@@ -1,7 +1,9 @@
 #include "engine.hpp"
 
 #include <algorithm>
+#include <cstdint>
 #include <cstdlib>
+#include <cstring>
 
 namespace obn {
 
@@ -49,6 +51,37 @@ bool GpuEvaluator::ci_submit(const TupleBatch& b, int kind) {
 }
 void GpuEvaluator::ci_collect(double* p) {
   check(obn_ci_tests_collect(Engine::instance().ctx(), nullptr, nullptr, p));
+}
+
+bool GpuEvaluator::pc_round(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind,
+                            double level, bool shard, std::vector<int32_t>& first) {
+  first.resize(n_slots);
+  check(obn_pc_round(Engine::instance().ctx(), ds_, b.var_ids.data(), b.offsets.data(), b.size(), b.x.data(), b.y.data(),
+                     slot_of_test.data(), n_slots, kind, level, shard ? 1 : 0, first.data()));
+  return true;
+}
+bool GpuEvaluator::pc_round_submit(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind,
+                                   double level, bool shard) {
+  check(obn_pc_round_submit(Engine::instance().ctx(), ds_, b.var_ids.data(), b.offsets.data(), b.size(), b.x.data(),
+                            b.y.data(), slot_of_test.data(), n_slots, kind, level, shard ? 1 : 0));
+  pending_slots_ = n_slots;
+  return true;
+}
+void GpuEvaluator::pc_round_collect(std::vector<int32_t>& first) {
+  first.assign(pending_slots_, INT32_MAX);
+  check(obn_pc_round_collect(Engine::instance().ctx(), first.data()));
+}
+
+Comm native_comm() {
+  obn_ctx* c = Engine::instance().ctx();
+  Comm m;
+  m.rank = obn_comm_rank(c);
+  m.world = obn_comm_world(c);
+  m.native = true;
+  m.allreduce_min_i32 = [c](int32_t* p, size_t n) { check(obn_comm_allreduce_min_i32(c, p, n)); };
+  m.allgather_dev = [c](uintptr_t p, size_t bytes) { check(obn_comm_allgather_inplace(c, reinterpret_cast<void*>(p), bytes)); };
+  m.allgather = [c](const void* s, void* recv, size_t bytes) { check(obn_comm_allgather_host(c, s, recv, bytes)); };
+  return m;
 }
 
 void GpuEvaluator::subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,

@@ -78,6 +78,14 @@ struct Evaluator {
   // computed, collect waits for it.  false = not supported, use ci_pvalues.
   virtual bool ci_submit(const TupleBatch&, int /*kind*/) { return false; }
   virtual void ci_collect(double* /*p*/) {}
+  // One PC round answered as a whole (obn_pc_round): first[s] = the first test of edge slot s whose
+  // p >= level, INT32_MAX if none.  shard: split the round over the ranks of the library's own
+  // communicator (collective).  false = not supported, the driver decides from ci_pvalues.
+  virtual bool pc_round(const TupleBatch&, const std::vector<uint32_t>& /*slot_of_test*/, size_t /*n_slots*/,
+                        int /*kind*/, double /*level*/, bool /*shard*/, std::vector<int32_t>& /*first*/) { return false; }
+  virtual bool pc_round_submit(const TupleBatch&, const std::vector<uint32_t>& /*slot_of_test*/, size_t /*n_slots*/,
+                               int /*kind*/, double /*level*/, bool /*shard*/) { return false; }
+  virtual void pc_round_collect(std::vector<int32_t>& /*first*/) {}
   // scores of every child of tuples [begin, end) -> out[offsets[t]-offsets[begin] + i]
   virtual void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                              double* out) = 0;
@@ -91,6 +99,11 @@ class GpuEvaluator : public Evaluator {
   void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) override;
   bool ci_submit(const TupleBatch& b, int kind) override;
   void ci_collect(double* p) override;
+  bool pc_round(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind, double level,
+                bool shard, std::vector<int32_t>& first) override;
+  bool pc_round_submit(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind,
+                       double level, bool shard) override;
+  void pc_round_collect(std::vector<int32_t>& first) override;
   void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                      double* out) override;
   void child_scores(const TupleBatch& b, const uint32_t* child, double ess, int exact_order, double* out) override;
@@ -98,12 +111,16 @@ class GpuEvaluator : public Evaluator {
  private:
   obn_dataset* ds_;
   std::vector<uint64_t> tmp_off_;
+  size_t pending_slots_ = 0;
 };
 
 // Collectives between the per-GPU processes.  Default = single rank.
 struct Comm {
   int rank = 0;
   int world = 1;
+  // the library's own NCCL communicator (obn_comm_init): sharded PC rounds reduce on the device inside
+  // obn_pc_round, the all-gathers below go through obn_comm_allgather_inplace
+  bool native = false;
   // in-place elementwise MIN over ranks
   std::function<void(int32_t*, size_t)> allreduce_min_i32;
   // gather `bytes` bytes from every rank into recv (world * bytes), rank order
@@ -112,6 +129,9 @@ struct Comm {
   // the r-th slice (NCCL over NVLink; the data never visits the host)
   std::function<void(uintptr_t, size_t)> allgather_dev;
 };
+
+// The communicator the ctx of this process owns (after obn_comm_init); world == 1 without one.
+Comm native_comm();
 
 // contiguous shard [begin, end) of n items for rank r of w
 inline void shard_range(size_t n, int r, int w, size_t* begin, size_t* end) {

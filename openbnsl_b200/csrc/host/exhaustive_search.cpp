@@ -158,7 +158,7 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
     for (size_t v = 0; v < n; ++v) lat_cells *= 1.0 + (double)opt.cards[v];
     const double lattice_s = lat_cells * 12.0 / 3e12 + 0.05;
     lattice = lattice_s < count_s && (opt.exact_order == 0 || count_s > 2.0);
-    if (const char* f = std::getenv("OBN_ES_LATTICE")) lattice = *f == '1';   // tests / A-B runs
+    if (opt.force_lattice >= 0) lattice = opt.force_lattice != 0;   // tests / A-B runs
   }
   if (lattice) {
     const auto t0 = clk::now();

@@ -149,7 +149,7 @@ void append_test(TupleBatch& b, uint32_t u, uint32_t v, const std::vector<uint32
 // The same decision in two halves (Evaluator::ci_submit / ci_collect): submit returns false when
 // the evaluator cannot work asynchronously, and the driver falls back to `decide`.
 struct AsyncDecide {
-  std::function<bool(const TupleBatch&)> submit;
+  std::function<bool(const TupleBatch&, const std::vector<uint32_t>& pair_of_test, size_t n_slots)> submit;
   std::function<void(const TupleBatch&, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
                      std::vector<int32_t>& first)> collect;
 };
@@ -339,7 +339,7 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         // while the device works on this round the next one is enumerated as if no edge were
         // removed, and the tests of the edges this round does remove are dropped afterwards.
         // Batch boundaries do not change what an edge resolves at: its first passing candidate.
-        const bool in_flight = async && async->submit(batch);
+        const bool in_flight = async && async->submit(batch, pair_of_test, cursors.size());
         quota *= 2;
         bool have_spec = false;
         if (in_flight) {
@@ -425,12 +425,17 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
 PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, const PcOptions& opt,
                                PcStats* stats) {
   std::vector<double> p;
-  TupleBatch mine;                   // this rank's share of a sharded round
+  TupleBatch mine;                   // this rank's share of a sharded round (host-side comm only)
+  auto sharded = [&](const TupleBatch& b) { return comm.world > 1 && b.var_ids.size() >= opt.shard_min_slots; };
   DecideFn decide = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
                         std::vector<int32_t>& first) {
+    const bool shard = sharded(b);
+    // The product path (obn_pc_round): the decision is taken on the device, a sharded round is merged
+    // by the library's own all-reduce(min) on the device buffer, only first[] comes back.  A sharded
+    // round over a host-side communicator (test seams) falls through to the generic path below.
+    if (!(shard && !comm.native) && ev.pc_round(b, pair_of_test, n_slots, opt.kind, opt.level, shard, first)) return;
     first.assign(n_slots, INT_MAX);
-    const bool sharded = comm.world > 1 && b.var_ids.size() >= opt.shard_min_slots;
-    if (!sharded) {
+    if (!shard) {
       p.resize(b.size());
       ev.ci_pvalues(b, 0, b.size(), opt.kind, p.data());
       for (size_t t = 0; t < b.size(); ++t)
@@ -459,11 +464,26 @@ PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, c
       }
     comm.allreduce_min_i32(first.data(), first.size());
   };
-  // single rank only: a sharded round ends in a collective, which would need its own split
+  // The same decision in two halves, so that round r+1 is enumerated while the device runs round r.
+  // A sharded round works too when the communicator is the library's (the collective is enqueued
+  // behind the kernels at submit); a host-side communicator would need its own split: not overlapped.
+  bool round_in_flight = false;
   AsyncDecide async;
-  async.submit = [&](const TupleBatch& b) { return ev.ci_submit(b, opt.kind); };
+  async.submit = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots) {
+    const bool shard = sharded(b);
+    if (shard && !comm.native) return false;
+    round_in_flight = ev.pc_round_submit(b, pair_of_test, n_slots, opt.kind, opt.level, shard);
+    if (round_in_flight) return true;
+    return !shard && ev.ci_submit(b, opt.kind);
+  };
   async.collect = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
                       std::vector<int32_t>& first) {
+    if (round_in_flight) {
+      round_in_flight = false;
+      ev.pc_round_collect(first);
+      first.resize(n_slots, INT_MAX);
+      return;
+    }
     first.assign(n_slots, INT_MAX);
     p.resize(b.size());
     ev.ci_collect(p.data());
@@ -473,7 +493,7 @@ PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, c
         if ((int32_t)t < f) f = (int32_t)t;
       }
   };
-  const bool overlap = opt.overlap && opt.stable && comm.world == 1;
+  const bool overlap = opt.overlap && opt.stable && (comm.world == 1 || comm.native);
   return run_pc(n_vars, opt.max_cond_vars, opt.stable, opt.target_batch, decide, stats, overlap ? &async : nullptr);
 }
 

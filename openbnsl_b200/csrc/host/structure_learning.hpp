@@ -59,6 +59,7 @@ struct EsOptions {
   std::vector<uint32_t> cards;    // cardinalities (device driver: cost model of the lattice mode)
   double shard_min_bytes = 0;     // multi-GPU: shard a level only if it has this many algorithmic bytes
   size_t dp_shard_min_subsets = 4096;   // multi-GPU lattice mode: shard the DP by child from the first level this large
+  int force_lattice = -1;         // -1 auto (by estimated counting time), 0 never, 1 always (exact_order != 1 only)
 };
 struct EsStats {
   uint64_t tables = 0, scores = 0;

@@ -26,15 +26,19 @@ struct BatchSpec {
   int32_t* counts = nullptr;
   int32_t* counts_dev = nullptr;  // COUNTS: leave the dense tables on the device at this address (no D2H)
   const uint64_t* counts_off = nullptr;
-  // MODE_CI_POOL (obn_ci_tests with pooling on): the tuples are POOLS (obn_ci_pool.inl), the
-  // outputs are per TEST
+  // MODE_CI: the tuples are GROUPS (obn_ci_groups.inl: the tests asked over one variable set share
+  // its table), the outputs are per TEST
   size_t n_out = 0;                 // number of tests
   const uint32_t* mem_off = nullptr;    // [n + 1]
   const uint32_t* members = nullptr;    // 2 words per member
-  uint32_t pool_cells = 0;
-  double alg_bytes = 0;             // sum over the TESTS of k * n_rows (the unit is the test)
-  // CI modes: return once everything is enqueued (obn_ci_tests_submit); obn_ci_tests_collect
-  // waits and hands the results out
+  // PC round (obn_pc_round): decision on the device, first[slot] = first passing test of the slot
+  const uint32_t* slot_of_test = nullptr;   // [n_out]
+  size_t n_slots = 0;
+  double level = 0.05;
+  int32_t* first = nullptr;         // host, [n_slots]
+  bool shard = false;               // split the groups over the ranks of the ctx's communicator + all-reduce(min)
+  // CI modes: return once everything is enqueued (obn_ci_tests_submit / obn_pc_round_submit);
+  // the matching collect waits and hands the results out
   bool defer = false;
 };
 
@@ -52,26 +56,52 @@ static const uint32_t kClassCells[kNumClasses - 2] = {64, 256, 1024, 4096, 16384
 
 static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-template <int KW, int TIER, bool SCALE4, bool POOL = false>
+template <int KW, int TIER, bool SCALE4>
 static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, size_t smem, cudaStream_t s) {
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4, POOL>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  // cudaFuncAttributeMaxDynamicSharedMemorySize is per device and a process may hold one ctx per
+  // device: set it whenever a launch needs more than the default 48 KB (a few microseconds)
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
     if (e != cudaSuccess) return e;
-    configured = smem;
   }
   (void)cudaGetLastError();      // a launch reports only its own error, not a stale one
-  count_kernel<KW, TIER, SCALE4, POOL><<<grid, nthr, smem, s>>>(a);
+  count_kernel<KW, TIER, SCALE4><<<grid, nthr, smem, s>>>(a);
   return cudaGetLastError();
 }
 
 static const size_t kScratchMaxBytes = (size_t)8 << 30;
 static const size_t kLutMaxBytes = (size_t)2 << 30;
 
-static int env_int(const char* name, int dflt) {
-  const char* v = std::getenv(name);
-  return v && *v ? std::atoi(v) : dflt;
+// Results of a finished batch: staging buffer -> the caller's arrays, profile counters.
+static void finish_batch(obn_ctx* c, const obn_ctx::Pending& P, double* stat, uint64_t* dof, double* p, int32_t* first) {
+  const unsigned char* hout = c->h_out.as<unsigned char>();
+  if (P.n_slots) {
+    if (first) {
+      const int32_t* f = reinterpret_cast<const int32_t*>(hout);
+      for (size_t i = 0; i < P.n_slots; ++i) first[i] = f[i] >= kFirstNone ? INT32_MAX : f[i];
+    }
+  } else {
+    const size_t n = P.n_results;
+    if (stat) memcpy(stat, hout, n * 8);
+    if (dof) memcpy(dof, hout + n * 8, n * 8);
+    if (p) memcpy(p, hout + n * 16, n * 8);
+  }
+  if (c->profile_on) {
+    for (size_t i = P.ev_first; i < c->ev_used; ++i) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, c->ev_pool[i].first, c->ev_pool[i].second);
+      c->prof.count_kernel_ms += ms;
+    }
+    c->ev_used = P.ev_first;
+  }
+  c->prof.h2d_bytes += (double)P.in_bytes;
+  c->prof.d2h_bytes += (double)P.out_bytes;
+  c->prof.algorithmic_bytes += P.alg_bytes;
+  c->prof.scanned_bytes += P.scanned_bytes;
+  c->prof.increments += P.increments;
+  c->prof.tuples += P.n_out;
+  c->prof.tables += P.tables;
 }
 
 static int run_batch(BatchSpec& S) {
@@ -79,44 +109,70 @@ static int run_batch(BatchSpec& S) {
   const obn_dataset* ds = S.ds;
   if (!c || !ds) return fail(OBN_ERR_INVALID, "ctx or dataset is NULL");
   if (ds->ctx != c) return fail(OBN_ERR_INVALID, "dataset belongs to another ctx");
-  if (c->pending.active) return fail(OBN_ERR_INVALID, "a submitted batch is waiting for obn_ci_tests_collect");
+  if (c->pending.active) return fail(OBN_ERR_INVALID, "a submitted batch is waiting to be collected");
   const size_t n = S.n;
-  if (n == 0) return OBN_OK;
+  const bool ci = (S.mode == MODE_CI);
+  const bool pc_round = ci && S.n_slots != 0;
+  const size_t n_out = ci ? S.n_out : n;
+  const int world = (S.shard && c->comm) ? c->comm_world : 1, rank = world > 1 ? c->comm_rank : 0;
+  if (n == 0) {                     // (a sharded round is the same batch on every rank: all of them return here)
+    if (pc_round && S.first) std::fill(S.first, S.first + S.n_slots, INT32_MAX);
+    return OBN_OK;
+  }
   if (!S.offsets) return fail(OBN_ERR_INVALID, "offsets is NULL");
   if (n >= 0xffffffffull) return fail(OBN_ERR_UNSUPPORTED, "more than 2^32-2 tuples in one batch");
   const size_t total_vars = S.offsets[n];
   if (total_vars && !S.var_ids) return fail(OBN_ERR_INVALID, "var_ids is NULL");
-  const bool ci = (S.mode == MODE_CI || S.mode == MODE_CI_POOL), pooled = (S.mode == MODE_CI_POOL);
-  const size_t n_out = pooled ? S.n_out : n;
-  if (ci && (!S.role_a || !S.role_b)) return fail(OBN_ERR_INVALID, "x or y is NULL");
   if ((S.mode == MODE_BDEU_ONE) && !S.role_a) return fail(OBN_ERR_INVALID, "child is NULL");
   OBN_CUDA(cudaSetDevice(c->device));
   const auto t_begin = std::chrono::steady_clock::now();
 
   // ---- validate + classify --------------------------------------------------
+  // (CI groups were validated test by test in plan_ci_groups)
   const size_t budget = c->smem_optin > 4096 ? c->smem_optin - 2048 : 46 * 1024;
-  std::vector<uint32_t> cells(n);
-  std::vector<uint8_t> group(n);
-  std::vector<uint32_t> rxy(n, 0);
+  static thread_local std::vector<uint32_t> cells, rxy, perm;
+  static thread_local std::vector<uint8_t> group;
+  cells.resize(n);
+  group.resize(n);
+  rxy.assign(n, 0);
   size_t group_count[kNumClasses] = {};
-  double alg_bytes = 0;
+  size_t class_seen[kNumClasses] = {};
+  double alg_bytes = 0, scanned_bytes = 0, increments = 0;
+  size_t n_mine = 0, tests_mine = 0;
   if (ds->n_vars > (1u << 24)) return fail(OBN_ERR_UNSUPPORTED, "more than 2^24 variables");
   for (size_t t = 0; t < n; ++t) {
     const uint64_t o0 = S.offsets[t], o1 = S.offsets[t + 1];
     if (o1 < o0) return fail(OBN_ERR_INVALID, "offsets must be non-decreasing");
     const size_t k = o1 - o0;
     uint64_t cl = 1;
-    if (int rc = check_tuple(ds->cards.data(), ds->n_vars, S.var_ids + o0, k, t, ci, S.mode == MODE_BDEU_ONE,
-                             S.role_a ? S.role_a[t] : 0xffffffffu, S.role_b ? S.role_b[t] : 0xffffffffu, &cl))
+    if (ci) {
+      uint32_t c1 = 0, c2 = 0;           // the two largest cardinalities bound rx + ry of every member
+      for (size_t i = 0; i < k; ++i) {
+        const uint32_t cd = ds->cards[S.var_ids[o0 + i]];
+        cl *= cd;
+        if (cd > c1) { c2 = c1; c1 = cd; } else if (cd > c2) c2 = cd;
+      }
+      rxy[t] = c1 + c2;
+    } else if (int rc = check_tuple(ds->cards.data(), ds->n_vars, S.var_ids + o0, k, t, false, S.mode == MODE_BDEU_ONE,
+                                    S.role_a ? S.role_a[t] : 0xffffffffu, 0xffffffffu, &cl)) {
       return rc;
-    if (ci) rxy[t] = ds->cards[S.role_a[t]] + ds->cards[S.role_b[t]];
+    }
     cells[t] = (uint32_t)cl;
     int g = 0;
     while (g < kNumClasses - 2 && cl > kClassCells[g]) ++g;
     if (g == kNumClasses - 2 && cl * 4 + 16 + 8 * 512 * 4 > budget) g = kNumClasses - 1;
-    group[t] = (uint8_t)g;
+    // sharded rounds: the groups of one class are dealt to the ranks in turn, so every rank gets the
+    // same mix of table sizes (the class boundaries move the deal so small classes do not all land on rank 0)
+    const bool mine = world == 1 || (int)((class_seen[g]++ + (size_t)g) % (size_t)world) == rank;
+    group[t] = mine ? (uint8_t)g : (uint8_t)0xff;
+    if (!mine) continue;
     ++group_count[g];
-    alg_bytes += (double)k * (double)ds->n_rows;
+    ++n_mine;
+    const double members = ci ? (double)(S.mem_off[t + 1] - S.mem_off[t]) : 1.0;
+    tests_mine += (size_t)members;
+    alg_bytes += members * (double)k * (double)ds->n_rows;      // the unit is the TEST
+    scanned_bytes += (double)k * (double)ds->n_rows;
+    increments += (double)ds->n_rows;
   }
 
   // ---- exact-order BDeu: host-libm lgamma tables, cached in the ctx across calls ------------
@@ -128,42 +184,52 @@ static int run_batch(BatchSpec& S) {
     LutCache& lc = c->lut;
     if (lc.stride != lut_stride) lc.clear();                 // another sample count: other tables
     lc.stride = lut_stride;
-    std::vector<double> pending;
-    std::map<uint64_t, uint32_t> pending_ids;
-    auto id_of = [&](double a) {
-      uint64_t bits;
-      memcpy(&bits, &a, 8);
-      auto it = lc.ids.find(bits);
-      if (it != lc.ids.end()) return it->second;
-      auto jt = pending_ids.find(bits);
-      if (jt != pending_ids.end()) return jt->second;
-      const uint32_t id = (uint32_t)(lc.rows + pending.size());
-      pending_ids[bits] = id;
-      pending.push_back(a);
-      return id;
-    };
-    lut_ijk.resize(n);
-    lut_ij.assign(total_vars, 0);
-    uint32_t last_cells = 0, last_ijk = 0;
-    for (size_t t = 0; t < n; ++t) {
-      const double a_ijk = S.ess / (double)(size_t)cells[t];      // local_score.h:41
-      if (cells[t] != last_cells) { last_ijk = id_of(a_ijk); last_cells = cells[t]; }
-      lut_ijk[t] = last_ijk;
-      uint32_t last_card = 0, last_id = 0;
-      for (uint64_t i = S.offsets[t]; i < S.offsets[t + 1]; ++i) {
-        const uint32_t cd = ds->cards[S.var_ids[i]];
-        if (cd != last_card) { last_id = id_of(a_ijk * (double)(size_t)cd); last_card = cd; }   // :45
-        lut_ij[i] = last_id;
+    for (int attempt = 0;; ++attempt) {
+      std::vector<double> pending;
+      std::map<uint64_t, uint32_t> pending_ids;
+      auto id_of = [&](double a) {
+        uint64_t bits;
+        memcpy(&bits, &a, 8);
+        auto it = lc.ids.find(bits);
+        if (it != lc.ids.end()) return it->second;
+        auto jt = pending_ids.find(bits);
+        if (jt != pending_ids.end()) return jt->second;
+        const uint32_t id = (uint32_t)(lc.rows + pending.size());
+        pending_ids[bits] = id;
+        pending.push_back(a);
+        return id;
+      };
+      lut_ijk.resize(n);
+      lut_ij.assign(total_vars, 0);
+      uint32_t last_cells = 0, last_ijk = 0;
+      for (size_t t = 0; t < n; ++t) {
+        const double a_ijk = S.ess / (double)(size_t)cells[t];      // local_score.h:41
+        if (cells[t] != last_cells) { last_ijk = id_of(a_ijk); last_cells = cells[t]; }
+        lut_ijk[t] = last_ijk;
+        uint32_t last_card = 0, last_id = 0;
+        for (uint64_t i = S.offsets[t]; i < S.offsets[t + 1]; ++i) {
+          const uint32_t cd = ds->cards[S.var_ids[i]];
+          if (cd != last_card) { last_id = id_of(a_ijk * (double)(size_t)cd); last_card = cd; }   // :45
+          lut_ij[i] = last_id;
+        }
       }
-    }
-    const size_t want_rows = lc.rows + pending.size();
-    if (want_rows * lut_stride * sizeof(double) > kLutMaxBytes) {
-      if (S.exact != 2)
-        return fail(OBN_ERR_UNSUPPORTED, "exact_order needs %zu lgamma tables of %zu entries", want_rows, lut_stride);
-      exact = false;
-    } else if (!pending.empty()) {
-      if (int rc = lc.append(c, pending)) return rc;
-      for (auto& kv : pending_ids) lc.ids[kv.first] = kv.second;
+      const size_t want_rows = lc.rows + pending.size();
+      if (want_rows * lut_stride * sizeof(double) > kLutMaxBytes) {
+        // the cap is hit by what EARLIER batches left in the cache: evict everything and number this
+        // batch's tables afresh, so that the outcome depends on this batch alone, not on the ctx's history
+        if (attempt == 0 && lc.rows) {
+          lc.clear();
+          continue;
+        }
+        if (S.exact != 2)
+          return fail(OBN_ERR_UNSUPPORTED, "exact_order needs %zu lgamma tables of %zu entries", want_rows, lut_stride);
+        exact = false;
+        ++c->prof.exact_fallbacks;
+      } else if (!pending.empty()) {
+        if (int rc = lc.append(c, pending)) return rc;
+        for (auto& kv : pending_ids) lc.ids[kv.first] = kv.second;
+      }
+      break;
     }
   }
 
@@ -171,30 +237,32 @@ static int run_batch(BatchSpec& S) {
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align16(off + bytes); return o; };
   if (total_vars >= 0xffffffffull) return fail(OBN_ERR_UNSUPPORTED, "more than 2^32-2 variable slots in one batch");
-  const size_t o_var = take(total_vars * 4), o_hdr = take(n * 16);
-  const size_t o_roles = take(S.role_a ? n * 8 : 0);
-  const size_t o_soff = take(n * 8);
+  const size_t o_var = take(total_vars * 4), o_hdr = take(n_mine * 16);
+  const size_t o_roles = take(S.role_a ? n_mine * 8 : 0);
+  const size_t o_soff = take(n_mine * 8);
   const size_t o_coff = take(S.mode == MODE_COUNTS ? n * 8 : 0);
   const size_t o_lijk = take(exact ? n * 4 : 0), o_lij = take(exact ? total_vars * 4 : 0);
-  const size_t n_members = pooled ? S.mem_off[n] : 0;
-  const size_t o_moff = take(pooled ? (n + 1) * 4 : 0), o_mem = take(n_members * 8);
+  const size_t n_members = ci ? S.mem_off[n] : 0;
+  const size_t o_moff = take(ci ? (n + 1) * 4 : 0), o_mem = take(n_members * 8);
+  const size_t o_slot = take(pc_round ? n_out * 4 : 0);
   const size_t in_bytes = off;
-  if (int rc = c->h_in.reserve(in_bytes)) return rc;
-  if (int rc = c->d_in.reserve(in_bytes)) return rc;
+  if (int rc = c->h_in.reserve(std::max<size_t>(in_bytes, 16))) return rc;
+  if (int rc = c->d_in.reserve(std::max<size_t>(in_bytes, 16))) return rc;
   unsigned char* hin = c->h_in.as<unsigned char>();
   {
     uint32_t* desc = reinterpret_cast<uint32_t*>(hin + o_var);
     for (size_t i = 0; i < total_vars; ++i) desc[i] = S.var_ids[i] | ((ds->cards[S.var_ids[i]] - 1u) << 24);
   }
-  if (pooled) {
+  if (ci) {
     memcpy(hin + o_moff, S.mem_off, (n + 1) * 4);
     memcpy(hin + o_mem, S.members, n_members * 8);
+    if (pc_round) memcpy(hin + o_slot, S.slot_of_test, n_out * 4);
   }
   if (exact) {
     memcpy(hin + o_lijk, lut_ijk.data(), n * 4);
     if (total_vars) memcpy(hin + o_lij, lut_ij.data(), total_vars * 4);
   }
-  std::vector<uint32_t> perm(n);
+  perm.resize(n_mine);
   uint64_t* soff = reinterpret_cast<uint64_t*>(hin + o_soff);
   size_t gstart[kNumClasses + 1];
   gstart[0] = 0;
@@ -202,29 +270,29 @@ static int run_batch(BatchSpec& S) {
   {
     size_t fill[kNumClasses];
     for (int g = 0; g < kNumClasses; ++g) fill[g] = gstart[g];
-    for (size_t t = 0; t < n; ++t) perm[fill[group[t]]++] = (uint32_t)t;
+    for (size_t t = 0; t < n; ++t)
+      if (group[t] != 0xff) perm[fill[group[t]]++] = (uint32_t)t;
   }
   {
     uint32_t* hdr = reinterpret_cast<uint32_t*>(hin + o_hdr);
     uint32_t* roles = S.role_a ? reinterpret_cast<uint32_t*>(hin + o_roles) : nullptr;
-    for (size_t q = 0; q < n; ++q) {
+    for (size_t q = 0; q < n_mine; ++q) {
       const uint32_t t = perm[q];
       hdr[4 * q + 0] = t;
       hdr[4 * q + 1] = (uint32_t)S.offsets[t];
       hdr[4 * q + 2] = (uint32_t)(S.offsets[t + 1] - S.offsets[t]);
       hdr[4 * q + 3] = cells[t];
       if (roles) {
-        uint32_t ra = S.role_a[t], rb = S.role_b ? S.role_b[t] : 0xffffffffu;
-        if (S.role_b && ra > rb) std::swap(ra, rb);                  // citest.h:48
-        roles[2 * q + 0] = ra;
-        roles[2 * q + 1] = rb;
+        roles[2 * q + 0] = S.role_a[t];
+        roles[2 * q + 1] = 0xffffffffu;
       }
     }
   }
 
   // ---- output buffer ----------------------------------------------------------
   size_t out_bytes = 0, counts_total = 0;
-  if (ci) out_bytes = n_out * 24;
+  if (pc_round) out_bytes = S.n_slots * 4;
+  else if (ci) out_bytes = n_out * 24;
   else if (S.mode == MODE_BDEU_ONE) out_bytes = n * 8;
   else if (S.mode == MODE_BDEU_ALL) out_bytes = S.scores_dev ? 0 : total_vars * 8;
   else {
@@ -235,13 +303,11 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
-  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t stage_off = 0; };
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; };
   std::vector<Launch> launches;
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
-  size_t max_scratch_ints = 0, max_launch_tuples = 0;
-  const int force_t = env_int("OBN_FORCE_T", 0), force_splits = env_int("OBN_FORCE_SPLITS", 0);
-  const int pool_wide = pooled ? env_int("OBN_CI_POOL_WIDE", 0) : 0;
-  const size_t target_threads = (size_t)c->sm_count * (size_t)env_int("OBN_THREADS_PER_SM", 768);
+  size_t max_scratch_ints = 0;
+  const size_t target_threads = (size_t)c->sm_count * (size_t)c->tune.threads_per_sm;
   for (int g = 0; g < kNumClasses; ++g) {
     if (!group_count[g]) continue;
     const bool global_tier = (g == kNumClasses - 1);
@@ -268,37 +334,12 @@ static int run_batch(BatchSpec& S) {
         splits = (int)std::min<size_t>(tpt / 256, std::max<uint32_t>(1u, n_vec / min_vps));
         splits = std::max(1, splits);
       }
-      if (force_t) nthr = force_t;
-      if (force_splits) splits = std::max(1, std::min<int>(force_splits, (int)std::max<uint32_t>(1u, n_vec)));
+      if (c->tune.force_threads) nthr = c->tune.force_threads;
+      if (c->tune.force_splits)
+        splits = std::max(1, std::min<int>(c->tune.force_splits, (int)std::max<uint32_t>(1u, n_vec)));
       const int nw = nthr / 32;
       size_t smem = (global_tier ? 0 : align16((size_t)max_cells * 4)) + (size_t)nw * max_rxy * 4;
-      if (pooled && !global_tier) {
-        // per tuple: table + the two pass buffers (cells/2, cells/4 ints) when it is a real pool,
-        // carved up the same way by count_kernel
-        size_t need = 0;
-        for (size_t q = i; q < gstart[g + 1]; ++q) {
-          const size_t cq = cells[perm[q]];
-          size_t b = align16(cq * 4);
-          if (cq <= S.pool_cells) b += align16((cq / 2) * 4) + align16((cq / 4) * 4);
-          need = std::max(need, b);
-        }
-        smem = need + (size_t)nw * max_rxy * 4;
-      }
       smem = std::max<size_t>(align16(smem), 16);
-      // scan_rows_tma (OBN_CI_POOL_WIDE=2): a ring of kTmaStages tiles of nthr 16-row vectors of every
-      // column behind everything else; used only when it fits next to the table
-      uint32_t stage_off = 0;
-      if (pooled && pool_wide == 2) {
-        size_t max_k = 0;
-        for (size_t q = i; q < gstart[g + 1]; ++q)
-          max_k = std::max<size_t>(max_k, S.offsets[perm[q] + 1] - S.offsets[perm[q]]);
-        const size_t off128 = (smem + 127) & ~(size_t)127;
-        const size_t ring = (size_t)kTmaStages * max_k * 16 * (size_t)nthr;
-        if (max_k > 6 && off128 + ring + 1024 <= budget) {
-          stage_off = (uint32_t)off128;
-          smem = off128 + ring;
-        }
-      }
       const bool need_scratch = splits > 1 || global_tier;
       size_t j = i, scratch_ints = 0;
       if (need_scratch) {
@@ -313,9 +354,8 @@ static int run_batch(BatchSpec& S) {
       }
       uint32_t vps = (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, stage_off});
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false});
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
-      max_launch_tuples = std::max(max_launch_tuples, j - i);
       i = j;
     }
   }
@@ -334,25 +374,16 @@ static int run_batch(BatchSpec& S) {
     }
     max_scratch_ints = need;
   }
-  (void)max_launch_tuples;
   if (max_scratch_ints)
     if (int rc = c->d_scratch.reserve(max_scratch_ints * 4, true)) return rc;
-  if (int rc = c->d_tickets.reserve(n * 4, true)) return rc;
+  if (int rc = c->d_tickets.reserve(std::max<size_t>(n_mine, 4) * 4, true)) return rc;
 
   const auto t_packed = std::chrono::steady_clock::now();
-  OBN_CUDA(cudaMemcpyAsync(c->d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
+  if (in_bytes) OBN_CUDA(cudaMemcpyAsync(c->d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
 
   // ---- launch ------------------------------------------------------------------
   unsigned char* din = c->d_in.as<unsigned char>();
   unsigned char* dout = c->d_out.as<unsigned char>();
-  // OBN_CI_ZERO_COPY=1 (plain CI batches; unmeasured, default off): the epilogue writes statistic, dof
-  // and p straight into the pinned host buffer (under UVA a cudaMallocHost pointer is valid on the
-  // device), so a round ends with the kernel instead of a D2H copy behind it
-  const bool zc_out = S.mode == MODE_CI && env_int("OBN_CI_ZERO_COPY", 0) != 0;
-  if (zc_out) {
-    if (int rc = c->h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
-    dout = c->h_out.as<unsigned char>();
-  }
   BatchArgs a{};
   a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows;
   a.desc = reinterpret_cast<const uint32_t*>(din + o_var);
@@ -362,15 +393,18 @@ static int run_batch(BatchSpec& S) {
     a.lut_ijk = reinterpret_cast<const uint32_t*>(din + o_lijk);
     a.lut_ij = reinterpret_cast<const uint32_t*>(din + o_lij);
   }
-  double* d_stat = reinterpret_cast<double*>(dout);
-  unsigned long long* d_dof = reinterpret_cast<unsigned long long*>(dout + n_out * 8);
-  double* d_p = reinterpret_cast<double*>(dout + n_out * 16);
   if (ci) {
-    a.stat = d_stat; a.dof = d_dof; a.pval = S.p ? d_p : nullptr;
-    if (pooled) {
-      a.mem_off = reinterpret_cast<const uint32_t*>(din + o_moff);
-      a.members = reinterpret_cast<const uint2*>(din + o_mem);
-      a.pool_cells = S.pool_cells;
+    a.mem_off = reinterpret_cast<const uint32_t*>(din + o_moff);
+    a.members = reinterpret_cast<const uint2*>(din + o_mem);
+    if (pc_round) {
+      a.first = reinterpret_cast<int32_t*>(dout);
+      a.slot_of_test = reinterpret_cast<const uint32_t*>(din + o_slot);
+      a.level = S.level;
+      OBN_CUDA(cudaMemsetAsync(dout, 0x7f, out_bytes, c->stream));      // kFirstNone in every slot
+    } else {
+      a.stat = reinterpret_cast<double*>(dout);
+      a.dof = reinterpret_cast<unsigned long long*>(dout + n_out * 8);
+      a.pval = S.p ? reinterpret_cast<double*>(dout + n_out * 16) : nullptr;
     }
   }
   else if (bdeu) a.scores = S.scores_dev ? S.scores_dev : reinterpret_cast<double*>(dout);
@@ -392,7 +426,7 @@ static int run_batch(BatchSpec& S) {
     ++c->ev_used;
     OBN_CUDA(cudaEventRecord(e0, c->stream));
   }
-  const int n_streams = std::max(1, std::min(1 + obn_ctx::kAuxStreams, env_int("OBN_STREAMS", 1 + obn_ctx::kAuxStreams)));
+  const int n_streams = std::max(1, std::min(1 + obn_ctx::kAuxStreams, c->tune.streams));
   bool aux_used[obn_ctx::kAuxStreams] = {};
   bool forked = false;
   int slot = 0;
@@ -431,17 +465,8 @@ static int run_batch(BatchSpec& S) {
     a.tickets = c->d_tickets.as<unsigned int>() + L.begin;
     a.splits = L.splits;
     a.vec_per_split = L.vps;
-    a.stage_off = L.stage_off;
-    a.wide_prefetch = (pool_wide == 2 && !L.stage_off) ? 0 : pool_wide;   // no room for the tile ring: plain loop
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
     cudaError_t e;
-    if (pooled) {
-      if (L.g == 0) e = launch_count<8, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
-      else if (L.g == 1) e = launch_count<8, TIER_SMEM, false, true>(a, grid, L.nthr, L.smem, st);
-      else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
-      else if (L.g == 5) e = launch_count<32, TIER_SMEM, false, true>(a, grid, L.nthr, L.smem, st);
-      else e = launch_count<32, TIER_GLOBAL, false, true>(a, grid, L.nthr, L.smem, st);
-    } else
     if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
     else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
     else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
@@ -455,20 +480,29 @@ static int run_batch(BatchSpec& S) {
   if (c->profile_on) OBN_CUDA(cudaEventRecord(e1, c->stream));
   const size_t ev_first = c->ev_used - (c->profile_on ? 1 : 0);
 
+  // ---- sharded PC round: merge the ranks' first-passing indices, still on the device -----------
+  if (pc_round && world > 1)
+    if (int rc = comm_allreduce_min_i32(c, reinterpret_cast<int32_t*>(dout), S.n_slots)) return rc;
+
   // ---- download ------------------------------------------------------------------
   if (int rc = c->h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
-  if (out_bytes && !zc_out) OBN_CUDA(cudaMemcpyAsync(c->h_out.p, dout, out_bytes, cudaMemcpyDeviceToHost, c->stream));
-  if (S.defer) {                    // CI modes only (obn_ci_tests_submit)
-    obn_ctx::Pending& P = c->pending;
+  if (out_bytes) OBN_CUDA(cudaMemcpyAsync(c->h_out.p, dout, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+  obn_ctx::Pending P;
+  P.n_out = ci ? tests_mine : n;
+  P.n_results = n_out;
+  P.n_slots = pc_round ? S.n_slots : 0;
+  P.out_bytes = out_bytes;
+  P.in_bytes = in_bytes;
+  P.ev_first = ev_first;
+  P.alg_bytes = alg_bytes;
+  P.scanned_bytes = scanned_bytes;
+  P.increments = increments;
+  P.tables = n_mine;
+  P.want_p = S.p != nullptr;
+  if (S.defer) {                    // CI modes only (obn_ci_tests_submit / obn_pc_round_submit)
     P.active = true;
-    P.n_out = n_out;
-    P.out_bytes = out_bytes;
-    P.in_bytes = in_bytes;
-    P.ev_first = ev_first;
-    P.alg_bytes = pooled ? S.alg_bytes : alg_bytes;
-    P.want_p = S.p != nullptr;
+    c->pending = P;
     const auto now = std::chrono::steady_clock::now();
-    P.t_submitted_ms = std::chrono::duration<double, std::milli>(now.time_since_epoch()).count();
     c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
     c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(now - t_packed).count();
     return OBN_OK;
@@ -479,10 +513,10 @@ static int run_batch(BatchSpec& S) {
   c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(t_synced - t_packed).count();
   const unsigned char* hout = c->h_out.as<unsigned char>();
   if (ci) {
-    if (S.stat) memcpy(S.stat, hout, n_out * 8);
-    if (S.dof) memcpy(S.dof, hout + n_out * 8, n_out * 8);
-    if (S.p) memcpy(S.p, hout + n_out * 16, n_out * 8);
-  } else if (S.mode == MODE_BDEU_ONE) {
+    finish_batch(c, P, S.stat, S.dof, S.p, S.first);
+    return OBN_OK;
+  }
+  if (S.mode == MODE_BDEU_ONE) {
     memcpy(S.scores, hout, n * 8);
   } else if (S.mode == MODE_BDEU_ALL) {
     if (total_vars && !S.scores_dev) memcpy(S.scores, hout, total_vars * 8);
@@ -494,18 +528,7 @@ static int run_batch(BatchSpec& S) {
       o += cells[t];
     }
   }
-  if (c->profile_on) {
-    for (size_t i = ev_first; i < c->ev_used; ++i) {
-      float ms = 0;
-      cudaEventElapsedTime(&ms, c->ev_pool[i].first, c->ev_pool[i].second);
-      c->prof.count_kernel_ms += ms;
-    }
-    c->ev_used = ev_first;
-  }
-  c->prof.h2d_bytes += (double)in_bytes;
-  c->prof.d2h_bytes += (double)out_bytes;
-  c->prof.algorithmic_bytes += pooled ? S.alg_bytes : alg_bytes;
-  c->prof.tuples += n_out;
+  finish_batch(c, P, nullptr, nullptr, nullptr, nullptr);
   return OBN_OK;
 }
 
@@ -544,51 +567,38 @@ int obn_bdeu_subset_scores(obn_ctx* c, const obn_dataset* ds, const uint32_t* va
   return run_batch(S);
 }
 
+// Every CI entry point: plan the groups (tests over one variable set share its table), then one batch.
 static int ci_tests_impl(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
                          size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
-                         uint64_t* dof_out, double* p_out, bool defer) {
+                         uint64_t* dof_out, double* p_out, bool defer, const uint32_t* slot_of_test, size_t n_slots,
+                         double level, int shard, int32_t* first_out) {
   if (kind != OBN_CI_CHI2 && kind != OBN_CI_G2) return fail(OBN_ERR_INVALID, "Unsupported CI test type");
-  // Count reuse across the tests of one (x, y) pair.  OFF unless OBN_CI_POOL=1:
-  // parity-green on a B200 and 12-25 % faster on the 1M-row configs, but slower at 100k rows and
-  // not yet profiled (profiles/r1_ab_ci_pool_v3.jsonl).
-  const uint32_t pool_cells = (uint32_t)std::min(16384, std::max(0, env_int("OBN_CI_POOL_CELLS", 4096)));
-  // OBN_CI_POOL: 0 off (default), 1 on, 2 on for data sets of at least OBN_CI_POOL_MIN_ROWS rows (the measured
-  // crossover lies between 100k and 1M rows)
-  const int pool_mode = env_int("OBN_CI_POOL", 0);
-  const bool pool_on = pool_mode == 1 ||
-                       (pool_mode == 2 && ds && ds->n_rows >= (size_t)std::max(0, env_int("OBN_CI_POOL_MIN_ROWS", 500000)));
-  if (pool_on && pool_cells && n_tuples > 1 && c && ds && ds->ctx == c && offsets && x && y &&
-      (var_ids || !offsets[n_tuples]) && n_tuples < 0xffffffffull) {
-    // tables much larger than the row count are not worth sharing (the passes cost ~2 ops per joint cell)
-    const uint32_t cap = (uint32_t)std::min<uint64_t>(pool_cells, std::max<uint64_t>(64, ds->n_rows / 8));
-    static thread_local CiPoolPlan P;           // capacity reused across the rounds of a PC run
-    // pools of <= 4 conditioning variables have <= 6 columns: the row loop specialised on the column count
-    const uint32_t max_z = (uint32_t)std::max(1, env_int("OBN_CI_POOL_VARS", 4));
-    if (int rc = plan_ci_pools(ds->cards.data(), ds->n_vars, var_ids, offsets, n_tuples, x, y, cap, max_z, P)) return rc;
-    if (P.pools() < n_tuples) {     // at least one table is shared
-      BatchSpec S{c, ds, P.var_ids.data(), P.offsets.data(), P.pools(), MODE_CI_POOL};
-      S.role_a = P.x.data();
-      S.role_b = P.y.data();
-      S.kind = kind;
-      S.stat = stat_out;
-      S.dof = dof_out;
-      S.p = p_out;
-      S.n_out = n_tuples;
-      S.mem_off = P.mem_off.data();
-      S.members = P.members.data();
-      S.pool_cells = cap;
-      S.alg_bytes = (double)offsets[n_tuples] * (double)ds->n_rows;
-      S.defer = defer;
-      return run_batch(S);
-    }
+  if (!c || !ds) return fail(OBN_ERR_INVALID, "ctx or dataset is NULL");
+  if (ds->ctx != c) return fail(OBN_ERR_INVALID, "dataset belongs to another ctx");
+  if (n_tuples && (!offsets || !x || !y)) return fail(OBN_ERR_INVALID, "offsets, x or y is NULL");
+  if (n_tuples && offsets[n_tuples] && !var_ids) return fail(OBN_ERR_INVALID, "var_ids is NULL");
+  if (n_tuples >= 0x7f000000ull) return fail(OBN_ERR_UNSUPPORTED, "more than 2^31-2^24 tests in one batch");
+  if (n_slots) {
+    if (!slot_of_test && n_tuples) return fail(OBN_ERR_INVALID, "slot_of_test is NULL");
+    for (size_t t = 0; t < n_tuples; ++t)
+      if (slot_of_test[t] >= n_slots) return fail(OBN_ERR_RANGE, "slot_of_test[%zu] = %u out of range", t, slot_of_test[t]);
   }
-  BatchSpec S{c, ds, var_ids, offsets, n_tuples, MODE_CI};
-  S.role_a = x;
-  S.role_b = y;
+  static thread_local CiGroupPlan P;            // capacity reused across the rounds of a PC run
+  static const uint64_t zero_off[1] = {0};
+  if (int rc = plan_ci_groups(ds->cards.data(), ds->n_vars, var_ids, n_tuples ? offsets : zero_off, n_tuples, x, y, P)) return rc;
+  BatchSpec S{c, ds, P.var_ids.data(), P.offsets.data(), P.groups(), MODE_CI};
   S.kind = kind;
   S.stat = stat_out;
   S.dof = dof_out;
   S.p = p_out;
+  S.n_out = n_tuples;
+  S.mem_off = P.mem_off.data();
+  S.members = P.members.data();
+  S.slot_of_test = slot_of_test;
+  S.n_slots = n_slots;
+  S.level = level;
+  S.first = first_out;
+  S.shard = shard != 0;
   S.defer = defer;
   return run_batch(S);
 }
@@ -596,48 +606,59 @@ static int ci_tests_impl(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_
 int obn_ci_tests(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
                  size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
                  uint64_t* dof_out, double* p_out) {
-  return ci_tests_impl(c, ds, var_ids, offsets, n_tuples, x, y, kind, stat_out, dof_out, p_out, false);
+  return ci_tests_impl(c, ds, var_ids, offsets, n_tuples, x, y, kind, stat_out, dof_out, p_out, false, nullptr, 0, 0.0,
+                       0, nullptr);
 }
 
-// Same work as obn_ci_tests, split in two so that the caller's host thread can prepare its next
-// batch while the device runs this one: submit packs, uploads and enqueues everything (the input
+int obn_pc_round(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets, size_t n_tests,
+                 const uint32_t* x, const uint32_t* y, const uint32_t* slot_of_test, size_t n_slots, int kind,
+                 double level, int shard, int32_t* first_out) {
+  if (!n_slots) return OBN_OK;
+  if (!first_out) return fail(OBN_ERR_INVALID, "first_out is NULL");
+  return ci_tests_impl(c, ds, var_ids, offsets, n_tests, x, y, kind, nullptr, nullptr, nullptr, false, slot_of_test,
+                       n_slots, level, shard, first_out);
+}
+
+// The same two calls split in halves, so that the caller's host thread can prepare its next batch
+// while the device runs this one: submit plans, packs, uploads and enqueues everything (the input
 // arrays may be reused as soon as it returns); collect waits and writes the results.  One batch
 // may be in flight per ctx; every other batch call fails until it is collected.
 int obn_ci_tests_submit(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
                         size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, int want_p) {
   static double dummy;              // run_batch only asks whether p is wanted
-  return ci_tests_impl(c, ds, var_ids, offsets, n_tuples, x, y, kind, nullptr, nullptr, want_p ? &dummy : nullptr, true);
+  return ci_tests_impl(c, ds, var_ids, offsets, n_tuples, x, y, kind, nullptr, nullptr, want_p ? &dummy : nullptr, true,
+                       nullptr, 0, 0.0, 0, nullptr);
 }
 
-int obn_ci_tests_collect(obn_ctx* c, double* stat_out, uint64_t* dof_out, double* p_out) {
+int obn_pc_round_submit(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
+                        size_t n_tests, const uint32_t* x, const uint32_t* y, const uint32_t* slot_of_test,
+                        size_t n_slots, int kind, double level, int shard) {
+  if (!n_slots) return OBN_OK;
+  return ci_tests_impl(c, ds, var_ids, offsets, n_tests, x, y, kind, nullptr, nullptr, nullptr, true, slot_of_test,
+                       n_slots, level, shard, nullptr);
+}
+
+static int collect_impl(obn_ctx* c, double* stat_out, uint64_t* dof_out, double* p_out, int32_t* first_out, bool round) {
   if (!c) return fail(OBN_ERR_INVALID, "ctx is NULL");
   obn_ctx::Pending& P = c->pending;
   if (!P.active) return OBN_OK;     // nothing was submitted (an empty batch): nothing to hand out
+  if (round != (P.n_slots != 0)) return fail(OBN_ERR_INVALID, "the batch in flight was submitted by the other submit call");
   if (p_out && !P.want_p) return fail(OBN_ERR_INVALID, "p-values were not requested at submit");
   OBN_CUDA(cudaSetDevice(c->device));
   const auto t0 = std::chrono::steady_clock::now();
   P.active = false;
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-  const unsigned char* hout = c->h_out.as<unsigned char>();
-  const size_t n = P.n_out;
-  if (stat_out) memcpy(stat_out, hout, n * 8);
-  if (dof_out) memcpy(dof_out, hout + n * 8, n * 8);
-  if (p_out) memcpy(p_out, hout + n * 16, n * 8);
-  if (c->profile_on) {
-    for (size_t i = P.ev_first; i < c->ev_used; ++i) {
-      float ms = 0;
-      cudaEventElapsedTime(&ms, c->ev_pool[i].first, c->ev_pool[i].second);
-      c->prof.count_kernel_ms += ms;
-    }
-    c->ev_used = P.ev_first;
-  }
-  c->prof.h2d_bytes += (double)P.in_bytes;
-  c->prof.d2h_bytes += (double)P.out_bytes;
-  c->prof.algorithmic_bytes += P.alg_bytes;
-  c->prof.tuples += n;
+  finish_batch(c, P, stat_out, dof_out, p_out, first_out);
   return OBN_OK;
 }
 
+int obn_ci_tests_collect(obn_ctx* c, double* stat_out, uint64_t* dof_out, double* p_out) {
+  return collect_impl(c, stat_out, dof_out, p_out, nullptr, false);
+}
+
+int obn_pc_round_collect(obn_ctx* c, int32_t* first_out) {
+  return collect_impl(c, nullptr, nullptr, nullptr, first_out, true);
+}
 
 }  // extern "C"

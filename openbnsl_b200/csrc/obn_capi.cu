@@ -98,7 +98,8 @@ void obn_ctx_destroy(obn_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_scratch, &c->d_tickets}) b->release();
+  obn_comm_destroy(c);
+  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_scratch, &c->d_tickets, &c->d_scalar}) b->release();
   c->lut.release();
   c->es_pool.release();
   if (c->ds_cache) cudaFree(c->ds_cache);
@@ -120,6 +121,26 @@ void obn_ctx_destroy(obn_ctx* c) {
 }
 
 void* obn_ctx_stream(obn_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int obn_ctx_set_option(obn_ctx* c, const char* name, double value) {
+  if (!c || !name) return fail(OBN_ERR_INVALID, "obn_ctx_set_option: NULL argument");
+  const std::string k(name);
+  const int v = (int)value;
+  if (k == "threads_per_sm") c->tune.threads_per_sm = std::max(32, v);
+  else if (k == "force_threads") c->tune.force_threads = v;
+  else if (k == "force_splits") c->tune.force_splits = v;
+  else if (k == "streams") c->tune.streams = std::max(1, v);
+  else if (k == "lattice_budget_gb") c->tune.lattice_budget_gb = std::max(1, v);
+  else if (k == "lattice_max_l") c->tune.lattice_max_l = std::max(1, v);
+  else if (k == "lattice_bottom") c->tune.lattice_bottom = v;
+  else if (k == "lattice_reorder") c->tune.lattice_reorder = v;
+  else if (k == "lattice_graph") c->tune.lattice_graph = v;
+  else if (k == "lattice_lanes") c->tune.lattice_lanes = v;
+  else if (k == "lattice_no_lut") c->tune.lattice_no_lut = v;
+  else if (k == "debug") c->tune.debug = v;
+  else return fail(OBN_ERR_INVALID, "unknown option '%s'", name);
+  return OBN_OK;
+}
 
 int obn_dataset_upload(obn_ctx* c, const uint8_t* col_major, size_t n_vars, size_t n_rows,
                        size_t row_stride, const uint32_t* cards, obn_dataset** out) {
@@ -221,7 +242,8 @@ int obn_profile_read(obn_ctx* c, obn_profile* out, int reset) {
 
 }  // extern "C"
 
-#include "obn_ci_pool.inl"
+#include "obn_ci_groups.inl"
+#include "obn_comm.inl"
 #include "obn_batch.inl"
 #include "obn_es.inl"
 #include "obn_lattice.inl"

@@ -28,16 +28,15 @@
 
 namespace obn {
 
-constexpr int kPoolMembers = 32;   // members of one pool (plan_ci_pools: kPoolMaxMembers)
+constexpr int kGroupMembers = 32;   // CI tests that may share one table (plan_ci_groups splits larger groups)
 
 struct CtaTuple {            // per-CTA tuple description in shared memory
-  const uint8_t* col[kMaxTupleVars];   // column pointers in KERNEL digit order
-  uint32_t card[kMaxTupleVars];        // cards in kernel digit order
-  uint32_t ref_card[kMaxTupleVars];    // cards in ascending-var (reference) order
+  const uint8_t* col[kMaxTupleVars];   // column pointers, ascending var ids (reference key order)
+  uint32_t card[kMaxTupleVars];        // their cardinalities
   // column groups (kernel order): consecutive columns whose cards multiply to <= 256 are folded
   // with packed 8-bit arithmetic (4 rows per IMAD) and only the group keys are widened
   uint32_t gcells[kMaxTupleVars];      // cells of the group that ends at column i (0: not a group end)
-  uint32_t rx, ry;
+  uint32_t weight[kMaxTupleVars];      // radix weight of digit i (contingency_table.h:43-49: the last digit has weight 1)
   int child_pos;             // BDEU_ONE: position of the child in reference order
   unsigned int ticket;
 };
@@ -138,7 +137,13 @@ __device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* base) {
   for (int r = 0; r < 16; ++r) {
     const uint32_t f = key.get(r);
     unsigned int* p = reinterpret_cast<unsigned int*>(base + (SCALE4 ? (size_t)f : ((size_t)f << 2)));
-    atomicAdd(p, 1u);      // TIER_SMEM: ATOMS.POPC.INC.32   TIER_GLOBAL: RED.E.ADD
+    if (TIER == TIER_GLOBAL) {
+      // non-returning reduction (REDG.E.ADD): a plain atomicAdd compiles to ATOMG here, which makes
+      // every row wait for an L2 round trip it has no use for
+      asm volatile("red.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
+    } else {
+      atomicAdd(p, 1u);    // ATOMS.POPC.INC.32
+    }
   }
 }
 
@@ -226,120 +231,7 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
   }
 }
 
-// Pools of more than six columns (POOL kernels, A.wide_prefetch): like scan_rows_any, but the first
-// eight columns of the NEXT 16-row vector are requested before the increments of the current one,
-// so that their L2 latency hides behind the ATOMS instead of being paid twice per vector (the A/B
-// of round 1 has wide pools 20 % slower than narrow ones on C4: scan_rows_any exposes one load
-// round trip per four columns).  UNMEASURED: written after the round's GPU budget was spent; off
-// unless OBN_CI_POOL_WIDE=1.
 template <int KW, int TIER, bool SCALE4>
-__device__ __forceinline__ void scan_rows_wide(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
-                                               uint32_t v_end, uint32_t tid, uint32_t nthr) {
-  uint4 pre[8];
-  uint32_t v = v_begin + tid;
-  if (v < v_end) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (j < k) pre[j] = ld_codes16(T.col[j] + ((size_t)v << 4));
-  }
-  for (; v < v_end; v += nthr) {
-    const size_t off = (size_t)v << 4;
-    KeyVec<KW> key;
-    KeyVec<8> part;
-    bool have_part = false, have_key = false;
-#pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (j < k) fold_column<KW>(part, key, have_part, have_key, pre[j], T.card[j], T.gcells[j]);
-    for (int i = 8; i < k; i += 4) {          // columns beyond the prefetch window (rare)
-      uint4 c[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (i + j < k) c[j] = ld_codes16(T.col[i + j] + off);
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
-    }
-    const uint32_t vn = v + nthr;
-    if (vn < v_end) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (j < k) pre[j] = ld_codes16(T.col[j] + ((size_t)vn << 4));
-    }
-    count16<KW, TIER, SCALE4>(key, base);
-  }
-}
-
-// Pools of any width, rows staged through shared memory by the TMA engine (POOL kernels,
-// A.wide_prefetch == 2).  A tile is blockDim.x 16-row vectors of every column of the pool: thread 0
-// arms `full[s]` with the tile's byte count and issues one 1-D bulk copy per column
-// (cp.async.bulk ... mbarrier::complete_tx::bytes); every thread then reads its vector of each
-// column with one conflict-free LDS.128, arrives on `empty[s]` as soon as its reads are done (the
-// increments do not need the slot any more) and applies its 16 increments.  kTmaStages tiles are in
-// flight; a slot is refilled one tile late, so that thread 0 rarely waits for the other warps.
-// No registers are spent on prefetch, so the loop does not care how wide the pool is.
-// UNMEASURED and never run: written after round 1's GPU budget was spent (OBN_CI_POOL_WIDE=2).
-constexpr int kTmaStages = 3;
-
-template <int KW, int TIER, bool SCALE4>
-__device__ __forceinline__ void scan_rows_tma(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
-                                              uint32_t v_end, uint32_t tid, uint32_t nthr, unsigned char* stage,
-                                              uint64_t* full, uint64_t* empty) {
-  const uint32_t tv = nthr;                               // vectors per tile
-  const uint32_t col_bytes = tv << 4, stage_bytes = (uint32_t)k * col_bytes;
-  const uint32_t n_tiles = (v_end > v_begin) ? (v_end - v_begin + tv - 1) / tv : 0;
-  if (tid == 0) {
-    for (int s = 0; s < kTmaStages; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], nthr);
-    }
-    mbar_fence_init();
-  }
-  __syncthreads();
-  auto issue = [&](uint32_t tile) {                       // thread 0 only
-    const uint32_t s = tile % kTmaStages;
-    const uint32_t v0 = v_begin + tile * tv;
-    const uint32_t bytes = min(tv, v_end - v0) << 4;
-    mbar_arrive_expect_tx(&full[s], (uint32_t)k * bytes);
-    for (int j = 0; j < k; ++j)
-      bulk_g2s(stage + s * stage_bytes + (uint32_t)j * col_bytes, T.col[j] + ((size_t)v0 << 4), bytes, &full[s]);
-  };
-  if (tid == 0)
-    for (uint32_t t = 0; t < n_tiles && t < (uint32_t)kTmaStages; ++t) issue(t);
-  for (uint32_t tile = 0; tile < n_tiles; ++tile) {
-    const uint32_t s = tile % kTmaStages;
-    mbar_wait(&full[s], (tile / kTmaStages) & 1u);
-    const uint32_t v = v_begin + tile * tv + tid;
-    const bool valid = v < v_end;
-    KeyVec<KW> key;
-    if (valid) {
-      const unsigned char* src = stage + s * stage_bytes + (tid << 4);
-      KeyVec<8> part;
-      bool have_part = false, have_key = false;
-      for (int i = 0; i < k; i += 4) {
-        uint4 c[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (i + j < k) c[j] = *reinterpret_cast<const uint4*>(src + (uint32_t)(i + j) * col_bytes);
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
-      }
-    }
-    mbar_arrive(&empty[s]);                               // this thread is done with the slot
-    if (valid) count16<KW, TIER, SCALE4>(key, base);
-    if (tid == 0 && tile >= 1) {                          // refill the slot of the previous tile
-      const uint32_t pt = tile - 1, nt = pt + kTmaStages;
-      if (nt < n_tiles) {
-        mbar_wait(&empty[pt % kTmaStages], (pt / kTmaStages) & 1u);
-        issue(nt);
-      }
-    }
-  }
-}
-
-// POOL = true is the MODE_CI_POOL variant (a separate instantiation, so that the default
-// kernels compile exactly as they did without it).
-template <int KW, int TIER, bool SCALE4, bool POOL = false>
 __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ CtaTuple T;
@@ -357,33 +249,16 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   const uint32_t cells = hdr.w;
 
   // ---- tuple prologue (one warp, one lane per variable) ---------------------
-  // desc[i] = var_id | (card-1) << 24, ascending var ids.  Kernel digit order:
-  // conditioning variables first (most significant), then x, then y, so that
-  // every Z-slice is a contiguous rx*ry block laid out like citest.h:83.
+  // desc[i] = var_id | (card-1) << 24, ascending var ids = the digits of the reference key, most
+  // significant first (contingency_table.h:43-49), which is also the order the table is built in.
   if (tid < 32) {
-    uint32_t xa = 0xffffffffu, ya = 0xffffffffu, child = 0xffffffffu;
-    if (POOL || A.mode == MODE_CI) {
-      const uint2 r = __ldg(&A.roles[lt]);
-      xa = r.x; ya = r.y;                                        // host stores x < y (citest.h:48)
-    } else if (A.mode == MODE_BDEU_ONE) {
-      child = __ldg(&A.roles[lt]).x;
-    }
+    const uint32_t child = (A.mode == MODE_BDEU_ONE) ? __ldg(&A.roles[lt]).x : 0xffffffffu;
     const bool live = (int)tid < k;
     const uint32_t d = live ? __ldg(&A.desc[hdr.y + tid]) : 0u;
     const uint32_t v = d & 0xffffffu, c = (d >> 24) + 1u;
-    const bool is_x = live && v == xa, is_y = live && v == ya;
-    const unsigned m_z = __ballot_sync(0xffffffffu, live && !is_x && !is_y);
-    const int n_z = __popc(m_z);
-    int pos;
-    if (is_x) pos = n_z;
-    else if (is_y) pos = n_z + 1;
-    else pos = __popc(m_z & ((1u << tid) - 1u));
     if (live) {
-      T.col[pos] = A.data + (size_t)v * A.stride;
-      T.card[pos] = c;
-      T.ref_card[tid] = c;
-      if (is_x) T.rx = c;
-      if (is_y) T.ry = c;
+      T.col[tid] = A.data + (size_t)v * A.stride;
+      T.card[tid] = c;
     }
     const unsigned m_child = __ballot_sync(0xffffffffu, live && v == child);
     __syncwarp();
@@ -396,24 +271,20 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
         T.gcells[i] = close ? g : 0u;
         if (close) g = 1;
       }
+      uint32_t w = 1;
+      for (int i = k - 1; i >= 0; --i) {
+        T.weight[i] = w;
+        w *= T.card[i];
+      }
     }
   }
 
   // ---- table + epilogue scratch (zeroed while the descriptor loads are in flight)
   int32_t* tab;
   int32_t* wscratch;                // per-warp epilogue scratch
-  int32_t* mbuf0 = nullptr;         // MODE_CI_POOL: ping-pong buffers of the marginalisation passes
-  int32_t* mbuf1 = nullptr;
   if (TIER == TIER_SMEM) {
     tab = reinterpret_cast<int32_t*>(smem_raw);
-    size_t o = ((size_t)cells * 4u + 15u) & ~(size_t)15u;
-    if (POOL && cells <= A.pool_cells) {   // cells/2 and cells/4 ints (run_batch sizes the launch the same way)
-      mbuf0 = reinterpret_cast<int32_t*>(smem_raw + o);
-      o += ((size_t)(cells / 2u) * 4u + 15u) & ~(size_t)15u;
-      mbuf1 = reinterpret_cast<int32_t*>(smem_raw + o);
-      o += ((size_t)(cells / 4u) * 4u + 15u) & ~(size_t)15u;
-    }
-    wscratch = reinterpret_cast<int32_t*>(smem_raw + o);
+    wscratch = reinterpret_cast<int32_t*>(smem_raw + (((size_t)cells * 4u + 15u) & ~(size_t)15u));
     for (uint32_t i = tid; i < cells; i += nthr) tab[i] = 0;
   } else {
     tab = A.scratch + A.scratch_off[lt];
@@ -435,20 +306,7 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     case 4: scan_rows_k<KW, TIER, SCALE4, 4>(T, base, v_begin, v_end, tid, nthr); break;
     case 5: scan_rows_k<KW, TIER, SCALE4, 5>(T, base, v_begin, v_end, tid, nthr); break;
     case 6: scan_rows_k<KW, TIER, SCALE4, 6>(T, base, v_begin, v_end, tid, nthr); break;
-    default:
-      if constexpr (POOL) {
-        __shared__ __align__(8) uint64_t tma_bar[2 * kTmaStages];
-        if (A.wide_prefetch == 2)
-          scan_rows_tma<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr, smem_raw + A.stage_off, tma_bar,
-                                          tma_bar + kTmaStages);
-        else if (KW != 8 && A.wide_prefetch == 1)
-          scan_rows_wide<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
-        else
-          scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
-      } else {
-        scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr);
-      }
-      break;
+    default: scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr); break;
   }
   if (tid == 0) {
     if (k == 0) {
@@ -490,43 +348,47 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   }
 
   // ---- fused epilogue -------------------------------------------------------
-  if constexpr (POOL) {
-    // one joint table, many tests: every member's (Z, x, y) table is summed out of the joint
-    // table in shared memory and goes through the same epilogue as a directly counted one
-    // (tables above A.pool_cells, in particular every global-tier one, are single tests that
-    // keep every digit: plan_ci_pools).  The p-values wait until every member has its statistic
+  if (A.mode == MODE_CI) {
+    // one table, every test asked over its variable set: member (px, py) reads the table with x at
+    // digit px and y at digit py (CiGeom).  The p-values wait until every member has its statistic
     // and are then evaluated by one thread per member instead of serially by thread 0.
-    __shared__ double m_stat[kPoolMembers];
-    __shared__ unsigned long long m_dof[kPoolMembers];
-    __shared__ uint32_t m_id[kPoolMembers];
+    __shared__ double m_stat[kGroupMembers];
+    __shared__ unsigned long long m_dof[kGroupMembers];
+    __shared__ uint32_t m_id[kGroupMembers];
     const uint32_t m_begin = __ldg(&A.mem_off[t]), m_end = __ldg(&A.mem_off[t + 1]);
     for (uint32_t m = m_begin; m < m_end; ++m) {
       const uint2 mem = __ldg(&A.members[m]);
-      const int32_t* mt = tab;
-      uint32_t mcells = cells;
-      if (mbuf0) mt = marginalise(tab, cells, T.card, k - 2, mem.y, mbuf0, mbuf1, mcells);
-      epilogue_ci(mt, mcells, T.rx, T.ry, A.kind, wscratch + (tid >> 5) * (T.rx + T.ry),
-                  red_d, red_u, &A.stat[mem.x], &A.dof[mem.x], nullptr);
-      if (tid == 0) {                 // thread 0 wrote them just now
-        m_stat[m - m_begin] = A.stat[mem.x];
-        m_dof[m - m_begin] = A.dof[mem.x];
+      const uint32_t px = mem.y & 0xffu, py = (mem.y >> 8) & 0xffu;
+      const CiGeom g(cells, T.card[px], T.card[py], T.weight[px], T.weight[py]);
+      double stat;
+      unsigned long long dof;
+      epilogue_ci(tab, g, A.kind, wscratch + (tid >> 5) * (g.rx + g.ry), red_d, red_u, stat, dof);
+      if (tid == 0) {
+        m_stat[m - m_begin] = stat;
+        m_dof[m - m_begin] = dof;
         m_id[m - m_begin] = mem.x;
       }
-      __syncthreads();                // the buffers are rewritten for the next member
     }
-    if (A.pval && tid < m_end - m_begin) A.pval[m_id[tid]] = pchisq(m_stat[tid], m_dof[tid]);   // citest.h:139
-  } else if (A.mode == MODE_CI) {
-    epilogue_ci(tab, cells, T.rx, T.ry, A.kind, wscratch + (tid >> 5) * (T.rx + T.ry),
-                red_d, red_u, &A.stat[t], &A.dof[t], A.pval ? &A.pval[t] : nullptr);
+    __syncthreads();
+    if (tid < m_end - m_begin) {
+      const uint32_t id = m_id[tid];
+      if (A.stat) A.stat[id] = m_stat[tid];
+      if (A.dof) A.dof[id] = m_dof[tid];
+      if (A.pval || A.first) {
+        const double p = pchisq(m_stat[tid], m_dof[tid]);                  // citest.h:139
+        if (A.pval) A.pval[id] = p;
+        if (A.first && p >= A.level) atomicMin(&A.first[__ldg(&A.slot_of_test[id])], (int32_t)id);   // :147
+      }
+    }
   } else if (A.mode == MODE_BDEU_ONE || A.mode == MODE_BDEU_ALL) {
     const int c0 = (A.mode == MODE_BDEU_ONE) ? T.child_pos : 0;
     const int c1 = (A.mode == MODE_BDEU_ONE) ? T.child_pos + 1 : k;
     double* out = (A.mode == MODE_BDEU_ONE) ? &A.scores[t] : &A.scores[hdr.y];
     if (A.lut) {
-      epilogue_bdeu_exact(tab, cells, k, T.ref_card, A.lut + (size_t)A.lut_ijk[t] * A.lut_stride,
+      epilogue_bdeu_exact(tab, cells, k, T.card, A.lut + (size_t)A.lut_ijk[t] * A.lut_stride,
                           A.lut, A.lut_stride, A.lut_ij + hdr.y, c0, c1, out);
     } else {
-      epilogue_bdeu_fast(tab, cells, k, T.ref_card, A.ess, c0, c1, red_d, out);
+      epilogue_bdeu_fast(tab, cells, k, T.card, A.ess, c0, c1, red_d, out);
     }
   } else {
     int32_t* out = A.counts_out + A.counts_off[t];

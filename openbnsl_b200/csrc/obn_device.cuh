@@ -12,9 +12,12 @@ constexpr int kMaxTupleVars = 32;   // a dense table has <= 2^31 cells => <= 31 
 // pchisq (reference include/citest/citest.h:17-21, which calls Boost.Math).
 // Power series for x < a+1, modified-Lentz continued fraction otherwise.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ double gamma_p(double a, double x) {
-  if (!(x > 0.0)) return 0.0;
-  if (isinf(x)) return 1.0;
+// Returns the UPPER tail Q = 1 - P.  In the continued-fraction branch Q is returned as computed
+// (the reference's 1 - cdf round trip, citest.h:20, flushes p below 2^-53 to 0; keeping Q differs
+// from it by at most 1.2e-16 absolute and cannot move a decision p >= level).
+__device__ __forceinline__ double gamma_q(double a, double x) {
+  if (!(x > 0.0)) return 1.0;
+  if (isinf(x)) return 0.0;
   const double lead = exp(-x + a * log(x) - lgamma(a));
   if (x < a + 1.0) {
     double ap = a, sum = 1.0 / a, del = sum;
@@ -25,7 +28,7 @@ __device__ __forceinline__ double gamma_p(double a, double x) {
       if (fabs(del) < fabs(sum) * 1e-17) break;
     }
     const double p = sum * lead;
-    return p > 1.0 ? 1.0 : p;
+    return p > 1.0 ? 0.0 : 1.0 - p;
   }
   const double tiny = 1e-300;
   double b = x + 1.0 - a, c = 1.0 / tiny, d = 1.0 / b, h = d;
@@ -41,14 +44,13 @@ __device__ __forceinline__ double gamma_p(double a, double x) {
     h *= del;
     if (fabs(del - 1.0) < 1e-16) break;
   }
-  double q = lead * h;
-  if (q > 1.0) q = 1.0;
-  return 1.0 - q;
+  const double q = lead * h;
+  return q > 1.0 ? 1.0 : q;
 }
 
 __device__ __forceinline__ double pchisq(double x, unsigned long long dof) {
   if (dof == 0) return (x == 0.0 ? 1.0 : 0.0);
-  return 1.0 - gamma_p(0.5 * (double)dof, 0.5 * x);
+  return gamma_q(0.5 * (double)dof, 0.5 * x);
 }
 
 // ---------------------------------------------------------------------------

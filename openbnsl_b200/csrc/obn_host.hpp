@@ -151,6 +151,12 @@ struct EsPool {
 };
 }  // namespace obn
 
+namespace obn {
+// "no test of this edge passed" in the device-side first[] array of a PC round: the array is
+// initialised with cudaMemsetAsync(0x7f), so every value >= kFirstNone means none
+static const int32_t kFirstNone = 0x7f000000;
+}  // namespace obn
+
 struct obn_dataset {
   obn_ctx* ctx = nullptr;
   uint8_t* data = nullptr;      // device, column-major, padded
@@ -175,6 +181,7 @@ struct obn_ctx {
   obn::EsPool es_pool;
   obn::DevBuf d_scratch;   // int32, kept all-zero between launches
   obn::DevBuf d_tickets;   // uint32, kept all-zero between launches
+  obn::DevBuf d_scalar;    // staging of small host values that go through a collective
   obn::PinBuf h_in, h_out;
   uint8_t* ds_cache = nullptr;  // device buffer of the last destroyed dataset, reused by the next upload
   size_t ds_cache_bytes = 0;
@@ -182,11 +189,27 @@ struct obn_ctx {
   // (obn_ci_tests_collect waits for them); at most one, it owns the staging buffers until then
   struct Pending {
     bool active = false;
-    size_t n_out = 0, out_bytes = 0, in_bytes = 0, ev_first = 0;
-    double alg_bytes = 0;
+    size_t n_out = 0;             // units this rank evaluated (tests / tuples)
+    size_t n_results = 0;         // CI: tests of the batch (= results handed out)
+    size_t n_slots = 0;           // PC round: edges of the round (0: a plain CI batch)
+    size_t out_bytes = 0, in_bytes = 0, ev_first = 0, tables = 0;
+    double alg_bytes = 0, scanned_bytes = 0, increments = 0;
     bool want_p = false;
-    double t_submitted_ms = 0;    // host clock at the end of submit (steady_clock, ms)
   } pending;
+  // launch policy of the counting kernels (obn_ctx_set_option; defaults from the sweep in
+  // profiles/r1_kernel_sweep.txt)
+  struct Tuning {
+    int threads_per_sm = 768;     // resident threads per SM a launch aims for
+    int force_threads = 0;        // != 0: CTA width of every launch (sweeps)
+    int force_splits = 0;         // != 0: row splits of every launch (sweeps)
+    int streams = 4;              // launches of one batch are forked over this many streams
+    // marginalisation lattice (obn_lattice.inl)
+    int lattice_budget_gb = 24, lattice_max_l = 20, lattice_bottom = 1, lattice_reorder = 1, lattice_graph = 1,
+        lattice_lanes = 2, lattice_no_lut = 0, debug = 0;
+  } tune;
+  // communicator between the per-GPU processes of one job (obn_comm_init): NCCL, owned by the ctx
+  void* comm = nullptr;           // ncclComm_t
+  int comm_rank = 0, comm_world = 1;
   // profiling
   bool profile_on = false;
   obn_profile prof = {};

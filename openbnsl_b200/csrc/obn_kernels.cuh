@@ -10,8 +10,7 @@
 
 namespace obn {
 
-enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3,
-                  MODE_CI_POOL = 4 };   // CI tests of one (x, y) pair sharing a joint table
+enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3 };
 enum Tier : int { TIER_SMEM = 0, TIER_GLOBAL = 1 };
 
 struct BatchArgs {
@@ -22,7 +21,7 @@ struct BatchArgs {
   // batch (device copies of the CSR arrays)
   const uint32_t* desc;     // [offsets[n]]  var_id | (card-1) << 24, ascending var ids per tuple
   const uint4* hdr;         // per launch tuple: {tuple id, desc offset, #vars, #cells}
-  const uint2* roles;       // per launch tuple: CI {x, y} with x < y; BDEU_ONE {child, -}
+  const uint2* roles;       // per launch tuple: BDEU_ONE {child, -}; unused otherwise
   int mode;
   int kind;                 // CI: 0 chi2, 1 G2
   double ess;
@@ -44,25 +43,52 @@ struct BatchArgs {
   int32_t* scratch;         // zero on entry, zero on exit
   const uint64_t* scratch_off;  // [launch tuples]
   unsigned int* tickets;        // [launch tuples], zero on entry and exit
-  // MODE_CI_POOL: the launch tuple is a POOL -- the joint table over (union of the members'
-  // conditioning sets, x, y); member m of pool q is the CI test members[m].x whose conditioning
-  // set is the subset members[m].y (bit i = i-th conditioning digit of the pool, kernel order)
-  const uint32_t* mem_off;  // [pools + 1], indexed by pool id (hdr.x)
+  // MODE_CI: the launch tuple is a GROUP -- the CI tests of the batch that are asked over the same
+  // variable set share ONE table (counted once, in reference key order); member m of group q is the
+  // test members[m].x whose x is digit (members[m].y & 0xff) and y digit (members[m].y >> 8) of the
+  // table, every other digit conditions (obn_ci_groups.inl)
+  const uint32_t* mem_off;  // [groups + 1], indexed by group id (hdr.x)
   const uint2* members;
-  uint32_t pool_cells;      // joint tables above this size are single tests: no pass buffers
-  int wide_prefetch;        // POOL kernels, tuples of more than six columns: 1 scan_rows_wide, 2 scan_rows_tma
-  uint32_t stage_off;       // scan_rows_tma: byte offset of the tile ring in dynamic shared memory (128-aligned)
+  // PC rounds (obn_pc_round): the decision p >= level (citest.h:147) is taken on the device and only
+  // the first passing test of every edge leaves it: first[slot_of_test[t]] = min(t) over passing tests
+  const uint32_t* slot_of_test;   // null unless a PC round
+  int32_t* first;
+  double level;
 };
 
 // ---------------------------------------------------------------------------
-// epilogues.  `tab` is the dense int32 table in KERNEL digit order (generic
-// pointer: shared or global).  All threads of the CTA participate.
+// epilogues.  `tab` is the dense int32 table in REFERENCE KEY ORDER (first variable most
+// significant, contingency_table.h:76-85; generic pointer: shared or global).  All threads of the
+// CTA participate.
 // ---------------------------------------------------------------------------
 
-// chi-square / G-square with per-slice observed-margin dof and Yates
-// (citest.h:86-137).  Kernel digit order puts x then y as the two fastest
-// digits, so slice s is the contiguous block tab[s*rx*ry ...) laid out
-// x_state * ry + y_state exactly like the reference's slice (citest.h:83).
+// chi-square / G-square with per-slice observed-margin dof and Yates (citest.h:86-137).
+// The reference groups the cells by slice_key = key - x_state*w_x - y_state*w_y (citest.h:77-78);
+// here the same slices are walked directly in the dense table.  With x at digit px and y at digit
+// py (px < py: citest.h:48 orders them and the table's digits ascend), a key splits as
+//     key = hi * (rx*wx) + xs * wx + mid * (ry*wy) + ys * wy + lo
+// (hi: digits above x, mid: between x and y, lo: below y), so slice s = (hi, mid, lo) starts at
+// hi*(rx*wx) + mid*(ry*wy) + lo and its cell (xs, ys) sits xs*wx + ys*wy further on -- laid out
+// x_state * ry + y_state exactly like the reference's slice vector (citest.h:83).  One table can
+// therefore serve every (x, y | rest) question over its variable set.
+struct CiGeom {
+  uint32_t rx, ry, wx, wy;
+  uint32_t n_lo, n_mid, mid_stride, hi_stride, n_slices;
+  __device__ __forceinline__ CiGeom(uint32_t cells, uint32_t rx_, uint32_t ry_, uint32_t wx_, uint32_t wy_)
+      : rx(rx_), ry(ry_), wx(wx_), wy(wy_) {
+    n_lo = wy;
+    mid_stride = ry * wy;
+    n_mid = wx / mid_stride;
+    hi_stride = rx * wx;
+    n_slices = cells / (rx * ry);
+  }
+  __device__ __forceinline__ uint32_t base(uint32_t s) const {
+    if (n_lo == 1u && n_mid == 1u) return s * hi_stride;      // x, y are the two fastest digits
+    const uint32_t t = s / n_lo, lo = s - t * n_lo;
+    const uint32_t hi = t / n_mid, mid = t - hi * n_mid;
+    return hi * hi_stride + mid * mid_stride + lo;
+  }
+};
 
 // one cell's contribution (citest.h:116-131)
 __device__ __forceinline__ double ci_cell(double obs, int ri, int cj, double n_total, bool yates, int kind) {
@@ -81,18 +107,18 @@ __device__ __forceinline__ double ci_cell(double obs, int ri, int cj, double n_t
 
 // Small slices (rx, ry <= 4, the common case for the named networks): ONE LANE
 // per slice, the slice held in registers.
-__device__ __forceinline__ void ci_slices_small(const int32_t* tab, uint32_t n_slices, uint32_t rx, uint32_t ry,
-                                                int kind, double& stat, unsigned long long& dof) {
-  const uint32_t sl = rx * ry;
-  for (uint32_t s = threadIdx.x; s < n_slices; s += blockDim.x) {
-    const int32_t* t = tab + (size_t)s * sl;
+__device__ __forceinline__ void ci_slices_small(const int32_t* tab, const CiGeom& g, int kind, double& stat,
+                                                unsigned long long& dof) {
+  const uint32_t rx = g.rx, ry = g.ry;
+  for (uint32_t s = threadIdx.x; s < g.n_slices; s += blockDim.x) {
+    const int32_t* t = tab + g.base(s);
     int o[4][4], rs[4] = {0, 0, 0, 0}, cs[4] = {0, 0, 0, 0};
     int tot = 0;
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int v = ((uint32_t)i < rx && (uint32_t)j < ry) ? t[i * ry + j] : 0;
+        const int v = ((uint32_t)i < rx && (uint32_t)j < ry) ? t[i * g.wx + j * g.wy] : 0;
         o[i][j] = v;
         rs[i] += v;
         cs[j] += v;
@@ -114,27 +140,26 @@ __device__ __forceinline__ void ci_slices_small(const int32_t* tab, uint32_t n_s
   }
 }
 
-// Any slice shape: one warp per slice, margins in per-warp scratch.
-__device__ __forceinline__ void ci_slices_any(const int32_t* tab, uint32_t n_slices, uint32_t rx, uint32_t ry,
-                                              int kind, int32_t* wscratch, double& stat,
-                                              unsigned long long& dof) {
+// Any slice shape: one warp per slice, margins in per-warp scratch (rx + ry ints).
+__device__ __forceinline__ void ci_slices_any(const int32_t* tab, const CiGeom& g, int kind, int32_t* wscratch,
+                                              double& stat, unsigned long long& dof) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  const uint32_t sl = rx * ry;
+  const uint32_t rx = g.rx, ry = g.ry, sl = rx * ry;
   int32_t* rs = wscratch;        // [rx]
   int32_t* cs = wscratch + rx;   // [ry]
-  for (uint32_t s = warp; s < n_slices; s += nw) {
-    const int32_t* t = tab + (size_t)s * sl;
+  for (uint32_t s = warp; s < g.n_slices; s += nw) {
+    const int32_t* t = tab + g.base(s);
     int tot = 0, robs = 0, cobs = 0;
     for (uint32_t i = lane; i < rx; i += 32) {
       int a = 0;
-      for (uint32_t j = 0; j < ry; ++j) a += t[i * ry + j];
+      for (uint32_t j = 0; j < ry; ++j) a += t[i * g.wx + j * g.wy];
       rs[i] = a;
       tot += a;
       robs += (a > 0);
     }
     for (uint32_t j = lane; j < ry; j += 32) {
       int a = 0;
-      for (uint32_t i = 0; i < rx; ++i) a += t[i * ry + j];
+      for (uint32_t i = 0; i < rx; ++i) a += t[i * g.wx + j * g.wy];
       cs[j] = a;
       cobs += (a > 0);
     }
@@ -150,90 +175,24 @@ __device__ __forceinline__ void ci_slices_any(const int32_t* tab, uint32_t n_sli
       for (uint32_t c = lane; c < sl; c += 32) {
         const uint32_t i = c / ry, j = c - i * ry;
         const int ri = rs[i], cj = cs[j];
-        if (ri > 0 && cj > 0) stat += ci_cell((double)t[c], ri, cj, n_total, yates, kind);
+        if (ri > 0 && cj > 0) stat += ci_cell((double)t[i * g.wx + j * g.wy], ri, cj, n_total, yates, kind);
       }
     }
     __syncwarp();
   }
 }
 
-__device__ __forceinline__ void epilogue_ci(const int32_t* tab, uint32_t cells, uint32_t rx,
-                                            uint32_t ry, int kind, int32_t* wscratch,
-                                            double* red_d, unsigned long long* red_u,
-                                            double* stat_out, unsigned long long* dof_out, double* p_out) {
-  const uint32_t n_slices = cells / (rx * ry);
+// Statistic and dof of (x at digit px, y at digit py | every other digit) from the table; the
+// result is valid in thread 0.
+__device__ __forceinline__ void epilogue_ci(const int32_t* tab, const CiGeom& g, int kind, int32_t* wscratch,
+                                            double* red_d, unsigned long long* red_u, double& stat_out,
+                                            unsigned long long& dof_out) {
   double stat = 0.0;
   unsigned long long dof = 0;
-  if (rx <= 4 && ry <= 4) ci_slices_small(tab, n_slices, rx, ry, kind, stat, dof);
-  else ci_slices_any(tab, n_slices, rx, ry, kind, wscratch, stat, dof);
-  stat = block_sum(stat, red_d);
-  dof = block_sum(dof, red_u);
-  if (threadIdx.x == 0) {
-    *stat_out = stat;
-    *dof_out = dof;
-    if (p_out) *p_out = pchisq(stat, dof);               // citest.h:139
-  }
-}
-
-// ---------------------------------------------------------------------------
-// MODE_CI_POOL: the table of (Z, x, y) from the joint table of (P, x, y), Z a subset of P, by
-// summing out the digits of P - Z one at a time, most significant first (so the weight of the
-// digit being removed is still its weight in the joint table).  Integer sums of the same rows:
-// the result IS the table the counting loop would have produced for (Z, x, y).
-// ---------------------------------------------------------------------------
-
-// one output cell of one pass: src viewed as [hi][c][w], out[j] = sum_d src[hi][d][lo], j = hi*w + lo
-__host__ __device__ __forceinline__ int32_t marg_cell(const int32_t* src, uint32_t j, uint32_t w, uint32_t c) {
-  const uint32_t hi = j / w, lo = j - hi * w;
-  const int32_t* p = src + (size_t)hi * c * w + lo;
-  int32_t a = 0;
-  for (uint32_t d = 0; d < c; ++d) a += p[(size_t)d * w];
-  return a;
-}
-
-// The pass schedule, shared by the kernel and its host replay (obn_ci_pool_marginalise).
-// card[0 .. n_z) are the pool's conditioning digits in kernel order; `cells` the joint table's.
-struct MargPasses {
-  uint32_t w, cur;          // weight of the digit last visited in the joint table; cells of the current table
-  int i;
-  __host__ __device__ MargPasses(uint32_t cells) : w(cells), cur(cells), i(0) {}
-  // next removed digit: its weight and cardinality, and the cells of the table after the pass
-  __host__ __device__ bool next(const uint32_t* card, int n_z, uint32_t keep, uint32_t& pw, uint32_t& pc,
-                                uint32_t& n_out) {
-    while (i < n_z) {
-      const uint32_t c = card[i];
-      w /= c;                                 // weight of digit i in the joint table
-      const bool kept = (keep >> i) & 1u;
-      ++i;
-      if (kept || c == 1u) continue;          // summing out a one-state digit changes nothing
-      // the digits removed so far were all more significant, the block below digit i is untouched:
-      // its weight in the current table is still w
-      cur /= c;
-      pw = w; pc = c; n_out = cur;
-      return true;
-    }
-    return false;
-  }
-};
-
-// All threads of the CTA.  buf0 holds >= cells/2 ints, buf1 >= cells/4 (every pass at least halves
-// the table: one-state digits are skipped); returns the table (tab itself when nothing is removed) and its size, visible to
-// every thread.
-__device__ __forceinline__ const int32_t* marginalise(const int32_t* tab, uint32_t cells, const uint32_t* card,
-                                                      int n_z, uint32_t keep, int32_t* buf0, int32_t* buf1,
-                                                      uint32_t& out_cells) {
-  const int32_t* src = tab;
-  int32_t* dst = buf0;
-  MargPasses it(cells);
-  uint32_t w, c, n_out;
-  while (it.next(card, n_z, keep, w, c, n_out)) {
-    for (uint32_t j = threadIdx.x; j < n_out; j += blockDim.x) dst[j] = marg_cell(src, j, w, c);
-    __syncthreads();
-    src = dst;
-    dst = (dst == buf0) ? buf1 : buf0;
-  }
-  out_cells = it.cur;
-  return src;
+  if (g.rx <= 4 && g.ry <= 4) ci_slices_small(tab, g, kind, stat, dof);
+  else ci_slices_any(tab, g, kind, wscratch, stat, dof);
+  stat_out = block_sum(stat, red_d);
+  dof_out = block_sum(dof, red_u);
 }
 
 __device__ __forceinline__ double bdeu_term(int n, double a, double lg_a) {

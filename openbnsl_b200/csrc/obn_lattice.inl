@@ -32,7 +32,7 @@ struct LatticePlan {
   std::vector<uint32_t> root_level_max;   // [h+1] max cells of a root at level k, in units of cells_low
 };
 
-static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes, int world, bool allow_bottom, LatticePlan& P) {
+static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes, int world, bool allow_bottom, int max_L_opt, LatticePlan& P) {
   const int n = (int)card.size();
   P.n = n;
   P.card = card;
@@ -40,7 +40,7 @@ static bool plan_lattice(const std::vector<uint32_t>& card, size_t budget_bytes,
   int bot = (allow_bottom && n >= kBotL) ? kBotL : 0;
   for (int v = n - bot; v < n; ++v)
     if (card[v] != 2) bot = 0;
-  const int max_L = std::min(n, std::max(1, env_int("OBN_LATTICE_MAX_L", 20)));
+  const int max_L = std::min(n, std::max(1, max_L_opt));
   if (max_L < bot) bot = 0;
   const double cells_bot = bot ? (double)kBotCells : 1.0;
   double joint = 1;
@@ -313,8 +313,15 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   OBN_CUDA(cudaMemGetInfo(&free_b, &total_b));
   const size_t pooled = c->es_pool.d_root.cap + c->es_pool.d_pp[0].cap + c->es_pool.d_pp[1].cap + c->es_pool.d_pp[2].cap +
                         c->es_pool.d_pp[3].cap;   // reusable
-  const size_t budget = std::min<size_t>((size_t)((free_b + pooled) * 0.7), (size_t)env_int("OBN_LATTICE_BUDGET_GB", 24) << 30);
-  const bool dbg = env_int("OBN_DEBUG", 0) != 0;
+  // The plan (tier split, F layout, all-gather slice) follows from the budget, so every rank must plan
+  // from the SAME number: the minimum over the ranks (one small all-reduce); without a communicator a
+  // multi-rank caller gets the fixed cap alone, independent of what happens to be free on each GPU.
+  uint64_t budget64 = (uint64_t)c->tune.lattice_budget_gb << 30;
+  if (world == 1 || c->comm) budget64 = std::min<uint64_t>(budget64, (uint64_t)((free_b + pooled) * 0.7));
+  if (world > 1 && c->comm)
+    if (int rc = comm_min_u64_host(c, &budget64)) return rc;
+  const size_t budget = (size_t)budget64;
+  const bool dbg = c->tune.debug != 0;
   auto t_dbg = std::chrono::steady_clock::now();
   auto lap = [&](const char* what) {
     if (!dbg) return;
@@ -323,7 +330,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     fprintf(stderr, "[obn_es_lattice] %-14s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_dbg).count());
     t_dbg = now;
   };
-  const bool use_graph = env_int("OBN_LATTICE_GRAPH", 1) != 0;
+  const bool use_graph = c->tune.lattice_graph != 0;
   const size_t combs = (size_t)1 << n;
   EsPool& pool = c->es_pool;
   LatticeGraphCache& G = pool.lattice;
@@ -334,9 +341,9 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     uint64_t ess_bits = 0;
     memcpy(&ess_bits, &e->ess, 8);
     k.insert(k.end(), {(uint64_t)n, (uint64_t)ds->n_rows, ess_bits, (uint64_t)rank, (uint64_t)world,
-                       (uint64_t)env_int("OBN_LATTICE_BUDGET_GB", 24), (uint64_t)env_int("OBN_LATTICE_BOTTOM", 1),
-                       (uint64_t)env_int("OBN_LATTICE_MAX_L", 20), (uint64_t)env_int("OBN_LATTICE_NO_LUT", 0),
-                       (uint64_t)env_int("OBN_LATTICE_REORDER", 1), (uint64_t)env_int("OBN_LATTICE_LANES", 2)});
+                       (uint64_t)budget, (uint64_t)c->tune.lattice_bottom,
+                       (uint64_t)c->tune.lattice_max_l, (uint64_t)c->tune.lattice_no_lut,
+                       (uint64_t)c->tune.lattice_reorder, (uint64_t)c->tune.lattice_lanes});
     for (int v = 0; v < n; ++v) k.push_back(ds->cards[v]);
     for (const DevBuf* d : {&pool.d_F, &pool.d_root, &pool.d_pp[0], &pool.d_pp[1], &pool.d_pp[2], &pool.d_pp[3], &pool.d_tasks, &pool.d_partials, &pool.d_lut_a, &pool.d_lutF, &pool.d_prog})
       k.push_back((uint64_t)(uintptr_t)d->p);
@@ -348,7 +355,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   // masks are translated to digit order by three small tables (es_f_index in obn_es.inl).
   std::vector<uint32_t> order(n);
   for (int v = 0; v < n; ++v) order[v] = (uint32_t)v;
-  if (env_int("OBN_LATTICE_BOTTOM", 1) != 0 && env_int("OBN_LATTICE_REORDER", 1) != 0 && n >= kBotL) {
+  if (c->tune.lattice_bottom != 0 && c->tune.lattice_reorder != 0 && n >= kBotL) {
     bool tail_binary = true;
     for (int v = n - kBotL; v < n; ++v) tail_binary &= ds->cards[v] == 2;
     std::vector<uint32_t> bin;
@@ -369,7 +376,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
   if (!hit) {
     G.clear();
     LatticePlan P;
-    if (!plan_lattice(cards_p, budget, world, env_int("OBN_LATTICE_BOTTOM", 1) != 0, P))
+    if (!plan_lattice(cards_p, budget, world, c->tune.lattice_bottom != 0, c->tune.lattice_max_l, P))
       return fail(OBN_ERR_UNSUPPORTED, "marginalisation lattice does not fit (joint table >= 2^31 cells or too little memory)");
     lap("plan");
     const int h = P.h, L = P.L, Lm = P.Lm;
@@ -386,7 +393,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     // stream lanes (own ping-pong pair each), so the small launches at the ends of one block's levels
     // overlap with the other lane's (matters when there are many small blocks, i.e. on several GPUs).
     const uint64_t pp_bytes = std::max<uint64_t>(buf_units * cells_all_high, 4) * 4;
-    const int lanes = (bot && env_int("OBN_LATTICE_LANES", 2) >= 2 && B / (uint32_t)world >= 2 &&
+    const int lanes = (bot && c->tune.lattice_lanes >= 2 && B / (uint32_t)world >= 2 &&
                        4 * pp_bytes + P.root_cells * 4 <= budget) ? 2 : 1;
     for (int i = 0; i < 2 * lanes; ++i)
       if (int rc = pool.d_pp[i].reserve(pp_bytes)) return rc;
@@ -481,7 +488,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
         distinct.erase(std::unique(distinct.begin(), distinct.end()), distinct.end());
       }
       const size_t stride = ds->n_rows + 1;
-      if (distinct.size() <= 256 && distinct.size() * stride * 8 <= ((size_t)2 << 30) && !env_int("OBN_LATTICE_NO_LUT", 0)) {
+      if (distinct.size() <= 256 && distinct.size() * stride * 8 <= ((size_t)2 << 30) && !c->tune.lattice_no_lut) {
         std::vector<double> a(distinct.size());
         for (size_t i = 0; i < distinct.size(); ++i) a[i] = e->ess / (double)(size_t)distinct[i];
         if (int rc = pool.d_lut_a.reserve(a.size() * 8)) return rc;

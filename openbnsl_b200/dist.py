@@ -5,11 +5,30 @@ collectives: all-reduce(min) of int32 "first passing
 candidate per edge" for PC, and an all-gather of score rows per lattice level
 for exhaustive search.  ``TorchComm`` adapts ``torch.distributed`` (NCCL over
 NVLink on GPUs, gloo in the CPU test-suite) to the ``comm`` argument of
-``openbnsllib.structure_learning.pc`` / ``exhaustive_search``.
+``openbnsllib.structure_learning.pc`` / ``exhaustive_search`` -- this is the HOST-SIDE communicator
+used by the CPU test-suite (gloo, world size 2) and kept as an A/B; the product path on GPUs is
+``init_native_comm`` below: NCCL owned by the library, below the C boundary.
 """
 from __future__ import annotations
 
 import numpy as np
+
+
+def init_native_comm(lib=None, group=None):
+    """Give this process's ctx the library's OWN NCCL communicator (obn_comm_init) and return the
+    ``comm=`` argument that selects it.  torch.distributed is used for one thing only: carrying the
+    128-byte NCCL unique id from rank 0 to the other ranks (any host-side channel would do).  After
+    this call the data-path collectives -- all-reduce(min) per PC round, all-gathers of the
+    exhaustive search -- are issued by libopenbnsl_b200 on its own device buffers and stream."""
+    import torch.distributed as dist
+    if lib is None:
+        import openbnsl_b200
+        lib = openbnsl_b200.openbnsllib
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    box = [lib.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    lib.comm_init(box[0], rank, world)
+    return lib.nccl_comm()
 
 
 class TorchComm:

@@ -32,9 +32,8 @@ class CountingEvaluator(OracleEvaluator):
 
 @pytest.mark.parametrize("seed", range(40))
 @pytest.mark.parametrize("overlap", [0, 1])
-def test_pc_driver_fuzz(seed, overlap, monkeypatch):
-    # overlap = 1: round r+1 is enumerated while round r is "in flight" (OBN_PC_OVERLAP, pc.cpp) -- same graphs
-    monkeypatch.setenv("OBN_PC_OVERLAP", str(overlap))
+def test_pc_driver_fuzz(seed, overlap):
+    # overlap = 1: round r+1 is enumerated while round r is "in flight" (pc(..., overlap=True), pc.cpp) -- same graphs
     net, codes, cards = case(seed)
     ods = oracle.Dataset(codes, cards)
     rng = np.random.default_rng(1000 + seed)
@@ -47,7 +46,7 @@ def test_pc_driver_fuzz(seed, overlap, monkeypatch):
         want = oracle.pc(ods, kind, level, depth, stable)
         for tb in (0, 1, 5):                                     # default rounds, one test per round, tiny rounds
             ev = CountingEvaluator(ods)
-            got = pdag_to_adj(L._testing.pc(net.n, ev, T, depth, stable, None, tb), net.n)
+            got = pdag_to_adj(L._testing.pc(net.n, ev, T, depth, stable, None, tb, False, bool(overlap)), net.n)
             assert (got == want).all(), (seed, stable, tb)
             assert (ev.submitted > 0) == bool(overlap and stable)    # the overlapped loop really ran
         if rdf is not None:

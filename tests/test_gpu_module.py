@@ -10,6 +10,7 @@ import oracle
 import openbnsl_b200
 from helpers import GOLDEN_SETS, close, load_golden, pdag_to_adj, ranked
 from openbnsl_b200 import networks as nw
+from openbnsl_b200 import structural_distance as sd
 
 pytestmark = pytest.mark.gpu
 L = openbnsl_b200.openbnsllib
@@ -156,22 +157,22 @@ def test_exhaustive_search_device_dp_equals_host_dp(max_parents, exact):
 
 
 @pytest.mark.parametrize("which,max_parents", [("mixed", 9), ("mixed", 3), ("binary", 11)])
-def test_exhaustive_search_lattice_mode(which, max_parents, monkeypatch):
+def test_exhaustive_search_lattice_mode(which, max_parents):
     """Fast mode: every local score is F(pa + child) - F(pa) with F from the marginalisation lattice
-    over the joint table.  The optimum must equal the exact-order path's within 1e-9 relative, and
-    the DAG it returns must really have that score (recomputed with the oracle's BDeu)."""
+    over the joint table.  The optimum must equal the exact-order path's within 1e-9 relative, the
+    DAG it returns must really have that score (recomputed with the oracle's BDeu), and -- the
+    reference's own criterion, pytest/structure_learning/test_exhaustive_search.py:26-30 over
+    helpers/structural_distance.py:95-96 -- its CPDAG must equal the exact-order DAG's CPDAG."""
     if which == "mixed":
         net = nw.random_network(10, 14, 3, [2, 3, 4, 2, 3, 2, 4, 2, 3, 2], seed=11)
     else:
         net = nw.random_binary(12, seed=9)
     codes, cards = ranked(net.sample(6000, 3))
     df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
-    monkeypatch.setenv("OBN_ES_LATTICE", "0")
-    L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=1)
+    g_exact = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=1, lattice=False)
     want = L.structure_learning.last_es_stats()
     assert not want["lattice"]
-    monkeypatch.setenv("OBN_ES_LATTICE", "1")
-    g = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=0)
+    g = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), max_parents, exact_order=0, lattice=True)
     got = L.structure_learning.last_es_stats()
     assert got["lattice"]
     assert got["tables"] == want["tables"] and got["scores"] == want["scores"]
@@ -184,6 +185,8 @@ def test_exhaustive_search_lattice_mode(which, max_parents, monkeypatch):
         assert len(pa) <= max_parents
         total += oracle.bdeu_local_score(ods, v, pa, 1.0)
     assert total == pytest.approx(got["best_score"], rel=1e-9)
+    assert np.array_equal(sd.pdag2cpdag(adj), sd.pdag2cpdag(pdag_to_adj(g_exact, net.n)))
+    assert np.array_equal(pdag_to_adj(g_exact, net.n), oracle.exhaustive_search(ods, 1.0, max_parents))
 
 
 @pytest.mark.parametrize("cards,max_l,no_lut", [
@@ -195,23 +198,26 @@ def test_exhaustive_search_lattice_mode(which, max_parents, monkeypatch):
     ([2, 3, 2, 2, 4, 2, 2, 3, 2, 2, 2], 20, 0),          # exactly 8 binary variables, scattered: digit order != variable order
     ([2, 2, 3, 2, 2, 2, 4, 2, 2, 2, 3, 2, 3], 11, 0),    # 9 binary variables, the last one is not binary; 4 blocks
 ])
-def test_lattice_bottom_tier_equals_hbm_tiers(cards, max_l, no_lut, monkeypatch):
+def test_lattice_bottom_tier_equals_hbm_tiers(cards, max_l, no_lut):
     """The shared-memory bottom tier (last 8 binary variables) and the all-HBM lattice build the same
     tables; F differs only by summation order (fixed point vs fp64), so the optimum agrees to 1e-11."""
     n = len(cards)
     net = nw.random_network(n, n + 4, 3, cards, seed=5)
     codes, cards_seen = ranked(net.sample(5000, 7))
     df = L.base.DataframeWrapper.from_codes(codes, net.names, cards_seen)
-    monkeypatch.setenv("OBN_ES_LATTICE", "1")
-    monkeypatch.setenv("OBN_LATTICE_MAX_L", str(max_l))
-    monkeypatch.setenv("OBN_LATTICE_NO_LUT", str(no_lut))
     out = {}
-    for bottom in ("0", "1", "1"):          # the second "1" run replays the cached graph
-        monkeypatch.setenv("OBN_LATTICE_BOTTOM", bottom)
-        g = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), n - 1, exact_order=0)
-        st = L.structure_learning.last_es_stats()
-        assert st["lattice"]
-        out.setdefault(bottom, []).append((st["best_score"], pdag_to_adj(g, n).tolist()))
+    try:
+        L.set_option("lattice_max_l", max_l)
+        L.set_option("lattice_no_lut", no_lut)
+        for bottom in ("0", "1", "1"):          # the second "1" run replays the cached graph
+            L.set_option("lattice_bottom", int(bottom))
+            g = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), n - 1, exact_order=0, lattice=True)
+            st = L.structure_learning.last_es_stats()
+            assert st["lattice"]
+            out.setdefault(bottom, []).append((st["best_score"], pdag_to_adj(g, n).tolist()))
+    finally:
+        for k, v in (("lattice_max_l", 20), ("lattice_no_lut", 0), ("lattice_bottom", 1)):
+            L.set_option(k, v)
     (s0, a0), = out["0"]
     (s1, a1), (s2, a2) = out["1"]
     assert s1 == s2 and a1 == a2                      # deterministic, cache hit or not
@@ -220,3 +226,9 @@ def test_lattice_bottom_tier_equals_hbm_tiers(cards, max_l, no_lut, monkeypatch)
     adj = np.array(a1)                                 # of the equivalence class than the fp64-order run)
     total = sum(oracle.bdeu_local_score(ods, v, [int(p) for p in np.nonzero(adj[:, v])[0]], 1.0) for v in range(n))
     assert total == pytest.approx(s1, rel=1e-9)
+    # identical structure up to Markov equivalence with the exact-order search and, through it, the oracle
+    g_exact = L.structure_learning.exhaustive_search(df, L.score.BDeu(1.0), n - 1, exact_order=1, lattice=False)
+    want = pdag_to_adj(g_exact, n)
+    assert np.array_equal(want, oracle.exhaustive_search(ods, 1.0, n - 1))
+    assert np.array_equal(sd.pdag2cpdag(adj), sd.pdag2cpdag(want))
+    assert np.array_equal(sd.pdag2cpdag(np.array(a0)), sd.pdag2cpdag(want))
