@@ -10,7 +10,9 @@
 //   6 ATOMS on a CTA-shared int32 table
 //   7 __match_any_sync aggregated ATOMS on a CTA-shared table
 //   8 variant 3 with two independent increments in flight (pairing)
-// usage: smem_incr <cells> <threads> <ctas_per_sm> <skew_pct>
+//   9 ATOMS on a CTA-shared table replicated R times, copy = lane & (R-1): word (cell * R + copy), so the
+//     lanes of one instruction spread over the banks whatever their cells (R = 32: conflict-free)
+// usage: smem_incr <cells> <threads> <ctas_per_sm> <skew_pct> [R]
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -32,7 +34,7 @@ struct Keys {
 };
 
 template <int V>
-__global__ void k(uint32_t cells, uint32_t iters, uint32_t skew, unsigned long long* out) {
+__global__ void k(uint32_t cells, uint32_t iters, uint32_t skew, unsigned long long* out, uint32_t R = 1) {
   extern __shared__ __align__(16) unsigned char sm[];
   const uint32_t tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5;
   size_t bytes;
@@ -40,7 +42,9 @@ __global__ void k(uint32_t cells, uint32_t iters, uint32_t skew, unsigned long l
   else if (V == 2 || V == 3 || V == 8) bytes = (size_t)((cells + 3) & ~3u) * T;
   else if (V == 4) bytes = (size_t)cells * T * 4;
   else if (V == 5) bytes = (size_t)cells * 4 * (T / 32);
+  else if (V == 9) bytes = (size_t)cells * 4 * R;
   else bytes = (size_t)cells * 4;
+  const uint32_t copy4 = (lane & (R - 1)) * 4, r4 = R * 4;
   for (uint32_t i = tid; i < bytes / 4; i += T) reinterpret_cast<uint32_t*>(sm)[i] = 0;
   __syncthreads();
   uint32_t s = blockIdx.x * 7919u + tid * 104729u + 1u;
@@ -62,6 +66,7 @@ __global__ void k(uint32_t cells, uint32_t iters, uint32_t skew, unsigned long l
       else if (V == 4) h32[c * T + tid] += 1;
       else if (V == 5) atomicAdd(&h32[warp * cells + c], 1u);
       else if (V == 6) atomicAdd(&h32[c], 1u);
+      else if (V == 9) atomicAdd(reinterpret_cast<uint32_t*>(sm + c * r4 + copy4), 1u);
       else if (V == 7) {
         const unsigned m = __match_any_sync(0xffffffffu, c);
         if ((m & ((1u << lane) - 1)) == 0) atomicAdd(&h32[c], (unsigned)__popc(m));
@@ -84,12 +89,13 @@ __global__ void k(uint32_t cells, uint32_t iters, uint32_t skew, unsigned long l
 }
 
 template <int V>
-static void run(uint32_t cells, int T, int occ, uint32_t skew) {
+static void run(uint32_t cells, int T, int occ, uint32_t skew, uint32_t R = 1) {
   size_t bytes;
   if (V == 0 || V == 1) bytes = (size_t)((cells + 1) & ~1u) * T * 2;
   else if (V == 2 || V == 3 || V == 8) bytes = (size_t)((cells + 3) & ~3u) * T;
   else if (V == 4) bytes = (size_t)cells * T * 4;
   else if (V == 5) bytes = (size_t)cells * 4 * (T / 32);
+  else if (V == 9) bytes = (size_t)cells * 4 * R;
   else bytes = (size_t)cells * 4;
   bytes = (bytes + 15) & ~(size_t)15;
   if (bytes > 227 * 1024) { printf("  v%d: smem too large\n", V); return; }
@@ -103,9 +109,9 @@ static void run(uint32_t cells, int T, int occ, uint32_t skew) {
   const uint32_t iters = 2000;
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
-  k<V><<<148 * use, T, bytes>>>(cells, 10, skew, out);
+  k<V><<<148 * use, T, bytes>>>(cells, 10, skew, out, R);
   cudaEventRecord(e0);
-  k<V><<<148 * use, T, bytes>>>(cells, iters, skew, out);
+  k<V><<<148 * use, T, bytes>>>(cells, iters, skew, out, R);
   cudaEventRecord(e1);
   cudaEventSynchronize(e1);
   float ms = 0;
@@ -113,6 +119,7 @@ static void run(uint32_t cells, int T, int occ, uint32_t skew) {
   const double incs = 148.0 * use * T * 16.0 * iters;
   int clk = 0;
   cudaDeviceGetAttribute(&clk, cudaDevAttrClockRate, 0);
+  if (V == 9) printf("  R=%u", R);
   printf("  v%d cells=%u T=%d ctas/sm=%d smem=%zuB: %.1f Ginc/s  (%.2f inc/clk/SM at %d MHz nominal) err=%s\n", V, cells, T, use,
          bytes, incs / ms * 1e-6, incs / ms * 1e-6 * 1e9 / (148.0 * clk * 1e3), clk / 1000, cudaGetErrorString(cudaGetLastError()));
   cudaFree(out);
@@ -124,6 +131,11 @@ int main(int argc, char** argv) {
   const int occ = argc > 3 ? atoi(argv[3]) : 8;
   const uint32_t skew = argc > 4 ? atoi(argv[4]) : 0;
   printf("cells=%u T=%d occ<=%d skew=%u/128\n", cells, T, occ, skew);
+  if (argc > 5) {                       // replication sweep only
+    run<6>(cells, T, occ, skew);
+    for (uint32_t R = 2; R <= 32; R *= 2) run<9>(cells, T, occ, skew, R);
+    return 0;
+  }
   run<0>(cells, T, occ, skew); run<1>(cells, T, occ, skew); run<2>(cells, T, occ, skew);
   run<3>(cells, T, occ, skew); run<4>(cells, T, occ, skew); run<5>(cells, T, occ, skew);
   run<6>(cells, T, occ, skew); run<7>(cells, T, occ, skew); run<8>(cells, T, occ, skew);

@@ -178,7 +178,8 @@ OBN_API int obn_pc_round(obn_ctx* ctx, const obn_dataset* ds,
  * reused as soon as it has returned.  collect waits for the results and writes them (any pointer
  * may be NULL; p_out only if want_p was set).  At most one batch is in flight per ctx: until it is
  * collected every other batch call on the ctx returns OBN_ERR_INVALID.  collect without a
- * submitted batch (or after submitting zero tuples) is a no-op. */
+ * submitted batch (or after submitting zero tuples) is a no-op that leaves the output arrays
+ * untouched: a caller of obn_pc_round_collect pre-fills first_out with INT32_MAX. */
 OBN_API int obn_ci_tests_submit(obn_ctx* ctx, const obn_dataset* ds,
                                 const uint32_t* var_ids, const uint64_t* offsets,
                                 size_t n_tuples, const uint32_t* x, const uint32_t* y,

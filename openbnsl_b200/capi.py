@@ -210,7 +210,8 @@ class Dataset:
 
     def close(self):
         if self._h:
-            load().obn_dataset_destroy(self._h)
+            if self.ctx._h:             # a ctx that is already gone took its device memory with it
+                load().obn_dataset_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
@@ -262,7 +263,7 @@ class Dataset:
         """obn_pc_round (or its submit / collect halves): first passing test index per edge slot."""
         n = len(offs) - 1
         slot = np.ascontiguousarray(np.asarray(slot_of_test, dtype=np.uint32))
-        first = np.zeros(max(1, n_slots), dtype=np.int32)
+        first = np.full(max(1, n_slots), 2**31 - 1, dtype=np.int32)    # collect leaves it untouched after an empty submit
         if split:
             _check(load().obn_pc_round_submit(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), n,
                                               _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), _ptr(slot, C.c_uint32),

@@ -160,9 +160,50 @@ def make_graphs(har):
     print("wrote graph_kat.json", os.path.getsize(os.path.join(HERE, "graph_kat.json")), "bytes")
 
 
+BIG_PC_CASES = [  # name, network, rows, seed, kind (0 chi2, 1 G2), level, max_cond_vars, stable
+    ("hepar2_like_20k", "hepar2_like", 20000, 4, 1, 0.05, 4, True),
+    ("hepar2_like_20k_nonstable", "hepar2_like", 20000, 4, 1, 0.05, 3, False),
+    ("munin1_like_20k", "munin1_like", 20000, 5, 0, 0.05, 3, True),
+    ("munin1_like_20k_g2", "munin1_like", 20000, 5, 1, 0.01, 2, True)]
+
+
+def make_big_pc(ref):
+    """pc_big.json: the STOCK reference pc() (bindings/submodules/structure_learning.cpp:31-37 ->
+    src/structure_learning/pc.cpp:76-86) on down-scaled stand-ins of BASELINE configs 4 and 5 -- the
+    same networks as the benchmark at a row count the serial reference finishes in minutes.  Depth >= 2
+    frontiers with cardinalities up to 21 and every table tier inside a real PC run are compared
+    PDAG for PDAG on the GPU (tests/test_gpu_module.py::test_pc_big_networks_match_reference)."""
+    import time
+    out = []
+    for name, netname, n_rows, seed, kind, level, mc, stable in BIG_PC_CASES:
+        net = getattr(nw, netname)()
+        codes = net.sample(n_rows, seed)
+        cols, cards = [], []
+        for v in range(net.n):
+            u, inv = np.unique(codes[:, v], return_inverse=True)
+            cols.append(inv.astype(np.uint8)); cards.append(len(u))
+        codes = np.stack(cols, axis=1)
+        df = ref.base.DataframeWrapper(nw.to_reference_frame(codes, net.names, cards))
+        T = ref.citest.ChiSquare(level) if kind == 0 else ref.citest.GSquare(level)
+        t0 = time.time()
+        g = ref.structure_learning.pc(df, T, mc, stable)
+        secs = time.time() - t0
+        arcs = [[p, v] for p in range(net.n) for v in range(net.n) if g.has_edge(p, v)]
+        out.append({"name": name, "network": netname, "n_rows": n_rows, "seed": seed, "kind": kind, "level": level,
+                    "max_cond_vars": mc, "stable": stable, "cards": cards, "arcs": arcs, "reference_seconds": secs,
+                    "codes_sha": int(np.frombuffer(codes.tobytes(), dtype=np.uint8).astype(np.uint64).sum())})
+        print(name, len(arcs), "arcs", "%.1f s" % secs, flush=True)
+    with open(os.path.join(HERE, "pc_big.json"), "w") as f:
+        json.dump(out, f)
+    print("wrote pc_big.json", os.path.getsize(os.path.join(HERE, "pc_big.json")), "bytes")
+
+
 def main():
     ref, har = oracle.reference_modules()
     assert ref is not None, "build oracle/_ref first (python oracle/build_ref.py)"
+    if "--big-pc" in sys.argv:
+        make_big_pc(ref)
+        return
     if "--sa" in sys.argv:
         make_sa(ref)
         return

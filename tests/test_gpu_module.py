@@ -108,6 +108,33 @@ def test_config0_asia_es_full_lattice_fast_and_exact():
     assert got_und == und - {(net.names.index("asia"), net.names.index("tub"))} or got_und == und
 
 
+def load_big_pc():
+    import json, os
+    from helpers import GOLDEN_DIR
+    with open(os.path.join(GOLDEN_DIR, "pc_big.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("case", load_big_pc(), ids=lambda c: c["name"])
+@pytest.mark.parametrize("target_batch", [0, 100000000])
+def test_pc_big_networks_match_reference(case, target_batch):
+    """Down-scaled stand-ins of BASELINE configs 4 and 5 (the benchmark's networks at 20 000 rows, where the
+    serial reference finishes): the STOCK reference pc() made the fixture (tests/golden/make_golden.py --big-pc);
+    depth >= 2 frontiers, cardinalities up to 21 and every table tier run inside a real PC call here and the
+    PDAG must be identical arc for arc -- with the default rounds (early exit) and with whole-depth rounds
+    (no early exit, maximal table sharing)."""
+    net = getattr(nw, case["network"])()
+    codes, cards = ranked(net.sample(case["n_rows"], case["seed"]))
+    assert cards == case["cards"]
+    assert int(np.frombuffer(codes.tobytes(), dtype=np.uint8).astype(np.uint64).sum()) == case["codes_sha"]
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+    T = L.citest.ChiSquare(case["level"]) if case["kind"] == 0 else L.citest.GSquare(case["level"])
+    for overlap in (False, True):
+        g = L.structure_learning.pc(df, T, case["max_cond_vars"], case["stable"], target_batch=target_batch, overlap=overlap)
+        arcs = [[p, v] for p in range(net.n) for v in range(net.n) if g.has_edge(p, v)]
+        assert arcs == case["arcs"]
+
+
 def test_config1_alarm_pc_full_size():
     net = nw.alarm()
     codes, cards = ranked(net.sample(100_000, 0))

@@ -60,3 +60,27 @@ def test_pc_small_alarm():
     for stable in (True, False):
         g = ref.structure_learning.pc(df, ref.citest.GSquare(0.01), 2, stable)
         assert (oracle.pc(ods, 1, 0.01, 2, stable) == pdag_to_adj(g, net.n)).all()
+
+
+def test_pc_full_config2_alarm_100k():
+    """BASELINE config 2 at full size through the STOCK reference entry point (pc.cpp:76-86, serial: about 25 s)
+    against the C restatement the GPU tests are checked with (tests/test_gpu_module.py::test_config1_alarm_pc_full_size)."""
+    net = nw.alarm()
+    codes, cards = ranked(net.sample(100_000, 0))
+    ods = oracle.Dataset(codes, cards)
+    df = ref.base.DataframeWrapper(nw.to_reference_frame(codes, net.names, cards))
+    g = ref.structure_learning.pc(df, ref.citest.GSquare(0.05), 4, True)
+    assert (oracle.pc(ods, 1, 0.05, 4, True) == pdag_to_adj(g, net.n)).all()
+
+
+def test_oracle_pc_matches_stock_reference_on_hepar2_like_20k():
+    """The fixture of the GPU test (tests/golden/pc_big.json, made by the stock reference) also pins the restatement:
+    70 variables, depth <= 3, non-stable order."""
+    import json, os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pc_big.json")) as f:
+        case = [c for c in json.load(f) if c["name"] == "hepar2_like_20k_nonstable"][0]
+    net = getattr(nw, case["network"])()
+    codes, cards = ranked(net.sample(case["n_rows"], case["seed"]))
+    assert cards == case["cards"]
+    adj = oracle.pc(oracle.Dataset(codes, cards), case["kind"], case["level"], case["max_cond_vars"], case["stable"])
+    assert [[p, v] for p in range(net.n) for v in range(net.n) if adj[p, v]] == case["arcs"]
