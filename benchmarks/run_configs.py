@@ -24,7 +24,8 @@ from openbnsl_b200 import networks as nw  # noqa: E402
 L = openbnsl_b200.openbnsllib
 COMM = None          # set in main() when launched under torchrun (one rank per GPU)
 RANK = 0
-PC_KW = {}           # extra keyword arguments of pc() from the command line (tb=<target_batch>, overlap=0/1, shard=<bytes>)
+PC_KW = {}
+OPTS = {}           # extra keyword arguments of pc() from the command line (tb=<target_batch>, overlap=0/1, shard=<bytes>)
 
 
 def peak():
@@ -90,7 +91,7 @@ def run_pc(name, net, n_rows, test, depth, what, reps=1):
             "evaluate_ms": st["evaluate_ms"], "resolve_ms": st["resolve_ms"], "data_gen_s": t_gen,
             "batches_per_depth": [int(x) for x in st["batches_per_depth"]], "tables": prof["tables"],
             "scanned_GB": prof["scanned_bytes"] / 1e9, "atoms_ceiling_ms": prof["increments"] / 4.65e12 * 1e3,
-            "collectives": prof["collectives"], "pc_kwargs": dict(PC_KW),
+            "collectives": prof["collectives"], "pc_kwargs": dict(PC_KW), "options": dict(OPTS),
             "adj_sha": int(sum((i + 1) * (j + 7) for i in range(net.n) for j in range(net.n) if g.has_edge(i, j)))})
 
 
@@ -166,6 +167,9 @@ def main():
             PC_KW["target_batch"] = int(a[3:]); args.remove(a)
         elif a.startswith("overlap="):
             PC_KW["overlap"] = bool(int(a[8:])); args.remove(a)
+        elif a.startswith("opt:"):                      # opt:<name>=<value> -> obn_ctx_set_option
+            name, val = a[4:].split("=")
+            L.set_option(name, float(val)); OPTS[name] = float(val); args.remove(a)
         elif a.startswith("shard="):
             PC_KW["shard_min_bytes"] = float(a[6:]); args.remove(a)
     which = args or ["c1", "c2", "c3", "c4", "c5"]

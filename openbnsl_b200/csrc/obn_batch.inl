@@ -56,17 +56,17 @@ static const uint32_t kClassCells[kNumClasses - 2] = {64, 256, 1024, 4096, 16384
 
 static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-template <int KW, int TIER, bool SCALE4>
+template <int KW, int TIER, bool SCALE4, bool REP = false>
 static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, size_t smem, cudaStream_t s) {
   // cudaFuncAttributeMaxDynamicSharedMemorySize is per device and a process may hold one ctx per
   // device: set it whenever a launch needs more than the default 48 KB (a few microseconds)
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4, REP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return e;
   }
   (void)cudaGetLastError();      // a launch reports only its own error, not a stale one
-  count_kernel<KW, TIER, SCALE4><<<grid, nthr, smem, s>>>(a);
+  count_kernel<KW, TIER, SCALE4, REP><<<grid, nthr, smem, s>>>(a);
   return cudaGetLastError();
 }
 
@@ -303,7 +303,7 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
-  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; };
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; };
   std::vector<Launch> launches;
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
   size_t max_scratch_ints = 0;
@@ -323,9 +323,24 @@ static int run_batch(BatchSpec& S) {
       // best geometry keeps about 768 threads per SM busy in total, with the widest CTA
       // that allows; row splits only pay when a launch has too few tuples to do that
       // (each split repeats the prologue and adds a merge through L2).
-      size_t tpt = target_threads / remaining;
+      // table copies (obn_count_kernel.cuh: Rep): the shared-memory classes 0..4, as many as the class's
+      // option says while the copies of one table stay within rep_max_kb
+      uint32_t rep_shift = 0;
+      if (g <= 4) {
+        rep_shift = (uint32_t)std::max(0, std::min(5, c->tune.rep_shift[g]));
+        while (rep_shift && ((size_t)max_cells << rep_shift) * 4 > (size_t)c->tune.rep_max_kb * 1024) --rep_shift;
+      }
+      const size_t table_bytes = global_tier ? 0
+                                 : align16((size_t)max_cells * 4) + (rep_shift ? ((size_t)max_cells << rep_shift) * 4 : 0);
+      const size_t tpt = target_threads / remaining;
       size_t p2 = 32;
       while (p2 * 2 <= tpt && p2 < 256) p2 <<= 1;
+      // shared memory may allow only a few CTAs per SM: each must then be wide enough to keep the SM busy
+      const size_t ctas_by_smem = std::max<size_t>(1, std::min<size_t>(32, (c->smem_optin + 1024) / (table_bytes + 2048)));
+      while (p2 * ctas_by_smem < (size_t)c->tune.threads_per_sm && p2 < 256) p2 <<= 1;
+      // copies pay with wide CTAs: eight warps on one set of copies (benchmarks/micro/smem_incr.cu variant 9:
+      // 23 increments/clk/SM at 256 threads against 19.7 with one warp per CTA)
+      if (rep_shift) p2 = 256;
       int nthr = (int)p2;
       int splits = 1;
       if (nthr == 256) {
@@ -338,7 +353,7 @@ static int run_batch(BatchSpec& S) {
       if (c->tune.force_splits)
         splits = std::max(1, std::min<int>(c->tune.force_splits, (int)std::max<uint32_t>(1u, n_vec)));
       const int nw = nthr / 32;
-      size_t smem = (global_tier ? 0 : align16((size_t)max_cells * 4)) + (size_t)nw * max_rxy * 4;
+      size_t smem = table_bytes + (size_t)nw * max_rxy * 4;
       smem = std::max<size_t>(align16(smem), 16);
       const bool need_scratch = splits > 1 || global_tier;
       size_t j = i, scratch_ints = 0;
@@ -354,7 +369,7 @@ static int run_batch(BatchSpec& S) {
       }
       uint32_t vps = (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false});
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, rep_shift});
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
       i = j;
     }
@@ -465,11 +480,12 @@ static int run_batch(BatchSpec& S) {
     a.tickets = c->d_tickets.as<unsigned int>() + L.begin;
     a.splits = L.splits;
     a.vec_per_split = L.vps;
+    a.rep_shift = L.rep_shift;
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
     cudaError_t e;
-    if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
-    else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
-    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
+    if (L.g == 0) e = launch_count<8, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
+    else if (L.g == 1) e = launch_count<8, TIER_SMEM, false, true>(a, grid, L.nthr, L.smem, st);
+    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
     else if (L.g == 5) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
     else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, st);
     if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "count_kernel launch failed: %s", cudaGetErrorString(e));

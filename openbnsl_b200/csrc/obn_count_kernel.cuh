@@ -129,14 +129,29 @@ struct KeyVec<32> {
   __device__ __forceinline__ uint32_t get(int r) const { return w[r]; }
 };
 
+// Replicated tables (REP kernels).  ATOMS applies one address per bank per pass, so the lanes of one
+// instruction that hit DIFFERENT cells of the same bank serialise: 1.5 passes per instruction at 64
+// cells, about 2.8 at 256 and 3.4 at 1 Ki on the PC frontiers (ncu: atom wavefronts per instruction),
+// which is what held the mid-size classes at 40 % of the increment ceiling.  With R copies of the
+// table interleaved cell-major -- word (cell * R + (lane & (R-1))) -- lane l can only meet lanes
+// l + R, l + 2R, ... in its bank: at R = 16 at most two addresses per bank, which fits the two
+// clocks an ATOMS instruction occupies anyway (benchmarks/micro/smem_incr.cu variant 9).  The copies
+// are summed into one compact table before the epilogue.
+struct Rep {
+  uint32_t mul;      // byte distance between consecutive cells: 4 * R (SCALE4 keys are pre-multiplied by 4: R)
+  uint32_t copy4;    // byte offset of this lane's copy: 4 * (lane & (R-1))
+};
+
 // 16 increments for one key vector.  `base` is the table as a byte pointer.
-template <int KW, int TIER, bool SCALE4>
-__device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* base) {
+template <int KW, int TIER, bool SCALE4, bool REP>
+__device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* base, const Rep& rep) {
   if (SCALE4) key.scale4();
 #pragma unroll
   for (int r = 0; r < 16; ++r) {
     const uint32_t f = key.get(r);
-    unsigned int* p = reinterpret_cast<unsigned int*>(base + (SCALE4 ? (size_t)f : ((size_t)f << 2)));
+    unsigned int* p;
+    if (REP) p = reinterpret_cast<unsigned int*>(base + (f * rep.mul + rep.copy4));
+    else p = reinterpret_cast<unsigned int*>(base + (SCALE4 ? (size_t)f : ((size_t)f << 2)));
     if (TIER == TIER_GLOBAL) {
       // non-returning reduction (REDG.E.ADD): a plain atomicAdd compiles to ATOMG here, which makes
       // every row wait for an L2 round trip it has no use for
@@ -172,8 +187,8 @@ __device__ __forceinline__ void fold_column(KeyVec<8>& part, KeyVec<KW>& key, bo
 // Row scan with the column count known at compile time: column pointers and
 // cards live in registers, and the loads of the NEXT 16-row vector are issued
 // before the increments of the current one (register double buffering).
-template <int KW, int TIER, bool SCALE4, int K>
-__device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, uint32_t v_begin,
+template <int KW, int TIER, bool SCALE4, bool REP, int K>
+__device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, const Rep& rep, uint32_t v_begin,
                                             uint32_t v_end, uint32_t tid, uint32_t nthr) {
   const uint8_t* col[K];
   uint32_t card[K], gcells[K];
@@ -202,7 +217,7 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 #pragma unroll
       for (int i = 0; i < K; ++i) fold_column<KW>(part, key, have_part, have_key, cur[i], card[i], gcells[i]);
     }
-    count16<KW, TIER, SCALE4>(key, base);
+    count16<KW, TIER, SCALE4, REP>(key, base, rep);
 #pragma unroll
     for (int i = 0; i < K; ++i) cur[i] = nxt[i];
   }
@@ -210,8 +225,8 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 
 // Any column count (descriptors stay in shared memory): columns are loaded four at a time so
 // that four 16-byte loads are in flight per thread.
-template <int KW, int TIER, bool SCALE4>
-__device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
+template <int KW, int TIER, bool SCALE4, bool REP>
+__device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, const Rep& rep, uint32_t v_begin,
                                               uint32_t v_end, uint32_t tid, uint32_t nthr) {
   for (uint32_t v = v_begin + tid; v < v_end; v += nthr) {
     const size_t off = (size_t)v << 4;
@@ -227,11 +242,11 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
       for (int j = 0; j < 4; ++j)
         if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
     }
-    count16<KW, TIER, SCALE4>(key, base);
+    count16<KW, TIER, SCALE4, REP>(key, base, rep);
   }
 }
 
-template <int KW, int TIER, bool SCALE4>
+template <int KW, int TIER, bool SCALE4, bool REP = false>
 __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ CtaTuple T;
@@ -280,12 +295,21 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   }
 
   // ---- table + epilogue scratch (zeroed while the descriptor loads are in flight)
-  int32_t* tab;
+  int32_t* tab;                     // the table the epilogue reads (one copy)
+  int32_t* tab_rep = nullptr;       // REP, R > 1: the R interleaved copies the row loop counts into
   int32_t* wscratch;                // per-warp epilogue scratch
+  const uint32_t R = REP ? (1u << A.rep_shift) : 1u;
   if (TIER == TIER_SMEM) {
-    tab = reinterpret_cast<int32_t*>(smem_raw);
-    wscratch = reinterpret_cast<int32_t*>(smem_raw + (((size_t)cells * 4u + 15u) & ~(size_t)15u));
-    for (uint32_t i = tid; i < cells; i += nthr) tab[i] = 0;
+    size_t o = 0;
+    if (REP && R > 1u) {
+      tab_rep = reinterpret_cast<int32_t*>(smem_raw);
+      o = (size_t)cells * R * 4u;
+      for (uint32_t i = tid; i < cells * R; i += nthr) tab_rep[i] = 0;
+    }
+    tab = reinterpret_cast<int32_t*>(smem_raw + o);
+    wscratch = reinterpret_cast<int32_t*>(smem_raw + o + (((size_t)cells * 4u + 15u) & ~(size_t)15u));
+    if (!tab_rep)
+      for (uint32_t i = tid; i < cells; i += nthr) tab[i] = 0;
   } else {
     tab = A.scratch + A.scratch_off[lt];
     wscratch = reinterpret_cast<int32_t*>(smem_raw);
@@ -297,16 +321,27 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   const uint32_t v_begin = split * A.vec_per_split;
   uint32_t v_end = v_begin + A.vec_per_split;
   if (v_end > n_vec) v_end = n_vec;
-  unsigned char* base = reinterpret_cast<unsigned char*>(tab);
+  unsigned char* base = reinterpret_cast<unsigned char*>(tab_rep ? tab_rep : tab);
+  const Rep rep{(SCALE4 ? 1u : 4u) * R, 4u * (tid & (R - 1u))};
   switch (k) {
     case 0: break;
-    case 1: scan_rows_k<KW, TIER, SCALE4, 1>(T, base, v_begin, v_end, tid, nthr); break;
-    case 2: scan_rows_k<KW, TIER, SCALE4, 2>(T, base, v_begin, v_end, tid, nthr); break;
-    case 3: scan_rows_k<KW, TIER, SCALE4, 3>(T, base, v_begin, v_end, tid, nthr); break;
-    case 4: scan_rows_k<KW, TIER, SCALE4, 4>(T, base, v_begin, v_end, tid, nthr); break;
-    case 5: scan_rows_k<KW, TIER, SCALE4, 5>(T, base, v_begin, v_end, tid, nthr); break;
-    case 6: scan_rows_k<KW, TIER, SCALE4, 6>(T, base, v_begin, v_end, tid, nthr); break;
-    default: scan_rows_any<KW, TIER, SCALE4>(T, k, base, v_begin, v_end, tid, nthr); break;
+    case 1: scan_rows_k<KW, TIER, SCALE4, REP, 1>(T, base, rep, v_begin, v_end, tid, nthr); break;
+    case 2: scan_rows_k<KW, TIER, SCALE4, REP, 2>(T, base, rep, v_begin, v_end, tid, nthr); break;
+    case 3: scan_rows_k<KW, TIER, SCALE4, REP, 3>(T, base, rep, v_begin, v_end, tid, nthr); break;
+    case 4: scan_rows_k<KW, TIER, SCALE4, REP, 4>(T, base, rep, v_begin, v_end, tid, nthr); break;
+    case 5: scan_rows_k<KW, TIER, SCALE4, REP, 5>(T, base, rep, v_begin, v_end, tid, nthr); break;
+    case 6: scan_rows_k<KW, TIER, SCALE4, REP, 6>(T, base, rep, v_begin, v_end, tid, nthr); break;
+    default: scan_rows_any<KW, TIER, SCALE4, REP>(T, k, base, rep, v_begin, v_end, tid, nthr); break;
+  }
+  if (tab_rep) {                     // sum the copies into the one table everything below reads
+    __syncthreads();
+    for (uint32_t c = tid; c < cells; c += nthr) {
+      const int32_t* p = tab_rep + (size_t)c * R;
+      int a = 0;
+      for (uint32_t r = 0; r < R; ++r) a += p[(r + tid) & (R - 1u)];     // staggered: lanes start in different banks
+      tab[c] = a;
+    }
+    __syncthreads();
   }
   if (tid == 0) {
     if (k == 0) {

@@ -43,6 +43,7 @@ struct BatchArgs {
   int32_t* scratch;         // zero on entry, zero on exit
   const uint64_t* scratch_off;  // [launch tuples]
   unsigned int* tickets;        // [launch tuples], zero on entry and exit
+  uint32_t rep_shift;           // REP kernels: log2 of the table copies of this launch (obn_count_kernel.cuh: Rep)
   // MODE_CI: the launch tuple is a GROUP -- the CI tests of the batch that are asked over the same
   // variable set share ONE table (counted once, in reference key order); member m of group q is the
   // test members[m].x whose x is digit (members[m].y & 0xff) and y digit (members[m].y >> 8) of the
