@@ -25,7 +25,8 @@ L = openbnsl_b200.openbnsllib
 COMM = None          # set in main() when launched under torchrun (one rank per GPU)
 RANK = 0
 PC_KW = {}
-OPTS = {}           # extra keyword arguments of pc() from the command line (tb=<target_batch>, overlap=0/1, shard=<bytes>)
+OPTS = {}
+REPS = None          # reps=<n> on the command line overrides the per-config repetition count           # extra keyword arguments of pc() from the command line (tb=<target_batch>, overlap=0/1, shard=<bytes>)
 
 
 def peak():
@@ -67,6 +68,7 @@ def report(name, what, units, unit_name, secs, prof, extra=None):
 
 
 def run_pc(name, net, n_rows, test, depth, what, reps=1):
+    reps = REPS or reps
     df, cards, t_gen = frame(net, n_rows, 0)
     L.profile_enable(True)
     df.to_device()
@@ -150,7 +152,7 @@ def run_sa(name, net, n_rows, max_parents, iters, chains, what):
 
 
 def main():
-    global COMM, RANK
+    global COMM, RANK, REPS
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:
         import torch
         import torch.distributed as dist
@@ -170,6 +172,8 @@ def main():
         elif a.startswith("opt:"):                      # opt:<name>=<value> -> obn_ctx_set_option
             name, val = a[4:].split("=")
             L.set_option(name, float(val)); OPTS[name] = float(val); args.remove(a)
+        elif a.startswith("reps="):
+            REPS = int(a[5:]); args.remove(a)
         elif a.startswith("shard="):
             PC_KW["shard_min_bytes"] = float(a[6:]); args.remove(a)
     which = args or ["c1", "c2", "c3", "c4", "c5"]
