@@ -238,6 +238,11 @@ OBN_API int obn_es_level_dp(obn_es* es);
  * has been done this way the rest of the search must be too; obn_es_finish then fills only this
  * rank's children in parent_masks (zero elsewhere: OR the ranks' arrays). */
 OBN_API int obn_es_level_dp_part(obn_es* es, int rank, int world, void** parts_dev, size_t* bytes_per_rank);
+/* The same level in ONE call when the ctx owns the communicator (obn_comm_init): this rank's children, then
+ * max over ranks of the sum and min over ranks of the child among those that reach it (two all-reduces of 8
+ * and 4 bytes per subset instead of gathering 16 bytes per subset and rank), then the commit -- all enqueued
+ * on the ctx's stream, no host synchronisation per level.  Collective. */
+OBN_API int obn_es_level_dp_sharded(obn_es* es);
 OBN_API int obn_es_level_dp_commit(obn_es* es, int world);
 /* Fast mode for deep searches: instead of steps 2 of every level, compute
  *   F(S) = sum over the cells of S of lgamma(N_c + ess/cells(S)) - lgamma(ess/cells(S))

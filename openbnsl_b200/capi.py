@@ -29,7 +29,7 @@ EXPORTS = [
     "obn_count_tables", "obn_bdeu_scores", "obn_bdeu_subset_scores", "obn_ci_tests",
     "obn_ci_tests_submit", "obn_ci_tests_collect", "obn_pc_round", "obn_pc_round_submit", "obn_pc_round_collect",
     "obn_ci_group_plan",
-    "obn_es_begin", "obn_es_level_begin", "obn_es_level_scores", "obn_es_level_buffer", "obn_es_level_dp", "obn_es_level_dp_part", "obn_es_level_dp_commit", "obn_lattice_bottom_program",
+    "obn_es_begin", "obn_es_level_begin", "obn_es_level_scores", "obn_es_level_buffer", "obn_es_level_dp", "obn_es_level_dp_part", "obn_es_level_dp_commit", "obn_es_level_dp_sharded", "obn_lattice_bottom_program",
     "obn_es_lattice", "obn_es_f_buffer", "obn_es_finish", "obn_es_end",
     "obn_profile_enable", "obn_profile_read",
 ]

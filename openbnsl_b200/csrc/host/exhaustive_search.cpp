@@ -215,11 +215,15 @@ PDAG exhaustive_search_device(obn_dataset* ds, const Comm& comm, const EsOptions
     // all-gather of (sum, child) per level (obn_es_level_dp_part).
     if (lattice && comm.world > 1 && (dp_by_child || T >= opt.dp_shard_min_subsets)) {
       dp_by_child = true;
-      void* parts = nullptr;
-      size_t per = 0;
-      check(obn_es_level_dp_part(es, comm.rank, comm.world, &parts, &per));
-      comm.allgather_dev((uintptr_t)parts, per);
-      check(obn_es_level_dp_commit(es, comm.world));
+      if (comm.native) {                // the library's communicator: the whole level stays on its stream
+        check(obn_es_level_dp_sharded(es));
+      } else {
+        void* parts = nullptr;
+        size_t per = 0;
+        check(obn_es_level_dp_part(es, comm.rank, comm.world, &parts, &per));
+        comm.allgather_dev((uintptr_t)parts, per);
+        check(obn_es_level_dp_commit(es, comm.world));
+      }
     } else {
       check(obn_es_level_dp(es));
     }

@@ -114,8 +114,10 @@ static int run_batch(BatchSpec& S) {
   const bool ci = (S.mode == MODE_CI);
   const bool pc_round = ci && S.n_slots != 0;
   const size_t n_out = ci ? S.n_out : n;
-  const int world = (S.shard && c->comm) ? c->comm_world : 1, rank = world > 1 ? c->comm_rank : 0;
-  if (n == 0) {                     // (a sharded round is the same batch on every rank: all of them return here)
+  // S.shard (PC rounds): the planner already kept this rank's share of the groups (plan_ci_groups); what is
+  // left to do here is the all-reduce of the per-edge minima after the kernels
+  const bool merge_ranks = S.shard && c->comm && c->comm_world > 1;
+  if (n == 0 && !merge_ranks) {
     if (pc_round && S.first) std::fill(S.first, S.first + S.n_slots, INT32_MAX);
     return OBN_OK;
   }
@@ -136,7 +138,6 @@ static int run_batch(BatchSpec& S) {
   group.resize(n);
   rxy.assign(n, 0);
   size_t group_count[kNumClasses] = {};
-  size_t class_seen[kNumClasses] = {};
   double alg_bytes = 0, scanned_bytes = 0, increments = 0;
   size_t n_mine = 0, tests_mine = 0;
   if (ds->n_vars > (1u << 24)) return fail(OBN_ERR_UNSUPPORTED, "more than 2^24 variables");
@@ -161,11 +162,7 @@ static int run_batch(BatchSpec& S) {
     int g = 0;
     while (g < kNumClasses - 2 && cl > kClassCells[g]) ++g;
     if (g == kNumClasses - 2 && cl * 4 + 16 + 8 * 512 * 4 > budget) g = kNumClasses - 1;
-    // sharded rounds: the groups of one class are dealt to the ranks in turn, so every rank gets the
-    // same mix of table sizes (the class boundaries move the deal so small classes do not all land on rank 0)
-    const bool mine = world == 1 || (int)((class_seen[g]++ + (size_t)g) % (size_t)world) == rank;
-    group[t] = mine ? (uint8_t)g : (uint8_t)0xff;
-    if (!mine) continue;
+    group[t] = (uint8_t)g;
     ++group_count[g];
     ++n_mine;
     const double members = ci ? (double)(S.mem_off[t + 1] - S.mem_off[t]) : 1.0;
@@ -270,8 +267,7 @@ static int run_batch(BatchSpec& S) {
   {
     size_t fill[kNumClasses];
     for (int g = 0; g < kNumClasses; ++g) fill[g] = gstart[g];
-    for (size_t t = 0; t < n; ++t)
-      if (group[t] != 0xff) perm[fill[group[t]]++] = (uint32_t)t;
+    for (size_t t = 0; t < n; ++t) perm[fill[group[t]]++] = (uint32_t)t;
   }
   {
     uint32_t* hdr = reinterpret_cast<uint32_t*>(hin + o_hdr);
@@ -348,6 +344,15 @@ static int run_batch(BatchSpec& S) {
         const uint32_t min_vps = global_tier ? 256u : std::max<uint32_t>(1024u, max_cells / 4u);
         splits = (int)std::min<size_t>(tpt / 256, std::max<uint32_t>(1u, n_vec / min_vps));
         splits = std::max(1, splits);
+        // a launch of only a few waves ends with SMs idling behind its last CTAs: cut the tuples into row
+        // ranges until the launch has min_waves waves of CTAs (the merge is one pass over the table through L2)
+        if (!global_tier && c->tune.min_waves > 0) {
+          const size_t ctas_per_sm = std::max<size_t>(1, std::min<size_t>(ctas_by_smem, 2048 / 256));
+          const size_t slots = (size_t)c->sm_count * ctas_per_sm;
+          const size_t want = ((size_t)c->tune.min_waves * slots + remaining - 1) / remaining;
+          const size_t cap = std::max<uint32_t>(1u, n_vec / std::max<uint32_t>(min_vps, 4096u));   // >= 64 Ki rows per range
+          splits = (int)std::max<size_t>((size_t)splits, std::min(want, cap));
+        }
       }
       if (c->tune.force_threads) nthr = c->tune.force_threads;
       if (c->tune.force_splits)
@@ -497,7 +502,7 @@ static int run_batch(BatchSpec& S) {
   const size_t ev_first = c->ev_used - (c->profile_on ? 1 : 0);
 
   // ---- sharded PC round: merge the ranks' first-passing indices, still on the device -----------
-  if (pc_round && world > 1)
+  if (pc_round && merge_ranks)
     if (int rc = comm_allreduce_min_i32(c, reinterpret_cast<int32_t*>(dout), S.n_slots)) return rc;
 
   // ---- download ------------------------------------------------------------------
@@ -601,7 +606,10 @@ static int ci_tests_impl(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_
   }
   static thread_local CiGroupPlan P;            // capacity reused across the rounds of a PC run
   static const uint64_t zero_off[1] = {0};
-  if (int rc = plan_ci_groups(ds->cards.data(), ds->n_vars, var_ids, n_tuples ? offsets : zero_off, n_tuples, x, y, P)) return rc;
+  const bool sharded = shard != 0 && n_slots && c->comm && c->comm_world > 1;
+  if (int rc = plan_ci_groups(ds->cards.data(), ds->n_vars, var_ids, n_tuples ? offsets : zero_off, n_tuples, x, y, P,
+                              sharded ? c->comm_rank : 0, sharded ? c->comm_world : 1))
+    return rc;
   BatchSpec S{c, ds, P.var_ids.data(), P.offsets.data(), P.groups(), MODE_CI};
   S.kind = kind;
   S.stat = stat_out;

@@ -74,8 +74,13 @@ struct CiGroupScratch {
 // Order-preserving: groups appear in the order of their first test, members in batch order; a
 // group takes at most kGroupMembers tests (the kernel keeps their statistics in shared memory),
 // further tests over the same set open another group.
+//
+// rank / world: a sharded round.  Every rank plans the same batch but keeps only the variable sets whose
+// hash falls to it, so all tests over one set land on one rank (the sharing survives the split), the
+// ranks agree without talking, and each pays for planning and packing its own share only.  Test ids
+// stay those of the whole batch.
 static int plan_ci_groups(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids, const uint64_t* offsets,
-                          size_t n, const uint32_t* xs, const uint32_t* ys, CiGroupPlan& P) {
+                          size_t n, const uint32_t* xs, const uint32_t* ys, CiGroupPlan& P, int rank = 0, int world = 1) {
   static thread_local CiGroupScratch W;
   W.hash_reset(n);
   W.head.clear(); W.tail.clear(); W.count.clear(); W.first_test.clear();
@@ -106,6 +111,7 @@ static int plan_ci_groups(const uint32_t* cards, size_t n_vars, const uint32_t* 
       if (int rc = check_tuple(cards, n_vars, ids, k, t, true, false, xs[t], ys[t], &dummy)) return rc;
       return fail(OBN_ERR_INVALID, "tuple %zu: inconsistent CI test", t);
     }
+    if (world > 1 && (int)((h >> 40) % (uint64_t)world) != rank) continue;      // another rank's table
     W.role[t] = px | (py << 8);
     W.next[t] = 0xffffffffu;
     if (h == ~0ull) h = 0;
@@ -135,7 +141,7 @@ static int plan_ci_groups(const uint32_t* cards, size_t n_vars, const uint32_t* 
   // ---- emit ------------------------------------------------------------------------------
   const size_t n_groups = W.head.size();
   P.var_ids.clear(); P.offsets.clear(); P.mem_off.clear();
-  P.members.resize(2 * n);
+  P.members.resize(2 * n + 2);
   P.var_ids.reserve(offsets[n]);
   P.offsets.reserve(n_groups + 1);
   P.mem_off.reserve(n_groups + 1);

@@ -145,6 +145,29 @@ __global__ void es_dp_commit_kernel(const LIST* list, size_t T, int world, const
   best_ch[W] = (uint8_t)bch;
 }
 
+// The same merge without gathering every rank's pair: ranks own ascending child ranges and the serial scan
+// keeps the FIRST child that reaches the largest sum, so the choice is (max over ranks of gs, then the
+// smallest child among the ranks whose gs equals that max) -- two all-reduces of 8 and 4 bytes per subset
+// (reduced inside the NVSwitch) instead of an all-gather of 16 bytes per subset and rank.
+template <int STEP>
+__global__ void es_dp_reduce_kernel(size_t T, const EsPart* part, double* gs_max, int32_t* ch_min) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  const EsPart p = part[t];
+  if (STEP == 0) gs_max[t] = p.gs;                                              // -> all-reduce(max)
+  else ch_min[t] = (p.ch != INT_MAX && p.gs == gs_max[t]) ? p.ch : INT_MAX;     // -> all-reduce(min)
+}
+template <typename LIST>
+__global__ void es_dp_commit2_kernel(const LIST* list, size_t T, const double* gs_max, const int32_t* ch_min, double* best_gs,
+                                     uint8_t* best_ch) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  const uint32_t W = (uint32_t)list[t];
+  const int32_t ch = ch_min[t];
+  best_gs[W] = (ch == INT_MAX) ? 0.0 : gs_max[t];
+  best_ch[W] = (uint8_t)((ch == INT_MAX) ? -1 : ch);
+}
+
 // Level lists for the lattice mode (no host mask lists there):
 // lists[off[k] + rank] = W for every subset W: rank = position of W among the k-subsets in
 // increasing numeric order = sum_i C(p_i, i+1) over its set bits p_0 < p_1 < ... (combinatorial
@@ -382,6 +405,44 @@ int obn_es_level_dp_part(obn_es* e, int rank, int world, void** parts_dev, size_
   obn::EsPart* mine = reinterpret_cast<obn::EsPart*>(c->es_pool.d_level.as<char>() + (size_t)rank * e->T * sizeof(obn::EsPart));
   if (int rc = es_launch_dp(e, first, end - first, mine)) return rc;
   OBN_CUDA(cudaStreamSynchronize(c->stream));
+  return OBN_OK;
+}
+
+// One level of the child-sharded DP entirely on the ctx's stream: this rank's children, the two
+// all-reduces over the ctx's communicator, the commit -- no host synchronisation in between (the next
+// level's kernels are ordered behind it on the same stream).
+int obn_es_level_dp_sharded(obn_es* e) {
+  if (!e) return fail(OBN_ERR_INVALID, "obn_es_level_dp_sharded: NULL argument");
+  if (!e->use_F) return fail(OBN_ERR_UNSUPPORTED, "the child-sharded DP needs the lattice mode (obn_es_lattice)");
+  obn_ctx* c = e->c;
+  if (!c->comm || c->comm_world <= 1) return fail(OBN_ERR_COMM, "obn_es_level_dp_sharded needs a communicator (obn_comm_init)");
+  OBN_CUDA(cudaSetDevice(c->device));
+  const int rank = c->comm_rank, world = c->comm_world;
+  const int first = (int)((size_t)e->n * (size_t)rank / (size_t)world), end = (int)((size_t)e->n * (size_t)(rank + 1) / (size_t)world);
+  if (e->own_first != 0 || e->own_end < e->n) {
+    if (e->own_first != first || e->own_end != end) return fail(OBN_ERR_INVALID, "rank/world changed inside a search");
+  }
+  e->own_first = first;
+  e->own_end = end;
+  if (!e->T) return OBN_OK;
+  const size_t T = e->T;
+  if (int rc = c->es_pool.d_level.reserve(T * 32 + 64)) return rc;
+  obn::EsPart* part = c->es_pool.d_level.as<obn::EsPart>();
+  double* gs_max = reinterpret_cast<double*>(c->es_pool.d_level.as<char>() + T * 16);
+  int32_t* ch_min = reinterpret_cast<int32_t*>(c->es_pool.d_level.as<char>() + T * 24);
+  if (int rc = es_launch_dp(e, first, end - first, part)) return rc;
+  const unsigned grid = (unsigned)((T + 255) / 256);
+  NcclApi* api = nccl_api();
+  if (!api) return fail(OBN_ERR_COMM, "NCCL is not available");
+  es_dp_reduce_kernel<0><<<grid, 256, 0, c->stream>>>(T, part, gs_max, ch_min);
+  OBN_NCCL(api, api->AllReduce(gs_max, gs_max, T, ncclDouble, ncclMax, (ncclComm_t)c->comm, c->stream));
+  es_dp_reduce_kernel<1><<<grid, 256, 0, c->stream>>>(T, part, gs_max, ch_min);
+  OBN_NCCL(api, api->AllReduce(ch_min, ch_min, T, ncclInt32, ncclMin, (ncclComm_t)c->comm, c->stream));
+  es_dp_commit2_kernel<uint32_t><<<grid, 256, 0, c->stream>>>(c->es_pool.d_lists.as<uint32_t>() + e->levels.off[e->k], T, gs_max,
+                                                              ch_min, e->best_gs, e->best_ch);
+  OBN_CUDA(cudaGetLastError());
+  c->prof.total_launches += 3;
+  c->prof.collectives += 2;
   return OBN_OK;
 }
 
