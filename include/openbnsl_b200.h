@@ -69,8 +69,7 @@ OBN_API void obn_ctx_destroy(obn_ctx* ctx);
 OBN_API void* obn_ctx_stream(obn_ctx* ctx);
 /* Tuning knobs for A/B runs and tests (defaults are what the published numbers use):
  *   "threads_per_sm" (768), "force_threads" (0), "force_splits" (0), "streams" (4)   counting-kernel launch policy
- *   "rep_c0" (5), "rep_c1" (5), "rep_c2" (4), "rep_c3" (2), "rep_c4" (0), "rep_max_kb" (64)    log2 of the shared-memory
- *                                        table copies per size class (<= 64 / 256 / 1 Ki / 4 Ki / 16 Ki cells) and their cap
+ *   "rep" (1), "min_waves" (0)            replicated shared-memory tables on / off; row-split small launches to this many waves
  *   "lattice_budget_gb" (24), "lattice_max_l" (20), "lattice_bottom" (1), "lattice_reorder" (1),
  *   "lattice_graph" (1), "lattice_lanes" (2), "lattice_no_lut" (0), "debug" (0)      marginalisation lattice
  * Unknown names fail with OBN_ERR_INVALID. */

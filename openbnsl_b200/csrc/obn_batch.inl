@@ -53,20 +53,23 @@ struct BatchSpec {
 //   6      larger       <32, GLOBAL, plain>  table in L2-resident global scratch
 static const int kNumClasses = 7;
 static const uint32_t kClassCells[kNumClasses - 2] = {64, 256, 1024, 4096, 16384};
+// log2 of the shared-memory table copies per class (0: none): 32 / 32 / 16 / 4 copies keep the copies of one
+// table within 8 / 32 / 64 / 64 KB (A/B: profiles/r2_ab_replication.jsonl)
+static constexpr int kRepShift[5] = {5, 5, 4, 2, 0};
 
 static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-template <int KW, int TIER, bool SCALE4, bool REP = false>
+template <int KW, int TIER, bool SCALE4, int RSH = -1>
 static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, size_t smem, cudaStream_t s) {
   // cudaFuncAttributeMaxDynamicSharedMemorySize is per device and a process may hold one ctx per
   // device: set it whenever a launch needs more than the default 48 KB (a few microseconds)
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4, REP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(count_kernel<KW, TIER, SCALE4, RSH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return e;
   }
   (void)cudaGetLastError();      // a launch reports only its own error, not a stale one
-  count_kernel<KW, TIER, SCALE4, REP><<<grid, nthr, smem, s>>>(a);
+  count_kernel<KW, TIER, SCALE4, RSH><<<grid, nthr, smem, s>>>(a);
   return cudaGetLastError();
 }
 
@@ -146,14 +149,13 @@ static int run_batch(BatchSpec& S) {
     if (o1 < o0) return fail(OBN_ERR_INVALID, "offsets must be non-decreasing");
     const size_t k = o1 - o0;
     uint64_t cl = 1;
+    uint32_t c1 = 0, c2 = 0;             // CI: the two largest cardinalities bound rx + ry of every member
     if (ci) {
-      uint32_t c1 = 0, c2 = 0;           // the two largest cardinalities bound rx + ry of every member
       for (size_t i = 0; i < k; ++i) {
         const uint32_t cd = ds->cards[S.var_ids[o0 + i]];
         cl *= cd;
         if (cd > c1) { c2 = c1; c1 = cd; } else if (cd > c2) c2 = cd;
       }
-      rxy[t] = c1 + c2;
     } else if (int rc = check_tuple(ds->cards.data(), ds->n_vars, S.var_ids + o0, k, t, false, S.mode == MODE_BDEU_ONE,
                                     S.role_a ? S.role_a[t] : 0xffffffffu, 0xffffffffu, &cl)) {
       return rc;
@@ -162,6 +164,8 @@ static int run_batch(BatchSpec& S) {
     int g = 0;
     while (g < kNumClasses - 2 && cl > kClassCells[g]) ++g;
     if (g == kNumClasses - 2 && cl * 4 + 16 + 8 * 512 * 4 > budget) g = kNumClasses - 1;
+    // epilogue scratch per warp: the margins, and for tables in global memory one staged slice (ci_slices_any)
+    if (ci) rxy[t] = c1 + c2 + (g == kNumClasses - 1 ? c1 * c2 : 0u);
     group[t] = (uint8_t)g;
     ++group_count[g];
     ++n_mine;
@@ -299,7 +303,7 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
-  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; };
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; uint32_t wstride; };
   std::vector<Launch> launches;
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
   size_t max_scratch_ints = 0;
@@ -319,13 +323,8 @@ static int run_batch(BatchSpec& S) {
       // best geometry keeps about 768 threads per SM busy in total, with the widest CTA
       // that allows; row splits only pay when a launch has too few tuples to do that
       // (each split repeats the prologue and adds a merge through L2).
-      // table copies (obn_count_kernel.cuh: Rep): the shared-memory classes 0..4, as many as the class's
-      // option says while the copies of one table stay within rep_max_kb
-      uint32_t rep_shift = 0;
-      if (g <= 4) {
-        rep_shift = (uint32_t)std::max(0, std::min(5, c->tune.rep_shift[g]));
-        while (rep_shift && ((size_t)max_cells << rep_shift) * 4 > (size_t)c->tune.rep_max_kb * 1024) --rep_shift;
-      }
+      // table copies (obn_count_kernel.cuh): fixed per shared-memory class, compile-time constants of the kernels
+      const uint32_t rep_shift = (c->tune.rep && g <= 4 && kRepShift[g] > 0) ? (uint32_t)kRepShift[g] : 0u;
       const size_t table_bytes = global_tier ? 0
                                  : align16((size_t)max_cells * 4) + (rep_shift ? ((size_t)max_cells << rep_shift) * 4 : 0);
       const size_t tpt = target_threads / remaining;
@@ -374,7 +373,7 @@ static int run_batch(BatchSpec& S) {
       }
       uint32_t vps = (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, rep_shift});
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, rep_shift, max_rxy});
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
       i = j;
     }
@@ -485,12 +484,18 @@ static int run_batch(BatchSpec& S) {
     a.tickets = c->d_tickets.as<unsigned int>() + L.begin;
     a.splits = L.splits;
     a.vec_per_split = L.vps;
-    a.rep_shift = L.rep_shift;
+    a.wstride = L.wstride;
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
     cudaError_t e;
-    if (L.g == 0) e = launch_count<8, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
-    else if (L.g == 1) e = launch_count<8, TIER_SMEM, false, true>(a, grid, L.nthr, L.smem, st);
-    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true, true>(a, grid, L.nthr, L.smem, st);
+    if (L.rep_shift) {
+      if (L.g == 0) e = launch_count<8, TIER_SMEM, true, kRepShift[0]>(a, grid, L.nthr, L.smem, st);
+      else if (L.g == 1) e = launch_count<8, TIER_SMEM, false, kRepShift[1]>(a, grid, L.nthr, L.smem, st);
+      else if (L.g == 2) e = launch_count<16, TIER_SMEM, true, kRepShift[2]>(a, grid, L.nthr, L.smem, st);
+      else e = launch_count<16, TIER_SMEM, true, kRepShift[3]>(a, grid, L.nthr, L.smem, st);
+    } else
+    if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
+    else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
+    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
     else if (L.g == 5) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
     else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, st);
     if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "count_kernel launch failed: %s", cudaGetErrorString(e));

@@ -130,13 +130,8 @@ int obn_ctx_set_option(obn_ctx* c, const char* name, double value) {
   else if (k == "force_threads") c->tune.force_threads = v;
   else if (k == "force_splits") c->tune.force_splits = v;
   else if (k == "streams") c->tune.streams = std::max(1, v);
-  else if (k == "rep_c0") c->tune.rep_shift[0] = v;
-  else if (k == "rep_c1") c->tune.rep_shift[1] = v;
-  else if (k == "rep_c2") c->tune.rep_shift[2] = v;
-  else if (k == "rep_c3") c->tune.rep_shift[3] = v;
-  else if (k == "rep_c4") c->tune.rep_shift[4] = v;
+  else if (k == "rep") c->tune.rep = v;
   else if (k == "min_waves") c->tune.min_waves = std::max(0, v);
-  else if (k == "rep_max_kb") c->tune.rep_max_kb = std::max(1, v);
   else if (k == "lattice_budget_gb") c->tune.lattice_budget_gb = std::max(1, v);
   else if (k == "lattice_max_l") c->tune.lattice_max_l = std::max(1, v);
   else if (k == "lattice_bottom") c->tune.lattice_bottom = v;

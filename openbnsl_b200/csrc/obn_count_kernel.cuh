@@ -137,28 +137,30 @@ struct KeyVec<32> {
 // l + R, l + 2R, ... in its bank: at R = 16 at most two addresses per bank, which fits the two
 // clocks an ATOMS instruction occupies anyway (benchmarks/micro/smem_incr.cu variant 9).  The copies
 // are summed into one compact table before the epilogue.
-struct Rep {
-  uint32_t mul;      // byte distance between consecutive cells: 4 * R (SCALE4 keys are pre-multiplied by 4: R)
-  uint32_t copy4;    // byte offset of this lane's copy: 4 * (lane & (R-1))
-};
+//
+// RSH = log2(R) is a compile-time constant of the kernel (-1: a single table): the address of an
+// increment is then `lane_base + (field << shift)`, one LEA, where lane_base = table + 4 * (lane & (R-1))
+// is computed once per thread.  (With R as a run-time value ptxas spent four ALU instructions per
+// increment on it and the <= 64-cell class became issue-bound at 82 % issue-active.)
 
-// 16 increments for one key vector.  `base` is the table as a byte pointer.
-template <int KW, int TIER, bool SCALE4, bool REP>
-__device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* base, const Rep& rep) {
+// 16 increments for one key vector.  `lane_base` is this lane's copy of the table as a byte pointer.
+template <int KW, int TIER, bool SCALE4, int RSH>
+__device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* lane_base) {
   if (SCALE4) key.scale4();
+  constexpr int kShift = (SCALE4 ? 0 : 2) + (RSH > 0 ? RSH : 0);
+  if (TIER == TIER_GLOBAL) {
 #pragma unroll
-  for (int r = 0; r < 16; ++r) {
-    const uint32_t f = key.get(r);
-    unsigned int* p;
-    if (REP) p = reinterpret_cast<unsigned int*>(base + (f * rep.mul + rep.copy4));
-    else p = reinterpret_cast<unsigned int*>(base + (SCALE4 ? (size_t)f : ((size_t)f << 2)));
-    if (TIER == TIER_GLOBAL) {
+    for (int r = 0; r < 16; ++r) {
       // non-returning reduction (REDG.E.ADD): a plain atomicAdd compiles to ATOMG here, which makes
       // every row wait for an L2 round trip it has no use for
-      asm volatile("red.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
-    } else {
-      atomicAdd(p, 1u);    // ATOMS.POPC.INC.32
+      asm volatile("red.global.add.u32 [%0], 1;" ::"l"(lane_base + ((size_t)key.get(r) << kShift)) : "memory");
     }
+  } else {
+    // one 32-bit shared-window address per lane, so that an increment is extract + LEA + ATOMS.POPC.INC
+    const uint32_t a0 = (uint32_t)__cvta_generic_to_shared(lane_base);
+#pragma unroll
+    for (int r = 0; r < 16; ++r)
+      asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a0 + (key.get(r) << kShift)) : "memory");
   }
 }
 
@@ -187,8 +189,8 @@ __device__ __forceinline__ void fold_column(KeyVec<8>& part, KeyVec<KW>& key, bo
 // Row scan with the column count known at compile time: column pointers and
 // cards live in registers, and the loads of the NEXT 16-row vector are issued
 // before the increments of the current one (register double buffering).
-template <int KW, int TIER, bool SCALE4, bool REP, int K>
-__device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, const Rep& rep, uint32_t v_begin,
+template <int KW, int TIER, bool SCALE4, int RSH, int K>
+__device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, uint32_t v_begin,
                                             uint32_t v_end, uint32_t tid, uint32_t nthr) {
   const uint8_t* col[K];
   uint32_t card[K], gcells[K];
@@ -217,7 +219,7 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 #pragma unroll
       for (int i = 0; i < K; ++i) fold_column<KW>(part, key, have_part, have_key, cur[i], card[i], gcells[i]);
     }
-    count16<KW, TIER, SCALE4, REP>(key, base, rep);
+    count16<KW, TIER, SCALE4, RSH>(key, base);
 #pragma unroll
     for (int i = 0; i < K; ++i) cur[i] = nxt[i];
   }
@@ -225,8 +227,8 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 
 // Any column count (descriptors stay in shared memory): columns are loaded four at a time so
 // that four 16-byte loads are in flight per thread.
-template <int KW, int TIER, bool SCALE4, bool REP>
-__device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, const Rep& rep, uint32_t v_begin,
+template <int KW, int TIER, bool SCALE4, int RSH>
+__device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
                                               uint32_t v_end, uint32_t tid, uint32_t nthr) {
   for (uint32_t v = v_begin + tid; v < v_end; v += nthr) {
     const size_t off = (size_t)v << 4;
@@ -242,11 +244,11 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
       for (int j = 0; j < 4; ++j)
         if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
     }
-    count16<KW, TIER, SCALE4, REP>(key, base, rep);
+    count16<KW, TIER, SCALE4, RSH>(key, base);
   }
 }
 
-template <int KW, int TIER, bool SCALE4, bool REP = false>
+template <int KW, int TIER, bool SCALE4, int RSH = -1>
 __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ CtaTuple T;
@@ -296,12 +298,12 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
 
   // ---- table + epilogue scratch (zeroed while the descriptor loads are in flight)
   int32_t* tab;                     // the table the epilogue reads (one copy)
-  int32_t* tab_rep = nullptr;       // REP, R > 1: the R interleaved copies the row loop counts into
+  int32_t* tab_rep = nullptr;       // RSH > 0: the R interleaved copies the row loop counts into
   int32_t* wscratch;                // per-warp epilogue scratch
-  const uint32_t R = REP ? (1u << A.rep_shift) : 1u;
+  constexpr uint32_t R = RSH > 0 ? (1u << RSH) : 1u;
   if (TIER == TIER_SMEM) {
     size_t o = 0;
-    if (REP && R > 1u) {
+    if (R > 1u) {
       tab_rep = reinterpret_cast<int32_t*>(smem_raw);
       o = (size_t)cells * R * 4u;
       for (uint32_t i = tid; i < cells * R; i += nthr) tab_rep[i] = 0;
@@ -321,17 +323,16 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   const uint32_t v_begin = split * A.vec_per_split;
   uint32_t v_end = v_begin + A.vec_per_split;
   if (v_end > n_vec) v_end = n_vec;
-  unsigned char* base = reinterpret_cast<unsigned char*>(tab_rep ? tab_rep : tab);
-  const Rep rep{(SCALE4 ? 1u : 4u) * R, 4u * (tid & (R - 1u))};
+  unsigned char* base = reinterpret_cast<unsigned char*>(tab_rep ? tab_rep : tab) + 4u * (tid & (R - 1u));   // this lane's copy
   switch (k) {
     case 0: break;
-    case 1: scan_rows_k<KW, TIER, SCALE4, REP, 1>(T, base, rep, v_begin, v_end, tid, nthr); break;
-    case 2: scan_rows_k<KW, TIER, SCALE4, REP, 2>(T, base, rep, v_begin, v_end, tid, nthr); break;
-    case 3: scan_rows_k<KW, TIER, SCALE4, REP, 3>(T, base, rep, v_begin, v_end, tid, nthr); break;
-    case 4: scan_rows_k<KW, TIER, SCALE4, REP, 4>(T, base, rep, v_begin, v_end, tid, nthr); break;
-    case 5: scan_rows_k<KW, TIER, SCALE4, REP, 5>(T, base, rep, v_begin, v_end, tid, nthr); break;
-    case 6: scan_rows_k<KW, TIER, SCALE4, REP, 6>(T, base, rep, v_begin, v_end, tid, nthr); break;
-    default: scan_rows_any<KW, TIER, SCALE4, REP>(T, k, base, rep, v_begin, v_end, tid, nthr); break;
+    case 1: scan_rows_k<KW, TIER, SCALE4, RSH, 1>(T, base, v_begin, v_end, tid, nthr); break;
+    case 2: scan_rows_k<KW, TIER, SCALE4, RSH, 2>(T, base, v_begin, v_end, tid, nthr); break;
+    case 3: scan_rows_k<KW, TIER, SCALE4, RSH, 3>(T, base, v_begin, v_end, tid, nthr); break;
+    case 4: scan_rows_k<KW, TIER, SCALE4, RSH, 4>(T, base, v_begin, v_end, tid, nthr); break;
+    case 5: scan_rows_k<KW, TIER, SCALE4, RSH, 5>(T, base, v_begin, v_end, tid, nthr); break;
+    case 6: scan_rows_k<KW, TIER, SCALE4, RSH, 6>(T, base, v_begin, v_end, tid, nthr); break;
+    default: scan_rows_any<KW, TIER, SCALE4, RSH>(T, k, base, v_begin, v_end, tid, nthr); break;
   }
   if (tab_rep) {                     // sum the copies into the one table everything below reads
     __syncthreads();
@@ -397,7 +398,7 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
       const CiGeom g(cells, T.card[px], T.card[py], T.weight[px], T.weight[py]);
       double stat;
       unsigned long long dof;
-      epilogue_ci(tab, g, A.kind, wscratch + (tid >> 5) * (g.rx + g.ry), red_d, red_u, stat, dof);
+      epilogue_ci<TIER == TIER_GLOBAL>(tab, g, A.kind, wscratch + (tid >> 5) * A.wstride, red_d, red_u, stat, dof);
       if (tid == 0) {
         m_stat[m - m_begin] = stat;
         m_dof[m - m_begin] = dof;

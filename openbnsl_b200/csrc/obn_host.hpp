@@ -203,9 +203,8 @@ struct obn_ctx {
     int force_threads = 0;        // != 0: CTA width of every launch (sweeps)
     int force_splits = 0;         // != 0: row splits of every launch (sweeps)
     int streams = 4;              // launches of one batch are forked over this many streams
-    int rep_shift[5] = {5, 5, 4, 2, 0};   // log2 of the table copies per size class 0..4 (obn_count_kernel.cuh: Rep)
+    int rep = 1;                  // replicated shared-memory tables (obn_count_kernel.cuh) on / off (A/B)
     int min_waves = 0;            // row-split the tuples of a launch until it has this many waves of CTAs (0: off)
-    int rep_max_kb = 64;          // ... capped so that the copies of one table stay within this many KB
     // marginalisation lattice (obn_lattice.inl)
     int lattice_budget_gb = 24, lattice_max_l = 20, lattice_bottom = 1, lattice_reorder = 1, lattice_graph = 1,
         lattice_lanes = 2, lattice_no_lut = 0, debug = 0;

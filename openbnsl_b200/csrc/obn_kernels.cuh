@@ -43,7 +43,7 @@ struct BatchArgs {
   int32_t* scratch;         // zero on entry, zero on exit
   const uint64_t* scratch_off;  // [launch tuples]
   unsigned int* tickets;        // [launch tuples], zero on entry and exit
-  uint32_t rep_shift;           // REP kernels: log2 of the table copies of this launch (obn_count_kernel.cuh: Rep)
+  uint32_t wstride;             // ints of epilogue scratch per warp (rx + ry, plus rx * ry for tables in global memory)
   // MODE_CI: the launch tuple is a GROUP -- the CI tests of the batch that are asked over the same
   // variable set share ONE table (counted once, in reference key order); member m of group q is the
   // test members[m].x whose x is digit (members[m].y & 0xff) and y digit (members[m].y >> 8) of the
@@ -142,25 +142,39 @@ __device__ __forceinline__ void ci_slices_small(const int32_t* tab, const CiGeom
 }
 
 // Any slice shape: one warp per slice, margins in per-warp scratch (rx + ry ints).
+// STAGE (tables in global memory): the slice is first gathered into the warp's scratch (rx * ry more
+// ints) with all its loads in flight at once -- walking a slice cell by cell through L2 is a chain of
+// dependent round trips, which made the last CTA of a 400 k-cell table the longest thing in a PC run.
+template <bool STAGE>
 __device__ __forceinline__ void ci_slices_any(const int32_t* tab, const CiGeom& g, int kind, int32_t* wscratch,
                                               double& stat, unsigned long long& dof) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const uint32_t rx = g.rx, ry = g.ry, sl = rx * ry;
   int32_t* rs = wscratch;        // [rx]
   int32_t* cs = wscratch + rx;   // [ry]
+  int32_t* buf = wscratch + rx + ry;   // [rx * ry], STAGE only
+  const uint32_t wx = STAGE ? ry : g.wx, wy = STAGE ? 1u : g.wy;
   for (uint32_t s = warp; s < g.n_slices; s += nw) {
     const int32_t* t = tab + g.base(s);
+    if (STAGE) {
+      for (uint32_t c = lane; c < sl; c += 32) {
+        const uint32_t i = c / ry, j = c - i * ry;
+        buf[c] = __ldcg(t + (size_t)i * g.wx + (size_t)j * g.wy);
+      }
+      __syncwarp();
+      t = buf;
+    }
     int tot = 0, robs = 0, cobs = 0;
     for (uint32_t i = lane; i < rx; i += 32) {
       int a = 0;
-      for (uint32_t j = 0; j < ry; ++j) a += t[i * g.wx + j * g.wy];
+      for (uint32_t j = 0; j < ry; ++j) a += t[i * wx + j * wy];
       rs[i] = a;
       tot += a;
       robs += (a > 0);
     }
     for (uint32_t j = lane; j < ry; j += 32) {
       int a = 0;
-      for (uint32_t i = 0; i < rx; ++i) a += t[i * g.wx + j * g.wy];
+      for (uint32_t i = 0; i < rx; ++i) a += t[i * wx + j * wy];
       cs[j] = a;
       cobs += (a > 0);
     }
@@ -176,7 +190,7 @@ __device__ __forceinline__ void ci_slices_any(const int32_t* tab, const CiGeom& 
       for (uint32_t c = lane; c < sl; c += 32) {
         const uint32_t i = c / ry, j = c - i * ry;
         const int ri = rs[i], cj = cs[j];
-        if (ri > 0 && cj > 0) stat += ci_cell((double)t[i * g.wx + j * g.wy], ri, cj, n_total, yates, kind);
+        if (ri > 0 && cj > 0) stat += ci_cell((double)t[i * wx + j * wy], ri, cj, n_total, yates, kind);
       }
     }
     __syncwarp();
@@ -185,13 +199,14 @@ __device__ __forceinline__ void ci_slices_any(const int32_t* tab, const CiGeom& 
 
 // Statistic and dof of (x at digit px, y at digit py | every other digit) from the table; the
 // result is valid in thread 0.
+template <bool GLOBAL_TABLE>
 __device__ __forceinline__ void epilogue_ci(const int32_t* tab, const CiGeom& g, int kind, int32_t* wscratch,
                                             double* red_d, unsigned long long* red_u, double& stat_out,
                                             unsigned long long& dof_out) {
   double stat = 0.0;
   unsigned long long dof = 0;
   if (g.rx <= 4 && g.ry <= 4) ci_slices_small(tab, g, kind, stat, dof);
-  else ci_slices_any(tab, g, kind, wscratch, stat, dof);
+  else ci_slices_any<GLOBAL_TABLE>(tab, g, kind, wscratch, stat, dof);
   stat_out = block_sum(stat, red_d);
   dof_out = block_sum(dof, red_u);
 }

@@ -141,3 +141,33 @@ def test_c3_binary24_scores(bin24):
                 assert one[i] == want, t
             else:
                 assert one[i] == pytest.approx(want, rel=1e-9)
+
+
+def _seam_cases():
+    import json, os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pc_fullsize_seam.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("case", _seam_cases(), ids=lambda c: c["config"])
+def test_full_size_pc_matches_reference_seam(case):
+    """BASELINE configs 4 and 5 at FULL size (1M rows): the PDAG learned on the GPU must equal, arc for arc, the one the
+    same host driver learns when every CI decision is taken by the UNMODIFIED reference functions
+    (tests/golden/make_fullsize_seam.py: ContingencyTable<true> + citest<true> under OpenMP, 5 and 10 minutes of CPU).
+    Covers what the sampled checks above cannot: every decision of the depth >= 2 frontiers, the cardinality-21 tables
+    and the global tier inside a real run, with early-exit rounds, whole-depth rounds and the overlapped driver."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    import openbnsl_b200
+    L = openbnsl_b200.openbnsllib
+    c = bench.CONFIGS[case["config"]]
+    net, codes, cards = bench.make_data(case["config"])
+    assert cards == case["cards"]
+    assert int(np.frombuffer(codes.tobytes(), dtype=np.uint8).astype(np.uint64).sum()) == case["codes_sha"]
+    df = L.base.DataframeWrapper.from_codes(codes, net.names, cards)
+    T = L.citest.ChiSquare(c["level"]) if c["ci_test"] == "chi2" else L.citest.GSquare(c["level"])
+    for kw in ({}, {"target_batch": 100000000, "overlap": False}):
+        g = L.structure_learning.pc(df, T, c["max_cond_vars"], True, **kw)
+        arcs = [[p, v] for p in range(net.n) for v in range(net.n) if g.has_edge(p, v)]
+        assert arcs == case["arcs"], kw
