@@ -50,9 +50,14 @@ struct BatchSpec {
 //   1      <= 256       <8,  SMEM, plain>
 //   2..4   <= 1Ki/4Ki/16Ki  <16, SMEM, scale4>
 //   5      <= smem      <32, SMEM, plain>
-//   6      larger       <32, GLOBAL, plain>  table in L2-resident global scratch
-static const int kNumClasses = 7;
-static const uint32_t kClassCells[kNumClasses - 2] = {64, 256, 1024, 4096, 16384};
+//   6      <= 1.5 Mi    <32, CHUNK, plain>   cell range cut into shared-memory chunks, merged into global scratch
+//   7      larger       <32, GLOBAL, plain>  table in L2-resident global scratch
+static const int kNumClasses = 8;
+static const int kClassSmemMax = 5, kClassChunk = 6, kClassGlobal = 7;
+static const uint32_t kClassCells[5] = {64, 256, 1024, 4096, 16384};
+// class 6 (TIER_CHUNK): the table is cut into chunks of this many cells (192 KB of shared memory), at most kMaxChunks of them
+static const uint32_t kChunkCells = 48 * 1024;
+static const uint32_t kMaxChunks = 32;
 // log2 of the shared-memory table copies per class (0: none): 32 / 32 / 16 / 4 copies keep the copies of one
 // table within 8 / 32 / 64 / 64 KB (A/B: profiles/r2_ab_replication.jsonl)
 static constexpr int kRepShift[5] = {5, 5, 4, 2, 0};
@@ -162,10 +167,11 @@ static int run_batch(BatchSpec& S) {
     }
     cells[t] = (uint32_t)cl;
     int g = 0;
-    while (g < kNumClasses - 2 && cl > kClassCells[g]) ++g;
-    if (g == kNumClasses - 2 && cl * 4 + 16 + 8 * 512 * 4 > budget) g = kNumClasses - 1;
+    while (g < kClassSmemMax && cl > kClassCells[g]) ++g;
+    if (g == kClassSmemMax && cl * 4 + 16 + 8 * 512 * 4 > budget)
+      g = (c->tune.chunk && cl <= (uint64_t)kChunkCells * kMaxChunks) ? kClassChunk : kClassGlobal;
     // epilogue scratch per warp: the margins, and for tables in global memory one staged slice (ci_slices_any)
-    if (ci) rxy[t] = c1 + c2 + (g == kNumClasses - 1 ? c1 * c2 : 0u);
+    if (ci) rxy[t] = c1 + c2 + (g >= kClassChunk ? c1 * c2 : 0u);
     group[t] = (uint8_t)g;
     ++group_count[g];
     ++n_mine;
@@ -303,14 +309,14 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
-  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; uint32_t wstride; };
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; uint32_t wstride; uint32_t row_splits; };
   std::vector<Launch> launches;
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
   size_t max_scratch_ints = 0;
   const size_t target_threads = (size_t)c->sm_count * (size_t)c->tune.threads_per_sm;
   for (int g = 0; g < kNumClasses; ++g) {
     if (!group_count[g]) continue;
-    const bool global_tier = (g == kNumClasses - 1);
+    const bool global_tier = (g == kClassGlobal), chunk_tier = (g == kClassChunk);
     size_t i = gstart[g];
     while (i < gstart[g + 1]) {
       const size_t remaining = gstart[g + 1] - i;
@@ -325,7 +331,7 @@ static int run_batch(BatchSpec& S) {
       // (each split repeats the prologue and adds a merge through L2).
       // table copies (obn_count_kernel.cuh): fixed per shared-memory class, compile-time constants of the kernels
       const uint32_t rep_shift = (c->tune.rep && g <= 4 && kRepShift[g] > 0) ? (uint32_t)kRepShift[g] : 0u;
-      const size_t table_bytes = global_tier ? 0
+      const size_t table_bytes = chunk_tier ? (size_t)kChunkCells * 4 : global_tier ? 0
                                  : align16((size_t)max_cells * 4) + (rep_shift ? ((size_t)max_cells << rep_shift) * 4 : 0);
       const size_t tpt = target_threads / remaining;
       size_t p2 = 32;
@@ -353,13 +359,22 @@ static int run_batch(BatchSpec& S) {
           splits = (int)std::max<size_t>((size_t)splits, std::min(want, cap));
         }
       }
+      uint32_t row_splits = 1;
+      if (chunk_tier) {
+        // CTA = (chunk, row range): enough row ranges for about three CTAs per SM over the launch
+        nthr = 256;
+        const uint32_t chunks = (max_cells + kChunkCells - 1) / kChunkCells;
+        const size_t want = (3 * (size_t)c->sm_count + remaining * chunks - 1) / (remaining * chunks);
+        row_splits = (uint32_t)std::max<size_t>(1, std::min<size_t>(want, std::max<uint32_t>(1u, n_vec / 2048u)));
+        splits = (int)(chunks * row_splits);
+      }
       if (c->tune.force_threads) nthr = c->tune.force_threads;
-      if (c->tune.force_splits)
+      if (c->tune.force_splits && !chunk_tier)
         splits = std::max(1, std::min<int>(c->tune.force_splits, (int)std::max<uint32_t>(1u, n_vec)));
       const int nw = nthr / 32;
       size_t smem = table_bytes + (size_t)nw * max_rxy * 4;
       smem = std::max<size_t>(align16(smem), 16);
-      const bool need_scratch = splits > 1 || global_tier;
+      const bool need_scratch = splits > 1 || global_tier || chunk_tier;
       size_t j = i, scratch_ints = 0;
       if (need_scratch) {
         for (j = i; j < gstart[g + 1]; ++j) {
@@ -371,9 +386,9 @@ static int run_batch(BatchSpec& S) {
       } else {
         for (j = i; j < gstart[g + 1]; ++j) soff[j] = 0;
       }
-      uint32_t vps = (n_vec + splits - 1) / splits;
+      uint32_t vps = chunk_tier ? (n_vec + row_splits - 1) / row_splits : (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, rep_shift, max_rxy});
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, rep_shift, max_rxy, row_splits});
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
       i = j;
     }
@@ -485,6 +500,8 @@ static int run_batch(BatchSpec& S) {
     a.splits = L.splits;
     a.vec_per_split = L.vps;
     a.wstride = L.wstride;
+    a.chunk_cells = kChunkCells;
+    a.row_splits = L.row_splits;
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
     cudaError_t e;
     if (L.rep_shift) {
@@ -496,7 +513,8 @@ static int run_batch(BatchSpec& S) {
     if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
     else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
     else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
-    else if (L.g == 5) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
+    else if (L.g == kClassSmemMax) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
+    else if (L.g == kClassChunk) e = launch_count<32, TIER_CHUNK, false>(a, grid, L.nthr, L.smem, st);
     else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, st);
     if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "count_kernel launch failed: %s", cudaGetErrorString(e));
     ++c->prof.count_launches;

@@ -131,6 +131,7 @@ int obn_ctx_set_option(obn_ctx* c, const char* name, double value) {
   else if (k == "force_splits") c->tune.force_splits = v;
   else if (k == "streams") c->tune.streams = std::max(1, v);
   else if (k == "rep") c->tune.rep = v;
+  else if (k == "chunk") c->tune.chunk = v;
   else if (k == "min_waves") c->tune.min_waves = std::max(0, v);
   else if (k == "lattice_budget_gb") c->tune.lattice_budget_gb = std::max(1, v);
   else if (k == "lattice_max_l") c->tune.lattice_max_l = std::max(1, v);

@@ -10,8 +10,15 @@
 //                (benchmarks/micro/smem_incr.cu, profiles/r1_micro_smem_incr.txt):
 //                16 increments/clk/SM, against 6-9 for lane-private LDS/IADD/STS
 //                counters and 0.5-3 for __match_any_sync aggregation in software.
-//   TIER_GLOBAL  table in global scratch (L2 atomics) for tables that do not
-//                fit shared memory.
+//   TIER_CHUNK   tables of up to 32 shared-memory-fulls: the cell range is cut into chunks, CTA
+//                (chunk, row range) scans its rows, builds the full key and counts only the rows
+//                whose cell falls into its chunk (in shared memory, same increments), then adds
+//                the chunk into the global table.  Every row is keyed once per chunk but counted
+//                once; hot cells stay in shared memory, where POPC.INC merges them.
+//   TIER_GLOBAL  table in global scratch (L2 reductions), for tables beyond that.  Same-address
+//                reductions serialise in L2: on skewed data (a PC frontier's 5-variable tables)
+//                39 tables of 55 k - 420 k cells took 5.4 ms this way -- a quarter of a C5 run --
+//                which is why TIER_CHUNK exists.
 //
 // Category codes are read as 16-byte vectors (16 rows of one column per load,
 // coalesced: consecutive lanes read consecutive 16-byte chunks) and combined
@@ -145,10 +152,17 @@ struct KeyVec<32> {
 
 // 16 increments for one key vector.  `lane_base` is this lane's copy of the table as a byte pointer.
 template <int KW, int TIER, bool SCALE4, int RSH>
-__device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* lane_base) {
+__device__ __forceinline__ void count16(KeyVec<KW>& key, unsigned char* lane_base, uint32_t lo, uint32_t span) {
   if (SCALE4) key.scale4();
   constexpr int kShift = (SCALE4 ? 0 : 2) + (RSH > 0 ? RSH : 0);
-  if (TIER == TIER_GLOBAL) {
+  if (TIER == TIER_CHUNK) {
+    const uint32_t a0 = (uint32_t)__cvta_generic_to_shared(lane_base);
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const uint32_t f = key.get(r) - lo;             // cells outside [lo, lo + span) belong to another CTA
+      if (f < span) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a0 + (f << 2)) : "memory");
+    }
+  } else if (TIER == TIER_GLOBAL) {
 #pragma unroll
     for (int r = 0; r < 16; ++r) {
       // non-returning reduction (REDG.E.ADD): a plain atomicAdd compiles to ATOMG here, which makes
@@ -191,7 +205,7 @@ __device__ __forceinline__ void fold_column(KeyVec<8>& part, KeyVec<KW>& key, bo
 // before the increments of the current one (register double buffering).
 template <int KW, int TIER, bool SCALE4, int RSH, int K>
 __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, uint32_t v_begin,
-                                            uint32_t v_end, uint32_t tid, uint32_t nthr) {
+                                            uint32_t v_end, uint32_t tid, uint32_t nthr, uint32_t lo, uint32_t span) {
   const uint8_t* col[K];
   uint32_t card[K], gcells[K];
 #pragma unroll
@@ -219,7 +233,7 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 #pragma unroll
       for (int i = 0; i < K; ++i) fold_column<KW>(part, key, have_part, have_key, cur[i], card[i], gcells[i]);
     }
-    count16<KW, TIER, SCALE4, RSH>(key, base);
+    count16<KW, TIER, SCALE4, RSH>(key, base, lo, span);
 #pragma unroll
     for (int i = 0; i < K; ++i) cur[i] = nxt[i];
   }
@@ -229,7 +243,7 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 // that four 16-byte loads are in flight per thread.
 template <int KW, int TIER, bool SCALE4, int RSH>
 __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
-                                              uint32_t v_end, uint32_t tid, uint32_t nthr) {
+                                              uint32_t v_end, uint32_t tid, uint32_t nthr, uint32_t lo, uint32_t span) {
   for (uint32_t v = v_begin + tid; v < v_end; v += nthr) {
     const size_t off = (size_t)v << 4;
     KeyVec<KW> key;
@@ -244,7 +258,7 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
       for (int j = 0; j < 4; ++j)
         if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
     }
-    count16<KW, TIER, SCALE4, RSH>(key, base);
+    count16<KW, TIER, SCALE4, RSH>(key, base, lo, span);
   }
 }
 
@@ -299,6 +313,8 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
   // ---- table + epilogue scratch (zeroed while the descriptor loads are in flight)
   int32_t* tab;                     // the table the epilogue reads (one copy)
   int32_t* tab_rep = nullptr;       // RSH > 0: the R interleaved copies the row loop counts into
+  int32_t* tab_chunk = nullptr;     // TIER_CHUNK: this CTA's cell range [chunk_lo, chunk_lo + chunk_span) in shared memory
+  uint32_t chunk_lo = 0, chunk_span = 0;
   int32_t* wscratch;                // per-warp epilogue scratch
   constexpr uint32_t R = RSH > 0 ? (1u << RSH) : 1u;
   if (TIER == TIER_SMEM) {
@@ -312,6 +328,13 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     wscratch = reinterpret_cast<int32_t*>(smem_raw + o + (((size_t)cells * 4u + 15u) & ~(size_t)15u));
     if (!tab_rep)
       for (uint32_t i = tid; i < cells; i += nthr) tab[i] = 0;
+  } else if (TIER == TIER_CHUNK) {
+    tab = A.scratch + A.scratch_off[lt];
+    chunk_lo = (split / A.row_splits) * A.chunk_cells;
+    chunk_span = chunk_lo < cells ? min(A.chunk_cells, cells - chunk_lo) : 0u;
+    tab_chunk = reinterpret_cast<int32_t*>(smem_raw);
+    wscratch = reinterpret_cast<int32_t*>(smem_raw + (size_t)A.chunk_cells * 4u);
+    for (uint32_t i = tid; i < chunk_span; i += nthr) tab_chunk[i] = 0;
   } else {
     tab = A.scratch + A.scratch_off[lt];
     wscratch = reinterpret_cast<int32_t*>(smem_raw);
@@ -320,19 +343,19 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
 
   // ---- main loop over this split's 16-row vectors -----------------------------
   const uint32_t n_vec = (A.n_rows + 15u) >> 4;
-  const uint32_t v_begin = split * A.vec_per_split;
+  const uint32_t v_begin = (TIER == TIER_CHUNK ? split % A.row_splits : split) * A.vec_per_split;
   uint32_t v_end = v_begin + A.vec_per_split;
   if (v_end > n_vec) v_end = n_vec;
-  unsigned char* base = reinterpret_cast<unsigned char*>(tab_rep ? tab_rep : tab) + 4u * (tid & (R - 1u));   // this lane's copy
+  unsigned char* base = reinterpret_cast<unsigned char*>(tab_chunk ? tab_chunk : tab_rep ? tab_rep : tab) + 4u * (tid & (R - 1u));   // this lane's copy
   switch (k) {
     case 0: break;
-    case 1: scan_rows_k<KW, TIER, SCALE4, RSH, 1>(T, base, v_begin, v_end, tid, nthr); break;
-    case 2: scan_rows_k<KW, TIER, SCALE4, RSH, 2>(T, base, v_begin, v_end, tid, nthr); break;
-    case 3: scan_rows_k<KW, TIER, SCALE4, RSH, 3>(T, base, v_begin, v_end, tid, nthr); break;
-    case 4: scan_rows_k<KW, TIER, SCALE4, RSH, 4>(T, base, v_begin, v_end, tid, nthr); break;
-    case 5: scan_rows_k<KW, TIER, SCALE4, RSH, 5>(T, base, v_begin, v_end, tid, nthr); break;
-    case 6: scan_rows_k<KW, TIER, SCALE4, RSH, 6>(T, base, v_begin, v_end, tid, nthr); break;
-    default: scan_rows_any<KW, TIER, SCALE4, RSH>(T, k, base, v_begin, v_end, tid, nthr); break;
+    case 1: scan_rows_k<KW, TIER, SCALE4, RSH, 1>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
+    case 2: scan_rows_k<KW, TIER, SCALE4, RSH, 2>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
+    case 3: scan_rows_k<KW, TIER, SCALE4, RSH, 3>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
+    case 4: scan_rows_k<KW, TIER, SCALE4, RSH, 4>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
+    case 5: scan_rows_k<KW, TIER, SCALE4, RSH, 5>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
+    case 6: scan_rows_k<KW, TIER, SCALE4, RSH, 6>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
+    default: scan_rows_any<KW, TIER, SCALE4, RSH>(T, k, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
   }
   if (tab_rep) {                     // sum the copies into the one table everything below reads
     __syncthreads();
@@ -344,24 +367,31 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     }
     __syncthreads();
   }
-  if (tid == 0) {
+  if (tid == 0 && (TIER != TIER_CHUNK || (chunk_lo == 0 && chunk_span))) {     // (cell 0 lives in chunk 0)
+    int32_t* cell0 = TIER == TIER_CHUNK ? tab_chunk : tab;
     if (k == 0) {
       // the empty tuple: one cell holding every row of the split (contingency_table.h:52-55)
       const uint32_t r0 = v_begin << 4;
       uint32_t r1 = v_end << 4;
       if (r1 > A.n_rows) r1 = A.n_rows;
-      if (r1 > r0) atomicAdd(&tab[0], (int)(r1 - r0));
+      if (r1 > r0) atomicAdd(cell0, (int)(r1 - r0));
     } else if (v_end == n_vec && v_end > v_begin) {
       const int pad = (int)((n_vec << 4) - A.n_rows);     // zero-padding rows counted into cell 0
-      if (pad) atomicAdd(&tab[0], -pad);
+      if (pad) atomicAdd(cell0, -pad);
     }
   }
   __syncthreads();
 
   // ---- row splits: merge through global scratch, last CTA continues ---------
-  if (A.splits > 1 || TIER == TIER_GLOBAL) {
+  if (A.splits > 1 || TIER != TIER_SMEM) {
     int32_t* g = A.scratch + A.scratch_off[lt];
-    if (TIER != TIER_GLOBAL) {
+    if (TIER == TIER_CHUNK) {
+      for (uint32_t c = tid; c < chunk_span; c += nthr) {
+        const int v = tab_chunk[c];
+        if (v) atomicAdd(&g[chunk_lo + c], v);
+      }
+    }
+    if (TIER == TIER_SMEM) {
       for (uint32_t c = tid; c < cells; c += nthr) {
         const int v = tab[c];
         if (v) atomicAdd(&g[c], v);
@@ -373,7 +403,7 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     __syncthreads();
     if (T.ticket != (unsigned)A.splits - 1) return;
     __threadfence();
-    if (TIER != TIER_GLOBAL) {
+    if (TIER == TIER_SMEM) {
       for (uint32_t c = tid; c < cells; c += nthr) {
         tab[c] = __ldcg(&g[c]);
         g[c] = 0;
@@ -398,7 +428,7 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
       const CiGeom g(cells, T.card[px], T.card[py], T.weight[px], T.weight[py]);
       double stat;
       unsigned long long dof;
-      epilogue_ci<TIER == TIER_GLOBAL>(tab, g, A.kind, wscratch + (tid >> 5) * A.wstride, red_d, red_u, stat, dof);
+      epilogue_ci<TIER != TIER_SMEM>(tab, g, A.kind, wscratch + (tid >> 5) * A.wstride, red_d, red_u, stat, dof);
       if (tid == 0) {
         m_stat[m - m_begin] = stat;
         m_dof[m - m_begin] = dof;
@@ -431,7 +461,7 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     for (uint32_t c = tid; c < cells; c += nthr) out[c] = tab[c];
   }
 
-  if (TIER == TIER_GLOBAL) {      // leave the scratch table zeroed for the next launch
+  if (TIER != TIER_SMEM) {        // leave the scratch table zeroed for the next launch
     __syncthreads();
     for (uint32_t c = tid; c < cells; c += nthr) tab[c] = 0;
     if (tid == 0) A.tickets[lt] = 0;

@@ -204,6 +204,7 @@ struct obn_ctx {
     int force_splits = 0;         // != 0: row splits of every launch (sweeps)
     int streams = 4;              // launches of one batch are forked over this many streams
     int rep = 1;                  // replicated shared-memory tables (obn_count_kernel.cuh) on / off (A/B)
+    int chunk = 1;                // tables beyond shared memory: chunked shared-memory counting (TIER_CHUNK) instead of L2 reductions
     int min_waves = 0;            // row-split the tuples of a launch until it has this many waves of CTAs (0: off)
     // marginalisation lattice (obn_lattice.inl)
     int lattice_budget_gb = 24, lattice_max_l = 20, lattice_bottom = 1, lattice_reorder = 1, lattice_graph = 1,

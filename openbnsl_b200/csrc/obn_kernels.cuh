@@ -11,7 +11,7 @@
 namespace obn {
 
 enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3 };
-enum Tier : int { TIER_SMEM = 0, TIER_GLOBAL = 1 };
+enum Tier : int { TIER_SMEM = 0, TIER_GLOBAL = 1, TIER_CHUNK = 2 };
 
 struct BatchArgs {
   // dataset
@@ -43,6 +43,8 @@ struct BatchArgs {
   int32_t* scratch;         // zero on entry, zero on exit
   const uint64_t* scratch_off;  // [launch tuples]
   unsigned int* tickets;        // [launch tuples], zero on entry and exit
+  uint32_t chunk_cells;         // TIER_CHUNK: cells of one shared-memory chunk of the table
+  uint32_t row_splits;          // TIER_CHUNK: splits = chunks * row_splits, CTA (chunk, row range) = (split / row_splits, split % row_splits)
   uint32_t wstride;             // ints of epilogue scratch per warp (rx + ry, plus rx * ry for tables in global memory)
   // MODE_CI: the launch tuple is a GROUP -- the CI tests of the batch that are asked over the same
   // variable set share ONE table (counted once, in reference key order); member m of group q is the
