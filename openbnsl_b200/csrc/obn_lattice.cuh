@@ -172,7 +172,7 @@ __global__ void joint_count_kernel(const uint8_t* data, size_t stride, uint32_t 
     KeyVec<32> key;
     key.init(ld_codes16(data + (size_t)cards.v[0] * stride + off));
     for (int i = 1; i < n; ++i) key.push(ld_codes16(data + (size_t)cards.v[i] * stride + off), cards.c[i]);
-    count16<32, TIER_GLOBAL, false, -1>(key, reinterpret_cast<unsigned char*>(tab));
+    count16<32, TIER_GLOBAL, false, -1>(key, reinterpret_cast<unsigned char*>(tab), 0u, 0u);
   }
   if (v == 0) {
     const int pad = (int)((n_vec << 4) - n_rows);
