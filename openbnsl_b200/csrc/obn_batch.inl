@@ -55,8 +55,8 @@ struct BatchSpec {
 static const int kNumClasses = 8;
 static const int kClassSmemMax = 5, kClassChunk = 6, kClassGlobal = 7;
 static const uint32_t kClassCells[5] = {64, 256, 1024, 4096, 16384};
-// class 6 (TIER_CHUNK): the table is cut into chunks of this many cells (192 KB of shared memory), at most kMaxChunks of them
-static const uint32_t kChunkCells = 48 * 1024;
+// class 6 (TIER_CHUNK): the table is cut into chunks of this many cells (176 KB of shared memory), at most kMaxChunks of them
+static const uint32_t kChunkCells = 44 * 1024;
 static const uint32_t kMaxChunks = 32;
 // log2 of the shared-memory table copies per class (0: none): 32 / 32 / 16 / 4 copies keep the copies of one
 // table within 8 / 32 / 64 / 64 KB (A/B: profiles/r2_ab_replication.jsonl)
@@ -309,10 +309,10 @@ static int run_batch(BatchSpec& S) {
   if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
-  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; uint32_t wstride; uint32_t row_splits; };
+  struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; uint32_t wstride; uint32_t row_splits; uint32_t epi_ctas; size_t partial_base; };
   std::vector<Launch> launches;
   const uint32_t n_vec = (uint32_t)((ds->n_rows + 15) >> 4);
-  size_t max_scratch_ints = 0;
+  size_t max_scratch_ints = 0, partial_doubles = 0;
   const size_t target_threads = (size_t)c->sm_count * (size_t)c->tune.threads_per_sm;
   for (int g = 0; g < kNumClasses; ++g) {
     if (!group_count[g]) continue;
@@ -334,25 +334,27 @@ static int run_batch(BatchSpec& S) {
       const size_t table_bytes = chunk_tier ? (size_t)kChunkCells * 4 : global_tier ? 0
                                  : align16((size_t)max_cells * 4) + (rep_shift ? ((size_t)max_cells << rep_shift) * 4 : 0);
       const size_t tpt = target_threads / remaining;
+      // the 32-bit-key kernels (tables of > 16 Ki cells: one CTA per SM by shared memory) run up to 512 threads
+      const size_t maxthr = g >= kClassSmemMax ? 512 : 256;
       size_t p2 = 32;
-      while (p2 * 2 <= tpt && p2 < 256) p2 <<= 1;
+      while (p2 * 2 <= tpt && p2 < maxthr) p2 <<= 1;
       // shared memory may allow only a few CTAs per SM: each must then be wide enough to keep the SM busy
       const size_t ctas_by_smem = std::max<size_t>(1, std::min<size_t>(32, (c->smem_optin + 1024) / (table_bytes + 2048)));
-      while (p2 * ctas_by_smem < (size_t)c->tune.threads_per_sm && p2 < 256) p2 <<= 1;
+      while (p2 * ctas_by_smem < (size_t)c->tune.threads_per_sm && p2 < maxthr) p2 <<= 1;
       // copies pay with wide CTAs: eight warps on one set of copies (benchmarks/micro/smem_incr.cu variant 9:
       // 23 increments/clk/SM at 256 threads against 19.7 with one warp per CTA)
       if (rep_shift) p2 = 256;
       int nthr = (int)p2;
       int splits = 1;
-      if (nthr == 256) {
+      if (nthr == (int)maxthr) {
         // global tier: every CTA adds straight into the one global table, a split costs no merge
         const uint32_t min_vps = global_tier ? 256u : std::max<uint32_t>(1024u, max_cells / 4u);
-        splits = (int)std::min<size_t>(tpt / 256, std::max<uint32_t>(1u, n_vec / min_vps));
+        splits = (int)std::min<size_t>(tpt / maxthr, std::max<uint32_t>(1u, n_vec / min_vps));
         splits = std::max(1, splits);
         // a launch of only a few waves ends with SMs idling behind its last CTAs: cut the tuples into row
         // ranges until the launch has min_waves waves of CTAs (the merge is one pass over the table through L2)
         if (!global_tier && c->tune.min_waves > 0) {
-          const size_t ctas_per_sm = std::max<size_t>(1, std::min<size_t>(ctas_by_smem, 2048 / 256));
+          const size_t ctas_per_sm = std::max<size_t>(1, std::min<size_t>(ctas_by_smem, 2048 / maxthr));
           const size_t slots = (size_t)c->sm_count * ctas_per_sm;
           const size_t want = ((size_t)c->tune.min_waves * slots + remaining - 1) / remaining;
           const size_t cap = std::max<uint32_t>(1u, n_vec / std::max<uint32_t>(min_vps, 4096u));   // >= 64 Ki rows per range
@@ -362,7 +364,7 @@ static int run_batch(BatchSpec& S) {
       uint32_t row_splits = 1;
       if (chunk_tier) {
         // CTA = (chunk, row range): enough row ranges for about three CTAs per SM over the launch
-        nthr = 256;
+        nthr = 512;
         const uint32_t chunks = (max_cells + kChunkCells - 1) / kChunkCells;
         const size_t want = (3 * (size_t)c->sm_count + remaining * chunks - 1) / (remaining * chunks);
         row_splits = (uint32_t)std::max<size_t>(1, std::min<size_t>(want, std::max<uint32_t>(1u, n_vec / 2048u)));
@@ -388,7 +390,12 @@ static int run_batch(BatchSpec& S) {
       }
       uint32_t vps = chunk_tier ? (n_vec + row_splits - 1) / row_splits : (n_vec + splits - 1) / splits;
       if (vps == 0) vps = 1;
-      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, rep_shift, max_rxy, row_splits});
+      // CI tables in global memory: the epilogue is a second launch of epi_ctas CTAs per tuple (ci_epilogue_kernel)
+      uint32_t epi_ctas = 0;
+      if (ci && (global_tier || chunk_tier))
+        epi_ctas = (uint32_t)std::max<size_t>(1, std::min<size_t>(64, (4 * (size_t)c->sm_count + (j - i) - 1) / std::max<size_t>(1, j - i)));
+      launches.push_back({g, i, j, nthr, splits, vps, smem, scratch_ints, 0, false, rep_shift, max_rxy, row_splits, epi_ctas, partial_doubles});
+      partial_doubles += (size_t)(j - i) * kGroupMembers * epi_ctas * 2;
       max_scratch_ints = std::max(max_scratch_ints, scratch_ints);
       i = j;
     }
@@ -411,6 +418,8 @@ static int run_batch(BatchSpec& S) {
   if (max_scratch_ints)
     if (int rc = c->d_scratch.reserve(max_scratch_ints * 4, true)) return rc;
   if (int rc = c->d_tickets.reserve(std::max<size_t>(n_mine, 4) * 4, true)) return rc;
+  if (partial_doubles)
+    if (int rc = c->d_partials.reserve(partial_doubles * 8)) return rc;
 
   const auto t_packed = std::chrono::steady_clock::now();
   if (in_bytes) OBN_CUDA(cudaMemcpyAsync(c->d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
@@ -460,6 +469,9 @@ static int run_batch(BatchSpec& S) {
     ++c->ev_used;
     OBN_CUDA(cudaEventRecord(e0, c->stream));
   }
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> dbg_events;
+  struct DbgDesc { int g, tuples, nthr, splits, smem; };
+  std::vector<DbgDesc> dbg_desc;
   const int n_streams = std::max(1, std::min(1 + obn_ctx::kAuxStreams, c->tune.streams));
   bool aux_used[obn_ctx::kAuxStreams] = {};
   bool forked = false;
@@ -502,6 +514,8 @@ static int run_batch(BatchSpec& S) {
     a.wstride = L.wstride;
     a.chunk_cells = kChunkCells;
     a.row_splits = L.row_splits;
+    a.epi_ctas = L.epi_ctas;
+    a.partials = L.epi_ctas ? c->d_partials.as<double>() + L.partial_base : nullptr;
     const unsigned grid = (unsigned)((L.end - L.begin) * (size_t)L.splits);
     cudaError_t e;
     if (L.rep_shift) {
@@ -517,6 +531,21 @@ static int run_batch(BatchSpec& S) {
     else if (L.g == kClassChunk) e = launch_count<32, TIER_CHUNK, false>(a, grid, L.nthr, L.smem, st);
     else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, st);
     if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "count_kernel launch failed: %s", cudaGetErrorString(e));
+    if (L.epi_ctas) {
+      ci_epilogue_kernel<<<(unsigned)((L.end - L.begin) * L.epi_ctas), 256, (size_t)8 * L.wstride * 4 + 16, st>>>(a);
+      e = cudaGetLastError();
+      if (e != cudaSuccess) return fail(OBN_ERR_CUDA, "ci_epilogue_kernel launch failed: %s", cudaGetErrorString(e));
+      ++c->prof.total_launches;
+    }
+    if (c->tune.debug >= 2) {               // launch log: [begin, end) of every launch relative to the batch's first event
+      cudaEvent_t b0, b1;
+      cudaEventCreate(&b0);
+      cudaEventCreate(&b1);
+      // (recorded AFTER the launch on the same stream: b1 - e0 is the launch's completion time; b0 is unused)
+      cudaEventRecord(b1, st);
+      dbg_events.push_back({b0, b1});
+      dbg_desc.push_back({L.g, (int)(L.end - L.begin), L.nthr, L.splits, (int)L.smem});
+    }
     ++c->prof.count_launches;
     ++c->prof.total_launches;
   }
@@ -552,6 +581,21 @@ static int run_batch(BatchSpec& S) {
     return OBN_OK;
   }
   OBN_CUDA(cudaStreamSynchronize(c->stream));
+  if (!dbg_events.empty() && e0) {
+    cudaDeviceSynchronize();
+    fprintf(stderr, "[obn batch] %zu tuples, %zu launches:", n, dbg_events.size());
+    for (size_t i = 0; i < dbg_events.size(); ++i) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, e0, dbg_events[i].second);
+      fprintf(stderr, "  c%d x%d t%d s%d smem%dK done@%.3f", dbg_desc[i].g, dbg_desc[i].tuples, dbg_desc[i].nthr, dbg_desc[i].splits,
+              dbg_desc[i].smem >> 10, ms);
+      cudaEventDestroy(dbg_events[i].first);
+      cudaEventDestroy(dbg_events[i].second);
+    }
+    float tot = 0;
+    cudaEventElapsedTime(&tot, e0, e1);
+    fprintf(stderr, "  all@%.3f ms\n", tot);
+  }
   const auto t_synced = std::chrono::steady_clock::now();
   c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
   c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(t_synced - t_packed).count();

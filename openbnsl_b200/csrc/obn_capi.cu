@@ -99,7 +99,7 @@ void obn_ctx_destroy(obn_ctx* c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   obn_comm_destroy(c);
-  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_scratch, &c->d_tickets, &c->d_scalar}) b->release();
+  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_scratch, &c->d_tickets, &c->d_scalar, &c->d_partials}) b->release();
   c->lut.release();
   c->es_pool.release();
   if (c->ds_cache) cudaFree(c->ds_cache);

@@ -263,7 +263,7 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
 }
 
 template <int KW, int TIER, bool SCALE4, int RSH = -1>
-__global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const BatchArgs A) {
+__global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 32 ? 1 : 3)) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ CtaTuple T;
   __shared__ double red_d[32];
@@ -397,6 +397,7 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
         if (v) atomicAdd(&g[c], v);
       }
     }
+    if (TIER != TIER_SMEM && A.epi_ctas) return;          // ci_epilogue_kernel reads the table after this launch
     __threadfence();
     __syncthreads();
     if (tid == 0) T.ticket = atomicAdd(&A.tickets[lt], 1u);
@@ -466,6 +467,76 @@ __global__ void __launch_bounds__(256, (KW == 8 ? 4 : 3)) count_kernel(const Bat
     for (uint32_t c = tid; c < cells; c += nthr) tab[c] = 0;
     if (tid == 0) A.tickets[lt] = 0;
   }
+}
+
+// The CI epilogue of tables that live in global memory, as its own launch: A.epi_ctas CTAs per tuple, CTA e
+// takes the slices [e, e+1) * ceil(n_slices / epi_ctas) of every member, so a 400 k-cell table with ten members
+// is read by the whole GPU instead of by the one CTA that happened to finish counting last (6 ms of a 21 ms C5
+// run before).  Partial sums are combined by the last CTA to arrive, in CTA order: deterministic.
+__global__ void __launch_bounds__(256) ci_epilogue_kernel(const BatchArgs A) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ CtaTuple T;
+  __shared__ double red_d[32];
+  __shared__ unsigned long long red_u[32];
+  const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+  const uint32_t lt = blockIdx.x / A.epi_ctas, e = blockIdx.x - lt * A.epi_ctas;
+  const uint4 hdr = __ldg(&A.hdr[lt]);
+  const uint32_t t = hdr.x, cells = hdr.w;
+  const int k = (int)hdr.z;
+  if (tid < 32) {
+    if ((int)tid < k) T.card[tid] = (__ldg(&A.desc[hdr.y + tid]) >> 24) + 1u;
+    __syncwarp();
+    if (tid == 0) {
+      uint32_t w = 1;
+      for (int i = k - 1; i >= 0; --i) {
+        T.weight[i] = w;
+        w *= T.card[i];
+      }
+    }
+  }
+  __syncthreads();
+  int32_t* tab = A.scratch + A.scratch_off[lt];
+  int32_t* wscratch = reinterpret_cast<int32_t*>(smem_raw);
+  const uint32_t m_begin = __ldg(&A.mem_off[t]), m_end = __ldg(&A.mem_off[t + 1]), n_mem = m_end - m_begin;
+  double* part = A.partials + (size_t)lt * kGroupMembers * A.epi_ctas * 2;
+  for (uint32_t m = 0; m < n_mem; ++m) {
+    const uint2 mem = __ldg(&A.members[m_begin + m]);
+    const uint32_t px = mem.y & 0xffu, py = (mem.y >> 8) & 0xffu;
+    const CiGeom g(cells, T.card[px], T.card[py], T.weight[px], T.weight[py]);
+    const uint32_t per = (g.n_slices + A.epi_ctas - 1) / A.epi_ctas;
+    const uint32_t s0 = min(g.n_slices, e * per), s1 = min(g.n_slices, s0 + per);
+    double stat;
+    unsigned long long dof;
+    epilogue_ci<true>(tab, g, A.kind, wscratch + (tid >> 5) * A.wstride, red_d, red_u, stat, dof, s0, s1);
+    if (tid == 0) {
+      part[((size_t)m * A.epi_ctas + e) * 2] = stat;
+      part[((size_t)m * A.epi_ctas + e) * 2 + 1] = __longlong_as_double((long long)dof);
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) T.ticket = atomicAdd(&A.tickets[lt], 1u);
+  __syncthreads();
+  if (T.ticket != A.epi_ctas - 1) return;
+  __threadfence();
+  if (tid < n_mem) {                                       // one thread per member: CTA order, then p and the decision
+    double stat = 0.0;
+    unsigned long long dof = 0;
+    for (uint32_t q = 0; q < A.epi_ctas; ++q) {
+      stat += __ldcg(&part[((size_t)tid * A.epi_ctas + q) * 2]);
+      dof += (unsigned long long)__double_as_longlong(__ldcg(&part[((size_t)tid * A.epi_ctas + q) * 2 + 1]));
+    }
+    const uint32_t id = __ldg(&A.members[m_begin + tid]).x;
+    if (A.stat) A.stat[id] = stat;
+    if (A.dof) A.dof[id] = dof;
+    if (A.pval || A.first) {
+      const double p = pchisq(stat, dof);                                  // citest.h:139
+      if (A.pval) A.pval[id] = p;
+      if (A.first && p >= A.level) atomicMin(&A.first[__ldg(&A.slot_of_test[id])], (int32_t)id);   // :147
+    }
+  }
+  for (uint32_t c = tid; c < cells; c += nthr) tab[c] = 0;         // the scratch table goes back zeroed
+  if (tid == 0) A.tickets[lt] = 0;
 }
 
 }  // namespace obn

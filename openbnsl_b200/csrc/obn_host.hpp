@@ -181,6 +181,7 @@ struct obn_ctx {
   obn::EsPool es_pool;
   obn::DevBuf d_scratch;   // int32, kept all-zero between launches
   obn::DevBuf d_tickets;   // uint32, kept all-zero between launches
+  obn::DevBuf d_partials;  // per-CTA partial statistics of the split CI epilogue (ci_epilogue_kernel)
   obn::DevBuf d_scalar;    // staging of small host values that go through a collective
   obn::PinBuf h_in, h_out;
   uint8_t* ds_cache = nullptr;  // device buffer of the last destroyed dataset, reused by the next upload

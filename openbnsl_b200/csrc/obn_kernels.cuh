@@ -45,6 +45,11 @@ struct BatchArgs {
   unsigned int* tickets;        // [launch tuples], zero on entry and exit
   uint32_t chunk_cells;         // TIER_CHUNK: cells of one shared-memory chunk of the table
   uint32_t row_splits;          // TIER_CHUNK: splits = chunks * row_splits, CTA (chunk, row range) = (split / row_splits, split % row_splits)
+  // tables in global memory (TIER_CHUNK / TIER_GLOBAL), CI mode: the epilogue is its own launch of
+  // epi_ctas CTAs per tuple (ci_epilogue_kernel); each takes a slice range and leaves partial (stat, dof)
+  // per member in `partials`, the last one to arrive sums them in CTA order
+  uint32_t epi_ctas;            // 0: epilogue inside count_kernel (last CTA of the tuple)
+  double* partials;             // [launch tuple][kGroupMembers][epi_ctas] {stat, dof as double bits}
   uint32_t wstride;             // ints of epilogue scratch per warp (rx + ry, plus rx * ry for tables in global memory)
   // MODE_CI: the launch tuple is a GROUP -- the CI tests of the batch that are asked over the same
   // variable set share ONE table (counted once, in reference key order); member m of group q is the
@@ -111,9 +116,9 @@ __device__ __forceinline__ double ci_cell(double obs, int ri, int cj, double n_t
 // Small slices (rx, ry <= 4, the common case for the named networks): ONE LANE
 // per slice, the slice held in registers.
 __device__ __forceinline__ void ci_slices_small(const int32_t* tab, const CiGeom& g, int kind, double& stat,
-                                                unsigned long long& dof) {
+                                                unsigned long long& dof, uint32_t s_begin, uint32_t s_end) {
   const uint32_t rx = g.rx, ry = g.ry;
-  for (uint32_t s = threadIdx.x; s < g.n_slices; s += blockDim.x) {
+  for (uint32_t s = s_begin + threadIdx.x; s < s_end; s += blockDim.x) {
     const int32_t* t = tab + g.base(s);
     int o[4][4], rs[4] = {0, 0, 0, 0}, cs[4] = {0, 0, 0, 0};
     int tot = 0;
@@ -149,14 +154,14 @@ __device__ __forceinline__ void ci_slices_small(const int32_t* tab, const CiGeom
 // dependent round trips, which made the last CTA of a 400 k-cell table the longest thing in a PC run.
 template <bool STAGE>
 __device__ __forceinline__ void ci_slices_any(const int32_t* tab, const CiGeom& g, int kind, int32_t* wscratch,
-                                              double& stat, unsigned long long& dof) {
+                                              double& stat, unsigned long long& dof, uint32_t s_begin, uint32_t s_end) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const uint32_t rx = g.rx, ry = g.ry, sl = rx * ry;
   int32_t* rs = wscratch;        // [rx]
   int32_t* cs = wscratch + rx;   // [ry]
   int32_t* buf = wscratch + rx + ry;   // [rx * ry], STAGE only
   const uint32_t wx = STAGE ? ry : g.wx, wy = STAGE ? 1u : g.wy;
-  for (uint32_t s = warp; s < g.n_slices; s += nw) {
+  for (uint32_t s = s_begin + warp; s < s_end; s += nw) {
     const int32_t* t = tab + g.base(s);
     if (STAGE) {
       for (uint32_t c = lane; c < sl; c += 32) {
@@ -204,11 +209,12 @@ __device__ __forceinline__ void ci_slices_any(const int32_t* tab, const CiGeom& 
 template <bool GLOBAL_TABLE>
 __device__ __forceinline__ void epilogue_ci(const int32_t* tab, const CiGeom& g, int kind, int32_t* wscratch,
                                             double* red_d, unsigned long long* red_u, double& stat_out,
-                                            unsigned long long& dof_out) {
+                                            unsigned long long& dof_out, uint32_t s_begin = 0, uint32_t s_end = 0xffffffffu) {
   double stat = 0.0;
   unsigned long long dof = 0;
-  if (g.rx <= 4 && g.ry <= 4) ci_slices_small(tab, g, kind, stat, dof);
-  else ci_slices_any<GLOBAL_TABLE>(tab, g, kind, wscratch, stat, dof);
+  if (s_end > g.n_slices) s_end = g.n_slices;             // (default: every slice)
+  if (g.rx <= 4 && g.ry <= 4) ci_slices_small(tab, g, kind, stat, dof, s_begin, s_end);
+  else ci_slices_any<GLOBAL_TABLE>(tab, g, kind, wscratch, stat, dof, s_begin, s_end);
   stat_out = block_sum(stat, red_d);
   dof_out = block_sum(dof, red_u);
 }
