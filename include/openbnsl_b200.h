@@ -69,6 +69,8 @@ OBN_API void obn_ctx_destroy(obn_ctx* ctx);
 OBN_API void* obn_ctx_stream(obn_ctx* ctx);
 /* Tuning knobs for A/B runs and tests (defaults are what the published numbers use):
  *   "threads_per_sm" (768), "force_threads" (0), "force_splits" (0), "streams" (4)   counting-kernel launch policy
+ *   "pack4" (1)                          keep a second copy of the matrix with two rows per byte for the variables of <= 16 states
+ *                                        and read that one whenever every column of a table has it (half the L2 traffic)
  *   "rep" (1), "chunk" (1), "min_waves" (0)   replicated shared-memory tables on / off; tables beyond shared memory counted
  *                                        chunk-wise in shared memory instead of by L2 reductions; row-split small launches to this many waves
  *   "lattice_budget_gb" (24), "lattice_max_l" (20), "lattice_bottom" (1), "lattice_reorder" (1),

@@ -429,6 +429,7 @@ static int run_batch(BatchSpec& S) {
   unsigned char* dout = c->d_out.as<unsigned char>();
   BatchArgs a{};
   a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows;
+  a.data4 = c->tune.pack4 ? ds->data4 : nullptr; a.stride4 = ds->stride4;
   a.desc = reinterpret_cast<const uint32_t*>(din + o_var);
   a.mode = S.mode; a.kind = S.kind; a.ess = S.ess;
   if (exact) {

@@ -59,6 +59,22 @@ int obn::LutCache::append(obn_ctx* c, const std::vector<double>& avals) {
   return OBN_OK;
 }
 
+namespace obn {
+// Two rows per byte (see BatchArgs::data4): one thread per 16-byte chunk = 32 rows of one column.
+__global__ void pack4_kernel(const uint8_t* data, size_t stride, uint8_t* data4, size_t stride4, size_t n_vars) {
+  const size_t chunks = stride4 >> 4;
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= chunks * n_vars) return;
+  const size_t v = i / chunks, ch = i - v * chunks;
+  const uint4 lo = *reinterpret_cast<const uint4*>(data + v * stride + ch * 32);
+  const uint4 hi = *reinterpret_cast<const uint4*>(data + v * stride + ch * 32 + 16);
+  const uint32_t m = 0x0f0f0f0fu;
+  *reinterpret_cast<uint4*>(data4 + v * stride4 + ch * 16) =
+      make_uint4((lo.x & m) | ((hi.x & m) << 4), (lo.y & m) | ((hi.y & m) << 4), (lo.z & m) | ((hi.z & m) << 4),
+                 (lo.w & m) | ((hi.w & m) << 4));
+}
+}  // namespace obn
+
 extern "C" {
 
 const char* obn_last_error(void) { return g_last_error.c_str(); }
@@ -132,6 +148,7 @@ int obn_ctx_set_option(obn_ctx* c, const char* name, double value) {
   else if (k == "streams") c->tune.streams = std::max(1, v);
   else if (k == "rep") c->tune.rep = v;
   else if (k == "chunk") c->tune.chunk = v;
+  else if (k == "pack4") c->tune.pack4 = v;
   else if (k == "min_waves") c->tune.min_waves = std::max(0, v);
   else if (k == "lattice_budget_gb") c->tune.lattice_budget_gb = std::max(1, v);
   else if (k == "lattice_max_l") c->tune.lattice_max_l = std::max(1, v);
@@ -164,7 +181,13 @@ int obn_dataset_upload(obn_ctx* c, const uint8_t* col_major, size_t n_vars, size
   d->stride = ((n_rows + 127) / 128) * 128;
   if (d->stride == 0) d->stride = 128;
   d->cards.assign(cards, cards + n_vars);
-  const size_t bytes = std::max<size_t>(d->stride * n_vars, 128);
+  // behind the byte matrix: the nibble-packed copy (half the size), when any variable can use it
+  bool any_small = false;
+  for (size_t v = 0; v < n_vars; ++v) any_small |= cards[v] <= 16;
+  const size_t byte_bytes = (std::max<size_t>(d->stride * n_vars, 128) + 255) & ~(size_t)255;
+  const bool pack = c->tune.pack4 && any_small && n_rows > 0;
+  d->stride4 = pack ? d->stride / 2 : 0;
+  const size_t bytes = byte_bytes + (pack ? d->stride4 * n_vars : 0);
   if (c->ds_cache && c->ds_cache_bytes >= bytes) {       // reuse the buffer of the last destroyed dataset
     d->data = c->ds_cache;
     d->capacity = c->ds_cache_bytes;
@@ -187,6 +210,12 @@ int obn_dataset_upload(obn_ctx* c, const uint8_t* col_major, size_t n_vars, size
       OBN_CUDA(cudaMemset2DAsync(d->data + n_rows, d->stride, 0, d->stride - n_rows, n_vars, c->stream));
     OBN_CUDA(cudaMemcpy2DAsync(d->data, d->stride, col_major, row_stride, n_rows, n_vars,
                                cudaMemcpyHostToDevice, c->stream));
+  }
+  if (pack) {
+    d->data4 = d->data + byte_bytes;
+    const size_t work = (d->stride4 >> 4) * n_vars;
+    obn::pack4_kernel<<<(unsigned)((work + 255) / 256), 256, 0, c->stream>>>(d->data, d->stride, d->data4, d->stride4, n_vars);
+    OBN_CUDA(cudaGetLastError());
   }
   OBN_CUDA(cudaStreamSynchronize(c->stream));
   c->prof.h2d_bytes += (double)(n_vars * n_rows);

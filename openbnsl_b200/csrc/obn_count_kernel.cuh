@@ -44,6 +44,7 @@ struct CtaTuple {            // per-CTA tuple description in shared memory
   // with packed 8-bit arithmetic (4 rows per IMAD) and only the group keys are widened
   uint32_t gcells[kMaxTupleVars];      // cells of the group that ends at column i (0: not a group end)
   uint32_t weight[kMaxTupleVars];      // radix weight of digit i (contingency_table.h:43-49: the last digit has weight 1)
+  int packed;                // every column of the tuple has <= 16 states and the data set carries nibble-packed columns
   int child_pos;             // BDEU_ONE: position of the child in reference order
   unsigned int ticket;
 };
@@ -203,7 +204,16 @@ __device__ __forceinline__ void fold_column(KeyVec<8>& part, KeyVec<KW>& key, bo
 // Row scan with the column count known at compile time: column pointers and
 // cards live in registers, and the loads of the NEXT 16-row vector are issued
 // before the increments of the current one (register double buffering).
-template <int KW, int TIER, bool SCALE4, int RSH, int K>
+// Nibble-packed columns (BatchArgs::data4): a 16-byte load holds 32 rows of a column whose cardinality is <= 16
+// -- byte j of chunk c carries row 32c + j in its low and row 32c + 16 + j in its high nibble -- so the two
+// halves unpack into the same byte vectors the unpacked loop builds its keys from.
+__device__ __forceinline__ uint4 nibbles(const uint4& p, int half) {
+  const uint32_t m = 0x0f0f0f0fu;
+  return half ? make_uint4((p.x >> 4) & m, (p.y >> 4) & m, (p.z >> 4) & m, (p.w >> 4) & m)
+              : make_uint4(p.x & m, p.y & m, p.z & m, p.w & m);
+}
+
+template <int KW, int TIER, bool SCALE4, int RSH, int K, bool PACK>
 __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* base, uint32_t v_begin,
                                             uint32_t v_end, uint32_t tid, uint32_t nthr, uint32_t lo, uint32_t span) {
   const uint8_t* col[K];
@@ -222,18 +232,24 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 #pragma unroll
       for (int i = 0; i < K; ++i) nxt[i] = ld_codes16(col[i] + ((size_t)vn << 4));
     }
-    KeyVec<KW> key;
-    if (KW == 8) {                    // tables of <= 256 cells: one group, all packed
-      key.init(cur[0]);
 #pragma unroll
-      for (int i = 1; i < K; ++i) key.push(cur[i], card[i]);
-    } else {
-      KeyVec<8> part;
-      bool have_part = false, have_key = false;
+    for (int half = 0; half < (PACK ? 2 : 1); ++half) {
+      uint4 c[K];
 #pragma unroll
-      for (int i = 0; i < K; ++i) fold_column<KW>(part, key, have_part, have_key, cur[i], card[i], gcells[i]);
+      for (int i = 0; i < K; ++i) c[i] = PACK ? nibbles(cur[i], half) : cur[i];
+      KeyVec<KW> key;
+      if (KW == 8) {                    // tables of <= 256 cells: one group, all packed
+        key.init(c[0]);
+#pragma unroll
+        for (int i = 1; i < K; ++i) key.push(c[i], card[i]);
+      } else {
+        KeyVec<8> part;
+        bool have_part = false, have_key = false;
+#pragma unroll
+        for (int i = 0; i < K; ++i) fold_column<KW>(part, key, have_part, have_key, c[i], card[i], gcells[i]);
+      }
+      count16<KW, TIER, SCALE4, RSH>(key, base, lo, span);
     }
-    count16<KW, TIER, SCALE4, RSH>(key, base, lo, span);
 #pragma unroll
     for (int i = 0; i < K; ++i) cur[i] = nxt[i];
   }
@@ -241,24 +257,30 @@ __device__ __forceinline__ void scan_rows_k(const CtaTuple& T, unsigned char* ba
 
 // Any column count (descriptors stay in shared memory): columns are loaded four at a time so
 // that four 16-byte loads are in flight per thread.
-template <int KW, int TIER, bool SCALE4, int RSH>
+template <int KW, int TIER, bool SCALE4, int RSH, bool PACK>
 __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned char* base, uint32_t v_begin,
                                               uint32_t v_end, uint32_t tid, uint32_t nthr, uint32_t lo, uint32_t span) {
   for (uint32_t v = v_begin + tid; v < v_end; v += nthr) {
     const size_t off = (size_t)v << 4;
-    KeyVec<KW> key;
-    KeyVec<8> part;
-    bool have_part = false, have_key = false;
-    for (int i = 0; i < k; i += 4) {
-      uint4 c[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (i + j < k) c[j] = ld_codes16(T.col[i + j] + off);
+    for (int half = 0; half < (PACK ? 2 : 1); ++half) {     // (the packed columns are read once per half: L1 hits)
+      KeyVec<KW> key;
+      KeyVec<8> part;
+      bool have_part = false, have_key = false;
+      for (int i = 0; i < k; i += 4) {
+        uint4 c[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
+        for (int j = 0; j < 4; ++j)
+          if (i + j < k) {
+            c[j] = ld_codes16(T.col[i + j] + off);
+            if (PACK) c[j] = nibbles(c[j], half);
+          }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (i + j < k) fold_column<KW>(part, key, have_part, have_key, c[j], T.card[i + j], T.gcells[i + j]);
+      }
+      count16<KW, TIER, SCALE4, RSH>(key, base, lo, span);
     }
-    count16<KW, TIER, SCALE4, RSH>(key, base, lo, span);
   }
 }
 
@@ -287,10 +309,12 @@ __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 3
     const bool live = (int)tid < k;
     const uint32_t d = live ? __ldg(&A.desc[hdr.y + tid]) : 0u;
     const uint32_t v = d & 0xffffffu, c = (d >> 24) + 1u;
+    const bool packed = A.data4 != nullptr && k > 0 && !__any_sync(0xffffffffu, live && c > 16u);
     if (live) {
-      T.col[tid] = A.data + (size_t)v * A.stride;
+      T.col[tid] = packed ? A.data4 + (size_t)v * A.stride4 : A.data + (size_t)v * A.stride;
       T.card[tid] = c;
     }
+    if (tid == 0) T.packed = packed;
     const unsigned m_child = __ballot_sync(0xffffffffu, live && v == child);
     __syncwarp();
     if (tid == 0) {
@@ -342,21 +366,28 @@ __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 3
   __syncthreads();
 
   // ---- main loop over this split's 16-row vectors -----------------------------
-  const uint32_t n_vec = (A.n_rows + 15u) >> 4;
-  const uint32_t v_begin = (TIER == TIER_CHUNK ? split % A.row_splits : split) * A.vec_per_split;
-  uint32_t v_end = v_begin + A.vec_per_split;
+  // a "vector" is what one 16-byte load of a column holds: 16 rows, or 32 of a nibble-packed column
+  const bool packed = T.packed != 0;
+  const int vshift = packed ? 5 : 4;
+  const uint32_t n_vec = (A.n_rows + (packed ? 31u : 15u)) >> vshift;
+  const uint32_t vps = packed ? (A.vec_per_split + 1u) >> 1 : A.vec_per_split;
+  const uint32_t v_begin = (TIER == TIER_CHUNK ? split % A.row_splits : split) * vps;
+  uint32_t v_end = v_begin + vps;
   if (v_end > n_vec) v_end = n_vec;
   unsigned char* base = reinterpret_cast<unsigned char*>(tab_chunk ? tab_chunk : tab_rep ? tab_rep : tab) + 4u * (tid & (R - 1u));   // this lane's copy
-  switch (k) {
-    case 0: break;
-    case 1: scan_rows_k<KW, TIER, SCALE4, RSH, 1>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
-    case 2: scan_rows_k<KW, TIER, SCALE4, RSH, 2>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
-    case 3: scan_rows_k<KW, TIER, SCALE4, RSH, 3>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
-    case 4: scan_rows_k<KW, TIER, SCALE4, RSH, 4>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
-    case 5: scan_rows_k<KW, TIER, SCALE4, RSH, 5>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
-    case 6: scan_rows_k<KW, TIER, SCALE4, RSH, 6>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
-    default: scan_rows_any<KW, TIER, SCALE4, RSH>(T, k, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break;
+#define OBN_SCAN(PACK)                                                                                              \
+  switch (k) {                                                                                                     \
+    case 0: break;                                                                                                 \
+    case 1: scan_rows_k<KW, TIER, SCALE4, RSH, 1, PACK>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break; \
+    case 2: scan_rows_k<KW, TIER, SCALE4, RSH, 2, PACK>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break; \
+    case 3: scan_rows_k<KW, TIER, SCALE4, RSH, 3, PACK>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break; \
+    case 4: scan_rows_k<KW, TIER, SCALE4, RSH, 4, PACK>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break; \
+    case 5: scan_rows_k<KW, TIER, SCALE4, RSH, 5, PACK>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break; \
+    case 6: scan_rows_k<KW, TIER, SCALE4, RSH, 6, PACK>(T, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break; \
+    default: scan_rows_any<KW, TIER, SCALE4, RSH, PACK>(T, k, base, v_begin, v_end, tid, nthr, chunk_lo, chunk_span); break; \
   }
+  if (packed) { OBN_SCAN(true) } else { OBN_SCAN(false) }
+#undef OBN_SCAN
   if (tab_rep) {                     // sum the copies into the one table everything below reads
     __syncthreads();
     for (uint32_t c = tid; c < cells; c += nthr) {
@@ -371,12 +402,12 @@ __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 3
     int32_t* cell0 = TIER == TIER_CHUNK ? tab_chunk : tab;
     if (k == 0) {
       // the empty tuple: one cell holding every row of the split (contingency_table.h:52-55)
-      const uint32_t r0 = v_begin << 4;
-      uint32_t r1 = v_end << 4;
+      const uint32_t r0 = v_begin << vshift;
+      uint32_t r1 = v_end << vshift;
       if (r1 > A.n_rows) r1 = A.n_rows;
       if (r1 > r0) atomicAdd(cell0, (int)(r1 - r0));
     } else if (v_end == n_vec && v_end > v_begin) {
-      const int pad = (int)((n_vec << 4) - A.n_rows);     // zero-padding rows counted into cell 0
+      const int pad = (int)((n_vec << vshift) - A.n_rows);     // zero-padding rows counted into cell 0
       if (pad) atomicAdd(cell0, -pad);
     }
   }

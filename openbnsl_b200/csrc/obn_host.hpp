@@ -160,6 +160,8 @@ static const int32_t kFirstNone = 0x7f000000;
 struct obn_dataset {
   obn_ctx* ctx = nullptr;
   uint8_t* data = nullptr;      // device, column-major, padded
+  uint8_t* data4 = nullptr;     // device, behind `data`: two rows per byte for the columns of <= 16 states (null: not built)
+  size_t stride4 = 0;
   size_t capacity = 0;          // bytes allocated behind `data`
   std::vector<uint32_t> cards;  // host copy
   size_t n_vars = 0, n_rows = 0, stride = 0;
@@ -205,6 +207,7 @@ struct obn_ctx {
     int force_splits = 0;         // != 0: row splits of every launch (sweeps)
     int streams = 4;              // launches of one batch are forked over this many streams
     int rep = 1;                  // replicated shared-memory tables (obn_count_kernel.cuh) on / off (A/B)
+    int pack4 = 1;                // build and use nibble-packed columns (two rows per byte) for variables of <= 16 states
     int chunk = 1;                // tables beyond shared memory: chunked shared-memory counting (TIER_CHUNK) instead of L2 reductions
     int min_waves = 0;            // row-split the tuples of a launch until it has this many waves of CTAs (0: off)
     // marginalisation lattice (obn_lattice.inl)

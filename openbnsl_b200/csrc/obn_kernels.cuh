@@ -17,6 +17,8 @@ struct BatchArgs {
   // dataset
   const uint8_t* data;      // column-major codes, column v at data + v*stride
   size_t stride;            // bytes between columns (multiple of 128)
+  const uint8_t* data4;     // the same matrix with two rows per byte for the columns of <= 16 states (null: none);
+  size_t stride4;           // byte j of 16-byte chunk c of a column = row 32c + j | row 32c + 16 + j << 4
   uint32_t n_rows;
   // batch (device copies of the CSR arrays)
   const uint32_t* desc;     // [offsets[n]]  var_id | (card-1) << 24, ascending var ids per tuple
