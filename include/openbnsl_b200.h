@@ -129,6 +129,30 @@ OBN_API int obn_count_tables(obn_ctx* ctx, const obn_dataset* ds,
                              size_t n_tuples, int32_t* counts_out,
                              const uint64_t* out_offsets);
 
+/* ONE table, no allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code
+ * under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * The same counts as obn_count_tables for one tuple -- dense int32, reference
+ * key order -- but every buffer is the CALLER's device memory and the global
+ * scratch table the kernel merges its CTAs into is a file-scope __device__
+ * array of the library (256 KiB + 256 bytes, held by every GPU that loads the
+ * library until the process exits), so the call issues no cudaMalloc / cudaFree:
+ * one cudaMemsetAsync of that array and one kernel launch on `stream`
+ * (a cudaStream_t; NULL = the default stream).  Needs no ctx.
+ *   data_dev        column-major uint8 matrix on `device`: column v, row r at v * row_stride + r
+ *   cols, cards     HOST arrays: the n_cols <= 16 columns of the table, ASCENDING, and their cardinalities
+ *   counts_out_dev  DEVICE buffer of n_cells = prod(cards) int32; n_cells > OBN_STATIC_MAX_CELLS
+ *                   fails with OBN_ERR_UNSUPPORTED (use obn_count_tables)
+ * ASYNCHRONOUS: the counts are valid once `stream` has reached this point.  All
+ * calls on a device share the one array (cleared at the start of every call):
+ * calls that overlap on the GPU -- different streams, no dependency -- race.  The
+ * first call per device resolves the array's address; make it outside capture. */
+#define OBN_STATIC_MAX_CELLS 65536
+OBN_API int obn_count_table_static(int device, void* stream, const uint8_t* data_dev,
+                                   size_t n_rows, size_t row_stride,
+                                   const uint32_t* cols, const uint32_t* cards, size_t n_cols,
+                                   int32_t* counts_out_dev, size_t n_cells);
+
 /* Replaces ContingencyTable + calculate_local_score (local_score.h:22-62) for
  * BDeu: score of child[t] given the other variables of tuple t.
  * exact_order != 0 reproduces the reference's floating-point term order with

@@ -19,6 +19,7 @@ LIB_PATH = os.path.join(HERE, "libopenbnsl_b200.so")
 
 OBN_OK, OBN_ERR_INVALID, OBN_ERR_CUDA, OBN_ERR_OOM, OBN_ERR_UNSUPPORTED, OBN_ERR_RANGE, OBN_ERR_COMM = range(7)
 COMM_ID_BYTES = 128
+STATIC_MAX_CELLS = 65536
 CI_CHI2, CI_G2 = 0, 1
 
 EXPORTS = [
@@ -26,7 +27,7 @@ EXPORTS = [
     "obn_comm_unique_id", "obn_comm_init", "obn_comm_destroy", "obn_comm_rank", "obn_comm_world",
     "obn_comm_allgather_inplace", "obn_comm_allgather_host", "obn_comm_allreduce_min_i32",
     "obn_dataset_upload", "obn_dataset_destroy", "obn_host_pin", "obn_host_unpin", "obn_dataset_n_vars", "obn_dataset_n_rows",
-    "obn_count_tables", "obn_bdeu_scores", "obn_bdeu_subset_scores", "obn_ci_tests",
+    "obn_count_tables", "obn_count_table_static", "obn_bdeu_scores", "obn_bdeu_subset_scores", "obn_ci_tests",
     "obn_ci_tests_submit", "obn_ci_tests_collect", "obn_pc_round", "obn_pc_round_submit", "obn_pc_round_collect",
     "obn_ci_group_plan",
     "obn_es_begin", "obn_es_level_begin", "obn_es_level_scores", "obn_es_level_buffer", "obn_es_level_dp", "obn_es_level_dp_part", "obn_es_level_dp_commit", "obn_es_level_dp_sharded", "obn_lattice_bottom_program",
@@ -75,6 +76,7 @@ def load():
     L.obn_dataset_n_rows.argtypes = [vp]
     L.obn_dataset_n_rows.restype = C.c_size_t
     L.obn_count_tables.argtypes = [vp, vp, u32p, u64p, C.c_size_t, i32p, u64p]
+    L.obn_count_table_static.argtypes = [C.c_int, vp, vp, C.c_size_t, C.c_size_t, u32p, u32p, C.c_size_t, vp, C.c_size_t]
     L.obn_bdeu_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, C.c_double, C.c_int, f64p]
     L.obn_bdeu_subset_scores.argtypes = [vp, vp, u32p, u64p, C.c_size_t, C.c_double, C.c_int, f64p]
     L.obn_ci_tests.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, f64p, u64p, f64p]
@@ -147,6 +149,21 @@ def ci_group_plan(cards, tuples, x, y):
                                     C.byref(n_groups)))
     groups = [gv[int(go[q]):int(go[q + 1])].tolist() for q in range(n_groups.value)]
     return groups, group_of[:n], [(int(d) & 0xff, (int(d) >> 8) & 0xff) for d in digits[:n]]
+
+
+def count_table_static(device, stream, data_dev, n_rows, row_stride, cols, cards, counts_out_dev):
+    """obn_count_table_static: one table into the caller's DEVICE buffer, no allocation inside the library
+    (global scratch = a static __device__ array; at most STATIC_MAX_CELLS cells).  data_dev / counts_out_dev / stream
+    are integers (device addresses, a cudaStream_t); asynchronous on `stream`."""
+    cols = np.ascontiguousarray(np.asarray(cols, dtype=np.uint32))
+    cards = np.ascontiguousarray(np.asarray(cards, dtype=np.uint32))
+    n_cells = 1
+    for c in cards.tolist():
+        n_cells *= int(c)
+    _check(load().obn_count_table_static(int(device), C.c_void_p(stream or None), C.c_void_p(data_dev), int(n_rows),
+                                         int(row_stride), _ptr(cols, C.c_uint32), _ptr(cards, C.c_uint32), len(cols),
+                                         C.c_void_p(counts_out_dev), n_cells))
+    return n_cells
 
 
 def comm_unique_id() -> bytes:

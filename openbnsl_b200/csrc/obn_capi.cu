@@ -279,3 +279,4 @@ int obn_profile_read(obn_ctx* c, obn_profile* out, int reset) {
 #include "obn_batch.inl"
 #include "obn_es.inl"
 #include "obn_lattice.inl"
+#include "obn_static.inl"
