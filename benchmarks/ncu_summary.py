@@ -3,11 +3,12 @@
 profiles/: a per-launch table (kernel variant, grid, block, duration, DRAM bytes, L2 hit rate, warps active,
 L1 data-pipe utilisation, shared-atomic wavefronts) and the DRAM traffic figures bench.py's `roofline` reads.
 
-usage: python benchmarks/ncu_summary.py <raw.csv> <config key> <launches per step> <out prefix>
-       e.g.  ... gpurun_out/r2_ncu_c5_raw.csv c5 37 profiles/r2_ncu_c5
+usage: python benchmarks/ncu_summary.py <raw.csv> <config key> <pc() calls captured> <out prefix>
+       e.g.  ... gpurun_out/r2_ncu_c5_raw.csv c5 2 profiles/r2_ncu_c5
 
-The capture holds warm-up launches first; the LAST <launches per step> counting-kernel launches are one
-complete pc() call and are the ones summarised.  Writes <out prefix>_launches.csv and merges
+The capture holds <pc() calls captured> identical pc() calls (run_configs.py reps=1: a warm-up call and one more);
+the launches of the LAST one -- count_kernel and, for tables in global memory, ci_epilogue_kernel -- are one
+complete step and are the ones summarised.  Writes <out prefix>_launches.csv and merges
 {"<key>": {"dram_bytes_per_step", "dram_bytes_per_launch", ...}} into profiles/r2_traffic.json.
 """
 import csv
@@ -32,11 +33,13 @@ SCALE = {"ns": 1e-9, "us": 1e-6, "usecond": 1e-6, "ms": 1e-3, "msecond": 1e-3, "
 
 
 def main():
-    raw, key, per_step, prefix = sys.argv[1], sys.argv[2], int(sys.argv[3]), sys.argv[4]
+    raw, key, n_calls, prefix = sys.argv[1], sys.argv[2], int(sys.argv[3]), sys.argv[4]
     rows = list(csv.reader(open(raw)))
     hdr, units, data = rows[0], rows[1], rows[2:]
     col = {h: i for i, h in enumerate(hdr)}
-    data = [r for r in data if "count_kernel" in r[col["Kernel Name"]]][-per_step:]
+    data = [r for r in data if "count_kernel" in r[col["Kernel Name"]] or "ci_epilogue_kernel" in r[col["Kernel Name"]]]
+    assert len(data) % n_calls == 0, (len(data), n_calls)
+    data = data[-(len(data) // n_calls):]
 
     def val(r, name):
         if name not in col or r[col[name]] in ("", "n/a"):
@@ -47,7 +50,7 @@ def main():
     out = []
     for r in data:
         m = re.search(r"count_kernel<(.*?)>", r[col["Kernel Name"]])
-        line = {"variant_KW_TIER_SCALE4_REP": m.group(1).replace(" ", "") if m else "?", "grid": r[col["Grid Size"]],
+        line = {"variant_KW_TIER_SCALE4_REP": m.group(1).replace(" ", "") if m else "ci_epilogue", "grid": r[col["Grid Size"]],
                 "block": r[col["Block Size"]]}
         for name, short in COLS:
             line[short] = val(r, name)

@@ -201,13 +201,20 @@ OBN_API int obn_pc_round(obn_ctx* ctx, const obn_dataset* ds,
                          size_t n_slots, int kind, double level, int shard, int32_t* first_out);
 
 /* obn_ci_tests / obn_pc_round in two halves, so that the caller's host thread can prepare its next
- * batch while the device works on this one (the PC driver enumerates round r+1 during round r).
- * submit validates, packs, uploads and enqueues everything and returns; the input arrays may be
- * reused as soon as it has returned.  collect waits for the results and writes them (any pointer
- * may be NULL; p_out only if want_p was set).  At most one batch is in flight per ctx: until it is
- * collected every other batch call on the ctx returns OBN_ERR_INVALID.  collect without a
+ * batch while the device works on this one.  submit validates, packs, uploads and enqueues everything
+ * and returns; the input arrays may be reused as soon as it has returned.  collect waits for the OLDEST
+ * submitted batch and writes its results (any pointer may be NULL; p_out only if want_p was set).
+ * Up to TWO batches may be in flight per ctx (they run in submission order); a third submit, and any
+ * other batch call on the ctx while one is in flight, returns OBN_ERR_INVALID.  collect without a
  * submitted batch (or after submitting zero tuples) is a no-op that leaves the output arrays
- * untouched: a caller of obn_pc_round_collect pre-fills first_out with INT32_MAX. */
+ * untouched: a caller of obn_pc_round_collect pre-fills first_out with INT32_MAX.
+ * Chained PC rounds (chain != 0): the batch continues the PC round submitted just before it -- the same
+ * n_slots edges in the same numbering, that round still in flight or the last one collected.  Tests of
+ * edges the previous round decided (first != none) are skipped on the device: not counted, not
+ * evaluated, never reported -- what the serial reference does by stopping at an edge's first
+ * independent candidate (pc.cpp:40-42).  The caller can therefore enqueue round r+1 of a depth before
+ * it has seen round r's result, and the device never idles between the two.  The profile counters
+ * account a chained round net of what was skipped. */
 OBN_API int obn_ci_tests_submit(obn_ctx* ctx, const obn_dataset* ds,
                                 const uint32_t* var_ids, const uint64_t* offsets,
                                 size_t n_tuples, const uint32_t* x, const uint32_t* y,
@@ -216,7 +223,7 @@ OBN_API int obn_ci_tests_collect(obn_ctx* ctx, double* stat_out, uint64_t* dof_o
 OBN_API int obn_pc_round_submit(obn_ctx* ctx, const obn_dataset* ds,
                                 const uint32_t* var_ids, const uint64_t* offsets, size_t n_tests,
                                 const uint32_t* x, const uint32_t* y, const uint32_t* slot_of_test,
-                                size_t n_slots, int kind, double level, int shard);
+                                size_t n_slots, int kind, double level, int shard, int chain);
 OBN_API int obn_pc_round_collect(obn_ctx* ctx, int32_t* first_out);
 
 /* Diagnostics (host only, needs no device): the table sharing obn_ci_tests / obn_pc_round use.

@@ -85,7 +85,7 @@ def load():
     L.obn_pc_round.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, u32p, C.c_size_t, C.c_int, C.c_double,
                                C.c_int, i32p]
     L.obn_pc_round_submit.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, u32p, C.c_size_t, C.c_int,
-                                      C.c_double, C.c_int]
+                                      C.c_double, C.c_int, C.c_int]
     L.obn_pc_round_collect.argtypes = [vp, i32p]
     L.obn_ci_group_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, u32p, u64p, u32p, u32p,
                                     C.POINTER(C.c_size_t)]
@@ -284,12 +284,24 @@ class Dataset:
         if split:
             _check(load().obn_pc_round_submit(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), n,
                                               _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), _ptr(slot, C.c_uint32),
-                                              int(n_slots), int(kind), float(level), int(shard)))
+                                              int(n_slots), int(kind), float(level), int(shard), 0))
             _check(load().obn_pc_round_collect(self.ctx._h, _ptr(first, C.c_int32)))
         else:
             _check(load().obn_pc_round(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), n,
                                        _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), _ptr(slot, C.c_uint32), int(n_slots),
                                        int(kind), float(level), int(shard), _ptr(first, C.c_int32)))
+        return first[:n_slots]
+
+    def pc_round_submit(self, flat, offs, x, y, slot_of_test, n_slots, kind, level, shard=False, chain=False):
+        """obn_pc_round_submit alone (up to two rounds in flight; chain: skip the edges the previous round decided)."""
+        slot = np.ascontiguousarray(np.asarray(slot_of_test, dtype=np.uint32))
+        _check(load().obn_pc_round_submit(self.ctx._h, self._h, _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64), len(offs) - 1,
+                                          _ptr(x, C.c_uint32), _ptr(y, C.c_uint32), _ptr(slot, C.c_uint32),
+                                          int(n_slots), int(kind), float(level), int(shard), int(chain)))
+
+    def pc_round_collect(self, n_slots):
+        first = np.full(max(1, n_slots), 2**31 - 1, dtype=np.int32)
+        _check(load().obn_pc_round_collect(self.ctx._h, _ptr(first, C.c_int32)))
         return first[:n_slots]
 
     def ci_tests_submit_collect(self, flat, offs, x, y, kind, between=None):

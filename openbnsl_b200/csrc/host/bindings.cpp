@@ -3,6 +3,7 @@
 // submodules base / score / citest / structure_learning, same class and
 // function names, argument names, defaults and exception classes.  The data
 // path of every function runs on the GPU through the C ABI.
+#include <deque>
 #include <pybind11/functional.h>
 #include <pybind11/numpy.h>
 #include <pybind11/pybind11.h>
@@ -65,19 +66,46 @@ struct PyEvaluator : Evaluator {
     if ((size_t)r.size() != end - begin) throw std::runtime_error("evaluator returned a wrong-sized array");
     std::memcpy(p, r.data(), (end - begin) * sizeof(double));
   }
-  // "asynchronous" half-calls for the test seam: the answer is computed at submit and handed out
-  // at collect, so the driver's overlap logic runs on machines without a GPU; a Python evaluator
-  // with a `submitted` attribute counts the calls
-  std::vector<double> pending_;
-  bool ci_submit(const TupleBatch& b, int kind) override {
-    pending_.assign(b.size(), 0.0);
-    ci_pvalues(b, 0, b.size(), kind, pending_.data());
+  // "asynchronous" rounds for the test seam: the answer is computed at submit and handed out at collect (FIFO of
+  // two, like the library), so the driver's pipelining runs on machines without a GPU.  `chain` is honoured the
+  // way the device does it: tests of edges the previously submitted round decided are not evaluated.  A Python
+  // evaluator with a `submitted` attribute counts the rounds, one with a `skipped` attribute the tests left out.
+  std::deque<std::vector<int32_t>> rounds_;
+  std::vector<int32_t> last_first_;
+  bool pc_round_submit(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind,
+                       double level, bool shard, bool chain) override {
+    if (shard) return false;                    // the seam has no device-side communicator
+    if (rounds_.size() == 2) throw std::runtime_error("three rounds in flight");
+    if (chain && last_first_.size() != n_slots) throw std::runtime_error("chain: no previous round over the same edge slots");
+    TupleBatch sub;
+    sub.clear();
+    std::vector<uint32_t> ids;
+    for (size_t t = 0; t < b.size(); ++t) {
+      if (chain && last_first_[slot_of_test[t]] != INT32_MAX) continue;
+      sub.var_ids.insert(sub.var_ids.end(), b.var_ids.begin() + b.offsets[t], b.var_ids.begin() + b.offsets[t + 1]);
+      sub.offsets.push_back(sub.var_ids.size());
+      sub.x.push_back(b.x[t]);
+      sub.y.push_back(b.y[t]);
+      ids.push_back((uint32_t)t);
+    }
+    std::vector<double> p(sub.size());
+    ci_pvalues(sub, 0, sub.size(), kind, p.data());
+    std::vector<int32_t> first(n_slots, INT32_MAX);
+    for (size_t i = 0; i < ids.size(); ++i)
+      if (p[i] >= level) {                      // citest.h:147
+        int32_t& f = first[slot_of_test[ids[i]]];
+        if ((int32_t)ids[i] < f) f = (int32_t)ids[i];
+      }
+    last_first_ = first;
+    rounds_.push_back(std::move(first));
     if (py::hasattr(obj, "submitted")) obj.attr("submitted") = obj.attr("submitted").cast<size_t>() + 1;
+    if (py::hasattr(obj, "skipped")) obj.attr("skipped") = obj.attr("skipped").cast<size_t>() + (b.size() - ids.size());
     return true;
   }
-  void ci_collect(double* p) override {
-    if (!pending_.empty()) std::memcpy(p, pending_.data(), pending_.size() * sizeof(double));
-    pending_.clear();
+  void pc_round_collect(std::vector<int32_t>& first) override {
+    if (rounds_.empty()) throw std::runtime_error("collect without a round in flight");
+    first = std::move(rounds_.front());
+    rounds_.pop_front();
   }
   void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact, double* out) override {
     if (end <= begin) return;

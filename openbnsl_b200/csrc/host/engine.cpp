@@ -44,15 +44,6 @@ void GpuEvaluator::ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int
                      b.x.data() + begin, b.y.data() + begin, kind, nullptr, nullptr, p));
 }
 
-bool GpuEvaluator::ci_submit(const TupleBatch& b, int kind) {
-  check(obn_ci_tests_submit(Engine::instance().ctx(), ds_, b.var_ids.data(), b.offsets.data(), b.size(),
-                            b.x.data(), b.y.data(), kind, 1));
-  return true;
-}
-void GpuEvaluator::ci_collect(double* p) {
-  check(obn_ci_tests_collect(Engine::instance().ctx(), nullptr, nullptr, p));
-}
-
 bool GpuEvaluator::pc_round(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind,
                             double level, bool shard, std::vector<int32_t>& first) {
   first.resize(n_slots);
@@ -61,14 +52,19 @@ bool GpuEvaluator::pc_round(const TupleBatch& b, const std::vector<uint32_t>& sl
   return true;
 }
 bool GpuEvaluator::pc_round_submit(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind,
-                                   double level, bool shard) {
+                                   double level, bool shard, bool chain) {
   check(obn_pc_round_submit(Engine::instance().ctx(), ds_, b.var_ids.data(), b.offsets.data(), b.size(), b.x.data(),
-                            b.y.data(), slot_of_test.data(), n_slots, kind, level, shard ? 1 : 0));
-  pending_slots_ = n_slots;
+                            b.y.data(), slot_of_test.data(), n_slots, kind, level, shard ? 1 : 0, chain ? 1 : 0));
+  pending_slots_[(pending_head_ + pending_count_) % 2] = n_slots;
+  ++pending_count_;
   return true;
 }
 void GpuEvaluator::pc_round_collect(std::vector<int32_t>& first) {
-  first.assign(pending_slots_, INT32_MAX);
+  first.assign(pending_count_ ? pending_slots_[pending_head_] : 0, INT32_MAX);
+  if (pending_count_) {
+    pending_head_ = (pending_head_ + 1) % 2;
+    --pending_count_;
+  }
   check(obn_pc_round_collect(Engine::instance().ctx(), first.data()));
 }
 

@@ -74,17 +74,17 @@ struct Evaluator {
   virtual ~Evaluator() = default;
   // p-values of tuples [begin, end) of the batch -> p[0 .. end-begin)
   virtual void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) = 0;
-  // the same question in two halves (whole batch): submit returns while the answer is being
-  // computed, collect waits for it.  false = not supported, use ci_pvalues.
-  virtual bool ci_submit(const TupleBatch&, int /*kind*/) { return false; }
-  virtual void ci_collect(double* /*p*/) {}
   // One PC round answered as a whole (obn_pc_round): first[s] = the first test of edge slot s whose
   // p >= level, INT32_MAX if none.  shard: split the round over the ranks of the library's own
   // communicator (collective).  false = not supported, the driver decides from ci_pvalues.
   virtual bool pc_round(const TupleBatch&, const std::vector<uint32_t>& /*slot_of_test*/, size_t /*n_slots*/,
                         int /*kind*/, double /*level*/, bool /*shard*/, std::vector<int32_t>& /*first*/) { return false; }
+  // The same round in two halves (obn_pc_round_submit / _collect): submit returns while the answer is being
+  // computed, collect waits for the OLDEST submitted round; two rounds may be in flight.  chain: the tests of
+  // edges the round submitted before this one decided are skipped by the evaluator (same slot numbering).
+  // false = not supported.
   virtual bool pc_round_submit(const TupleBatch&, const std::vector<uint32_t>& /*slot_of_test*/, size_t /*n_slots*/,
-                               int /*kind*/, double /*level*/, bool /*shard*/) { return false; }
+                               int /*kind*/, double /*level*/, bool /*shard*/, bool /*chain*/) { return false; }
   virtual void pc_round_collect(std::vector<int32_t>& /*first*/) {}
   // scores of every child of tuples [begin, end) -> out[offsets[t]-offsets[begin] + i]
   virtual void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
@@ -97,12 +97,10 @@ class GpuEvaluator : public Evaluator {
  public:
   explicit GpuEvaluator(obn_dataset* ds) : ds_(ds) {}
   void ci_pvalues(const TupleBatch& b, size_t begin, size_t end, int kind, double* p) override;
-  bool ci_submit(const TupleBatch& b, int kind) override;
-  void ci_collect(double* p) override;
   bool pc_round(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind, double level,
                 bool shard, std::vector<int32_t>& first) override;
   bool pc_round_submit(const TupleBatch& b, const std::vector<uint32_t>& slot_of_test, size_t n_slots, int kind,
-                       double level, bool shard) override;
+                       double level, bool shard, bool chain) override;
   void pc_round_collect(std::vector<int32_t>& first) override;
   void subset_scores(const TupleBatch& b, size_t begin, size_t end, double ess, int exact_order,
                      double* out) override;
@@ -111,7 +109,8 @@ class GpuEvaluator : public Evaluator {
  private:
   obn_dataset* ds_;
   std::vector<uint64_t> tmp_off_;
-  size_t pending_slots_ = 0;
+  size_t pending_slots_[2] = {0, 0};   // FIFO of the rounds in flight
+  int pending_head_ = 0, pending_count_ = 0;
 };
 
 // Collectives between the per-GPU processes.  Default = single rank.

@@ -146,12 +146,12 @@ void append_test(TupleBatch& b, uint32_t u, uint32_t v, const std::vector<uint32
   b.y.push_back(v);
 }
 
-// The same decision in two halves (Evaluator::ci_submit / ci_collect): submit returns false when
-// the evaluator cannot work asynchronously, and the driver falls back to `decide`.
+// The same decision in two halves (Evaluator::pc_round_submit / pc_round_collect): submit enqueues a round and
+// returns, collect waits for the OLDEST round in flight.  Two rounds may be in flight; chain = the evaluator
+// skips the tests of edges the round submitted before this one decided.
 struct AsyncDecide {
-  std::function<bool(const TupleBatch&, const std::vector<uint32_t>& pair_of_test, size_t n_slots)> submit;
-  std::function<void(const TupleBatch&, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
-                     std::vector<int32_t>& first)> collect;
+  std::function<void(const TupleBatch&, const std::vector<uint32_t>& pair_of_test, size_t n_slots, bool chain)> submit;
+  std::function<void(size_t n_slots, std::vector<int32_t>& first)> collect;
 };
 
 PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, const DecideFn& decide,
@@ -180,35 +180,41 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
   // (a C2 run is 0.8 ms in all; growing these vectors from empty was a measurable part of it)
   struct Scratch {
     std::vector<FastCursor> cursors;
-    std::vector<uint32_t> idx_arena, pair_of_test, pair_of_spec;
+    std::vector<uint32_t> idx_arena, pair_of_test;
     std::vector<std::vector<uint32_t>> adj;
-    TupleBatch batch, spec;
+    TupleBatch batch, ring[3];
+    std::vector<uint32_t> ring_pairs[3];
   };
   static thread_local Scratch W;
   std::vector<FastCursor>& cursors = W.cursors;
   std::vector<uint32_t>& idx_arena = W.idx_arena;
   std::vector<std::vector<uint32_t>>& adj = W.adj;
   adj.resize(n);
-  TupleBatch& batch = W.batch;                // spec: the next round, built while this one is evaluated
-  TupleBatch& spec = W.spec;
+  TupleBatch& batch = W.batch;
   std::vector<uint32_t>& pair_of_test = W.pair_of_test;
-  std::vector<uint32_t>& pair_of_spec = W.pair_of_spec;
   batch.clear();
-  spec.clear();
   std::vector<uint32_t> z, tmp;
   std::vector<std::vector<uint32_t>> z_of_test;
   std::vector<int32_t> first;
-  auto note_batch = [&](size_t k) {           // accounts `batch`
+  // accounts a round; skip(t): test t was left out by the evaluator (chained rounds)
+  auto note_batch = [&](size_t k, const TupleBatch& b, const std::function<bool(size_t)>* skip) {
     if (!stats) return;
-    stats->tests_per_depth[k] += batch.size();
+    size_t asked = b.size();
+    if (skip) {
+      asked = 0;
+      for (size_t t = 0; t < b.size(); ++t) asked += !(*skip)(t);
+    }
+    stats->tests_per_depth[k] += asked;
     stats->batches_per_depth[k] += 1;
     if (!stats->record) return;
     TupleBatch& r = stats->recorded;
-    const uint64_t base = r.var_ids.size();
-    r.var_ids.insert(r.var_ids.end(), batch.var_ids.begin(), batch.var_ids.end());
-    for (size_t q = 1; q < batch.offsets.size(); ++q) r.offsets.push_back(base + batch.offsets[q]);
-    r.x.insert(r.x.end(), batch.x.begin(), batch.x.end());
-    r.y.insert(r.y.end(), batch.y.begin(), batch.y.end());
+    for (size_t t = 0; t < b.size(); ++t) {
+      if (skip && (*skip)(t)) continue;
+      r.var_ids.insert(r.var_ids.end(), b.var_ids.begin() + b.offsets[t], b.var_ids.begin() + b.offsets[t + 1]);
+      r.offsets.push_back(r.var_ids.size());
+      r.x.push_back(b.x[t]);
+      r.y.push_back(b.y[t]);
+    }
   };
 
   for (size_t k = 0; k <= max_cond_vars; ++k) {              // pc.cpp:22 (no early exit)
@@ -313,73 +319,90 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         }
       };
       // every edge is resolved at its FIRST passing candidate (pc.cpp:40-42)
-      auto resolve_round = [&]() {
+      auto resolve_round = [&](const TupleBatch& b) {
         for (size_t pi = 0; pi < cursors.size(); ++pi) {
           if (first[pi] == INT_MAX) continue;
           FastCursor& c = cursors[pi];
+          if (c.removed) continue;
           c.removed = true;
           g.remove_undirected_edge(c.x, c.y);
           std::vector<uint32_t>& sz = sep[(size_t)c.x * n + c.y];
           sz.clear();
           const size_t t = (size_t)first[pi];
-          for (uint64_t i = batch.offsets[t]; i < batch.offsets[t + 1]; ++i)
-            if (batch.var_ids[i] != c.x && batch.var_ids[i] != c.y) sz.push_back(batch.var_ids[i]);
+          for (uint64_t i = b.offsets[t]; i < b.offsets[t + 1]; ++i)
+            if (b.var_ids[i] != c.x && b.var_ids[i] != c.y) sz.push_back(b.var_ids[i]);
           sep[(size_t)c.y * n + c.x] = sz;
         }
       };
       size_t quota = 1;
       size_t live = count_live();
-      if (live) {
-        quota = std::max<size_t>(quota, target_batch / live);
-        build_round(batch, pair_of_test, quota);
-      }
-      while (live && batch.size()) {
-        lap(&PcStats::enumerate_ms);
-        // Overlap (async evaluators): the candidates of a depth depend only on the snapshot, so
-        // while the device works on this round the next one is enumerated as if no edge were
-        // removed, and the tests of the edges this round does remove are dropped afterwards.
-        // Batch boundaries do not change what an edge resolves at: its first passing candidate.
-        const bool in_flight = async && async->submit(batch, pair_of_test, cursors.size());
-        quota *= 2;
-        bool have_spec = false;
-        if (in_flight) {
-          lap(&PcStats::evaluate_ms);
-          const size_t l2 = count_live();
-          if (l2) {
-            quota = std::max<size_t>(quota, target_batch / l2);
-            build_round(spec, pair_of_spec, quota);
-            have_spec = true;
-          }
-          lap(&PcStats::enumerate_ms);
-          async->collect(batch, pair_of_test, cursors.size(), first);
-        } else {
-          decide(batch, pair_of_test, cursors.size(), first);
+      if (!async) {
+        if (live) {
+          quota = std::max<size_t>(quota, target_batch / live);
+          build_round(batch, pair_of_test, quota);
         }
-        lap(&PcStats::evaluate_ms);
-        note_batch(k);
-        resolve_round();
-        if (in_flight) {
-          batch.clear();
-          pair_of_test.clear();
-          if (have_spec)
-            for (size_t t = 0; t < spec.size(); ++t) {
-              if (cursors[pair_of_spec[t]].removed) continue;
-              batch.var_ids.insert(batch.var_ids.end(), spec.var_ids.begin() + spec.offsets[t],
-                                   spec.var_ids.begin() + spec.offsets[t + 1]);
-              batch.offsets.push_back(batch.var_ids.size());
-              batch.x.push_back(spec.x[t]);
-              batch.y.push_back(spec.y[t]);
-              pair_of_test.push_back(pair_of_spec[t]);
-            }
-          live = batch.size();      // an edge that is still undecided kept its tests
-        } else {
+        while (live && batch.size()) {
+          lap(&PcStats::enumerate_ms);
+          decide(batch, pair_of_test, cursors.size(), first);
+          quota *= 2;
+          lap(&PcStats::evaluate_ms);
+          note_batch(k, batch, nullptr);
+          resolve_round(batch);
           live = count_live();
           if (live) {
             quota = std::max<size_t>(quota, target_batch / live);
             build_round(batch, pair_of_test, quota);
           }
+          lap(&PcStats::resolve_ms);
         }
-        lap(&PcStats::resolve_ms);
+      } else if (live) {
+        // Pipelined rounds (asynchronous evaluators).  The candidates of a depth depend only on the snapshot,
+        // so the next round can be enumerated -- and handed to the evaluator -- before this one has answered:
+        // it is built as if this round removed no edge, and the evaluator itself drops the tests of the edges
+        // this round does remove (chain), which is what the serial reference does by stopping at an edge's first
+        // independent candidate (pc.cpp:40-42).  The device always has the next round queued behind the one it
+        // is working on; the host enumerates, packs and resolves in its shadow.  Batch boundaries do not change
+        // what an edge resolves at.  Ring of three rounds: being resolved / in flight behind it / being built.
+        quota = std::max<size_t>(quota, target_batch / live);
+        size_t head = 0, n_flight = 0;
+        build_round(W.ring[0], W.ring_pairs[0], quota);
+        lap(&PcStats::enumerate_ms);
+        bool more = W.ring[0].size() != 0;
+        if (more) {
+          async->submit(W.ring[0], W.ring_pairs[0], cursors.size(), false);
+          n_flight = 1;
+        }
+        lap(&PcStats::evaluate_ms);
+        while (n_flight) {
+          if (more && n_flight < 2) {
+            more = false;
+            quota *= 2;
+            const size_t l2 = count_live();
+            if (l2) {
+              quota = std::max<size_t>(quota, target_batch / l2);
+              const size_t nxt = (head + n_flight) % 3;
+              build_round(W.ring[nxt], W.ring_pairs[nxt], quota);
+              lap(&PcStats::enumerate_ms);
+              if (W.ring[nxt].size()) {
+                async->submit(W.ring[nxt], W.ring_pairs[nxt], cursors.size(), true);
+                ++n_flight;
+                more = true;
+              }
+              lap(&PcStats::evaluate_ms);
+            }
+          }
+          const TupleBatch& b = W.ring[head];
+          const std::vector<uint32_t>& pairs = W.ring_pairs[head];
+          async->collect(cursors.size(), first);
+          lap(&PcStats::evaluate_ms);
+          // an edge that is marked removed by now was decided by the round before this one: its tests were skipped
+          const std::function<bool(size_t)> skipped = [&](size_t t) { return cursors[pairs[t]].removed; };
+          note_batch(k, b, &skipped);
+          resolve_round(b);
+          head = (head + 1) % 3;
+          --n_flight;
+          lap(&PcStats::resolve_ms);
+        }
       }
     } else {
       for (size_t x = 0; x < n; ++x)
@@ -404,7 +427,7 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
             p.advance(k);
           }
           decide(batch, pair_of_test, 1, first);
-          note_batch(k);
+          note_batch(k, batch, nullptr);
           if (first[0] != INT_MAX) {
             g.remove_undirected_edge(x, y);
             sep[x * n + y] = z_of_test[(size_t)first[0]];
@@ -464,34 +487,17 @@ PDAG pc_skeleton_and_colliders(size_t n_vars, Evaluator& ev, const Comm& comm, c
       }
     comm.allreduce_min_i32(first.data(), first.size());
   };
-  // The same decision in two halves, so that round r+1 is enumerated while the device runs round r.
-  // A sharded round works too when the communicator is the library's (the collective is enqueued
-  // behind the kernels at submit); a host-side communicator would need its own split: not overlapped.
-  bool round_in_flight = false;
+  // The same decision in two halves, so that the device is kept one round ahead of the host.  A sharded
+  // round works too when the communicator is the library's (the collective is enqueued behind the kernels at
+  // submit); a host-side communicator would need its own split: not pipelined.
   AsyncDecide async;
-  async.submit = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots) {
-    const bool shard = sharded(b);
-    if (shard && !comm.native) return false;
-    round_in_flight = ev.pc_round_submit(b, pair_of_test, n_slots, opt.kind, opt.level, shard);
-    if (round_in_flight) return true;
-    return !shard && ev.ci_submit(b, opt.kind);
+  async.submit = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots, bool chain) {
+    if (!ev.pc_round_submit(b, pair_of_test, n_slots, opt.kind, opt.level, sharded(b), chain))
+      throw std::runtime_error("pc: the evaluator does not take asynchronous rounds (overlap=False runs them one by one)");
   };
-  async.collect = [&](const TupleBatch& b, const std::vector<uint32_t>& pair_of_test, size_t n_slots,
-                      std::vector<int32_t>& first) {
-    if (round_in_flight) {
-      round_in_flight = false;
-      ev.pc_round_collect(first);
-      first.resize(n_slots, INT_MAX);
-      return;
-    }
-    first.assign(n_slots, INT_MAX);
-    p.resize(b.size());
-    ev.ci_collect(p.data());
-    for (size_t t = 0; t < b.size(); ++t)
-      if (p[t] >= opt.level) {                                // citest.h:147
-        int32_t& f = first[pair_of_test[t]];
-        if ((int32_t)t < f) f = (int32_t)t;
-      }
+  async.collect = [&](size_t n_slots, std::vector<int32_t>& first) {
+    ev.pc_round_collect(first);
+    first.resize(n_slots, INT_MAX);
   };
   const bool overlap = opt.overlap && opt.stable && (comm.world == 1 || comm.native);
   return run_pc(n_vars, opt.max_cond_vars, opt.stable, opt.target_batch, decide, stats, overlap ? &async : nullptr);

@@ -37,8 +37,9 @@ struct PcOptions {
   int kind = OBN_CI_G2;
   double level = 0.05;
   size_t target_batch = 8192;     // tests per round the driver aims for
-  // stable mode, one rank: enumerate round r+1 while the evaluator works on round r
-  // (Evaluator::ci_submit / ci_collect); the learned graph does not depend on it
+  // stable mode: keep the evaluator one round ahead of the host -- round r+1 is enumerated and submitted
+  // (chained: the evaluator drops the tests of edges round r decides) before round r is collected
+  // (Evaluator::pc_round_submit / pc_round_collect); the learned graph does not depend on it
   bool overlap = false;
   // multi-GPU: a round is sharded over ranks (+ one all-reduce) only when it holds at least this
   // many variable slots (sum of tuple widths); smaller rounds are evaluated redundantly by every

@@ -40,6 +40,8 @@ struct BatchSpec {
   // CI modes: return once everything is enqueued (obn_ci_tests_submit / obn_pc_round_submit);
   // the matching collect waits and hands the results out
   bool defer = false;
+  // PC rounds: skip the tests of edges the round submitted before this one decided (BatchArgs::prev_first)
+  bool chain = false;
 };
 
 // Table-size classes.  One launch covers the tuples of one class, so that the
@@ -82,34 +84,35 @@ static const size_t kScratchMaxBytes = (size_t)8 << 30;
 static const size_t kLutMaxBytes = (size_t)2 << 30;
 
 // Results of a finished batch: staging buffer -> the caller's arrays, profile counters.
-static void finish_batch(obn_ctx* c, const obn_ctx::Pending& P, double* stat, uint64_t* dof, double* p, int32_t* first) {
-  const unsigned char* hout = c->h_out.as<unsigned char>();
+static void finish_batch(obn_ctx* c, const obn_ctx::Staging& G, double* stat, uint64_t* dof, double* p, int32_t* first) {
+  const obn_ctx::Pending& P = G.pending;
+  const unsigned char* hout = G.h_out.as<unsigned char>();
+  unsigned long long skipped[4] = {0, 0, 0, 0};
   if (P.n_slots) {
     if (first) {
       const int32_t* f = reinterpret_cast<const int32_t*>(hout);
       for (size_t i = 0; i < P.n_slots; ++i) first[i] = f[i] >= kFirstNone ? INT32_MAX : f[i];
     }
+    // a chained round: what the device left out (tests of edges the previous round decided) was not evaluated
+    if (P.chained) memcpy(skipped, hout + ((P.n_slots * 4 + 7) & ~(size_t)7), sizeof(skipped));
   } else {
     const size_t n = P.n_results;
     if (stat) memcpy(stat, hout, n * 8);
     if (dof) memcpy(dof, hout + n * 8, n * 8);
     if (p) memcpy(p, hout + n * 16, n * 8);
   }
-  if (c->profile_on) {
-    for (size_t i = P.ev_first; i < c->ev_used; ++i) {
-      float ms = 0;
-      cudaEventElapsedTime(&ms, c->ev_pool[i].first, c->ev_pool[i].second);
-      c->prof.count_kernel_ms += ms;
-    }
-    c->ev_used = P.ev_first;
+  if (P.timed) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, G.e0, G.e1);
+    c->prof.count_kernel_ms += ms;
   }
   c->prof.h2d_bytes += (double)P.in_bytes;
   c->prof.d2h_bytes += (double)P.out_bytes;
-  c->prof.algorithmic_bytes += P.alg_bytes;
-  c->prof.scanned_bytes += P.scanned_bytes;
-  c->prof.increments += P.increments;
-  c->prof.tuples += P.n_out;
-  c->prof.tables += P.tables;
+  c->prof.algorithmic_bytes += P.alg_bytes - (double)skipped[1] * P.n_rows;
+  c->prof.scanned_bytes += P.scanned_bytes - (double)skipped[3] * P.n_rows;
+  c->prof.increments += P.increments - (double)skipped[2] * P.n_rows;
+  c->prof.tuples += P.n_out - (size_t)skipped[0];
+  c->prof.tables += P.tables - (size_t)skipped[2];
 }
 
 static int run_batch(BatchSpec& S) {
@@ -117,7 +120,11 @@ static int run_batch(BatchSpec& S) {
   const obn_dataset* ds = S.ds;
   if (!c || !ds) return fail(OBN_ERR_INVALID, "ctx or dataset is NULL");
   if (ds->ctx != c) return fail(OBN_ERR_INVALID, "dataset belongs to another ctx");
-  if (c->pending.active) return fail(OBN_ERR_INVALID, "a submitted batch is waiting to be collected");
+  if (S.defer ? c->q_count == obn_ctx::kStagings : c->q_count != 0)
+    return fail(OBN_ERR_INVALID, S.defer ? "two submitted batches are waiting to be collected"
+                                         : "a submitted batch is waiting to be collected");
+  const int g_idx = (c->q_head + c->q_count) % obn_ctx::kStagings;
+  obn_ctx::Staging& G = c->st[g_idx];
   const size_t n = S.n;
   const bool ci = (S.mode == MODE_CI);
   const bool pc_round = ci && S.n_slots != 0;
@@ -253,9 +260,9 @@ static int run_batch(BatchSpec& S) {
   const size_t o_moff = take(ci ? (n + 1) * 4 : 0), o_mem = take(n_members * 8);
   const size_t o_slot = take(pc_round ? n_out * 4 : 0);
   const size_t in_bytes = off;
-  if (int rc = c->h_in.reserve(std::max<size_t>(in_bytes, 16))) return rc;
-  if (int rc = c->d_in.reserve(std::max<size_t>(in_bytes, 16))) return rc;
-  unsigned char* hin = c->h_in.as<unsigned char>();
+  if (int rc = G.h_in.reserve(std::max<size_t>(in_bytes, 16))) return rc;
+  if (int rc = G.d_in.reserve(std::max<size_t>(in_bytes, 16))) return rc;
+  unsigned char* hin = G.h_in.as<unsigned char>();
   {
     uint32_t* desc = reinterpret_cast<uint32_t*>(hin + o_var);
     for (size_t i = 0; i < total_vars; ++i) desc[i] = S.var_ids[i] | ((ds->cards[S.var_ids[i]] - 1u) << 24);
@@ -297,7 +304,8 @@ static int run_batch(BatchSpec& S) {
 
   // ---- output buffer ----------------------------------------------------------
   size_t out_bytes = 0, counts_total = 0;
-  if (pc_round) out_bytes = S.n_slots * 4;
+  const size_t first_bytes = (S.n_slots * 4 + 7) & ~(size_t)7;
+  if (pc_round) out_bytes = first_bytes + 32;          // first[n_slots], then the four counters of a chained round
   else if (ci) out_bytes = n_out * 24;
   else if (S.mode == MODE_BDEU_ONE) out_bytes = n * 8;
   else if (S.mode == MODE_BDEU_ALL) out_bytes = S.scores_dev ? 0 : total_vars * 8;
@@ -306,7 +314,7 @@ static int run_batch(BatchSpec& S) {
     for (size_t t = 0; t < n; ++t) { coff[t] = counts_total; counts_total += cells[t]; }
     out_bytes = S.counts_dev ? 0 : counts_total * 4;
   }
-  if (int rc = c->d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
+  if (int rc = G.d_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
 
   // ---- plan launches: one per class (chunked only when the scratch would not fit)
   struct Launch { int g; size_t begin, end; int nthr, splits; uint32_t vps; size_t smem; size_t scratch_ints; size_t scratch_base; bool barrier_before; uint32_t rep_shift; uint32_t wstride; uint32_t row_splits; uint32_t epi_ctas; size_t partial_base; };
@@ -422,11 +430,20 @@ static int run_batch(BatchSpec& S) {
     if (int rc = c->d_partials.reserve(partial_doubles * 8)) return rc;
 
   const auto t_packed = std::chrono::steady_clock::now();
-  if (in_bytes) OBN_CUDA(cudaMemcpyAsync(c->d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
+  if (in_bytes) {
+    if (c->q_count) {
+      // another batch is running: copy beside it (this staging's buffers are free -- its last batch was collected)
+      OBN_CUDA(cudaMemcpyAsync(G.d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->up_stream));
+      OBN_CUDA(cudaEventRecord(G.uploaded, c->up_stream));
+      OBN_CUDA(cudaStreamWaitEvent(c->stream, G.uploaded, 0));
+    } else {
+      OBN_CUDA(cudaMemcpyAsync(G.d_in.p, hin, in_bytes, cudaMemcpyHostToDevice, c->stream));
+    }
+  }
 
   // ---- launch ------------------------------------------------------------------
-  unsigned char* din = c->d_in.as<unsigned char>();
-  unsigned char* dout = c->d_out.as<unsigned char>();
+  unsigned char* din = G.d_in.as<unsigned char>();
+  unsigned char* dout = G.d_out.as<unsigned char>();
   BatchArgs a{};
   a.data = ds->data; a.stride = ds->stride; a.n_rows = (uint32_t)ds->n_rows;
   a.data4 = c->tune.pack4 ? ds->data4 : nullptr; a.stride4 = ds->stride4;
@@ -444,7 +461,15 @@ static int run_batch(BatchSpec& S) {
       a.first = reinterpret_cast<int32_t*>(dout);
       a.slot_of_test = reinterpret_cast<const uint32_t*>(din + o_slot);
       a.level = S.level;
-      OBN_CUDA(cudaMemsetAsync(dout, 0x7f, out_bytes, c->stream));      // kFirstNone in every slot
+      OBN_CUDA(cudaMemsetAsync(dout, 0x7f, first_bytes, c->stream));      // kFirstNone in every slot
+      if (S.chain) {
+        // the round submitted before this one, still in flight or collected last: its first[] is in the other staging
+        if (c->last_round < 0 || c->last_round == g_idx || c->last_round_slots != S.n_slots)
+          return fail(OBN_ERR_INVALID, "chain: no previous PC round over the same %zu edge slots to continue", S.n_slots);
+        a.prev_first = c->st[c->last_round].d_out.as<int32_t>();
+        a.skipped = reinterpret_cast<unsigned long long*>(dout + first_bytes);
+        OBN_CUDA(cudaMemsetAsync(dout + first_bytes, 0, 32, c->stream));
+      }
     } else {
       a.stat = reinterpret_cast<double*>(dout);
       a.dof = reinterpret_cast<unsigned long long*>(dout + n_out * 8);
@@ -459,15 +484,8 @@ static int run_batch(BatchSpec& S) {
   // fork/join over the ctx's auxiliary streams: launch i of a segment goes to stream i % (1+kAuxStreams)
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (c->profile_on) {
-    if (c->ev_used == c->ev_pool.size()) {
-      cudaEvent_t x, y;
-      OBN_CUDA(cudaEventCreate(&x));
-      OBN_CUDA(cudaEventCreate(&y));
-      c->ev_pool.push_back({x, y});
-    }
-    e0 = c->ev_pool[c->ev_used].first;
-    e1 = c->ev_pool[c->ev_used].second;
-    ++c->ev_used;
+    e0 = G.e0;
+    e1 = G.e1;
     OBN_CUDA(cudaEventRecord(e0, c->stream));
   }
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> dbg_events;
@@ -552,30 +570,39 @@ static int run_batch(BatchSpec& S) {
   }
   if (int rc = join()) return rc;
   if (c->profile_on) OBN_CUDA(cudaEventRecord(e1, c->stream));
-  const size_t ev_first = c->ev_used - (c->profile_on ? 1 : 0);
 
   // ---- sharded PC round: merge the ranks' first-passing indices, still on the device -----------
   if (pc_round && merge_ranks)
     if (int rc = comm_allreduce_min_i32(c, reinterpret_cast<int32_t*>(dout), S.n_slots)) return rc;
 
   // ---- download ------------------------------------------------------------------
-  if (int rc = c->h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
-  if (out_bytes) OBN_CUDA(cudaMemcpyAsync(c->h_out.p, dout, out_bytes, cudaMemcpyDeviceToHost, c->stream));
-  obn_ctx::Pending P;
+  if (int rc = G.h_out.reserve(std::max<size_t>(out_bytes, 16))) return rc;
+  if (out_bytes) OBN_CUDA(cudaMemcpyAsync(G.h_out.p, dout, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+  // whatever this staging held of an earlier PC round is gone now
+  if (pc_round) {
+    c->last_round = g_idx;
+    c->last_round_slots = S.n_slots;
+  } else if (c->last_round == g_idx) {
+    c->last_round = -1;
+  }
+  obn_ctx::Pending& P = G.pending;
+  P = obn_ctx::Pending();
   P.n_out = ci ? tests_mine : n;
   P.n_results = n_out;
   P.n_slots = pc_round ? S.n_slots : 0;
   P.out_bytes = out_bytes;
   P.in_bytes = in_bytes;
-  P.ev_first = ev_first;
   P.alg_bytes = alg_bytes;
   P.scanned_bytes = scanned_bytes;
   P.increments = increments;
+  P.n_rows = (double)ds->n_rows;
   P.tables = n_mine;
   P.want_p = S.p != nullptr;
+  P.timed = c->profile_on;
+  P.chained = pc_round && S.chain;
   if (S.defer) {                    // CI modes only (obn_ci_tests_submit / obn_pc_round_submit)
-    P.active = true;
-    c->pending = P;
+    OBN_CUDA(cudaEventRecord(G.done, c->stream));
+    ++c->q_count;
     const auto now = std::chrono::steady_clock::now();
     c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
     c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(now - t_packed).count();
@@ -600,9 +627,9 @@ static int run_batch(BatchSpec& S) {
   const auto t_synced = std::chrono::steady_clock::now();
   c->prof.host_prep_ms += std::chrono::duration<double, std::milli>(t_packed - t_begin).count();
   c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(t_synced - t_packed).count();
-  const unsigned char* hout = c->h_out.as<unsigned char>();
+  const unsigned char* hout = G.h_out.as<unsigned char>();
   if (ci) {
-    finish_batch(c, P, S.stat, S.dof, S.p, S.first);
+    finish_batch(c, G, S.stat, S.dof, S.p, S.first);
     return OBN_OK;
   }
   if (S.mode == MODE_BDEU_ONE) {
@@ -617,7 +644,7 @@ static int run_batch(BatchSpec& S) {
       o += cells[t];
     }
   }
-  finish_batch(c, P, nullptr, nullptr, nullptr, nullptr);
+  finish_batch(c, G, nullptr, nullptr, nullptr, nullptr);
   return OBN_OK;
 }
 
@@ -660,7 +687,7 @@ int obn_bdeu_subset_scores(obn_ctx* c, const obn_dataset* ds, const uint32_t* va
 static int ci_tests_impl(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
                          size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, double* stat_out,
                          uint64_t* dof_out, double* p_out, bool defer, const uint32_t* slot_of_test, size_t n_slots,
-                         double level, int shard, int32_t* first_out) {
+                         double level, int shard, int32_t* first_out, bool chain = false) {
   if (kind != OBN_CI_CHI2 && kind != OBN_CI_G2) return fail(OBN_ERR_INVALID, "Unsupported CI test type");
   if (!c || !ds) return fail(OBN_ERR_INVALID, "ctx or dataset is NULL");
   if (ds->ctx != c) return fail(OBN_ERR_INVALID, "dataset belongs to another ctx");
@@ -692,6 +719,7 @@ static int ci_tests_impl(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_
   S.first = first_out;
   S.shard = shard != 0;
   S.defer = defer;
+  S.chain = chain && n_slots;
   return run_batch(S);
 }
 
@@ -713,8 +741,8 @@ int obn_pc_round(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, con
 
 // The same two calls split in halves, so that the caller's host thread can prepare its next batch
 // while the device runs this one: submit plans, packs, uploads and enqueues everything (the input
-// arrays may be reused as soon as it returns); collect waits and writes the results.  One batch
-// may be in flight per ctx; every other batch call fails until it is collected.
+// arrays may be reused as soon as it returns); collect waits for the OLDEST submitted batch and writes its
+// results.  Two batches may be in flight per ctx; every other batch call fails until both are collected.
 int obn_ci_tests_submit(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
                         size_t n_tuples, const uint32_t* x, const uint32_t* y, int kind, int want_p) {
   static double dummy;              // run_batch only asks whether p is wanted
@@ -724,24 +752,26 @@ int obn_ci_tests_submit(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_i
 
 int obn_pc_round_submit(obn_ctx* c, const obn_dataset* ds, const uint32_t* var_ids, const uint64_t* offsets,
                         size_t n_tests, const uint32_t* x, const uint32_t* y, const uint32_t* slot_of_test,
-                        size_t n_slots, int kind, double level, int shard) {
+                        size_t n_slots, int kind, double level, int shard, int chain) {
   if (!n_slots) return OBN_OK;
   return ci_tests_impl(c, ds, var_ids, offsets, n_tests, x, y, kind, nullptr, nullptr, nullptr, true, slot_of_test,
-                       n_slots, level, shard, nullptr);
+                       n_slots, level, shard, nullptr, chain != 0);
 }
 
 static int collect_impl(obn_ctx* c, double* stat_out, uint64_t* dof_out, double* p_out, int32_t* first_out, bool round) {
   if (!c) return fail(OBN_ERR_INVALID, "ctx is NULL");
-  obn_ctx::Pending& P = c->pending;
-  if (!P.active) return OBN_OK;     // nothing was submitted (an empty batch): nothing to hand out
+  if (!c->q_count) return OBN_OK;     // nothing was submitted (an empty batch): nothing to hand out
+  obn_ctx::Staging& G = c->st[c->q_head];           // the oldest batch in flight
+  const obn_ctx::Pending& P = G.pending;
   if (round != (P.n_slots != 0)) return fail(OBN_ERR_INVALID, "the batch in flight was submitted by the other submit call");
   if (p_out && !P.want_p) return fail(OBN_ERR_INVALID, "p-values were not requested at submit");
   OBN_CUDA(cudaSetDevice(c->device));
   const auto t0 = std::chrono::steady_clock::now();
-  P.active = false;
-  OBN_CUDA(cudaStreamSynchronize(c->stream));
+  c->q_head = (c->q_head + 1) % obn_ctx::kStagings;
+  --c->q_count;
+  OBN_CUDA(cudaEventSynchronize(G.done));
   c->prof.host_wait_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-  finish_batch(c, P, stat_out, dof_out, p_out, first_out);
+  finish_batch(c, G, stat_out, dof_out, p_out, first_out);
   return OBN_OK;
 }
 

@@ -106,6 +106,13 @@ int obn_ctx_create(int device, obn_ctx** out) {
   OBN_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   OBN_CUDA(cudaEventCreate(&c->ev0));
   OBN_CUDA(cudaEventCreate(&c->ev1));
+  for (obn_ctx::Staging& G : c->st) {
+    OBN_CUDA(cudaEventCreate(&G.e0));
+    OBN_CUDA(cudaEventCreate(&G.e1));
+    OBN_CUDA(cudaEventCreateWithFlags(&G.done, cudaEventDisableTiming));
+    OBN_CUDA(cudaEventCreateWithFlags(&G.uploaded, cudaEventDisableTiming));
+  }
+  OBN_CUDA(cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
   *out = c;
   return OBN_OK;
 }
@@ -115,16 +122,21 @@ void obn_ctx_destroy(obn_ctx* c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   obn_comm_destroy(c);
-  for (DevBuf* b : {&c->d_in, &c->d_out, &c->d_scratch, &c->d_tickets, &c->d_scalar, &c->d_partials}) b->release();
+  for (DevBuf* b : {&c->d_scratch, &c->d_tickets, &c->d_scalar, &c->d_partials}) b->release();
+  for (obn_ctx::Staging& G : c->st) {
+    G.d_in.release();
+    G.d_out.release();
+    G.h_in.release();
+    G.h_out.release();
+    if (G.e0) cudaEventDestroy(G.e0);
+    if (G.e1) cudaEventDestroy(G.e1);
+    if (G.done) cudaEventDestroy(G.done);
+    if (G.uploaded) cudaEventDestroy(G.uploaded);
+  }
+  if (c->up_stream) cudaStreamDestroy(c->up_stream);
   c->lut.release();
   c->es_pool.release();
   if (c->ds_cache) cudaFree(c->ds_cache);
-  c->h_in.release();
-  c->h_out.release();
-  for (auto& pr : c->ev_pool) {
-    cudaEventDestroy(pr.first);
-    cudaEventDestroy(pr.second);
-  }
   for (int j = 0; j < obn_ctx::kAuxStreams; ++j) {
     cudaStreamDestroy(c->aux[j]);
     cudaEventDestroy(c->ev_join[j]);

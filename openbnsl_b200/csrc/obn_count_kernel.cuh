@@ -47,6 +47,7 @@ struct CtaTuple {            // per-CTA tuple description in shared memory
   int packed;                // every column of the tuple has <= 16 states and the data set carries nibble-packed columns
   int child_pos;             // BDEU_ONE: position of the child in reference order
   unsigned int ticket;
+  uint32_t live;                       // CI: bit m = member m of the group is still asked (all ones unless a chained PC round)
 };
 
 template <int KW>
@@ -284,6 +285,20 @@ __device__ __forceinline__ void scan_rows_any(const CtaTuple& T, int k, unsigned
   }
 }
 
+// Chained PC rounds: which members of group t are still asked.  Called by all 32 lanes of warp 0; lane m looks at
+// member m (a group has at most kGroupMembers = 32 tests).  The previous round's first[] is final before this kernel
+// starts (stream order), so every CTA of the tuple, and the epilogue kernel, take the same decision.
+__device__ __forceinline__ uint32_t live_members(const BatchArgs& A, uint32_t t, uint32_t lane, uint32_t* n_mem_out) {
+  const uint32_t m_begin = __ldg(&A.mem_off[t]), n_mem = __ldg(&A.mem_off[t + 1]) - m_begin;
+  bool live = false;
+  if (lane < n_mem) {
+    const uint32_t id = __ldg(&A.members[m_begin + lane]).x;
+    live = __ldcg(&A.prev_first[__ldg(&A.slot_of_test[id])]) >= kFirstNone;
+  }
+  *n_mem_out = n_mem;
+  return __ballot_sync(0xffffffffu, live);
+}
+
 template <int KW, int TIER, bool SCALE4, int RSH = -1>
 __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 32 ? 1 : 3)) count_kernel(const BatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -315,6 +330,24 @@ __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 3
       T.card[tid] = c;
     }
     if (tid == 0) T.packed = packed;
+    if (A.prev_first) {                            // chained PC round: drop the tests of edges the previous round decided
+      uint32_t n_mem;
+      const uint32_t mask = live_members(A, t, tid, &n_mem);
+      if (tid == 0) {
+        T.live = mask;
+        const uint32_t n_dead = n_mem - (uint32_t)__popc(mask);
+        if (split == 0 && n_dead) {                // accounting: one CTA per tuple
+          atomicAdd(&A.skipped[0], (unsigned long long)n_dead);
+          atomicAdd(&A.skipped[1], (unsigned long long)n_dead * (unsigned)k);
+          if (!mask) {
+            atomicAdd(&A.skipped[2], 1ull);
+            atomicAdd(&A.skipped[3], (unsigned long long)k);
+          }
+        }
+      }
+    } else if (tid == 0) {
+      T.live = 0xffffffffu;
+    }
     const unsigned m_child = __ballot_sync(0xffffffffu, live && v == child);
     __syncwarp();
     if (tid == 0) {
@@ -364,6 +397,7 @@ __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 3
     wscratch = reinterpret_cast<int32_t*>(smem_raw);
   }
   __syncthreads();
+  if (A.mode == MODE_CI && T.live == 0u) return;     // nothing of this table is asked any more (nothing was touched yet)
 
   // ---- main loop over this split's 16-row vectors -----------------------------
   // a "vector" is what one 16-byte load of a column holds: 16 rows, or 32 of a nibble-packed column
@@ -454,7 +488,9 @@ __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 3
     __shared__ unsigned long long m_dof[kGroupMembers];
     __shared__ uint32_t m_id[kGroupMembers];
     const uint32_t m_begin = __ldg(&A.mem_off[t]), m_end = __ldg(&A.mem_off[t + 1]);
+    const uint32_t live = T.live;
     for (uint32_t m = m_begin; m < m_end; ++m) {
+      if (!((live >> (m - m_begin)) & 1u)) continue;
       const uint2 mem = __ldg(&A.members[m]);
       const uint32_t px = mem.y & 0xffu, py = (mem.y >> 8) & 0xffu;
       const CiGeom g(cells, T.card[px], T.card[py], T.weight[px], T.weight[py]);
@@ -468,7 +504,7 @@ __global__ void __launch_bounds__((KW == 32 ? 512 : 256), (KW == 8 ? 4 : KW == 3
       }
     }
     __syncthreads();
-    if (tid < m_end - m_begin) {
+    if (tid < m_end - m_begin && ((live >> tid) & 1u)) {
       const uint32_t id = m_id[tid];
       if (A.stat) A.stat[id] = m_stat[tid];
       if (A.dof) A.dof[id] = m_dof[tid];
@@ -524,13 +560,19 @@ __global__ void __launch_bounds__(256) ci_epilogue_kernel(const BatchArgs A) {
         w *= T.card[i];
       }
     }
+    uint32_t mask = 0xffffffffu, n_mem_unused;
+    if (A.prev_first) mask = live_members(A, t, tid, &n_mem_unused);
+    if (tid == 0) T.live = mask;
   }
   __syncthreads();
+  const uint32_t live = T.live;
+  if (live == 0u) return;                                  // the counting kernel skipped this table: it is still all zero
   int32_t* tab = A.scratch + A.scratch_off[lt];
   int32_t* wscratch = reinterpret_cast<int32_t*>(smem_raw);
   const uint32_t m_begin = __ldg(&A.mem_off[t]), m_end = __ldg(&A.mem_off[t + 1]), n_mem = m_end - m_begin;
   double* part = A.partials + (size_t)lt * kGroupMembers * A.epi_ctas * 2;
   for (uint32_t m = 0; m < n_mem; ++m) {
+    if (!((live >> m) & 1u)) continue;
     const uint2 mem = __ldg(&A.members[m_begin + m]);
     const uint32_t px = mem.y & 0xffu, py = (mem.y >> 8) & 0xffu;
     const CiGeom g(cells, T.card[px], T.card[py], T.weight[px], T.weight[py]);
@@ -550,7 +592,7 @@ __global__ void __launch_bounds__(256) ci_epilogue_kernel(const BatchArgs A) {
   __syncthreads();
   if (T.ticket != A.epi_ctas - 1) return;
   __threadfence();
-  if (tid < n_mem) {                                       // one thread per member: CTA order, then p and the decision
+  if (tid < n_mem && ((live >> tid) & 1u)) {               // one thread per member: CTA order, then p and the decision
     double stat = 0.0;
     unsigned long long dof = 0;
     for (uint32_t q = 0; q < A.epi_ctas; ++q) {

@@ -151,12 +151,6 @@ struct EsPool {
 };
 }  // namespace obn
 
-namespace obn {
-// "no test of this edge passed" in the device-side first[] array of a PC round: the array is
-// initialised with cudaMemsetAsync(0x7f), so every value >= kFirstNone means none
-static const int32_t kFirstNone = 0x7f000000;
-}  // namespace obn
-
 struct obn_dataset {
   obn_ctx* ctx = nullptr;
   uint8_t* data = nullptr;      // device, column-major, padded
@@ -177,28 +171,42 @@ struct obn_ctx {
   cudaStream_t aux[kAuxStreams] = {};
   cudaEvent_t ev_fork = nullptr, ev_join[kAuxStreams] = {};
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  // batch staging: one packed upload and one packed download per batch
-  obn::DevBuf d_in, d_out;
+  // uploads of a batch that is submitted while another one is running go here, so that the copy overlaps
+  // the running batch's kernels instead of queueing behind them
+  cudaStream_t up_stream = nullptr;
   obn::LutCache lut;
   obn::EsPool es_pool;
   obn::DevBuf d_scratch;   // int32, kept all-zero between launches
   obn::DevBuf d_tickets;   // uint32, kept all-zero between launches
   obn::DevBuf d_partials;  // per-CTA partial statistics of the split CI epilogue (ci_epilogue_kernel)
   obn::DevBuf d_scalar;    // staging of small host values that go through a collective
-  obn::PinBuf h_in, h_out;
   uint8_t* ds_cache = nullptr;  // device buffer of the last destroyed dataset, reused by the next upload
   size_t ds_cache_bytes = 0;
-  // a CI batch submitted with obn_ci_tests_submit whose results are still on their way
-  // (obn_ci_tests_collect waits for them); at most one, it owns the staging buffers until then
+  // What run_batch remembers of a batch between enqueueing it and handing out its results.
   struct Pending {
-    bool active = false;
     size_t n_out = 0;             // units this rank evaluated (tests / tuples)
     size_t n_results = 0;         // CI: tests of the batch (= results handed out)
     size_t n_slots = 0;           // PC round: edges of the round (0: a plain CI batch)
-    size_t out_bytes = 0, in_bytes = 0, ev_first = 0, tables = 0;
-    double alg_bytes = 0, scanned_bytes = 0, increments = 0;
-    bool want_p = false;
-  } pending;
+    size_t out_bytes = 0, in_bytes = 0, tables = 0;
+    double alg_bytes = 0, scanned_bytes = 0, increments = 0, n_rows = 0;
+    bool want_p = false, timed = false, chained = false;
+  };
+  // Batch staging: one packed upload and one packed download per batch.  Two sets, so that a second
+  // CI batch can be packed, uploaded and enqueued while the first is still running (obn_ci_tests_submit /
+  // obn_pc_round_submit; the PC driver keeps the device one round ahead of the host).  The batches of a
+  // ctx run in stream order, so the kernels' scratch (d_scratch, d_tickets, d_partials) stays single.
+  struct Staging {
+    obn::DevBuf d_in, d_out;
+    obn::PinBuf h_in, h_out;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, done = nullptr;   // kernel phase [e0, e1]; done: results are in h_out
+    cudaEvent_t uploaded = nullptr;                            // d_in holds the batch (copy on obn_ctx::up_stream)
+    Pending pending;
+  };
+  static constexpr int kStagings = 2;
+  Staging st[kStagings];
+  int q_head = 0, q_count = 0;    // FIFO of submitted batches: st[q_head] is the oldest
+  int last_round = -1;            // staging that holds first[] of the PC round submitted last (chained rounds read it)
+  size_t last_round_slots = 0;
   // launch policy of the counting kernels (obn_ctx_set_option; defaults from the sweep in
   // profiles/r1_kernel_sweep.txt)
   struct Tuning {
@@ -220,6 +228,4 @@ struct obn_ctx {
   // profiling
   bool profile_on = false;
   obn_profile prof = {};
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool;
-  size_t ev_used = 0;
 };

@@ -13,6 +13,10 @@ namespace obn {
 enum Mode : int { MODE_COUNTS = 0, MODE_CI = 1, MODE_BDEU_ONE = 2, MODE_BDEU_ALL = 3 };
 enum Tier : int { TIER_SMEM = 0, TIER_GLOBAL = 1, TIER_CHUNK = 2 };
 
+// "no test of this edge passed" in the device-side first[] array of a PC round: the array is
+// initialised with cudaMemsetAsync(0x7f), so every value >= kFirstNone means none
+constexpr int32_t kFirstNone = 0x7f000000;
+
 struct BatchArgs {
   // dataset
   const uint8_t* data;      // column-major codes, column v at data + v*stride
@@ -64,6 +68,12 @@ struct BatchArgs {
   const uint32_t* slot_of_test;   // null unless a PC round
   int32_t* first;
   double level;
+  // Chained PC rounds (obn_pc_round_submit, chain != 0): first[] of the round submitted before this one, over the
+  // same edge slots.  A test whose edge that round decided is skipped -- the serial reference had stopped at that
+  // candidate (pc.cpp:40-42) -- and a table none of whose tests is left is not counted at all.  The host enqueues
+  // this round before it has seen those results, so the device never waits for the host between two rounds.
+  const int32_t* prev_first;      // null unless chained
+  unsigned long long* skipped;    // [4]: tests skipped, sum of their tuple sizes, tables skipped, sum of their tuple sizes
 };
 
 // ---------------------------------------------------------------------------

@@ -415,9 +415,9 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
     for (int k = 0; k < h; ++k) { root_at[k] = n_all; n_all += P.root_tasks[k].size(); }
     const size_t joint_task_at = 0;
     if (int rc = pool.d_tasks.reserve(n_all * sizeof(MargTask))) return rc;
-    if (int rc = c->h_in.reserve(n_all * sizeof(MargTask))) return rc;               // page-locked staging
+    if (int rc = c->st[0].h_in.reserve(n_all * sizeof(MargTask))) return rc;               // page-locked staging
     {
-      MargTask* all = c->h_in.as<MargTask>();
+      MargTask* all = c->st[0].h_in.as<MargTask>();
       MargTask t{};
       t.f_index = P.slot[B - 1] * NT + (NT - 1);
       t.lo_shift = -1;
@@ -433,7 +433,7 @@ int obn_es_lattice(obn_es* e, int rank, int world) {
       for (int k = 0; k < h; ++k)
         if (!P.root_tasks[k].empty()) memcpy(all + root_at[k], P.root_tasks[k].data(), P.root_tasks[k].size() * sizeof(MargTask));
     }
-    OBN_CUDA(cudaMemcpyAsync(pool.d_tasks.p, c->h_in.p, n_all * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
+    OBN_CUDA(cudaMemcpyAsync(pool.d_tasks.p, c->st[0].h_in.p, n_all * sizeof(MargTask), cudaMemcpyHostToDevice, c->stream));
     OBN_CUDA(cudaStreamSynchronize(c->stream));                                        // h_in is reused by run_batch
     if (int rc = pool.d_slot.reserve(B * 4)) return rc;
     OBN_CUDA(cudaMemcpyAsync(pool.d_slot.p, P.slot.data(), B * 4, cudaMemcpyHostToDevice, c->stream));

@@ -26,14 +26,17 @@ def case(seed):
 
 
 class CountingEvaluator(OracleEvaluator):
-    """Also answers the two-half calls of the test seam (bindings.cpp: PyEvaluator::ci_submit)."""
+    """Also counts the asynchronous rounds of the test seam (bindings.cpp: PyEvaluator::pc_round_submit) and the
+    tests a chained round left out."""
     submitted = 0
+    skipped = 0
 
 
 @pytest.mark.parametrize("seed", range(40))
 @pytest.mark.parametrize("overlap", [0, 1])
 def test_pc_driver_fuzz(seed, overlap):
-    # overlap = 1: round r+1 is enumerated while round r is "in flight" (pc(..., overlap=True), pc.cpp) -- same graphs
+    # overlap = 1: round r+1 is enumerated AND submitted (chained) while round r is "in flight" (pc(..., overlap=True),
+    # pc.cpp) -- same graphs
     net, codes, cards = case(seed)
     ods = oracle.Dataset(codes, cards)
     rng = np.random.default_rng(1000 + seed)
@@ -52,6 +55,34 @@ def test_pc_driver_fuzz(seed, overlap):
         if rdf is not None:
             RT = REF.citest.ChiSquare(level) if kind == 0 else REF.citest.GSquare(level)
             assert (pdag_to_adj(REF.structure_learning.pc(rdf, RT, depth, stable), net.n) == want).all(), (seed, stable)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_pc_pipelined_rounds_ask_the_same_tests(seed):
+    """The pipelined driver submits round r+1 before it knows what round r removed; the evaluator drops those tests
+    (chain).  What is finally ASKED -- and accounted in last_pc_stats / recorded -- must be exactly the serial run's."""
+    net, codes, cards = case(300 + seed)
+    ods = oracle.Dataset(codes, cards)
+    T = L.citest.GSquare(0.05)
+    seen, skipped_any = [], 0
+    for overlap in (False, True):
+        ev = CountingEvaluator(ods)
+        g = L._testing.pc(net.n, ev, T, 3, True, None, 3, True, overlap)
+        st = L.structure_learning.last_pc_stats()
+        rec = [np.asarray(a).copy() for a in L.structure_learning.last_pc_tests()]
+        tests = sorted((int(x), int(y), tuple(rec[0][int(rec[1][t]):int(rec[1][t + 1])].tolist()))
+                       for t, (x, y) in enumerate(zip(rec[2], rec[3])))
+        seen.append((pdag_to_adj(g, net.n), int(st["total_tests"]), list(st["tests_per_depth"]), tests))
+        skipped_any += ev.skipped
+        assert len(tests) == st["total_tests"]
+    assert (seen[0][0] == seen[1][0]).all()
+    assert seen[0][1:] == seen[1][1:]
+    test_pc_pipelined_rounds_ask_the_same_tests.skipped_total = getattr(
+        test_pc_pipelined_rounds_ask_the_same_tests, "skipped_total", 0) + skipped_any
+
+
+def test_pc_pipelined_rounds_did_skip_something():
+    assert getattr(test_pc_pipelined_rounds_ask_the_same_tests, "skipped_total", 0) > 0      # the chain path really ran
 
 
 @pytest.mark.parametrize("seed", range(16))

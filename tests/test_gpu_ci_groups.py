@@ -110,3 +110,88 @@ def test_pc_round_takes_the_decision_on_the_device(gpu_ctx, split):
     with pytest.raises(IndexError):
         ds.pc_round(flat, offs, xa, ya, slot + 1000, n_slots, 1, 0.05)
     ds.close()
+
+
+def test_two_rounds_in_flight_and_chained_rounds(gpu_ctx):
+    """Two PC rounds in flight per ctx; the second one chained to the first: the tests of the edges the first round
+    decides are skipped on the device (never counted, never reported), so first[] and the profile counters equal
+    those of a host that had waited for round one and filtered round two itself."""
+    net = nw.hepar2_like()
+    codes, cards = ranked(net.sample(40000, 4))
+    ds = gpu_ctx.upload(codes, cards)
+    rng = np.random.default_rng(8)
+    xs, ys, tuples = star_frontier(rng, net.n, 10, 2, 6)
+    n = len(tuples)
+    xa, ya = np.asarray(xs, dtype=np.uint32), np.asarray(ys, dtype=np.uint32)
+    pairs = {}
+    slot = np.array([pairs.setdefault((min(a, b), max(a, b)), len(pairs)) for a, b in zip(xs, ys)], dtype=np.uint32)
+    n_slots = len(pairs)
+    order = rng.permutation(n)
+    ia, ib = np.sort(order[: n // 2]), np.sort(order[n // 2:])          # round one / round two, interleaved edges
+
+    def sub(idx):
+        flat, offs = capi._csr([tuples[i] for i in idx])
+        return flat, offs, xa[idx], ya[idx], slot[idx]
+
+    for kind, level in ((1, 0.05), (0, 0.3), (1, 1e-9)):
+        A, B = sub(ia), sub(ib)
+        first_a = ds.pc_round(*A, n_slots, kind, level)
+        keep = np.array([first_a[s] == INT32_MAX for s in B[4]])          # what a waiting host would still ask
+        assert 0 < keep.sum() < len(ib) or level == 1e-9
+        Bf = sub(ib[keep])
+        gpu_ctx.profile_enable(True)
+        gpu_ctx.profile_read(True)
+        want_b = ds.pc_round(*Bf, n_slots, kind, level)
+        prof_want = gpu_ctx.profile_read(True)
+        back = np.flatnonzero(keep)                                      # index in the filtered round -> index in the full one
+        want_b = np.array([INT32_MAX if v == INT32_MAX else back[v] for v in want_b.tolist()])
+        # pipelined: both rounds enqueued before anything is collected
+        ds.pc_round_submit(*A, n_slots, kind, level)
+        ds.pc_round_submit(*B, n_slots, kind, level, chain=True)
+        with pytest.raises(ValueError, match="two submitted batches"):
+            ds.pc_round_submit(*B, n_slots, kind, level, chain=True)
+        with pytest.raises(ValueError, match="waiting to be collected"):
+            ds.count_tables([[0, 1]])
+        got_a = ds.pc_round_collect(n_slots)
+        prof_a = gpu_ctx.profile_read(True)
+        got_b = ds.pc_round_collect(n_slots)
+        prof_b = gpu_ctx.profile_read(True)
+        assert got_a.tolist() == first_a.tolist()
+        assert got_b.tolist() == want_b.tolist()
+        assert prof_a.tuples == len(ia)
+        for f in ("tuples", "tables", "algorithmic_bytes", "scanned_bytes", "increments"):
+            assert getattr(prof_b, f) == getattr(prof_want, f), f
+        # a third round chained to the second (the first one's staging is reused)
+        ds.pc_round_submit(*A, n_slots, kind, level, chain=True)
+        got_c = ds.pc_round_collect(n_slots)
+        keep_c = np.array([want_b[s] == INT32_MAX for s in A[4]])
+        if keep_c.any():
+            Af = sub(ia[keep_c])
+            back_c = np.flatnonzero(keep_c)
+            want_c = [INT32_MAX if v == INT32_MAX else back_c[v] for v in ds.pc_round(*Af, n_slots, kind, level).tolist()]
+            assert got_c.tolist() == want_c
+        else:
+            assert got_c.tolist() == [INT32_MAX] * n_slots
+        gpu_ctx.profile_enable(False)
+    # chain without a round to continue, or over other slots
+    ds.count_tables([[0, 1]])
+    A = sub(ia)
+    ds.pc_round_submit(*A, n_slots, 1, 0.05)
+    with pytest.raises(ValueError, match="chain"):
+        ds.pc_round_submit(*A, n_slots + 1, 1, 0.05, chain=True)
+    ds.pc_round_collect(n_slots)
+    # two plain CI batches in flight, collected in submission order
+    L = capi.load()
+    import ctypes as C
+    flat_a, offs_a = capi._csr([tuples[i] for i in ia])
+    flat_b, offs_b = capi._csr([tuples[i] for i in ib])
+    for flat, offs, idx in ((flat_a, offs_a, ia), (flat_b, offs_b, ib)):
+        capi._check(L.obn_ci_tests_submit(gpu_ctx._h, ds._h, capi._ptr(flat, C.c_uint32), capi._ptr(offs, C.c_uint64), len(idx),
+                                          capi._ptr(np.ascontiguousarray(xa[idx]), C.c_uint32),
+                                          capi._ptr(np.ascontiguousarray(ya[idx]), C.c_uint32), 1, 1))
+    for flat, offs, idx in ((flat_a, offs_a, ia), (flat_b, offs_b, ib)):
+        stat = np.zeros(len(idx)); dof = np.zeros(len(idx), dtype=np.uint64); p = np.zeros(len(idx))
+        capi._check(L.obn_ci_tests_collect(gpu_ctx._h, capi._ptr(stat, C.c_double), capi._ptr(dof, C.c_uint64), capi._ptr(p, C.c_double)))
+        ws, wd, wp = ds.ci_tests_csr(flat, offs, np.ascontiguousarray(xa[idx]), np.ascontiguousarray(ya[idx]), 1)
+        assert np.array_equal(stat, ws) and np.array_equal(dof, wd) and np.array_equal(p, wp)
+    ds.close()
