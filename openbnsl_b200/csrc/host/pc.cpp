@@ -286,13 +286,17 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         for (const auto& c : cursors) live += (!c.done && !c.removed);
         return live;
       };
-      // the next `quota` candidates of every undecided edge, in the reference's enumeration order
-      auto build_round = [&](TupleBatch& out, std::vector<uint32_t>& pair_out, size_t quota) {
+      // the next `quota` candidates of every undecided edge, in the reference's enumeration order.  A round may be
+      // cut into windows of edges: starts at cursor pi_begin, stops in front of the first edge that would begin
+      // beyond max_tests tests, and returns where it stopped (cursors.size(): the sweep is complete).
+      auto build_round = [&](TupleBatch& out, std::vector<uint32_t>& pair_out, size_t quota, size_t pi_begin = 0,
+                             size_t max_tests = (size_t)-1) -> size_t {
         out.clear();
         pair_out.clear();
-        for (size_t pi = 0; pi < cursors.size(); ++pi) {
+        for (size_t pi = pi_begin; pi < cursors.size(); ++pi) {
           FastCursor& c = cursors[pi];
           if (c.done || c.removed) continue;
+          if (out.size() >= max_tests) return pi;
           uint32_t* idx = idx_arena.data() + pi * std::max<size_t>(k, 1);
           for (size_t q = 0; q < quota && !c.done; ++q) {
             // tuple = sort(Z + {x,y}) (pc.cpp:34-37): Z is ascending already, merge x < y into it
@@ -317,6 +321,7 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
             settle(c, idx);
           }
         }
+        return cursors.size();
       };
       // every edge is resolved at its FIRST passing candidate (pc.cpp:40-42)
       auto resolve_round = [&](const TupleBatch& b) {
@@ -363,11 +368,34 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         // independent candidate (pc.cpp:40-42).  The device always has the next round queued behind the one it
         // is working on; the host enumerates, packs and resolves in its shadow.  Batch boundaries do not change
         // what an edge resolves at.  Ring of three rounds: being resolved / in flight behind it / being built.
-        quota = std::max<size_t>(quota, target_batch / live);
-        size_t head = 0, n_flight = 0;
-        build_round(W.ring[0], W.ring_pairs[0], quota);
+        // Sweeps and windows: a sweep hands every undecided edge its next `quota` candidates (the quota doubles
+        // from sweep to sweep, as in the serial loop).  The FIRST batch of a depth is only a window of the first
+        // sweep (a quarter of target_batch): the device starts after a short build, and the rest of the sweep is
+        // enumerated and packed in its shadow.  Edges are independent within a depth, so cutting a sweep anywhere
+        // changes nothing an edge resolves at.
+        size_t head = 0, n_flight = 0, sweep_pos = cursors.size();
+        bool first_sweep = true, first_window = true;
+        auto next_window = [&](TupleBatch& out, std::vector<uint32_t>& pairs) -> bool {
+          for (int attempt = 0; attempt < 2; ++attempt) {
+            if (sweep_pos >= cursors.size()) {            // start the next sweep
+              const size_t l2 = count_live();
+              if (!l2) return false;
+              if (!first_sweep) quota *= 2;
+              first_sweep = false;
+              quota = std::max<size_t>(quota, target_batch / l2);
+              sweep_pos = 0;
+            }
+            const size_t budget = first_window ? std::max<size_t>(1, target_batch / 4) : (size_t)-1;
+            sweep_pos = build_round(out, pairs, quota, sweep_pos, budget);
+            if (out.size()) {
+              first_window = false;
+              return true;
+            }
+          }
+          return false;
+        };
+        bool more = next_window(W.ring[0], W.ring_pairs[0]);
         lap(&PcStats::enumerate_ms);
-        bool more = W.ring[0].size() != 0;
         if (more) {
           async->submit(W.ring[0], W.ring_pairs[0], cursors.size(), false);
           n_flight = 1;
@@ -375,21 +403,14 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         lap(&PcStats::evaluate_ms);
         while (n_flight) {
           if (more && n_flight < 2) {
-            more = false;
-            quota *= 2;
-            const size_t l2 = count_live();
-            if (l2) {
-              quota = std::max<size_t>(quota, target_batch / l2);
-              const size_t nxt = (head + n_flight) % 3;
-              build_round(W.ring[nxt], W.ring_pairs[nxt], quota);
-              lap(&PcStats::enumerate_ms);
-              if (W.ring[nxt].size()) {
-                async->submit(W.ring[nxt], W.ring_pairs[nxt], cursors.size(), true);
-                ++n_flight;
-                more = true;
-              }
-              lap(&PcStats::evaluate_ms);
+            const size_t nxt = (head + n_flight) % 3;
+            more = next_window(W.ring[nxt], W.ring_pairs[nxt]);
+            lap(&PcStats::enumerate_ms);
+            if (more) {
+              async->submit(W.ring[nxt], W.ring_pairs[nxt], cursors.size(), true);
+              ++n_flight;
             }
+            lap(&PcStats::evaluate_ms);
           }
           const TupleBatch& b = W.ring[head];
           const std::vector<uint32_t>& pairs = W.ring_pairs[head];

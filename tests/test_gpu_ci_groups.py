@@ -189,9 +189,12 @@ def test_two_rounds_in_flight_and_chained_rounds(gpu_ctx):
         capi._check(L.obn_ci_tests_submit(gpu_ctx._h, ds._h, capi._ptr(flat, C.c_uint32), capi._ptr(offs, C.c_uint64), len(idx),
                                           capi._ptr(np.ascontiguousarray(xa[idx]), C.c_uint32),
                                           capi._ptr(np.ascontiguousarray(ya[idx]), C.c_uint32), 1, 1))
+    got = []
     for flat, offs, idx in ((flat_a, offs_a, ia), (flat_b, offs_b, ib)):
         stat = np.zeros(len(idx)); dof = np.zeros(len(idx), dtype=np.uint64); p = np.zeros(len(idx))
         capi._check(L.obn_ci_tests_collect(gpu_ctx._h, capi._ptr(stat, C.c_double), capi._ptr(dof, C.c_uint64), capi._ptr(p, C.c_double)))
+        got.append((stat, dof, p))
+    for (flat, offs, idx), (stat, dof, p) in zip(((flat_a, offs_a, ia), (flat_b, offs_b, ib)), got):
         ws, wd, wp = ds.ci_tests_csr(flat, offs, np.ascontiguousarray(xa[idx]), np.ascontiguousarray(ya[idx]), 1)
         assert np.array_equal(stat, ws) and np.array_equal(dof, wd) and np.array_equal(p, wp)
     ds.close()
