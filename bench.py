@@ -355,13 +355,13 @@ def time_pc(job, key, steps, warmup, e2e_steps, want_clocks=False, record=False)
     job.barrier()
     event_ms.clear()
     times = []
-    phases = {"enumerate_ms": 0.0, "evaluate_ms": 0.0, "resolve_ms": 0.0}
+    phases = {"enumerate_ms": 0.0, "evaluate_ms": 0.0, "resolve_ms": 0.0, "exposed_ms": 0.0, "collect_wait_ms": 0.0}
     for _ in range(steps):
         dt, g, _ = step(True)
         times.append(dt)
         st = L.structure_learning.last_pc_stats()
         for k in phases:
-            phases[k] += st[k] / steps
+            phases[k] += st.get(k, 0.0) / steps
     job.barrier()
     prof = L.profile_read(True)
     st = L.structure_learning.last_pc_stats()
@@ -420,7 +420,9 @@ def time_pc(job, key, steps, warmup, e2e_steps, want_clocks=False, record=False)
         "limiter": dict(phases, kernel_ms=prof["count_kernel_ms"] / steps, host_pack_ms=prof["host_prep_ms"] / steps,
                         collectives_per_step=prof["collectives"] / steps,
                         note="host wall time of the driver phases per step on rank 0: enumerate (frontier), evaluate "
-                             "(plan + pack + kernels + all-reduce + wait; the next round is enumerated inside it), resolve"),
+                             "(plan + pack + enqueue + wait), resolve; rounds are pipelined two deep, so only exposed_ms "
+                             "(host time with no round in flight: the start and end of every depth) is not hidden behind "
+                             "the kernels; collect_wait_ms = host blocked waiting for the device"),
     }
     del df
     return out

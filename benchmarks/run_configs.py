@@ -90,7 +90,8 @@ def run_pc(name, net, n_rows, test, depth, what, reps=1):
     report(name, what, st["total_tests"], "ci_tests", secs, prof,
            {"tests_per_depth": [int(x) for x in st["tests_per_depth"]], "n_vars": net.n, "n_rows": n_rows,
             "max_card": int(max(cards)), "pdag_arcs": n_edges, "enumerate_ms": st["enumerate_ms"],
-            "evaluate_ms": st["evaluate_ms"], "resolve_ms": st["resolve_ms"], "data_gen_s": t_gen,
+            "evaluate_ms": st["evaluate_ms"], "resolve_ms": st["resolve_ms"], "exposed_ms": st.get("exposed_ms"),
+            "collect_wait_ms": st.get("collect_wait_ms"), "data_gen_s": t_gen,
             "batches_per_depth": [int(x) for x in st["batches_per_depth"]], "tables": prof["tables"],
             "scanned_GB": prof["scanned_bytes"] / 1e9, "atoms_ceiling_ms": prof["increments"] / 4.65e12 * 1e3,
             "collectives": prof["collectives"], "pc_kwargs": dict(PC_KW), "options": dict(OPTS),

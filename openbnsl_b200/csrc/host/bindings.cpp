@@ -448,6 +448,8 @@ PYBIND11_MODULE(openbnsllib, m) {
     d["enumerate_ms"] = g_last_pc_stats.enumerate_ms;
     d["evaluate_ms"] = g_last_pc_stats.evaluate_ms;
     d["resolve_ms"] = g_last_pc_stats.resolve_ms;
+    d["exposed_ms"] = g_last_pc_stats.exposed_ms;
+    d["collect_wait_ms"] = g_last_pc_stats.collect_wait_ms;
     return d;
   });
   sl.def("last_es_stats", []() {

@@ -165,8 +165,9 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
   }
   using clk = std::chrono::steady_clock;
   auto ms_since = [](clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); };
-  if (stats) stats->enumerate_ms = stats->evaluate_ms = stats->resolve_ms = 0;
+  if (stats) stats->enumerate_ms = stats->evaluate_ms = stats->resolve_ms = stats->exposed_ms = stats->collect_wait_ms = 0;
   clk::time_point t_phase = clk::now();
+  clk::time_point t_empty = clk::now();       // since when no round is in flight
   auto lap = [&](double PcStats::*slot) {
     if (stats) stats->*slot += ms_since(t_phase);
     t_phase = clk::now();
@@ -399,6 +400,7 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         if (more) {
           async->submit(W.ring[0], W.ring_pairs[0], cursors.size(), false);
           n_flight = 1;
+          if (stats) stats->exposed_ms += ms_since(t_empty);
         }
         lap(&PcStats::evaluate_ms);
         while (n_flight) {
@@ -414,7 +416,10 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
           }
           const TupleBatch& b = W.ring[head];
           const std::vector<uint32_t>& pairs = W.ring_pairs[head];
+          const clk::time_point t_wait = clk::now();
           async->collect(cursors.size(), first);
+          if (stats) stats->collect_wait_ms += ms_since(t_wait);
+          if (n_flight == 1) t_empty = clk::now();
           lap(&PcStats::evaluate_ms);
           // an edge that is marked removed by now was decided by the round before this one: its tests were skipped
           const std::function<bool(size_t)> skipped = [&](size_t t) { return cursors[pairs[t]].removed; };

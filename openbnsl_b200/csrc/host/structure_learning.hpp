@@ -19,6 +19,9 @@ struct PcStats {
   std::vector<uint64_t> tests_per_depth;   // CI tests evaluated (after de-duplication)
   std::vector<uint64_t> batches_per_depth;
   double enumerate_ms = 0, evaluate_ms = 0, resolve_ms = 0;   // host wall time of the three driver phases
+  // pipelined rounds: host time with NO round in flight (depth starts and ends: nothing hides it), and time the
+  // host spent blocked in collect (the device was the one being waited for)
+  double exposed_ms = 0, collect_wait_ms = 0;
   bool record = false;                     // keep every evaluated test in `recorded`
   TupleBatch recorded;
   uint64_t total_tests() const {
