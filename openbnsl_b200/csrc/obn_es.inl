@@ -468,6 +468,9 @@ int obn_es_finish(obn_es* e, uint64_t* parent_masks, double* best_score) {
   OBN_CUDA(cudaSetDevice(c->device));
   const int n = e->n;
   for (int v = 0; v < n; ++v) parent_masks[v] = 0;
+  // the levels of a child-sharded DP are only ENQUEUED (obn_es_level_dp_sharded), and the blocking copies below
+  // do not order themselves behind a non-blocking stream
+  OBN_CUDA(cudaStreamSynchronize(c->stream));
   uint32_t W = (uint32_t)(((uint64_t)1 << n) - 1);
   if (best_score)
     OBN_CUDA(cudaMemcpy(best_score, e->best_gs + W, sizeof(double), cudaMemcpyDeviceToHost));
