@@ -50,20 +50,19 @@ struct BatchSpec {
 //   class  cells        kernel
 //   0      <= 64        <8,  SMEM, scale4>   four 8-bit keys per register, key = byte offset
 //   1      <= 256       <8,  SMEM, plain>
-//   2..5   <= 512/1Ki/4Ki/16Ki  <16, SMEM, scale4>
-//   6      <= smem      <32, SMEM, plain>
-//   7      <= 1.5 Mi    <32, CHUNK, plain>   cell range cut into shared-memory chunks, merged into global scratch
-//   8      larger       <32, GLOBAL, plain>  table in L2-resident global scratch
-static const int kNumClasses = 9;
-static const int kClassSmemMax = 6, kClassChunk = 7, kClassGlobal = 8;
-static const uint32_t kClassCells[6] = {64, 256, 512, 1024, 4096, 16384};
-// class 7 (TIER_CHUNK): the table is cut into chunks of this many cells (176 KB of shared memory), at most kMaxChunks of them
+//   2..4   <= 1Ki/4Ki/16Ki  <16, SMEM, scale4>
+//   5      <= smem      <32, SMEM, plain>
+//   6      <= 1.5 Mi    <32, CHUNK, plain>   cell range cut into shared-memory chunks, merged into global scratch
+//   7      larger       <32, GLOBAL, plain>  table in L2-resident global scratch
+static const int kNumClasses = 8;
+static const int kClassSmemMax = 5, kClassChunk = 6, kClassGlobal = 7;
+static const uint32_t kClassCells[5] = {64, 256, 1024, 4096, 16384};
+// class 6 (TIER_CHUNK): the table is cut into chunks of this many cells (176 KB of shared memory), at most kMaxChunks of them
 static const uint32_t kChunkCells = 44 * 1024;
 static const uint32_t kMaxChunks = 32;
-// log2 of the shared-memory table copies per class (0: none): 32 / 32 / 32 / 16 / 4 copies keep the copies of one
-// table within 8 / 32 / 64 / 64 / 64 KB (A/B: profiles/r2_ab_replication.jsonl; the 512-cell class was split off
-// the 1 Ki one after ncu showed 2.3 wavefronts per increment there with 16 copies, 68 % of its tables being <= 512 cells)
-static constexpr int kRepShift[6] = {5, 5, 5, 4, 2, 0};
+// log2 of the shared-memory table copies per class (0: none): 32 / 32 / 16 / 4 copies keep the copies of one
+// table within 8 / 32 / 64 / 64 KB (A/B: profiles/r2_ab_replication.jsonl)
+static constexpr int kRepShift[5] = {5, 5, 4, 2, 0};
 
 static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
@@ -339,7 +338,7 @@ static int run_batch(BatchSpec& S) {
       // that allows; row splits only pay when a launch has too few tuples to do that
       // (each split repeats the prologue and adds a merge through L2).
       // table copies (obn_count_kernel.cuh): fixed per shared-memory class, compile-time constants of the kernels
-      const uint32_t rep_shift = (c->tune.rep && g < kClassSmemMax && kRepShift[g] > 0) ? (uint32_t)kRepShift[g] : 0u;
+      const uint32_t rep_shift = (c->tune.rep && g <= 4 && kRepShift[g] > 0) ? (uint32_t)kRepShift[g] : 0u;
       const size_t table_bytes = chunk_tier ? (size_t)kChunkCells * 4 : global_tier ? 0
                                  : align16((size_t)max_cells * 4) + (rep_shift ? ((size_t)max_cells << rep_shift) * 4 : 0);
       const size_t tpt = target_threads / remaining;
@@ -542,12 +541,11 @@ static int run_batch(BatchSpec& S) {
       if (L.g == 0) e = launch_count<8, TIER_SMEM, true, kRepShift[0]>(a, grid, L.nthr, L.smem, st);
       else if (L.g == 1) e = launch_count<8, TIER_SMEM, false, kRepShift[1]>(a, grid, L.nthr, L.smem, st);
       else if (L.g == 2) e = launch_count<16, TIER_SMEM, true, kRepShift[2]>(a, grid, L.nthr, L.smem, st);
-      else if (L.g == 3) e = launch_count<16, TIER_SMEM, true, kRepShift[3]>(a, grid, L.nthr, L.smem, st);
-      else e = launch_count<16, TIER_SMEM, true, kRepShift[4]>(a, grid, L.nthr, L.smem, st);
+      else e = launch_count<16, TIER_SMEM, true, kRepShift[3]>(a, grid, L.nthr, L.smem, st);
     } else
     if (L.g == 0) e = launch_count<8, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
     else if (L.g == 1) e = launch_count<8, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
-    else if (L.g < kClassSmemMax) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
+    else if (L.g <= 4) e = launch_count<16, TIER_SMEM, true>(a, grid, L.nthr, L.smem, st);
     else if (L.g == kClassSmemMax) e = launch_count<32, TIER_SMEM, false>(a, grid, L.nthr, L.smem, st);
     else if (L.g == kClassChunk) e = launch_count<32, TIER_CHUNK, false>(a, grid, L.nthr, L.smem, st);
     else e = launch_count<32, TIER_GLOBAL, false>(a, grid, L.nthr, L.smem, st);
