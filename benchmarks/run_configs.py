@@ -67,19 +67,19 @@ def report(name, what, units, unit_name, secs, prof, extra=None):
         print(json.dumps(line), flush=True)
 
 
-def run_pc(name, net, n_rows, test, depth, what, reps=1):
+def run_pc(name, net, n_rows, test, depth, what, reps=1, stable=True):
     reps = REPS or reps
     df, cards, t_gen = frame(net, n_rows, 0)
     L.profile_enable(True)
     df.to_device()
-    L.structure_learning.pc(df, test, depth, True, comm=COMM, **PC_KW)   # warm-up (allocations, first launches, NCCL)
+    L.structure_learning.pc(df, test, depth, stable, comm=COMM, **PC_KW)   # warm-up (allocations, first launches, NCCL)
     L.profile_read(True)
     if COMM is not None:
         import torch.distributed as dist
         dist.barrier()
     t0 = time.perf_counter()
     for _ in range(reps):
-        g = L.structure_learning.pc(df, test, depth, True, comm=COMM, **PC_KW)
+        g = L.structure_learning.pc(df, test, depth, stable, comm=COMM, **PC_KW)
     secs = (time.perf_counter() - t0) / reps
     prof = L.profile_read(True)
     for key in ("count_kernel_ms", "algorithmic_bytes", "host_prep_ms", "host_wait_ms", "count_launches", "scanned_bytes",
@@ -187,6 +187,9 @@ def main():
     if "c2" in which:
         run_pc("C2", nw.alarm(), 100_000, L.citest.GSquare(0.05), 4,
                "PC-stable G2, Alarm structure, 37 vars, 100k rows, depth<=4", reps=20)
+    if "c2ns" in which:                   # the original (order-dependent) PC: sequential over pairs by definition, one batch per pair
+        run_pc("C2-nonstable", nw.alarm(), 100_000, L.citest.GSquare(0.05), 4,
+               "PC (stable=False) G2, Alarm structure, 37 vars, 100k rows, depth<=4", reps=3, stable=False)
     if "c3" in which:
         net = nw.random_binary(24)
         run_es("C3", net, 1_000_000, 3, "exhaustive search BDeu, 24 binary vars, 1M rows, max_parents=3 (12 951 tables)", exact=0)

@@ -73,6 +73,8 @@ OBN_API void* obn_ctx_stream(obn_ctx* ctx);
  *                                        and read that one whenever every column of a table has it (half the L2 traffic)
  *   "rep" (1), "chunk" (1), "min_waves" (0)   replicated shared-memory tables on / off; tables beyond shared memory counted
  *                                        chunk-wise in shared memory instead of by L2 reductions; row-split small launches to this many waves
+ *   "min_class" (0), "lut_max_mb" (2048)  smallest table-size class used (fewer, larger launches per batch); cap of the
+ *                                        exact-order lgamma tables kept on the device (evicted and rebuilt beyond it)
  *   "lattice_budget_gb" (24), "lattice_max_l" (20), "lattice_bottom" (1), "lattice_reorder" (1),
  *   "lattice_graph" (1), "lattice_lanes" (2), "lattice_no_lut" (0), "debug" (0)      marginalisation lattice
  * Unknown names fail with OBN_ERR_INVALID. */

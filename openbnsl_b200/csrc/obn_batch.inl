@@ -81,7 +81,6 @@ static cudaError_t launch_count(const BatchArgs& a, unsigned grid, int nthr, siz
 }
 
 static const size_t kScratchMaxBytes = (size_t)8 << 30;
-static const size_t kLutMaxBytes = (size_t)2 << 30;
 
 // Results of a finished batch: staging buffer -> the caller's arrays, profile counters.
 static void finish_batch(obn_ctx* c, const obn_ctx::Staging& G, double* stat, uint64_t* dof, double* p, int32_t* first) {
@@ -175,6 +174,7 @@ static int run_batch(BatchSpec& S) {
     cells[t] = (uint32_t)cl;
     int g = 0;
     while (g < kClassSmemMax && cl > kClassCells[g]) ++g;
+    if (g < c->tune.min_class) g = c->tune.min_class;
     if (g == kClassSmemMax && cl * 4 + 16 + 8 * 512 * 4 > budget)
       g = (c->tune.chunk && cl <= (uint64_t)kChunkCells * kMaxChunks) ? kClassChunk : kClassGlobal;
     // epilogue scratch per warp: the margins, and for tables in global memory one staged slice (ci_slices_any)
@@ -228,7 +228,7 @@ static int run_batch(BatchSpec& S) {
         }
       }
       const size_t want_rows = lc.rows + pending.size();
-      if (want_rows * lut_stride * sizeof(double) > kLutMaxBytes) {
+      if (want_rows * lut_stride * sizeof(double) > (size_t)c->tune.lut_max_mb << 20) {
         // the cap is hit by what EARLIER batches left in the cache: evict everything and number this
         // batch's tables afresh, so that the outcome depends on this batch alone, not on the ctx's history
         if (attempt == 0 && lc.rows) {

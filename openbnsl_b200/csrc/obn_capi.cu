@@ -162,6 +162,8 @@ int obn_ctx_set_option(obn_ctx* c, const char* name, double value) {
   else if (k == "chunk") c->tune.chunk = v;
   else if (k == "pack4") c->tune.pack4 = v;
   else if (k == "min_waves") c->tune.min_waves = std::max(0, v);
+  else if (k == "min_class") c->tune.min_class = std::max(0, std::min(4, v));
+  else if (k == "lut_max_mb") c->tune.lut_max_mb = std::max(1, v);
   else if (k == "lattice_budget_gb") c->tune.lattice_budget_gb = std::max(1, v);
   else if (k == "lattice_max_l") c->tune.lattice_max_l = std::max(1, v);
   else if (k == "lattice_bottom") c->tune.lattice_bottom = v;

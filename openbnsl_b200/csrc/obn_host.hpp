@@ -218,6 +218,8 @@ struct obn_ctx {
     int pack4 = 1;                // build and use nibble-packed columns (two rows per byte) for variables of <= 16 states
     int chunk = 1;                // tables beyond shared memory: chunked shared-memory counting (TIER_CHUNK) instead of L2 reductions
     int min_waves = 0;            // row-split the tuples of a launch until it has this many waves of CTAs (0: off)
+    int min_class = 0;            // tables of the shared-memory classes below this one are counted by this one (fewer launches per batch; A/B)
+    int lut_max_mb = 2048;        // cap of the lgamma tables kept for the exact-order BDeu epilogue (tests lower it)
     // marginalisation lattice (obn_lattice.inl)
     int lattice_budget_gb = 24, lattice_max_l = 20, lattice_bottom = 1, lattice_reorder = 1, lattice_graph = 1,
         lattice_lanes = 2, lattice_no_lut = 0, debug = 0;

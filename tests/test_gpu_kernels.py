@@ -75,6 +75,38 @@ def test_ci_random_alarm(alarm, kind):
                 assert (p[i] >= level) == (pv >= level)
 
 
+def test_exact_order_table_cache_evicts_instead_of_failing(gpu_ctx, alarm):
+    """The lgamma tables of the exact-order epilogue are cached on the ctx up to a cap.  A ctx that has served many
+    ess values must not fail (or silently change precision) because of what EARLIER calls left in the cache: it evicts
+    and rebuilds.  Only a single batch that needs more than the cap by itself is refused (exact_order=1) or answered
+    in fast mode and counted in the profile (exact_order=2)."""
+    net, ods, ds = alarm                         # 20011 rows: one table = 160 KB
+    tuples, child = [[0, 1, 2], [3, 4], [5, 9, 22]], [1, 3, 22]
+    gpu_ctx.set_option("lut_max_mb", 2)          # room for thirteen tables; one call below needs up to nine
+    try:
+        gpu_ctx.profile_enable(True)
+        gpu_ctx.profile_read(True)
+        for i in range(12):                      # every call brings new tables; the cache overflows several times
+            ess = 0.5 + 0.37 * i
+            got = ds.bdeu_scores(tuples, child, ess, exact_order=1)
+            for t, c, g in zip(tuples, child, got):
+                assert g == oracle.bdeu_local_score(ods, c, [v for v in t if v != c], ess), (i, t)
+        assert gpu_ctx.profile_read(True).exact_fallbacks == 0
+        # one batch that cannot fit by itself
+        rng = np.random.default_rng(2)
+        many = [sorted(rng.choice(37, size=k, replace=False).tolist()) for k in (1, 2, 3, 4, 5, 6) for _ in range(4)]
+        ch = [t[0] for t in many]
+        with pytest.raises(RuntimeError, match="lgamma tables"):
+            ds.bdeu_scores(many, ch, 1.0, exact_order=1)
+        got = ds.bdeu_scores(many, ch, 1.0, exact_order=2)
+        assert gpu_ctx.profile_read(True).exact_fallbacks == 1
+        for t, c, g in zip(many, ch, got):
+            assert g == pytest.approx(oracle.bdeu_local_score(ods, c, [v for v in t if v != c], 1.0), rel=1e-9)
+    finally:
+        gpu_ctx.set_option("lut_max_mb", 2048)
+        gpu_ctx.profile_enable(False)
+
+
 @pytest.mark.parametrize("exact", [False, True])
 def test_bdeu_random(asia, alarm, exact):
     for net, ods, ds in (asia, alarm):

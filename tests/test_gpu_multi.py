@@ -96,7 +96,7 @@ def test_two_gpu_pc_and_es_match_golden(tmp_path):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                         "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script)],
                        capture_output=True, text=True, env=env, timeout=540)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-8000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("MULTI_GPU_RESULT")]
     assert line, r.stdout[-2000:]
     import json
