@@ -541,6 +541,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--stock-rows", type=int, default=20000, help="reference arm: rows of the stock pc() call")
     args = ap.parse_args()
+    # stdout carries ONE JSON line: whatever NCCL logs (it prints its version banner to stdout) goes to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
