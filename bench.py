@@ -133,6 +133,27 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    """stdout carries ONE JSON line.  Libraries write banners to fd 1 (torch prints "NCCL version ..." when the first
+    communicator is created): everything written to fd 1 from here on goes to stderr, the line itself to the real stdout."""
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _STDOUT_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_STDOUT_FD, data)
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -265,7 +286,7 @@ def run_reference_arm(args, rank):
                  "cpu_baseline": {"value": val, "unit": "CI tests/s", "cores": cores, "kind": kindname, "sample": sample},
                  "e2e": {"value": val, "unit": "CI tests/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "frontier_learn_time_s_extrapolated": n_tests / val, "stock_pc": stock, "gpu_launches": 0})
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ----------------------------------------------------------------------------
@@ -525,7 +546,7 @@ def run_ours(args, rank, world, local_rank):
         "clocks": head["clocks"], "cpu_baseline": cpu,
         "secondary": secondary,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -541,8 +562,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--stock-rows", type=int, default=20000, help="reference arm: rows of the stock pc() call")
     args = ap.parse_args()
-    # stdout carries ONE JSON line: whatever NCCL logs (it prints its version banner to stdout) goes to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
