@@ -220,6 +220,30 @@ static int es_ensure_lists(obn_es* e) {
   return OBN_OK;
 }
 
+
+// exhaustive_search.cpp:133-148 on the device: walk the sink choices from the full set down, one dependent read
+// per variable (2n tiny loads instead of 2n + 1 blocking copies over PCIe).  out[0 .. n) = parent set of every
+// child this rank owns (0 elsewhere), out[n] = bits of the best score, out[n + 1] = 0 or 1 + the step that found
+// no sink choice (the search did not process every level).
+__global__ void es_backtrack_kernel(int n, const uint8_t* __restrict__ best_ch, const uint32_t* __restrict__ bl_ps,
+                                    const double* __restrict__ best_gs, int own_first, int own_end,
+                                    unsigned long long* __restrict__ out) {
+  if (threadIdx.x || blockIdx.x) return;
+  uint32_t W = (uint32_t)(((uint64_t)1 << n) - 1);
+  for (int v = 0; v < n; ++v) out[v] = 0ull;
+  out[n] = (unsigned long long)__double_as_longlong(best_gs[W]);
+  out[n + 1] = 0ull;
+  for (int i = 0; i < n; ++i) {
+    const uint32_t ch = best_ch[W];
+    if (ch >= (uint32_t)n) {
+      out[n + 1] = 1ull + (unsigned long long)i;
+      return;
+    }
+    if ((int)ch >= own_first && (int)ch < own_end) out[ch] = bl_ps[(size_t)W * n + ch];     // row of W = pa + ch
+    W &= ~(1u << ch);
+  }
+}
+
 }  // namespace obn
 
 extern "C" {
@@ -468,24 +492,19 @@ int obn_es_finish(obn_es* e, uint64_t* parent_masks, double* best_score) {
   OBN_CUDA(cudaSetDevice(c->device));
   const int n = e->n;
   for (int v = 0; v < n; ++v) parent_masks[v] = 0;
-  // the levels of a child-sharded DP are only ENQUEUED (obn_es_level_dp_sharded), and the blocking copies below
-  // do not order themselves behind a non-blocking stream
+  // one tiny kernel behind whatever is still enqueued on the ctx's stream (the levels of a child-sharded DP are
+  // only enqueued, obn_es_level_dp_sharded), one copy back
+  if (int rc = c->d_scalar.reserve((size_t)(n + 2) * 8)) return rc;
+  unsigned long long* d_out = c->d_scalar.as<unsigned long long>();
+  es_backtrack_kernel<<<1, 32, 0, c->stream>>>(n, e->best_ch, e->bl_ps, e->best_gs, e->own_first, e->own_end, d_out);
+  OBN_CUDA(cudaGetLastError());
+  unsigned long long h_out[66];
+  OBN_CUDA(cudaMemcpyAsync(h_out, d_out, (size_t)(n + 2) * 8, cudaMemcpyDeviceToHost, c->stream));
   OBN_CUDA(cudaStreamSynchronize(c->stream));
-  uint32_t W = (uint32_t)(((uint64_t)1 << n) - 1);
-  if (best_score)
-    OBN_CUDA(cudaMemcpy(best_score, e->best_gs + W, sizeof(double), cudaMemcpyDeviceToHost));
-  for (int i = 0; i < n; ++i) {                                                   // :133-148
-    uint8_t ch = 0;
-    OBN_CUDA(cudaMemcpy(&ch, e->best_ch + W, 1, cudaMemcpyDeviceToHost));
-    if (ch >= n) return fail(OBN_ERR_INVALID, "obn_es_finish called before every level was processed");
-    const uint32_t pa = W & ~(1u << ch);
-    uint32_t ps = 0;
-    if ((int)ch >= e->own_first && (int)ch < e->own_end) {      // child-sharded DP: the other ranks report theirs (OR them)
-      OBN_CUDA(cudaMemcpy(&ps, e->bl_ps + (size_t)W * n + ch, sizeof(uint32_t), cudaMemcpyDeviceToHost));   // row of W = pa + ch
-      parent_masks[ch] = ps;
-    }
-    W = pa;
-  }
+  ++c->prof.total_launches;
+  if (h_out[n + 1]) return fail(OBN_ERR_INVALID, "obn_es_finish called before every level was processed");
+  for (int v = 0; v < n; ++v) parent_masks[v] = h_out[v];
+  if (best_score) memcpy(best_score, &h_out[n], 8);
   return OBN_OK;
 }
 
