@@ -73,6 +73,7 @@ OBN_API void* obn_ctx_stream(obn_ctx* ctx);
  *                                        and read that one whenever every column of a table has it (half the L2 traffic)
  *   "rep" (1), "chunk" (1), "min_waves" (0)   replicated shared-memory tables on / off; tables beyond shared memory counted
  *                                        chunk-wise in shared memory instead of by L2 reductions; row-split small launches to this many waves
+ *   "largest_first" (0)                  launch order of a batch's classes (A/B)
  *   "min_class" (0), "lut_max_mb" (2048)  smallest table-size class used (fewer, larger launches per batch); cap of the
  *                                        exact-order lgamma tables kept on the device (evicted and rebuilt beyond it)
  *   "lattice_budget_gb" (24), "lattice_max_l" (20), "lattice_bottom" (1), "lattice_reorder" (1),

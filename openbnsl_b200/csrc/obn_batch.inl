@@ -408,6 +408,7 @@ static int run_batch(BatchSpec& S) {
       i = j;
     }
   }
+  if (c->tune.largest_first) std::reverse(launches.begin(), launches.end());
   // launches of one batch run concurrently on the ctx's streams, so each gets its own slice of
   // the scratch; when the slices would not fit, a barrier serialises and the slices restart at 0
   {

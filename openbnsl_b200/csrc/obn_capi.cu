@@ -158,6 +158,7 @@ int obn_ctx_set_option(obn_ctx* c, const char* name, double value) {
   else if (k == "force_threads") c->tune.force_threads = v;
   else if (k == "force_splits") c->tune.force_splits = v;
   else if (k == "streams") c->tune.streams = std::max(1, v);
+  else if (k == "largest_first") c->tune.largest_first = v;
   else if (k == "rep") c->tune.rep = v;
   else if (k == "chunk") c->tune.chunk = v;
   else if (k == "pack4") c->tune.pack4 = v;

@@ -167,7 +167,7 @@ struct obn_ctx {
   size_t smem_optin = 0;
   cudaStream_t stream = nullptr;
   // the launches of one batch (one per table-size class) overlap on these
-  static constexpr int kAuxStreams = 3;
+  static constexpr int kAuxStreams = 7;
   cudaStream_t aux[kAuxStreams] = {};
   cudaEvent_t ev_fork = nullptr, ev_join[kAuxStreams] = {};
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -213,7 +213,8 @@ struct obn_ctx {
     int threads_per_sm = 768;     // resident threads per SM a launch aims for
     int force_threads = 0;        // != 0: CTA width of every launch (sweeps)
     int force_splits = 0;         // != 0: row splits of every launch (sweeps)
-    int streams = 4;              // launches of one batch are forked over this many streams
+    int streams = 4;              // launches of one batch are forked over this many streams (<= 1 + kAuxStreams)
+    int largest_first = 0;        // launch the classes of a batch from the largest tables down (the long poles start first)
     int rep = 1;                  // replicated shared-memory tables (obn_count_kernel.cuh) on / off (A/B)
     int pack4 = 1;                // build and use nibble-packed columns (two rows per byte) for variables of <= 16 states
     int chunk = 1;                // tables beyond shared memory: chunked shared-memory counting (TIER_CHUNK) instead of L2 reductions
