@@ -294,34 +294,61 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
                              size_t max_tests = (size_t)-1) -> size_t {
         out.clear();
         pair_out.clear();
+        // raw writes into storage sized once per window (a push_back per field and test was a third of the loop)
+        const size_t w = k + 2;
+        size_t cap = 0, n_out = 0;
+        uint32_t *vp = nullptr, *xp = nullptr, *yp = nullptr, *pp = nullptr;
+        uint64_t* op = nullptr;
+        auto grow = [&](size_t need) {
+          cap = std::max<size_t>(need, cap ? 2 * cap : 4096);
+          out.var_ids.resize(cap * w);
+          out.offsets.resize(cap + 1);
+          out.x.resize(cap);
+          out.y.resize(cap);
+          pair_out.resize(cap);
+          vp = out.var_ids.data(); op = out.offsets.data(); xp = out.x.data(); yp = out.y.data(); pp = pair_out.data();
+        };
+        auto finish = [&]() {
+          out.var_ids.resize(n_out * w);
+          out.offsets.resize(n_out + 1);
+          out.x.resize(n_out);
+          out.y.resize(n_out);
+          pair_out.resize(n_out);
+        };
+        grow(4096);
+        op[0] = 0;
         for (size_t pi = pi_begin; pi < cursors.size(); ++pi) {
           FastCursor& c = cursors[pi];
           if (c.done || c.removed) continue;
-          if (out.size() >= max_tests) return pi;
+          if (n_out >= max_tests) {
+            finish();
+            return pi;
+          }
           uint32_t* idx = idx_arena.data() + pi * std::max<size_t>(k, 1);
+          if (n_out + quota > cap) grow(n_out + quota);
           for (size_t q = 0; q < quota && !c.done; ++q) {
             // tuple = sort(Z + {x,y}) (pc.cpp:34-37): Z is ascending already, merge x < y into it
             const uint32_t* a = adj[c.dir ? c.y : c.x].data();
             const uint32_t skip = c.skip[c.dir];
-            const size_t at = out.var_ids.size();
-            out.var_ids.resize(at + k + 2);
-            uint32_t* w = out.var_ids.data() + at;
+            uint32_t* wr = vp + n_out * w;
             uint32_t pend[2] = {c.x, c.y};
             int np = 0;
             for (size_t i = 0; i < k; ++i) {
               const uint32_t z = a[idx[i] + (idx[i] >= skip ? 1u : 0u)];
-              while (np < 2 && pend[np] < z) *w++ = pend[np++];
-              *w++ = z;
+              while (np < 2 && pend[np] < z) *wr++ = pend[np++];
+              *wr++ = z;
             }
-            while (np < 2) *w++ = pend[np++];
-            out.offsets.push_back(out.var_ids.size());
-            out.x.push_back(c.dir ? c.y : c.x);
-            out.y.push_back(c.dir ? c.x : c.y);
-            pair_out.push_back((uint32_t)pi);
+            while (np < 2) *wr++ = pend[np++];
+            xp[n_out] = c.dir ? c.y : c.x;
+            yp[n_out] = c.dir ? c.x : c.y;
+            pp[n_out] = (uint32_t)pi;
+            ++n_out;
+            op[n_out] = (uint64_t)n_out * w;
             next_comb(c, idx);
             settle(c, idx);
           }
         }
+        finish();
         return cursors.size();
       };
       // every edge is resolved at its FIRST passing candidate (pc.cpp:40-42)
