@@ -232,9 +232,12 @@ OBN_API int obn_pc_round_collect(obn_ctx* ctx, int32_t* first_out);
 /* Diagnostics (host only, needs no device): the table sharing obn_ci_tests / obn_pc_round use.
  * Groups in CSR form (group_var_ids needs room for offsets[n_tests] ids, group_offsets for
  * n_tests + 1), the group of every test and its digits (px | py << 8: positions of x < y in the
- * group's ascending variable list).  Any output pointer but n_groups may be NULL. */
+ * group's ascending variable list).  rank / world: the share of a sharded round that rank evaluates
+ * (0 / 1: everything) -- every variable set goes to exactly one rank, group_of_test is 0xffffffff
+ * for the tests of the other ranks.  Any output pointer but n_groups may be NULL. */
 OBN_API int obn_ci_group_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids,
                               const uint64_t* offsets, size_t n_tests, const uint32_t* x, const uint32_t* y,
+                              int rank, int world,
                               uint32_t* group_var_ids, uint64_t* group_offsets, uint32_t* group_of_test,
                               uint32_t* digits_of_test, size_t* n_groups);
 

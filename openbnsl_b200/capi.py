@@ -87,8 +87,8 @@ def load():
     L.obn_pc_round_submit.argtypes = [vp, vp, u32p, u64p, C.c_size_t, u32p, u32p, u32p, C.c_size_t, C.c_int,
                                       C.c_double, C.c_int, C.c_int]
     L.obn_pc_round_collect.argtypes = [vp, i32p]
-    L.obn_ci_group_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, u32p, u64p, u32p, u32p,
-                                    C.POINTER(C.c_size_t)]
+    L.obn_ci_group_plan.argtypes = [u32p, C.c_size_t, u32p, u64p, C.c_size_t, u32p, u32p, C.c_int, C.c_int, u32p, u64p, u32p,
+                                    u32p, C.POINTER(C.c_size_t)]
     L.obn_ctx_set_option.argtypes = [vp, C.c_char_p, C.c_double]
     L.obn_comm_unique_id.argtypes = [u8p]
     L.obn_comm_init.argtypes = [vp, u8p, C.c_int, C.c_int]
@@ -131,9 +131,10 @@ def _csr(tuples):
     return flat, offs
 
 
-def ci_group_plan(cards, tuples, x, y):
+def ci_group_plan(cards, tuples, x, y, rank=0, world=1):
     """The table sharing obn_ci_tests / obn_pc_round use (host only).  Returns (groups, group_of_test,
-    digits_of_test): groups = list of ascending variable lists, digits = (px, py) positions of x < y."""
+    digits_of_test): groups = list of ascending variable lists, digits = (px, py) positions of x < y.
+    rank / world: the share of a sharded round (group_of_test is 0xffffffff for the other ranks' tests)."""
     flat, offs = _csr(tuples)
     cards = np.ascontiguousarray(np.asarray(cards, dtype=np.uint32))
     xa = np.ascontiguousarray(np.asarray(x, dtype=np.uint32))
@@ -144,8 +145,8 @@ def ci_group_plan(cards, tuples, x, y):
     group_of, digits = np.zeros(max(1, n), dtype=np.uint32), np.zeros(max(1, n), dtype=np.uint32)
     n_groups = C.c_size_t(0)
     _check(load().obn_ci_group_plan(_ptr(cards, C.c_uint32), len(cards), _ptr(flat, C.c_uint32), _ptr(offs, C.c_uint64),
-                                    n, _ptr(xa, C.c_uint32), _ptr(ya, C.c_uint32), _ptr(gv, C.c_uint32),
-                                    _ptr(go, C.c_uint64), _ptr(group_of, C.c_uint32), _ptr(digits, C.c_uint32),
+                                    n, _ptr(xa, C.c_uint32), _ptr(ya, C.c_uint32), int(rank), int(world),
+                                    _ptr(gv, C.c_uint32), _ptr(go, C.c_uint64), _ptr(group_of, C.c_uint32), _ptr(digits, C.c_uint32),
                                     C.byref(n_groups)))
     groups = [gv[int(go[q]):int(go[q + 1])].tolist() for q in range(n_groups.value)]
     return groups, group_of[:n], [(int(d) & 0xff, (int(d) >> 8) & 0xff) for d in digits[:n]]

@@ -168,13 +168,15 @@ extern "C" {
 
 // Diagnostics, host only (include/openbnsl_b200.h): the plan obn_ci_tests / obn_pc_round use.
 int obn_ci_group_plan(const uint32_t* cards, size_t n_vars, const uint32_t* var_ids, const uint64_t* offsets,
-                      size_t n_tests, const uint32_t* x, const uint32_t* y, uint32_t* group_var_ids,
+                      size_t n_tests, const uint32_t* x, const uint32_t* y, int rank, int world, uint32_t* group_var_ids,
                       uint64_t* group_offsets, uint32_t* group_of_test, uint32_t* digits_of_test, size_t* n_groups) {
   if (!cards || !offsets || !n_groups || (n_tests && (!x || !y))) return fail(OBN_ERR_INVALID, "NULL argument");
   if (n_tests && offsets[n_tests] && !var_ids) return fail(OBN_ERR_INVALID, "var_ids is NULL");
+  if (world < 1 || rank < 0 || rank >= world) return fail(OBN_ERR_INVALID, "bad rank/world %d/%d", rank, world);
   static thread_local CiGroupPlan P;
-  if (int rc = plan_ci_groups(cards, n_vars, var_ids, offsets, n_tests, x, y, P)) return rc;
+  if (int rc = plan_ci_groups(cards, n_vars, var_ids, offsets, n_tests, x, y, P, rank, world)) return rc;
   *n_groups = P.groups();
+  if (group_of_test) std::fill(group_of_test, group_of_test + n_tests, 0xffffffffu);      // tests of other ranks' tables
   if (group_offsets) memcpy(group_offsets, P.offsets.data(), P.offsets.size() * sizeof(uint64_t));
   if (group_var_ids && !P.var_ids.empty()) memcpy(group_var_ids, P.var_ids.data(), P.var_ids.size() * sizeof(uint32_t));
   for (size_t q = 0; q < P.groups(); ++q)

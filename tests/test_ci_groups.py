@@ -118,3 +118,38 @@ def test_one_table_serves_every_role_assignment(kind):
             got_stat, got_dof = strided_citest(table, cs, px, py, kind)
             assert got_dof == want_dof
             assert got_stat == pytest.approx(want_stat, rel=1e-9, abs=1e-9)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_sharded_plan_deals_every_variable_set_to_exactly_one_rank(world):
+    """A sharded PC round (obn_pc_round, shard != 0): every rank plans the same batch and keeps the variable sets
+    whose hash falls to it.  The ranks must partition the tests, no set may be split between ranks (the table
+    sharing survives the split), and a rank's groups must be the unsharded groups of its own tests."""
+    net = nw.hepar2_like()
+    cards = [int(c) for c in net.cards]
+    rng = np.random.default_rng(world)
+    xs, ys, tuples = star_frontier(rng, net.n, 12, 2, 6)
+    n = len(tuples)
+    g_all, of_all, dig_all = capi.ci_group_plan(cards, tuples, xs, ys)
+    owner = np.full(n, -1)
+    sizes = []
+    for rank in range(world):
+        groups, group_of, digits = capi.ci_group_plan(cards, tuples, xs, ys, rank, world)
+        mine = np.flatnonzero(group_of != 0xffffffff)
+        assert (owner[mine] == -1).all()                       # nobody else took these tests
+        owner[mine] = rank
+        sizes.append(len(mine))
+        assert sorted(set(group_of[mine].tolist())) == list(range(len(groups)))
+        for t in mine.tolist():
+            assert groups[group_of[t]] == list(tuples[t])      # its group is its variable set
+            assert digits[t] == dig_all[t]                     # and the roles are those of the unsharded plan
+        # the same sets are grouped the same way as without sharding: one group per distinct set here (< 32 tests each)
+        assert len(groups) == len({tuple(tuples[t]) for t in mine.tolist()})
+    assert (owner >= 0).all()                                  # every test has an owner
+    by_set = {}
+    for t in range(n):
+        by_set.setdefault(tuple(tuples[t]), set()).add(int(owner[t]))
+    assert all(len(r) == 1 for r in by_set.values())           # a variable set lives on one rank
+    assert min(sizes) > 0.4 * n / world                        # and the deal is not lopsided
+    with pytest.raises(ValueError):
+        capi.ci_group_plan(cards, tuples, xs, ys, world, world)
