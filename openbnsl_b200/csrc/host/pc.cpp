@@ -402,6 +402,20 @@ PDAG run_pc(size_t n, size_t max_cond_vars, bool stable, size_t target_batch, co
         // enumerated and packed in its shadow.  Edges are independent within a depth, so cutting a sweep anywhere
         // changes nothing an edge resolves at.
         size_t head = 0, n_flight = 0, sweep_pos = cursors.size();
+        // an exception (a CUDA error, a Python evaluator that raises) must not leave rounds in flight in the
+        // evaluator: the next call on the same ctx would be refused
+        struct Drain {
+          const AsyncDecide* a;
+          size_t* n;
+          size_t slots;
+          ~Drain() {
+            std::vector<int32_t> sink;
+            while (*n) {
+              --*n;
+              try { a->collect(slots, sink); } catch (...) {}
+            }
+          }
+        } drain{async, &n_flight, cursors.size()};
         bool first_sweep = true, first_window = true;
         auto next_window = [&](TupleBatch& out, std::vector<uint32_t>& pairs) -> bool {
           for (int attempt = 0; attempt < 2; ++attempt) {

@@ -104,3 +104,26 @@ def test_exhaustive_search_driver_fuzz(seed):
         if rdf is not None:
             g = REF.structure_learning.exhaustive_search(rdf, REF.score.BDeu(ess), mp)
             assert (pdag_to_adj(g, n) == want).all(), (seed, mp)
+
+
+def test_pipelined_driver_survives_an_evaluator_that_raises():
+    """An exception in the middle of the pipeline (a CUDA error on the device path) must surface as an exception and
+    leave nothing in flight; the next run is unaffected."""
+    net, codes, cards = case(7)
+    ods = oracle.Dataset(codes, cards)
+
+    class Failing(CountingEvaluator):
+        calls = 0
+
+        def ci_pvalues(self, *a):
+            Failing.calls += 1
+            if Failing.calls == 3:
+                raise RuntimeError("boom")
+            return super().ci_pvalues(*a)
+
+    T = L.citest.GSquare(0.05)
+    with pytest.raises(RuntimeError, match="boom"):
+        L._testing.pc(net.n, Failing(ods), T, 3, True, None, 1, False, True)
+    want = oracle.pc(ods, 1, 0.05, 3, True)
+    got = pdag_to_adj(L._testing.pc(net.n, CountingEvaluator(ods), T, 3, True, None, 1, False, True), net.n)
+    assert (got == want).all()
