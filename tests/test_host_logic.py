@@ -28,6 +28,19 @@ def test_c_abi_exports_every_declared_symbol():
     assert b"sm_100a" in capi.load().obn_version()
 
 
+def test_header_is_plain_c(tmp_path):
+    """The drop-in boundary is a C ABI: the header must compile as C99 (no C++ types, no torch types)."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "openbnsl_b200.h"\nint main(void) { obn_profile p; (void)p; return OBN_OK; }\n')
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-I",
+                        os.path.join(ROOT, "include"), str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
 def test_two_half_ci_call_rejects_a_missing_ctx():
     # obn_ci_tests_submit / _collect validate before touching a device, like every other entry point
     lib = capi.load()
